@@ -1,0 +1,291 @@
+// extern "C" entry points of libgsr_b200.so (see include/gsr_b200.h).  Plain pointers and sizes only; no torch types,
+// no allocation, no device synchronisation, no exceptions.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace gsr {
+
+static thread_local char g_cuda_err[512] = "";
+
+void set_cuda_error(cudaError_t e, const char* where) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s (%s)", where, cudaGetErrorName(e), cudaGetErrorString(e));
+}
+
+static void fill_cam(const GsrCamera& c, CamDev& d) {
+    memset(&d, 0, sizeof(d));
+    memcpy(d.view, c.viewmatrix, sizeof(d.view));
+    memcpy(d.proj, c.projmatrix, sizeof(d.proj));
+    memcpy(d.campos, c.campos, sizeof(d.campos));
+    memcpy(d.bg, c.bg, sizeof(d.bg));
+    const int W = c.image_width, H = c.image_height;
+    // host float arithmetic exactly as rasterizer_impl.cu:227-228 and forward.cu:87-99 (IEEE single ops)
+    d.focal_y = (float)H / (2.0f * c.tanfovy);
+    d.focal_x = (float)W / (2.0f * c.tanfovx);
+    d.tanfovx = c.tanfovx;
+    d.tanfovy = c.tanfovy;
+    d.c_x = c.c_x;
+    d.c_y = c.c_y;
+    d.lim_x_pos = fmaf(c.tanfovx, 0.3f, ((float)W - c.c_x) / d.focal_x);
+    d.lim_x_neg = fmaf(c.tanfovx, 0.3f, c.c_x / d.focal_x);
+    d.lim_y_pos = fmaf(c.tanfovy, 0.3f, ((float)H - c.c_y) / d.focal_y);
+    d.lim_y_neg = fmaf(c.tanfovy, 0.3f, c.c_y / d.focal_y);
+    d.scale_modifier = c.scale_modifier;
+    d.sh_degree = c.sh_degree;
+    d.prefiltered = c.prefiltered;
+    d.width = W;
+    d.height = H;
+}
+
+__global__ void fp32_peak_kernel(float* out, int iters) {
+    // 8 independent FFMA chains per thread: enough ILP to saturate the FP32 pipes at full occupancy
+    float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f,
+          a6 = a0 + 6.f, a7 = a0 + 7.f;
+    const float m = 0.9999f, c = 1e-4f;
+    for (int i = 0; i < iters; ++i) {
+        a0 = __fmaf_rn(a0, m, c); a1 = __fmaf_rn(a1, m, c); a2 = __fmaf_rn(a2, m, c); a3 = __fmaf_rn(a3, m, c);
+        a4 = __fmaf_rn(a4, m, c); a5 = __fmaf_rn(a5, m, c); a6 = __fmaf_rn(a6, m, c); a7 = __fmaf_rn(a7, m, c);
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+}  // namespace gsr
+
+using namespace gsr;
+
+extern "C" {
+
+int gsr_abi_version(void) { return 1; }
+
+const char* gsr_strerror(int status) {
+    switch (status) {
+        case GSR_OK: return "ok";
+        case GSR_ERR_INVALID_ARGUMENT: return "invalid argument";
+        case GSR_ERR_WORKSPACE_TOO_SMALL: return "workspace too small";
+        case GSR_ERR_CUDA: return "CUDA error";
+        case GSR_ERR_UNSUPPORTED: return "unsupported configuration";
+        case GSR_ERR_CAPACITY: return "instance capacity exceeded";
+        default: return "unknown status";
+    }
+}
+
+const char* gsr_last_cuda_error(void) { return g_cuda_err; }
+
+static int check_dims(int P, int V, int W, int H, int channels, int sh_coeffs, int64_t capacity) {
+    if (P < 0 || V < 0 || W <= 0 || H <= 0 || capacity < 0 || sh_coeffs < 0 || sh_coeffs > 16)
+        return GSR_ERR_INVALID_ARGUMENT;
+    if (channels != 3 && channels != 6) return GSR_ERR_UNSUPPORTED;
+    if ((int64_t)V * P >= (1ll << 30) || capacity >= (1ll << 30)) return GSR_ERR_UNSUPPORTED;
+    const int64_t VT = (int64_t)V * ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+    if (VT >= (1ll << 31)) return GSR_ERR_UNSUPPORTED;
+    return GSR_OK;
+}
+
+int gsr_workspace_layout(int P, int V, int W, int H, int channels, int sh_coeffs, int64_t capacity, GsrLayout* out) {
+    if (!out) return GSR_ERR_INVALID_ARGUMENT;
+    int rc = check_dims(P, V, W, H, channels, sh_coeffs, capacity);
+    if (rc) return rc;
+    Layout L;
+    compute_layout(P, V, W, H, channels, sh_coeffs, capacity, L);
+    *out = static_cast<GsrLayout&>(L);
+    return GSR_OK;
+}
+
+int gsr_workspace_sizes(int P, int V, int W, int H, int channels, int sh_coeffs, int64_t capacity,
+                        GsrWorkspaceSizes* out) {
+    if (!out) return GSR_ERR_INVALID_ARGUMENT;
+    int rc = check_dims(P, V, W, H, channels, sh_coeffs, capacity);
+    if (rc) return rc;
+    Layout L;
+    compute_layout(P, V, W, H, channels, sh_coeffs, capacity, L);
+    out->geom_bytes = L.geom_bytes;
+    out->binning_bytes = L.binning_bytes;
+    out->image_bytes = L.image_bytes;
+    return GSR_OK;
+}
+
+int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels, int sh_coeffs, const float* means3D,
+                         const float* opacities, const float* scales, const float* rotations,
+                         const float* cov3D_precomp, const float* sh, void* geom_ws, size_t geom_bytes,
+                         int32_t* radii, uint32_t* num_rendered_dev, gsr_stream_t stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!cams_host || V <= 0 || !geom_ws) return GSR_ERR_INVALID_ARGUMENT;
+    if (P > 0 && (!means3D || !opacities)) return GSR_ERR_INVALID_ARGUMENT;
+    const bool has_sr = scales != nullptr && rotations != nullptr;
+    if (P > 0 && (has_sr == (cov3D_precomp != nullptr))) return GSR_ERR_INVALID_ARGUMENT;
+    if ((sh != nullptr) != (sh_coeffs > 0)) return GSR_ERR_INVALID_ARGUMENT;
+    const int W = cams_host[0].image_width, H = cams_host[0].image_height;
+    for (int v = 1; v < V; ++v) {
+        if (cams_host[v].image_width != W || cams_host[v].image_height != H) return GSR_ERR_UNSUPPORTED;
+        if (cams_host[v].scale_modifier != cams_host[0].scale_modifier) return GSR_ERR_UNSUPPORTED;
+    }
+    int rc = check_dims(P, V, W, H, channels, sh_coeffs, 0);
+    if (rc) return rc;
+    Layout L;
+    compute_layout(P, V, W, H, channels, sh_coeffs, 0, L);
+    if (geom_bytes < L.geom_bytes) return GSR_ERR_WORKSPACE_TOO_SMALL;
+
+    // cameras -> device (small; staged through the driver for pageable memory)
+    {
+        CamDev tmp[64];
+        CamDev* cd = at<CamDev>(geom_ws, L.cams);
+        for (int v0 = 0; v0 < V; v0 += 64) {
+            const int n = V - v0 < 64 ? V - v0 : 64;
+            for (int i = 0; i < n; ++i) fill_cam(cams_host[v0 + i], tmp[i]);
+            GSR_CUDA_TRY(cudaMemcpyAsync(cd + v0, tmp, sizeof(CamDev) * n, cudaMemcpyHostToDevice, s));
+            // tmp lives on this stack frame: the copy from pageable memory is staged before the call returns
+        }
+    }
+    uint32_t* counters = at<uint32_t>(geom_ws, L.counters);
+    GSR_CUDA_TRY(cudaMemsetAsync(counters, 0, NUM_COUNTERS * sizeof(uint32_t), s));
+    rc = launch_preprocess(at<CamDev>(geom_ws, L.cams), V, P, sh_coeffs, means3D, opacities, scales, rotations,
+                           cov3D_precomp, sh, geom_ws, L, radii, s);
+    if (rc) return rc;
+    const int view_bits = V > 1 ? ceil_log2((uint32_t)V) : 0;
+    rc = radix_sort_pairs<uint64_t>(at<uint64_t>(geom_ws, L.dkeys0), at<uint64_t>(geom_ws, L.dkeys1),
+                                    at<uint32_t>(geom_ws, L.dvals0), at<uint32_t>(geom_ws, L.dvals1),
+                                    (int64_t)V * P, nullptr, 0, 32 + view_bits, at<uint32_t>(geom_ws, L.dhist),
+                                    at<uint32_t>(geom_ws, L.dlookback), counters + CNT_DEPTH_TILE, s);
+    if (rc) return rc;
+    rc = launch_tile_scan(V, P, geom_ws, L, s);
+    if (rc) return rc;
+    if (num_rendered_dev)
+        GSR_CUDA_TRY(cudaMemcpyAsync(num_rendered_dev, counters + CNT_RENDERED, 4, cudaMemcpyDeviceToDevice, s));
+    return GSR_OK;
+}
+
+int gsr_forward_render(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
+                       const float* colors_precomp, const float* extra_colors, void* geom_ws, void* binning_ws,
+                       void* image_ws, float* out_color, float* out_extra, float* out_depth, float* out_alpha,
+                       gsr_stream_t stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = check_dims(P, V, W, H, channels, sh_coeffs, capacity);
+    if (rc) return rc;
+    if (!geom_ws || !image_ws || !out_color || !out_depth || !out_alpha) return GSR_ERR_INVALID_ARGUMENT;
+    if (capacity > 0 && !binning_ws) return GSR_ERR_INVALID_ARGUMENT;
+    if (channels == 6 && (!extra_colors || !out_extra)) return GSR_ERR_INVALID_ARGUMENT;
+    if ((sh_coeffs > 0) == (colors_precomp != nullptr) && P > 0) return GSR_ERR_INVALID_ARGUMENT;
+    Layout L;
+    compute_layout(P, V, W, H, channels, sh_coeffs, capacity, L);
+    rc = launch_binning(V, P, W, H, channels, sh_coeffs, capacity, colors_precomp, extra_colors, geom_ws, binning_ws,
+                        image_ws, L, s);
+    if (rc) return rc;
+    return launch_blend_forward(V, W, H, channels, geom_ws, binning_ws, image_ws, L, out_color, out_extra, out_depth,
+                                out_alpha, s);
+}
+
+int gsr_read_counters(const void* geom_ws, uint32_t* counters_host, gsr_stream_t stream) {
+    if (!geom_ws || !counters_host) return GSR_ERR_INVALID_ARGUMENT;
+    // the counter block sits at offset 0 of the geometry workspace for every problem size (compute_layout)
+    GSR_CUDA_TRY(cudaMemcpyAsync(counters_host, geom_ws, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                                 (cudaStream_t)stream));
+    return GSR_OK;
+}
+
+int gsr_backward(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity, const float* means3D,
+                 const float* opacities, const float* scales, const float* rotations, const float* cov3D_precomp,
+                 const float* sh, const float* colors_precomp, const float* extra_colors, const int32_t* radii,
+                 void* geom_ws, void* binning_ws, void* image_ws, const float* dL_dcolor, const float* dL_dextra,
+                 const float* dL_ddepth, const float* dL_dalpha, const float* label, float* dL_dmeans3D,
+                 float* dL_dmeans2D, float* dL_dcolors, float* dL_dextra_colors, float* dL_dopacity,
+                 float* dL_dscales, float* dL_drotations, float* dL_dcov3D, float* dL_dsh, gsr_stream_t stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = check_dims(P, V, W, H, channels, sh_coeffs, capacity);
+    if (rc) return rc;
+    if (!geom_ws || !image_ws) return GSR_ERR_INVALID_ARGUMENT;
+    if (capacity > 0 && !binning_ws) return GSR_ERR_INVALID_ARGUMENT;
+    if (P > 0 && !means3D) return GSR_ERR_INVALID_ARGUMENT;
+    (void)opacities; (void)colors_precomp; (void)extra_colors;
+    Layout L;
+    compute_layout(P, V, W, H, channels, sh_coeffs, capacity, L);
+    rc = launch_blend_backward(V, P, W, H, channels, geom_ws, binning_ws, image_ws, L, dL_dcolor, dL_dextra, dL_ddepth,
+                               dL_dalpha, s);
+    if (rc) return rc;
+    return launch_preprocess_backward(V, P, W, H, channels, sh_coeffs, means3D, opacities, scales, rotations,
+                                      cov3D_precomp, sh, radii, geom_ws, L, label, dL_dmeans3D, dL_dmeans2D,
+                                      dL_dcolors, dL_dextra_colors, dL_dopacity, dL_dscales, dL_drotations, dL_dcov3D,
+                                      dL_dsh, s);
+}
+
+int gsr_mark_visible(const GsrCamera* cam_host, int P, const float* means3D, uint8_t* present, gsr_stream_t stream) {
+    if (!cam_host || P < 0 || (P > 0 && (!means3D || !present))) return GSR_ERR_INVALID_ARGUMENT;
+    return launch_mark_visible(cam_host->viewmatrix, P, means3D, present, (cudaStream_t)stream);
+}
+
+int gsr_export_view_binning(int view, int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
+                            const void* geom_ws, const void* binning_ws, const void* image_ws, uint64_t* keys_out,
+                            uint32_t* list_out, uint32_t* ranges_out, uint32_t* n_contrib_out, gsr_stream_t stream) {
+    int rc = check_dims(P, V, W, H, channels, sh_coeffs, capacity);
+    if (rc) return rc;
+    if (view < 0 || view >= V || !geom_ws || !binning_ws || !image_ws) return GSR_ERR_INVALID_ARGUMENT;
+    Layout L;
+    compute_layout(P, V, W, H, channels, sh_coeffs, capacity, L);
+    return launch_export_view(view, V, P, W, H, geom_ws, binning_ws, image_ws, L, keys_out, list_out, ranges_out,
+                              n_contrib_out, (cudaStream_t)stream);
+}
+
+// ---- stand-alone sort (tests) ----
+static size_t sort_layout(int64_t n, int key_bytes, size_t off[7]) {
+    size_t o = 0;
+    auto take = [&](size_t b) { size_t r = o; o = align_up(o + b); return r; };
+    const size_t nn = (size_t)(n > 0 ? n : 0);
+    off[0] = take(nn * key_bytes);                 // keys A
+    off[1] = take(nn * key_bytes);                 // keys B
+    off[2] = take(nn * 4);                         // vals A
+    off[3] = take(nn * 4);                         // vals B
+    off[4] = take((size_t)MAX_PASSES * RADIX * 4); // hist
+    off[5] = take((size_t)MAX_PASSES * (sort_num_tiles(n, key_bytes) + 1) * RADIX * 4);  // lookback
+    off[6] = take(MAX_PASSES * 4);                 // tile counters
+    return o;
+}
+
+size_t gsr_sort_temp_bytes(int64_t n, int key_bytes) {
+    size_t off[7];
+    return sort_layout(n, key_bytes, off);
+}
+
+int gsr_sort_pairs(int key_bytes, const void* keys_in, void* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                   int64_t n, int begin_bit, int end_bit, void* tmp, size_t tmp_bytes, gsr_stream_t stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    if (key_bytes != 4 && key_bytes != 8) return GSR_ERR_INVALID_ARGUMENT;
+    if (n < 0 || begin_bit < 0 || end_bit > key_bytes * 8 || end_bit < begin_bit) return GSR_ERR_INVALID_ARGUMENT;
+    if (n == 0) return GSR_OK;
+    if (!keys_in || !keys_out || !vals_in || !vals_out || !tmp) return GSR_ERR_INVALID_ARGUMENT;
+    size_t off[7];
+    if (tmp_bytes < sort_layout(n, key_bytes, off)) return GSR_ERR_WORKSPACE_TOO_SMALL;
+    char* t = (char*)tmp;
+    GSR_CUDA_TRY(cudaMemcpyAsync(t + off[0], keys_in, (size_t)n * key_bytes, cudaMemcpyDeviceToDevice, s));
+    GSR_CUDA_TRY(cudaMemcpyAsync(t + off[2], vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+    const int passes = (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS;
+    int rc;
+    if (key_bytes == 4)
+        rc = radix_sort_pairs<uint32_t>((uint32_t*)(t + off[0]), (uint32_t*)(t + off[1]), (uint32_t*)(t + off[2]),
+                                        (uint32_t*)(t + off[3]), n, nullptr, begin_bit, end_bit,
+                                        (uint32_t*)(t + off[4]), (uint32_t*)(t + off[5]), (uint32_t*)(t + off[6]), s);
+    else
+        rc = radix_sort_pairs<uint64_t>((uint64_t*)(t + off[0]), (uint64_t*)(t + off[1]), (uint32_t*)(t + off[2]),
+                                        (uint32_t*)(t + off[3]), n, nullptr, begin_bit, end_bit,
+                                        (uint32_t*)(t + off[4]), (uint32_t*)(t + off[5]), (uint32_t*)(t + off[6]), s);
+    if (rc) return rc;
+    const int res = passes & 1;
+    GSR_CUDA_TRY(cudaMemcpyAsync(keys_out, t + off[res ? 1 : 0], (size_t)n * key_bytes, cudaMemcpyDeviceToDevice, s));
+    GSR_CUDA_TRY(cudaMemcpyAsync(vals_out, t + off[res ? 3 : 2], (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+    return GSR_OK;
+}
+
+int gsr_probe_geometry(int* blocks, int* threads) {
+    if (blocks) *blocks = 148 * 8;
+    if (threads) *threads = 256;
+    return GSR_OK;
+}
+
+int gsr_fp32_peak_probe(float* out, int iters, gsr_stream_t stream) {
+    if (!out || iters <= 0) return GSR_ERR_INVALID_ARGUMENT;
+    fp32_peak_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(out, iters);
+    GSR_LAUNCH_CHECK();
+    return GSR_OK;
+}
+
+}  // extern "C"

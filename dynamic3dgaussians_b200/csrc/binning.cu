@@ -1,0 +1,300 @@
+// (b) binning: instance counting, instance emission in depth order, stable tile sort, tile ranges, record gather.
+// Replaces cub::DeviceScan::InclusiveSum + duplicateWithKeys + SortPairs + identifyTileRanges
+// (R/cuda_rasterizer/rasterizer_impl.cu:70-138,283-323).
+//
+// The reference sorts R instances on a 64-bit (tile | depth) key.  Here Gaussians are already in per-view depth order
+// (sort of P entries per view), so instances are emitted in that order with a 32-bit (view*T + tile) key and a stable
+// sort on the tile bits alone produces exactly the reference's order: (tile, depth bits, Gaussian index).
+#include "geom_math.cuh"
+
+namespace gsr {
+
+namespace {
+
+constexpr unsigned FULL = 0xffffffffu;
+
+__device__ __forceinline__ uint32_t block_exclusive_scan_256(uint32_t v, uint32_t* s_warp /*[8]*/, uint32_t& total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(FULL, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < SCAN_BLOCK / 32; ++w) {
+        const uint32_t c = s_warp[w];
+        if (w < warp) base += c;
+        tot += c;
+    }
+    total = tot;
+    __syncthreads();
+    return base + inc - v;
+}
+
+// slot i of the depth-sorted list: view = i / P, Gaussian = sorted_g[i]
+__device__ __forceinline__ uint32_t slot_tiles(uint32_t i, uint32_t VP, int P, const uint32_t* __restrict__ sorted_g,
+                                               const uint32_t* __restrict__ tiles_touched, uint32_t& gidx) {
+    if (i >= VP) { gidx = 0; return 0; }
+    const uint32_t view = i / (uint32_t)P;
+    gidx = view * (uint32_t)P + sorted_g[i];
+    return tiles_touched[gidx];
+}
+
+__global__ void __launch_bounds__(SCAN_BLOCK)
+tile_count_reduce_kernel(uint32_t VP, int P, const uint32_t* __restrict__ sorted_g,
+                         const uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ block_sums) {
+    __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
+    const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    uint32_t sum = 0, gidx;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) sum += slot_tiles(base + k, VP, P, sorted_g, tiles_touched, gidx);
+    uint32_t total;
+    block_exclusive_scan_256(sum, s_warp, total);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+
+// single block: exclusive scan of the per-block sums in place; total -> counters[CNT_RENDERED]
+__global__ void __launch_bounds__(SCAN_BLOCK)
+block_sums_scan_kernel(uint32_t nblocks, uint32_t* __restrict__ block_sums, uint32_t* __restrict__ counters) {
+    __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
+    uint32_t carry = 0;
+    for (uint32_t start = 0; start < nblocks; start += SCAN_BLOCK) {
+        const uint32_t i = start + threadIdx.x;
+        const uint32_t v = i < nblocks ? block_sums[i] : 0u;
+        uint32_t total;
+        const uint32_t ex = block_exclusive_scan_256(v, s_warp, total);
+        if (i < nblocks) block_sums[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) {
+        counters[CNT_RENDERED] = carry;
+        counters[CNT_OVERFLOW] = 0;
+    }
+}
+
+// Emits the (view*T + tile, Gaussian) pairs of every visible (view, Gaussian) in depth order.
+// Row-major tile order inside a Gaussian (y outer, x inner) as duplicateWithKeys, rasterizer_impl.cu:98-109.
+__global__ void __launch_bounds__(SCAN_BLOCK)
+emit_instances_kernel(uint32_t VP, int P, int tiles_x, int tiles_y, const uint32_t* __restrict__ sorted_g,
+                      const uint32_t* __restrict__ tiles_touched, const uint32_t* __restrict__ block_sums,
+                      const float2* __restrict__ means2D, const int32_t* __restrict__ radii, uint32_t capacity,
+                      uint32_t* __restrict__ ikeys, uint32_t* __restrict__ ivals, uint32_t* __restrict__ counters) {
+    __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
+    const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    uint32_t cnt[SCAN_ITEMS], gidx[SCAN_ITEMS];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        cnt[k] = slot_tiles(base + k, VP, P, sorted_g, tiles_touched, gidx[k]);
+        sum += cnt[k];
+    }
+    uint32_t total;
+    uint32_t off = block_sums[blockIdx.x] + block_exclusive_scan_256(sum, s_warp, total);
+    const uint32_t T = (uint32_t)tiles_x * (uint32_t)tiles_y;
+    bool overflow = false;
+#pragma unroll 1
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        if (cnt[k] == 0) continue;
+        const uint32_t gi = gidx[k];
+        const uint32_t view = gi / (uint32_t)P;
+        const uint32_t g = gi - view * (uint32_t)P;
+        uint2 mn, mx;
+        tile_rect(means2D[gi], radii[gi], tiles_x, tiles_y, mn, mx);
+        const uint32_t key_base = view * T;
+        for (uint32_t ty = mn.y; ty < mx.y; ++ty) {
+            for (uint32_t tx = mn.x; tx < mx.x; ++tx) {
+                if (off < capacity) {
+                    ikeys[off] = key_base + ty * (uint32_t)tiles_x + tx;
+                    ivals[off] = g;
+                } else {
+                    overflow = true;
+                }
+                ++off;
+            }
+        }
+    }
+    if (overflow) counters[CNT_OVERFLOW] = 1;
+}
+
+// identifyTileRanges, rasterizer_impl.cu:116-138, on the 32-bit (view*T + tile) keys
+__global__ void __launch_bounds__(256)
+tile_ranges_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, const uint32_t* __restrict__ keys,
+                   uint2* __restrict__ ranges) {
+    const uint32_t n = min(counters[CNT_RENDERED], capacity);
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t cur = keys[i];
+    if (i == 0) {
+        ranges[cur].x = 0;
+    } else {
+        const uint32_t prev = keys[i - 1];
+        if (cur != prev) {
+            ranges[prev].y = i;
+            ranges[cur].x = i;
+        }
+    }
+    if (i == n - 1) ranges[cur].y = n;
+}
+
+// Gathers the per-instance records the blend kernels stream with TMA bulk copies:
+//   A = (mean.x, mean.y, conic.x, conic.y)   B = (conic.z, opacity, depth, bits(view*P + g))
+//   C = (r, g, b, 0)                         D = (extra colour r, g, b, 0)   [channels == 6]
+__global__ void __launch_bounds__(256)
+gather_records_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, int P, uint32_t T, int channels,
+                      const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
+                      const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
+                      const float* __restrict__ depths, const float* __restrict__ colors_precomp,
+                      const float* __restrict__ rgb_sh, const float* __restrict__ extra_colors,
+                      float4* __restrict__ recA, float4* __restrict__ recB, float4* __restrict__ recC,
+                      float4* __restrict__ recD) {
+    const uint32_t n = min(counters[CNT_RENDERED], capacity);
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t view = keys[i] / T;
+    const uint32_t g = vals[i];
+    const uint32_t gi = view * (uint32_t)P + g;
+    const float2 m = means2D[gi];
+    const float4 co = conic_opacity[gi];
+    recA[i] = make_float4(m.x, m.y, co.x, co.y);
+    recB[i] = make_float4(co.z, co.w, depths[gi], __uint_as_float(gi));
+    const float* c = colors_precomp ? colors_precomp + 3 * (size_t)g : rgb_sh + 3 * (size_t)gi;
+    recC[i] = make_float4(c[0], c[1], c[2], 0.0f);
+    if (channels > 3) {
+        const float* e = extra_colors + 3 * (size_t)g;
+        recD[i] = make_float4(e[0], e[1], e[2], 0.0f);
+    }
+}
+
+// ---- export of one view in the reference's format (tests / tools) ----
+__global__ void find_view_start_kernel(const uint32_t* __restrict__ counters, uint32_t capacity,
+                                       const uint32_t* __restrict__ keys, uint32_t first_key,
+                                       uint32_t* __restrict__ out) {
+    const uint32_t n = min(counters[CNT_RENDERED], capacity);
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) {
+        const uint32_t mid = lo + (hi - lo) / 2;
+        if (keys[mid] < first_key) lo = mid + 1; else hi = mid;
+    }
+    out[0] = lo;
+}
+
+__global__ void export_view_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, int view, int P,
+                                   uint32_t T, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
+                                   const float* __restrict__ depths, const uint32_t* __restrict__ view_start,
+                                   uint64_t* __restrict__ keys_out, uint32_t* __restrict__ list_out) {
+    const uint32_t n = min(counters[CNT_RENDERED], capacity);
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x + view_start[0];
+    if (i >= n) return;
+    const uint32_t k = keys[i];
+    if (k / T != (uint32_t)view) return;
+    const uint32_t local = i - view_start[0];
+    const uint32_t g = vals[i];
+    if (keys_out)
+        keys_out[local] = ((uint64_t)(k - (uint32_t)view * T) << 32) |
+                          (uint64_t)__float_as_uint(depths[(size_t)view * P + g]);
+    if (list_out) list_out[local] = g;
+}
+
+__global__ void export_ranges_kernel(int view, uint32_t T, const uint2* __restrict__ ranges,
+                                     const uint32_t* __restrict__ view_start, uint32_t* __restrict__ ranges_out) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= T) return;
+    const uint2 r = ranges[(size_t)view * T + t];
+    const bool empty = r.y == r.x;
+    ranges_out[2 * t] = empty ? 0u : r.x - view_start[0];
+    ranges_out[2 * t + 1] = empty ? 0u : r.y - view_start[0];
+}
+
+}  // namespace
+
+int launch_tile_scan(int V, int P, void* ws, const Layout& L, cudaStream_t s) {
+    const uint32_t VP = (uint32_t)((size_t)V * P);
+    if (VP == 0) return GSR_OK;
+    const uint32_t nblocks = (VP + SCAN_TILE - 1) / SCAN_TILE;
+    const uint32_t* sorted_g = at<uint32_t>(ws, L.sorted_vals_in ? L.dvals1 : L.dvals0);
+    tile_count_reduce_kernel<<<nblocks, SCAN_BLOCK, 0, s>>>(VP, P, sorted_g, at<uint32_t>(ws, L.tiles_touched),
+                                                           at<uint32_t>(ws, L.block_sums));
+    GSR_LAUNCH_CHECK();
+    block_sums_scan_kernel<<<1, SCAN_BLOCK, 0, s>>>(nblocks, at<uint32_t>(ws, L.block_sums),
+                                                    at<uint32_t>(ws, L.counters));
+    GSR_LAUNCH_CHECK();
+    return GSR_OK;
+}
+
+int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
+                   const float* colors_precomp, const float* extra_colors, void* gws, void* bws, void* iws,
+                   const Layout& L, cudaStream_t s) {
+    const uint32_t VP = (uint32_t)((size_t)V * P);
+    const uint32_t T = (uint32_t)L.tiles_x * (uint32_t)L.tiles_y;
+    const size_t VT = (size_t)V * T;
+    GSR_CUDA_TRY(cudaMemsetAsync(at<uint2>(iws, L.ranges), 0, VT * sizeof(uint2), s));
+    if (VP == 0 || capacity <= 0) return GSR_OK;
+    const uint32_t cap = (uint32_t)capacity;
+    uint32_t* counters = at<uint32_t>(gws, L.counters);
+    const uint32_t nblocks = (VP + SCAN_TILE - 1) / SCAN_TILE;
+    const uint32_t* sorted_g = at<uint32_t>(gws, L.sorted_vals_in ? L.dvals1 : L.dvals0);
+    emit_instances_kernel<<<nblocks, SCAN_BLOCK, 0, s>>>(
+        VP, P, L.tiles_x, L.tiles_y, sorted_g, at<uint32_t>(gws, L.tiles_touched), at<uint32_t>(gws, L.block_sums),
+        at<float2>(gws, L.means2D), at<int32_t>(gws, L.radii), cap, at<uint32_t>(bws, L.ikeys0),
+        at<uint32_t>(bws, L.ivals0), counters);
+    GSR_LAUNCH_CHECK();
+    int rc = radix_sort_pairs<uint32_t>(at<uint32_t>(bws, L.ikeys0), at<uint32_t>(bws, L.ikeys1),
+                                        at<uint32_t>(bws, L.ivals0), at<uint32_t>(bws, L.ivals1), capacity,
+                                        counters + CNT_RENDERED, 0, L.tile_bits, at<uint32_t>(bws, L.ihist),
+                                        at<uint32_t>(bws, L.ilookback), counters + CNT_INST_TILE, s);
+    if (rc != GSR_OK) return rc;
+    const uint32_t* skeys = at<uint32_t>(bws, L.sorted_keys_in ? L.ikeys1 : L.ikeys0);
+    const uint32_t* svals = at<uint32_t>(bws, L.sorted_keys_in ? L.ivals1 : L.ivals0);
+    const uint32_t gblocks = (cap + 255) / 256;
+    tile_ranges_kernel<<<gblocks, 256, 0, s>>>(counters, cap, skeys, at<uint2>(iws, L.ranges));
+    GSR_LAUNCH_CHECK();
+    gather_records_kernel<<<gblocks, 256, 0, s>>>(
+        counters, cap, P, T, channels, skeys, svals, at<float2>(gws, L.means2D), at<float4>(gws, L.conic_opacity),
+        at<float>(gws, L.depths), colors_precomp, sh_coeffs > 0 ? at<float>(gws, L.rgb) : nullptr, extra_colors,
+        at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC),
+        channels > 3 ? at<float4>(bws, L.recD) : nullptr);
+    GSR_LAUNCH_CHECK();
+    return GSR_OK;
+}
+
+int launch_export_view(int view, int V, int P, int W, int H, const void* gws, const void* bws, const void* iws,
+                       const Layout& L, uint64_t* keys_out, uint32_t* list_out, uint32_t* ranges_out,
+                       uint32_t* n_contrib_out, cudaStream_t s) {
+    const uint32_t T = (uint32_t)L.tiles_x * (uint32_t)L.tiles_y;
+    // scratch slot for the view's first sorted position: counters[2]
+    uint32_t* counters = const_cast<uint32_t*>(at<uint32_t>(gws, L.counters));
+    const uint32_t* skeys = at<uint32_t>(bws, L.sorted_keys_in ? L.ikeys1 : L.ikeys0);
+    const uint32_t* svals = at<uint32_t>(bws, L.sorted_keys_in ? L.ivals1 : L.ivals0);
+    // capacity is not needed beyond clamping; counters[CNT_RENDERED] <= capacity is enforced by the caller's check
+    const uint32_t cap = 0xffffffffu;
+    find_view_start_kernel<<<1, 1, 0, s>>>(counters, cap, skeys, (uint32_t)view * T, counters + 2);
+    GSR_LAUNCH_CHECK();
+    if (keys_out || list_out) {
+        // upper bound on this view's instances: everything after its start; threads past the view return early
+        uint32_t host_n = 0;
+        GSR_CUDA_TRY(cudaMemcpyAsync(&host_n, counters + CNT_RENDERED, 4, cudaMemcpyDeviceToHost, s));
+        GSR_CUDA_TRY(cudaStreamSynchronize(s));
+        if (host_n > 0) {
+            export_view_kernel<<<(host_n + 255) / 256, 256, 0, s>>>(counters, cap, view, P, T, skeys, svals,
+                                                                    at<float>(gws, L.depths), counters + 2, keys_out,
+                                                                    list_out);
+            GSR_LAUNCH_CHECK();
+        }
+    }
+    if (ranges_out) {
+        export_ranges_kernel<<<(T + 255) / 256, 256, 0, s>>>(view, T, at<uint2>(iws, L.ranges), counters + 2,
+                                                             ranges_out);
+        GSR_LAUNCH_CHECK();
+    }
+    if (n_contrib_out) {
+        GSR_CUDA_TRY(cudaMemcpyAsync(n_contrib_out, at<uint32_t>(iws, L.n_contrib) + (size_t)view * W * H,
+                                     (size_t)W * H * 4, cudaMemcpyDeviceToDevice, s));
+    }
+    return GSR_OK;
+}
+
+}  // namespace gsr

@@ -1,0 +1,288 @@
+// (d) tile blend backward, all views of the batch in one launch.
+// Replaces BACKWARD::render / renderCUDA (R/cuda_rasterizer/backward.cu:432-652).
+//
+// Differences in structure from the reference (the gradients computed are the same quantities):
+//  * per-instance records arrive through the same double-buffered TMA bulk copies as the forward, walked back to front;
+//    the walk starts at the tile's largest n_contrib instead of at the end of the list;
+//  * the colour / depth / alpha "colour behind me" recurrences (backward.cu:578,591,600,617) and the background term
+//    (backward.cu:626-629) collapse into ONE scalar recurrence, because the pixel cotangent is fixed per thread:
+//        s_j   = <c_j, dL/dC> + depth_j * dL/dD + dL/dA          (extended colour dotted with the pixel cotangent)
+//        acc_j = alpha_{j+1} * s_{j+1} + (1 - alpha_{j+1}) * acc_{j+1},   acc_last = <bg, dL/dC>
+//        dL/dalpha_j = T_j * (s_j - acc_j)
+//    which removes ~3 registers and ~3 flops per blended channel per pair (the reference kernel needs 198 registers);
+//  * the 7+C per-Gaussian partial sums of a warp are reduced with a packed butterfly (12 shuffles for 10 values instead
+//    of 50), the 8 warps of the CTA are combined through shared memory, and ONE set of global atomics per
+//    (tile, Gaussian) is issued: the reference issues one set per (pixel, Gaussian) pair (backward.cu:586-649).
+#include "geom_math.cuh"
+
+namespace gsr {
+
+namespace {
+
+constexpr int BATCH = 128;
+constexpr int SUB = 32;
+constexpr unsigned FULL = 0xffffffffu;
+
+// Packed butterfly: after run(), v[0] of lane l holds the warp-wide sum of the original v[slot(l)].
+template <int K>
+struct PackedReduce {
+    template <int KC, int OFF>
+    __device__ __forceinline__ static void step(float (&v)[K], int lane) {
+        if constexpr (OFF >= 1) {
+            constexpr int H = (KC + 1) / 2;
+            constexpr int PAIRS = KC / 2;
+            const bool up = (lane & OFF) != 0;
+#pragma unroll
+            for (int i = 0; i < PAIRS; ++i) {
+                const float send = up ? v[i] : v[i + H];
+                const float keep = up ? v[i + H] : v[i];
+                v[i] = keep + __shfl_xor_sync(FULL, send, OFF);
+            }
+            if constexpr ((KC & 1) != 0) v[H - 1] += __shfl_xor_sync(FULL, v[H - 1], OFF);
+            step<H, OFF / 2>(v, lane);
+        }
+    }
+    __device__ __forceinline__ static void run(float (&v)[K], int lane) { step<K, 16>(v, lane); }
+
+    template <int KC, int OFF>
+    __device__ __forceinline__ static void slot_step(int (&idx)[K], int lane) {
+        if constexpr (OFF >= 1) {
+            constexpr int H = (KC + 1) / 2;
+            constexpr int PAIRS = KC / 2;
+            const bool up = (lane & OFF) != 0;
+#pragma unroll
+            for (int i = 0; i < PAIRS; ++i) idx[i] = up ? idx[i + H] : idx[i];
+            slot_step<H, OFF / 2>(idx, lane);
+        }
+    }
+    __device__ __forceinline__ static int slot(int lane) {
+        int idx[K];
+#pragma unroll
+        for (int i = 0; i < K; ++i) idx[i] = i;
+        slot_step<K, 16>(idx, lane);
+        return idx[0];
+    }
+};
+
+template <int NCH>
+__global__ void __launch_bounds__(TILE_PIX)
+blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ recA,
+                      const float4* __restrict__ recB, const float4* __restrict__ recC,
+                      const float4* __restrict__ recD, const CamDev* __restrict__ cams, int W, int H, int tiles_x,
+                      int tiles_per_view, const uint32_t* __restrict__ n_contrib, const float* __restrict__ final_T,
+                      const float* __restrict__ dL_dcolor, const float* __restrict__ dL_dextra,
+                      const float* __restrict__ dL_ddepth, const float* __restrict__ dL_dalpha,
+                      float* __restrict__ grad_rec) {
+    constexpr bool EXTRA = NCH > 3;
+    constexpr int K = GR_COL + NCH;
+    static_assert(K <= GRAD_REC, "gradient record too small");
+    __shared__ __align__(128) float4 sA[2][BATCH];
+    __shared__ __align__(128) float4 sB[2][BATCH];
+    __shared__ __align__(128) float4 sC[2][BATCH];
+    __shared__ __align__(128) float4 sD[EXTRA ? 2 : 1][EXTRA ? BATCH : 1];
+    __shared__ __align__(8) uint64_t full[2];
+    __shared__ float s_part[TILE_PIX / 32][SUB][GRAD_REC];
+    __shared__ uint32_t s_mask[TILE_PIX / 32];
+    __shared__ uint32_t s_max;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int vt = blockIdx.x;
+    const int view = vt / tiles_per_view;
+    const int tile = vt - view * tiles_per_view;
+    const int tile_yi = tile / tiles_x, tile_xi = tile - tile_yi * tiles_x;
+    const int px = tile_xi * TILE_X + (warp & 1) * 8 + (lane & 7);
+    const int py = tile_yi * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+    const bool inside = px < W && py < H;
+    const float pxf = (float)px, pyf = (float)py;
+    const size_t HW = (size_t)H * W;
+    const size_t pix = (size_t)py * W + px;
+
+    const uint2 range = ranges[vt];
+    const uint32_t last_contributor = inside ? n_contrib[(size_t)view * HW + pix] : 0u;
+    float T = inside ? final_T[(size_t)view * HW + pix] : 0.0f;
+
+    if (tid == 0) {
+        s_max = 0;
+        mbar_init(&full[0], 1);
+        mbar_init(&full[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    {
+        const uint32_t wmax = __reduce_max_sync(FULL, last_contributor);
+        if (lane == 0 && wmax > 0) atomicMax(&s_max, wmax);
+    }
+    __syncthreads();
+    const int n_proc = (int)min(s_max, range.y - range.x);   // positions [0, n_proc) can contribute to some pixel
+    const int rounds = (n_proc + BATCH - 1) / BATCH;
+    if (rounds == 0) return;
+
+    auto issue = [&](int r) {   // thread 0 only; round r walks chunk (rounds-1-r)
+        const int buf = r & 1;
+        const int c = rounds - 1 - r;
+        const int nb = min(BATCH, n_proc - c * BATCH);
+        const uint32_t bytes = (uint32_t)nb * 16u;
+        const size_t src = (size_t)range.x + (size_t)c * BATCH;
+        mbar_expect_tx(&full[buf], bytes * (EXTRA ? 4u : 3u));
+        tma_load_1d(sA[buf], recA + src, bytes, &full[buf]);
+        tma_load_1d(sB[buf], recB + src, bytes, &full[buf]);
+        tma_load_1d(sC[buf], recC + src, bytes, &full[buf]);
+        if (EXTRA) tma_load_1d(sD[buf], recD + src, bytes, &full[buf]);
+    };
+    if (tid == 0) {
+        issue(0);
+        if (rounds > 1) issue(1);
+    }
+
+    // pixel cotangents
+    float gC[NCH];
+    float gD = 0.0f, gA = 0.0f;
+#pragma unroll
+    for (int k = 0; k < NCH; ++k) gC[k] = 0.0f;
+    const CamDev& cam = cams[view];
+    float acc = 0.0f;   // "extended colour behind me" dotted with the cotangent; starts as the background term
+    if (inside) {
+        if (dL_dcolor) {
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) {
+                gC[ch] = dL_dcolor[((size_t)view * 3 + ch) * HW + pix];
+                acc += cam.bg[ch] * gC[ch];
+            }
+        }
+        if (EXTRA && dL_dextra) {
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) {
+                gC[NCH - 3 + ch] = dL_dextra[((size_t)view * 3 + ch) * HW + pix];
+                acc += cam.bg[3 + ch] * gC[NCH - 3 + ch];
+            }
+        }
+        if (dL_ddepth) gD = dL_ddepth[(size_t)view * HW + pix];
+        if (dL_dalpha) gA = dL_dalpha[(size_t)view * HW + pix];
+    }
+    float last_alpha = 0.0f, last_s = 0.0f;
+    const float ddelx_dx = 0.5f * (float)W, ddely_dy = 0.5f * (float)H;   // backward.cu:520-521
+
+    const int my_slot = PackedReduce<K>::slot(lane);
+    const unsigned slot_peers = __match_any_sync(FULL, my_slot);
+    const bool writer = lane == (__ffs(slot_peers) - 1);
+
+    for (int r = 0; r < rounds; ++r) {
+        const int buf = r & 1;
+        const int c = rounds - 1 - r;
+        const int nb = min(BATCH, n_proc - c * BATCH);
+        mbar_wait(&full[buf], (uint32_t)((r >> 1) & 1));
+        for (int sub = (nb - 1) / SUB; sub >= 0; --sub) {
+            const int lo = sub * SUB;
+            const int hi = min(lo + SUB, nb);
+            uint32_t hit_mask = 0;
+            for (int j = hi - 1; j >= lo; --j) {
+                const float4 a = sA[buf][j];
+                const float4 b = sB[buf][j];
+                const uint32_t pos = (uint32_t)(c * BATCH + j);
+                const float dx = __fsub_rn(a.x, pxf), dy = __fsub_rn(a.y, pyf);
+                const float power = blend_power(dx, dy, a.z, a.w, b.x);
+                const float G = expf(fminf(power, 0.0f));
+                const float alpha = fminf(0.99f, __fmul_rn(b.y, G));
+                const bool valid = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                if (__ballot_sync(FULL, valid) == 0u) continue;      // warp-uniform
+
+                float v[K];
+#pragma unroll
+                for (int k = 0; k < K; ++k) v[k] = 0.0f;
+                if (valid) {
+                    T = __fdividef(T, 1.0f - alpha);                 // transmittance in front of this Gaussian
+                    const float w = alpha * T;
+                    const float4 col = sC[buf][j];
+                    float s = col.x * gC[0] + col.y * gC[1] + col.z * gC[2] + b.z * gD + gA;
+                    v[GR_COL + 0] = w * gC[0];
+                    v[GR_COL + 1] = w * gC[1];
+                    v[GR_COL + 2] = w * gC[2];
+                    if (EXTRA) {
+                        const float4 e = sD[buf][j];
+                        s += e.x * gC[NCH - 3] + e.y * gC[NCH - 2] + e.z * gC[NCH - 1];
+                        v[GR_COL + NCH - 3] = w * gC[NCH - 3];
+                        v[GR_COL + NCH - 2] = w * gC[NCH - 2];
+                        v[GR_COL + NCH - 1] = w * gC[NCH - 1];
+                    }
+                    acc = last_alpha * last_s + (1.0f - last_alpha) * acc;
+                    last_s = s;
+                    last_alpha = alpha;
+                    const float dL_dalpha_j = (s - acc) * T;
+                    const float dL_dG = b.y * dL_dalpha_j;            // straight through the 0.99 clamp
+                    const float gdx = G * dx, gdy = G * dy;
+                    const float dG_ddelx = -gdx * a.z - gdy * a.w;
+                    const float dG_ddely = -gdy * b.x - gdx * a.w;
+                    v[GR_MX] = dL_dG * dG_ddelx * ddelx_dx;
+                    v[GR_MY] = dL_dG * dG_ddely * ddely_dy;
+                    v[GR_CA] = -0.5f * gdx * dx * dL_dG;
+                    v[GR_CB] = -gdx * dy * dL_dG;                     // true d/d(conic.y): no 0.5 (see preprocess_backward)
+                    v[GR_CC] = -0.5f * gdy * dy * dL_dG;
+                    v[GR_OP] = G * dL_dalpha_j;
+                    v[GR_DEPTH] = w * gD;
+                }
+                PackedReduce<K>::run(v, lane);
+                if (writer) s_part[warp][j - lo][my_slot] = v[0];
+                hit_mask |= 1u << (j - lo);
+            }
+            if (lane == 0) s_mask[warp] = hit_mask;
+            __syncthreads();
+            {   // combine the 8 warps; one atomic set per (tile, Gaussian)
+                const int jl = tid >> 3, kk = tid & 7;
+                if (lo + jl < hi) {
+                    float s0 = 0.0f, s1 = 0.0f;
+                    bool any = false;
+#pragma unroll
+                    for (int w = 0; w < TILE_PIX / 32; ++w) {
+                        if ((s_mask[w] >> jl) & 1u) {
+                            s0 += s_part[w][jl][kk];
+                            if (kk + 8 < K) s1 += s_part[w][jl][kk + 8];
+                            any = true;
+                        }
+                    }
+                    if (any) {
+                        const uint32_t gi = __float_as_uint(sB[buf][lo + jl].w);
+                        float* rec = grad_rec + (size_t)gi * GRAD_REC;
+                        atomicAdd(rec + kk, s0);
+                        if (kk + 8 < K) atomicAdd(rec + kk + 8, s1);
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        // all threads are past the last read of `buf` (barrier above)
+        if (tid == 0 && r + 2 < rounds) issue(r + 2);
+    }
+}
+
+}  // namespace
+
+int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, const void* bws, const void* iws,
+                          const Layout& L, const float* dL_dcolor, const float* dL_dextra, const float* dL_ddepth,
+                          const float* dL_dalpha, cudaStream_t s) {
+    const int T = L.tiles_x * L.tiles_y;
+    const int blocks = V * T;
+    GSR_CUDA_TRY(cudaMemsetAsync(at<float>(gws, L.grad_rec), 0, (size_t)V * P * GRAD_REC * 4, s));
+    if (blocks == 0 || P == 0) return GSR_OK;
+    const uint2* ranges = at<uint2>(iws, L.ranges);
+    const float4* A = at<float4>(bws, L.recA);
+    const float4* B = at<float4>(bws, L.recB);
+    const float4* C = at<float4>(bws, L.recC);
+    const float4* D = at<float4>(bws, L.recD);
+    const CamDev* cams = at<CamDev>(gws, L.cams);
+    const uint32_t* nc = at<uint32_t>(iws, L.n_contrib);
+    const float* fT = at<float>(iws, L.final_T);
+    float* rec = at<float>(gws, L.grad_rec);
+    if (channels == 3) {
+        blend_backward_kernel<3><<<blocks, TILE_PIX, 0, s>>>(ranges, A, B, C, D, cams, W, H, L.tiles_x, T, nc, fT,
+                                                            dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, rec);
+    } else if (channels == 6) {
+        blend_backward_kernel<6><<<blocks, TILE_PIX, 0, s>>>(ranges, A, B, C, D, cams, W, H, L.tiles_x, T, nc, fT,
+                                                            dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, rec);
+    } else {
+        return GSR_ERR_UNSUPPORTED;
+    }
+    GSR_LAUNCH_CHECK();
+    return GSR_OK;
+}
+
+}  // namespace gsr

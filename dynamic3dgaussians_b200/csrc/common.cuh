@@ -1,0 +1,222 @@
+// Shared declarations for the sm_100a rasterizer kernels.  Internal header (the public C ABI is include/gsr_b200.h).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#include "../../include/gsr_b200.h"
+
+namespace gsr {
+
+constexpr int TILE_X = 16;            // R/cuda_rasterizer/config.h:18-19
+constexpr int TILE_Y = 16;
+constexpr int TILE_PIX = TILE_X * TILE_Y;
+constexpr int GRAD_REC = 16;          // floats per (view, Gaussian) gradient record written by the blend backward
+constexpr int NUM_COUNTERS = 64;
+
+// gradient-record slots
+enum : int { GR_MX = 0, GR_MY = 1, GR_CA = 2, GR_CB = 3, GR_CC = 4, GR_OP = 5, GR_DEPTH = 6, GR_COL = 7 };
+// counter slots
+enum : int { CNT_RENDERED = 0, CNT_OVERFLOW = 1, CNT_DEPTH_TILE = 8, CNT_INST_TILE = 24 };
+
+// Device-side camera: GsrCamera plus the per-view constants the reference derives on the host
+// (focal lengths, rasterizer_impl.cu:227-228) or in every thread (clamp limits, forward.cu:87-99).
+struct CamDev {
+    float view[16];
+    float proj[16];
+    float campos[3];
+    float focal_x, focal_y;
+    float tanfovx, tanfovy;
+    float lim_x_pos, lim_x_neg, lim_y_pos, lim_y_neg;
+    float c_x, c_y;
+    float scale_modifier;
+    float bg[8];
+    int sh_degree;
+    int prefiltered;
+    int width, height;
+    int pad[3];
+};
+
+// ------------------------------------------------------------------------------------------------------------
+// radix sort geometry
+// ------------------------------------------------------------------------------------------------------------
+constexpr int SORT_THREADS = 256;
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+template <typename KeyT> struct SortCfg;
+template <> struct SortCfg<uint32_t> { static constexpr int ITEMS = 16; };
+template <> struct SortCfg<uint64_t> { static constexpr int ITEMS = 12; };
+template <typename KeyT> constexpr int sort_tile() { return SORT_THREADS * SortCfg<KeyT>::ITEMS; }
+constexpr int MAX_PASSES = 8;
+
+inline int sort_num_tiles(int64_t n, int key_bytes) {
+    const int tile = key_bytes == 8 ? sort_tile<uint64_t>() : sort_tile<uint32_t>();
+    return (int)((n + tile - 1) / tile);
+}
+
+constexpr int SCAN_BLOCK = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_BLOCK * SCAN_ITEMS;
+
+inline int ceil_log2(uint32_t n) {  // smallest b with (1<<b) >= n, at least 1
+    int b = 1;
+    while ((1ull << b) < n) ++b;
+    return b;
+}
+
+struct Layout : GsrLayout {
+    size_t geom_bytes, binning_bytes, image_bytes;
+};
+
+inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coeffs, int64_t capacity, Layout& L) {
+    const size_t VP = (size_t)V * (size_t)P;
+    const int tx = (W + TILE_X - 1) / TILE_X, ty = (H + TILE_Y - 1) / TILE_Y;
+    const size_t VT = (size_t)V * tx * ty;
+    L.tiles_x = tx;
+    L.tiles_y = ty;
+    L.tile_bits = ceil_log2((uint32_t)VT);
+    const int view_bits = V > 1 ? ceil_log2((uint32_t)V) : 0;
+    L.depth_passes = (32 + view_bits + RADIX_BITS - 1) / RADIX_BITS;
+    L.tile_passes = (L.tile_bits + RADIX_BITS - 1) / RADIX_BITS;
+    L.sorted_keys_in = (L.tile_passes & 1);   // which ping-pong buffer holds the result of the instance sort
+    L.sorted_vals_in = (L.depth_passes & 1);  // ... and of the depth sort
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes); return r; };
+    // geom
+    L.counters = take(NUM_COUNTERS * sizeof(uint32_t));   // always at offset 0 (gsr_read_counters relies on it)
+    L.cams = take((size_t)V * sizeof(CamDev));
+    L.depths = take(VP * 4);
+    L.radii = take(VP * 4);
+    L.means2D = take(VP * 8);
+    L.conic_opacity = take(VP * 16);
+    L.tiles_touched = take(VP * 4);
+    L.cov3D = take((size_t)P * 24);
+    L.rgb = take(sh_coeffs > 0 ? VP * 12 : 0);
+    L.clamped = take(sh_coeffs > 0 ? VP * 3 : 0);
+    L.dkeys0 = take(VP * 8);
+    L.dkeys1 = take(VP * 8);
+    L.dvals0 = take(VP * 4);
+    L.dvals1 = take(VP * 4);
+    L.dhist = take((size_t)MAX_PASSES * RADIX * 4);
+    L.dlookback = take((size_t)MAX_PASSES * sort_num_tiles((int64_t)VP, 8) * RADIX * 4);
+    L.block_sums = take(((VP + SCAN_TILE - 1) / SCAN_TILE + 2) * 4);
+    L.grad_rec = take(VP * GRAD_REC * 4);
+    L.geom_bytes = o;
+    // binning
+    o = 0;
+    const size_t cap = (size_t)(capacity > 0 ? capacity : 0);
+    L.ikeys0 = take(cap * 4);
+    L.ikeys1 = take(cap * 4);
+    L.ivals0 = take(cap * 4);
+    L.ivals1 = take(cap * 4);
+    L.ihist = take((size_t)MAX_PASSES * RADIX * 4);
+    L.ilookback = take((size_t)MAX_PASSES * (sort_num_tiles((int64_t)cap, 4) + 1) * RADIX * 4);
+    L.recA = take(cap * 16);
+    L.recB = take(cap * 16);
+    L.recC = take(cap * 16);
+    L.recD = take(channels > 3 ? cap * 16 : 0);
+    L.binning_bytes = o;
+    // image
+    o = 0;
+    L.ranges = take(VT * 8);
+    L.n_contrib = take((size_t)V * W * H * 4);
+    L.final_T = take((size_t)V * W * H * 4);
+    L.image_bytes = o;
+}
+
+template <typename T>
+__host__ __device__ inline T* at(void* base, size_t off) { return reinterpret_cast<T*>(reinterpret_cast<char*>(base) + off); }
+template <typename T>
+__host__ __device__ inline const T* at(const void* base, size_t off) {
+    return reinterpret_cast<const T*>(reinterpret_cast<const char*>(base) + off);
+}
+
+// error plumbing (no exceptions across the C ABI)
+void set_cuda_error(cudaError_t e, const char* where);
+#define GSR_CUDA_TRY(expr)                                              \
+    do {                                                                \
+        cudaError_t _e = (expr);                                        \
+        if (_e != cudaSuccess) { ::gsr::set_cuda_error(_e, #expr); return GSR_ERR_CUDA; } \
+    } while (0)
+#define GSR_LAUNCH_CHECK() GSR_CUDA_TRY(cudaGetLastError())
+
+// ------------------------------------------------------------------------------------------------------------
+// stage launchers (defined in the respective .cu files)
+// ------------------------------------------------------------------------------------------------------------
+int launch_preprocess(const CamDev* cams, int V, int P, int sh_coeffs,
+                      const float* means3D, const float* opacities, const float* scales, const float* rotations,
+                      const float* cov3D_precomp, const float* sh, void* geom_ws, const Layout& L,
+                      int32_t* radii_out, cudaStream_t s);
+int launch_mark_visible(const float* view, int P, const float* means3D, uint8_t* present, cudaStream_t s);
+
+template <typename KeyT>
+int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1, int64_t n_max,
+                     const uint32_t* n_dev, int begin_bit, int end_bit, uint32_t* hist, uint32_t* lookback,
+                     uint32_t* tile_counters, cudaStream_t s);
+
+int launch_tile_scan(int V, int P, void* geom_ws, const Layout& L, cudaStream_t s);
+int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
+                   const float* colors_precomp, const float* extra_colors,
+                   void* geom_ws, void* binning_ws, void* image_ws, const Layout& L, cudaStream_t s);
+int launch_blend_forward(int V, int W, int H, int channels, const void* geom_ws, const void* binning_ws,
+                         void* image_ws, const Layout& L, float* out_color, float* out_extra, float* out_depth,
+                         float* out_alpha, cudaStream_t s);
+int launch_blend_backward(int V, int P, int W, int H, int channels, void* geom_ws, const void* binning_ws,
+                          const void* image_ws, const Layout& L, const float* dL_dcolor, const float* dL_dextra,
+                          const float* dL_ddepth, const float* dL_dalpha, cudaStream_t s);
+int launch_preprocess_backward(int V, int P, int W, int H, int channels, int sh_coeffs,
+                               const float* means3D, const float* opacities, const float* scales,
+                               const float* rotations, const float* cov3D_precomp, const float* sh,
+                               const int32_t* radii, const void* geom_ws, const Layout& L, const float* label,
+                               float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors, float* dL_dextra_colors,
+                               float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
+                               float* dL_dsh, cudaStream_t s);
+int launch_export_view(int view, int V, int P, int W, int H, const void* geom_ws, const void* binning_ws,
+                       const void* image_ws, const Layout& L, uint64_t* keys_out, uint32_t* list_out,
+                       uint32_t* ranges_out, uint32_t* n_contrib_out, cudaStream_t s);
+
+// ------------------------------------------------------------------------------------------------------------
+// device helpers: mbarrier + 1-D TMA bulk copy (cp.async.bulk), sm_90+ PTX
+// ------------------------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {}
+}
+// global -> shared bulk copy; bytes must be a multiple of 16, both addresses 16-byte aligned.
+__device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+#endif
+
+}  // namespace gsr

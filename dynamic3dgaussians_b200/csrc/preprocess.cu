@@ -1,0 +1,204 @@
+// (a) per-Gaussian forward preprocess for all V views of a batch.
+// Replaces FORWARD::preprocess / preprocessCUDA (R/cuda_rasterizer/forward.cu:166-269) and checkFrustum
+// (R/cuda_rasterizer/rasterizer_impl.cu:54-66).
+//
+// One thread per (view, Gaussian).  Besides the reference's per-Gaussian state it emits the depth-sort pair
+// (view << 32 | depth bits, Gaussian index): the (tile, depth) instance sort of the reference is split into a depth
+// sort over Gaussians (here, P entries per view) followed by a stable tile sort over instances, which yields the
+// identical order with ~4x less sort traffic.
+#include "geom_math.cuh"
+
+namespace gsr {
+
+namespace {
+
+__device__ __forceinline__ float3 eval_sh_pinned(int deg, int M, const float* __restrict__ sh_g, float3 pos,
+                                                 const float* campos, bool* clamped) {
+    // computeColorFromSH, forward.cu:20-71 (contraction pinned from the reference PTX)
+    const float dx = __fsub_rn(pos.x, campos[0]), dy = __fsub_rn(pos.y, campos[1]), dz = __fsub_rn(pos.z, campos[2]);
+    const float len = __fsqrt_rn(__fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy))));
+    const float x = __fdiv_rn(dx, len), y = __fdiv_rn(dy, len), z = __fdiv_rn(dz, len);
+    float res[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) res[c] = __fmul_rn(GSR_SH_C0, sh_g[c]);
+    auto SH = [&](int k, int c) { return sh_g[k * 3 + c]; };
+    if (deg > 0) {
+        const float a = __fmul_rn(y, GSR_SH_C1), b = __fmul_rn(z, GSR_SH_C1), d = __fmul_rn(x, GSR_SH_C1);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            float r = __fsub_rn(res[c], __fmul_rn(a, SH(1, c)));
+            r = __fmaf_rn(b, SH(2, c), r);
+            res[c] = __fsub_rn(r, __fmul_rn(d, SH(3, c)));
+        }
+        if (deg > 1) {
+            const float xx = __fmul_rn(x, x), yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+            const float xy = __fmul_rn(x, y), yz = __fmul_rn(y, z), xz = __fmul_rn(x, z);
+            const float zz2 = __fadd_rn(zz, zz);
+            const float xx_yy = __fsub_rn(xx, yy);
+            const float k4 = __fmul_rn(xy, GSR_SH_C2_0), k5 = __fmul_rn(yz, GSR_SH_C2_1);
+            const float k6 = __fmul_rn(__fsub_rn(__fsub_rn(zz2, xx), yy), GSR_SH_C2_2);
+            const float k7 = __fmul_rn(xz, GSR_SH_C2_3), k8 = __fmul_rn(xx_yy, GSR_SH_C2_4);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                float r = __fmaf_rn(k4, SH(4, c), res[c]);
+                r = __fmaf_rn(k5, SH(5, c), r);
+                r = __fmaf_rn(k6, SH(6, c), r);
+                r = __fmaf_rn(k7, SH(7, c), r);
+                res[c] = __fmaf_rn(k8, SH(8, c), r);
+            }
+            if (deg > 2) {
+                const float xx3 = __fmul_rn(xx, 3.0f), yy3 = __fmul_rn(yy, 3.0f);
+                const float f401 = __fsub_rn(__fsub_rn(__fmul_rn(zz, 4.0f), xx), yy);
+                const float k9 = __fmul_rn(__fmul_rn(y, GSR_SH_C3_0), __fsub_rn(xx3, yy));
+                const float k10 = __fmul_rn(z, __fmul_rn(xy, GSR_SH_C3_1));
+                const float k11 = __fmul_rn(__fmul_rn(y, GSR_SH_C3_2), f401);
+                const float k12 = __fmul_rn(__fmul_rn(z, GSR_SH_C3_3), __fsub_rn(__fsub_rn(zz2, xx3), yy3));
+                const float k13 = __fmul_rn(__fmul_rn(x, GSR_SH_C3_4), f401);
+                const float k14 = __fmul_rn(__fmul_rn(z, GSR_SH_C3_5), xx_yy);
+                const float k15 = __fmul_rn(__fmul_rn(x, GSR_SH_C3_6), __fsub_rn(xx, yy3));
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    float r = __fmaf_rn(k9, SH(9, c), res[c]);
+                    r = __fmaf_rn(k10, SH(10, c), r);
+                    r = __fmaf_rn(k11, SH(11, c), r);
+                    r = __fmaf_rn(k12, SH(12, c), r);
+                    r = __fmaf_rn(k13, SH(13, c), r);
+                    r = __fmaf_rn(k14, SH(14, c), r);
+                    res[c] = __fmaf_rn(k15, SH(15, c), r);
+                }
+            }
+        }
+    }
+    float3 out;
+    float* o = &out.x;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float r = __fadd_rn(res[c], 0.5f);
+        clamped[c] = r < 0.0f;
+        o[c] = r < 0.0f ? 0.0f : r;
+    }
+    return out;
+}
+
+__global__ void __launch_bounds__(256)
+preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
+                  const float* __restrict__ means3D, const float* __restrict__ opacities,
+                  const float* __restrict__ scales, const float* __restrict__ rotations,
+                  const float* __restrict__ cov3D_precomp, const float* __restrict__ sh,
+                  int tiles_x, int tiles_y,
+                  float* __restrict__ depths, int32_t* __restrict__ radii, float2* __restrict__ means2D,
+                  float4* __restrict__ conic_opacity, uint32_t* __restrict__ tiles_touched,
+                  float* __restrict__ rgb, uint8_t* __restrict__ clamped,
+                  uint64_t* __restrict__ dkeys, uint32_t* __restrict__ dvals, int32_t* __restrict__ radii_out) {
+    __shared__ CamDev cam;
+    const int v = blockIdx.y;
+    {
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(cams + v);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(&cam);
+        for (int i = threadIdx.x; i < (int)(sizeof(CamDev) / 4); i += blockDim.x) dst[i] = src[i];
+    }
+    __syncthreads();
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= P) return;
+    const size_t idx = (size_t)v * P + g;
+
+    int radius = 0;
+    uint32_t tiles = 0;
+    uint32_t depth_key = 0xffffffffu;      // culled Gaussians sort behind every visible one of their view
+
+    const float x = means3D[3 * g], y = means3D[3 * g + 1], z = means3D[3 * g + 2];
+    const float depth = xform_row(cam.view, 2, x, y, z);          // p_view.z, auxiliary.h:156
+    if (depth > 0.0f) {                                           // near cull: z <= 0 (auxiliary.h:158)
+        const float hx = xform_row(cam.proj, 0, x, y, z);
+        const float hy = xform_row(cam.proj, 1, x, y, z);
+        const float hw = xform_row(cam.proj, 3, x, y, z);
+        const float pw = __frcp_rn(__fadd_rn(hw, 0.0000001f));
+        const float ndc_x = __fmul_rn(hx, pw), ndc_y = __fmul_rn(hy, pw);
+
+        float cv[6];
+        if (cov3D_precomp != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 6; ++i) cv[i] = cov3D_precomp[6 * (size_t)g + i];
+        } else {
+            const float3 s = make_float3(scales[3 * g], scales[3 * g + 1], scales[3 * g + 2]);
+            const float4 q = reinterpret_cast<const float4*>(rotations)[g];
+            cov3d_from_scale_rot(s, cam.scale_modifier, q, cv);
+        }
+        Cov2DInter ci;
+        cov2d(cam, x, y, z, cv, ci);
+        const float det = __fsub_rn(__fmul_rn(ci.a, ci.c), __fmul_rn(ci.b, ci.b));
+        if (det != 0.0f) {
+            const float det_inv = __frcp_rn(det);
+            const float conic_x = __fmul_rn(ci.c, det_inv);
+            const float conic_y = __fmul_rn(det_inv, -ci.b);
+            const float conic_z = __fmul_rn(ci.a, det_inv);
+            const float mid = __fmul_rn(__fadd_rn(ci.a, ci.c), 0.5f);
+            const float sq = __fsqrt_rn(fmaxf(__fsub_rn(__fmul_rn(mid, mid), det), 0.1f));
+            const float lam = fmaxf(__fadd_rn(mid, sq), __fsub_rn(mid, sq));
+            const float my_radius = ceilf(__fmul_rn(__fsqrt_rn(lam), 3.0f));
+            const float2 pix = make_float2(ndc2pix(ndc_x, cam.width), ndc2pix(ndc_y, cam.height));
+            const int r_i = (int)my_radius;
+            uint2 mn, mx;
+            tile_rect(pix, r_i, tiles_x, tiles_y, mn, mx);
+            const uint32_t area = (mx.x - mn.x) * (mx.y - mn.y);
+            if (area != 0) {
+                if (sh != nullptr) {
+                    bool cl[3];
+                    const float3 c = eval_sh_pinned(cam.sh_degree, sh_coeffs, sh + (size_t)g * sh_coeffs * 3,
+                                                    make_float3(x, y, z), cam.campos, cl);
+                    rgb[3 * idx] = c.x;
+                    rgb[3 * idx + 1] = c.y;
+                    rgb[3 * idx + 2] = c.z;
+                    clamped[3 * idx] = cl[0];
+                    clamped[3 * idx + 1] = cl[1];
+                    clamped[3 * idx + 2] = cl[2];
+                }
+                depths[idx] = depth;
+                means2D[idx] = pix;
+                conic_opacity[idx] = make_float4(conic_x, conic_y, conic_z, opacities[g]);
+                radius = r_i;
+                tiles = area;
+                depth_key = __float_as_uint(depth);
+            }
+        }
+    }
+    radii[idx] = radius;
+    if (radii_out) radii_out[idx] = radius;
+    tiles_touched[idx] = tiles;
+    dkeys[idx] = ((uint64_t)(uint32_t)v << 32) | depth_key;
+    dvals[idx] = (uint32_t)g;
+}
+
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, float v2, float v6, float v10, float v14,
+                                    uint8_t* __restrict__ present) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= P) return;
+    const float x = means3D[3 * g], y = means3D[3 * g + 1], z = means3D[3 * g + 2];
+    const float d = __fadd_rn(v14, __fmaf_rn(z, v10, __fmaf_rn(x, v2, __fmul_rn(y, v6))));
+    present[g] = d > 0.0f ? 1 : 0;
+}
+
+}  // namespace
+
+int launch_preprocess(const CamDev* cams, int V, int P, int sh_coeffs, const float* means3D, const float* opacities,
+                      const float* scales, const float* rotations, const float* cov3D_precomp, const float* sh,
+                      void* ws, const Layout& L, int32_t* radii_out, cudaStream_t s) {
+    if (P == 0 || V == 0) return GSR_OK;
+    dim3 grid((P + 255) / 256, V);
+    preprocess_kernel<<<grid, 256, 0, s>>>(
+        cams, P, sh_coeffs, means3D, opacities, scales, rotations, cov3D_precomp, sh, L.tiles_x, L.tiles_y,
+        at<float>(ws, L.depths), at<int32_t>(ws, L.radii), at<float2>(ws, L.means2D),
+        at<float4>(ws, L.conic_opacity), at<uint32_t>(ws, L.tiles_touched), at<float>(ws, L.rgb),
+        at<uint8_t>(ws, L.clamped), at<uint64_t>(ws, L.dkeys0), at<uint32_t>(ws, L.dvals0), radii_out);
+    GSR_LAUNCH_CHECK();
+    return GSR_OK;
+}
+
+int launch_mark_visible(const float* view, int P, const float* means3D, uint8_t* present, cudaStream_t s) {
+    if (P == 0) return GSR_OK;
+    mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, view[2], view[6], view[10], view[14], present);
+    GSR_LAUNCH_CHECK();
+    return GSR_OK;
+}
+
+}  // namespace gsr

@@ -1,0 +1,249 @@
+// Hand-written stable LSD radix sort ("onesweep": one global histogram pass, then one chained-scan
+// scatter pass per 8-bit digit with decoupled look-back).  Replaces cub::DeviceRadixSort::SortPairs
+// (R/cuda_rasterizer/rasterizer_impl.cu:309-314, K/simple_knn.cu:217-220).
+//
+// Stability is what makes "bit-exact sorted lists" well defined (equal keys keep their input order):
+//   * inside a tile, keys are ranked in (warp, item, lane) order == input order (warp-striped layout);
+//   * tiles are ordered by a dynamically assigned tile index, which also gives the forward-progress guarantee the
+//     look-back needs (a tile only waits on tiles whose index was handed out earlier, i.e. that already run).
+//
+// HBM traffic per pass: read (key,value) once, write once.  The look-back state is one 32-bit word per
+// (tile, digit): 2 flag bits + 30-bit count, so a single volatile load carries flag and value together.
+#include "common.cuh"
+
+namespace gsr {
+
+namespace {
+
+constexpr uint32_t FLAG_AGG = 1u << 30;     // tile-local count published
+constexpr uint32_t FLAG_INC = 1u << 31;     // inclusive prefix (all tiles <= this one) published
+constexpr uint32_t VALUE_MASK = (1u << 30) - 1u;
+constexpr unsigned FULL = 0xffffffffu;
+
+__device__ __forceinline__ uint32_t ld_volatile(const uint32_t* p) { return *reinterpret_cast<const volatile uint32_t*>(p); }
+__device__ __forceinline__ void st_volatile(uint32_t* p, uint32_t v) { *reinterpret_cast<volatile uint32_t*>(p) = v; }
+
+template <typename KeyT>
+__global__ void __launch_bounds__(256)
+radix_histogram_kernel(const KeyT* __restrict__ keys, uint32_t n_max, const uint32_t* __restrict__ n_dev,
+                       int begin_bit, int end_bit, int passes, uint32_t* __restrict__ hist) {
+    __shared__ uint32_t sh[MAX_PASSES * RADIX];
+    for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) sh[i] = 0;
+    __syncthreads();
+    const uint32_t n = n_dev ? min(*n_dev, n_max) : n_max;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const KeyT key = keys[i];
+#pragma unroll
+        for (int p = 0; p < MAX_PASSES; ++p) {
+            if (p < passes) {
+                const int shift = begin_bit + p * RADIX_BITS;
+                const int bits = min(RADIX_BITS, end_bit - shift);
+                const uint32_t d = (uint32_t)(key >> shift) & ((1u << bits) - 1u);
+                // warp-aggregate equal digits so that near-constant high digits do not serialise on one bank
+                const unsigned peers = __match_any_sync(__activemask(), d);
+                if ((int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&sh[p * RADIX + d], __popc(peers));
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) {
+        const uint32_t c = sh[i];
+        if (c) atomicAdd(&hist[i], c);
+    }
+}
+
+// exclusive scan of each pass's 256 bins, in place (one block of 256 threads per pass)
+__global__ void __launch_bounds__(RADIX) radix_scan_hist_kernel(uint32_t* __restrict__ hist) {
+    __shared__ uint32_t warp_tot[RADIX / 32];
+    uint32_t* h = hist + blockIdx.x * RADIX;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t v = h[tid];
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(FULL, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    uint32_t base = 0;
+    for (int w = 0; w < warp; ++w) base += warp_tot[w];
+    h[tid] = base + inc - v;
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(SORT_THREADS)
+onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
+                     const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
+                     uint32_t n_max, const uint32_t* __restrict__ n_dev, int shift, uint32_t digit_mask,
+                     const uint32_t* __restrict__ hist_excl, uint32_t* __restrict__ lookback,
+                     uint32_t* __restrict__ tile_counter) {
+    constexpr int ITEMS = SortCfg<KeyT>::ITEMS;
+    constexpr int TILE = SORT_THREADS * ITEMS;
+    constexpr int WARPS = SORT_THREADS / 32;
+    __shared__ uint32_t s_warp_hist[WARPS][RADIX];
+    __shared__ uint32_t s_block_excl[RADIX];
+    __shared__ uint32_t s_glob_base[RADIX];
+    __shared__ uint32_t s_warp_tot[WARPS];
+    __shared__ uint32_t s_tile;
+    extern __shared__ __align__(16) unsigned char s_dyn[];
+    KeyT* s_keys = reinterpret_cast<KeyT*>(s_dyn);
+    uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_dyn + sizeof(KeyT) * TILE);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) s_warp_hist[w][tid] = 0;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t n = n_dev ? min(*n_dev, n_max) : n_max;
+    const uint64_t base64 = (uint64_t)tile * TILE;
+    if (base64 >= n) return;                       // uniform: whole block leaves
+    const uint32_t base = (uint32_t)base64;
+    const uint32_t valid_count = min((uint32_t)TILE, n - base);
+
+    // ---- load (warp-striped: element e = warp*32*ITEMS + i*32 + lane) ----
+    KeyT key[ITEMS];
+    uint32_t val[ITEMS];
+    uint32_t rank[ITEMS];
+    const uint32_t e0 = warp * 32 * ITEMS + lane;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+        const uint32_t e = e0 + i * 32;
+        const bool valid = e < valid_count;
+        key[i] = valid ? keys_in[base + e] : (KeyT)0;
+        val[i] = valid ? vals_in[base + e] : 0u;
+    }
+
+    // ---- stable in-warp ranking, one item row at a time ----
+    const unsigned lt_mask = (1u << lane) - 1u;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+        const bool valid = (e0 + i * 32) < valid_count;
+        const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
+        const uint32_t dm = valid ? d : (RADIX + lane);         // invalid lanes match nobody
+        const unsigned peers = __match_any_sync(FULL, dm);
+        const int leader = __ffs(peers) - 1;
+        uint32_t prev = 0;
+        if (valid && lane == leader) prev = s_warp_hist[warp][d];
+        prev = __shfl_sync(FULL, prev, leader);
+        rank[i] = prev + __popc(peers & lt_mask);
+        if (valid && lane == leader) s_warp_hist[warp][d] = prev + __popc(peers);
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // ---- per digit (thread == digit): warp-exclusive offsets, tile count, publish, look back ----
+    {
+        const int d = tid;
+        uint32_t run = 0;
+#pragma unroll
+        for (int w = 0; w < WARPS; ++w) {
+            const uint32_t c = s_warp_hist[w][d];
+            s_warp_hist[w][d] = run;
+            run += c;
+        }
+        const uint32_t count = run;
+        uint32_t* lb = lookback + (size_t)tile * RADIX;
+        st_volatile(&lb[d], count | (tile == 0 ? FLAG_INC : FLAG_AGG));
+
+        // exclusive scan of `count` across the 256 digits
+        uint32_t inc = count;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(FULL, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_warp_tot[warp] = inc;
+        __syncthreads();
+        uint32_t wbase = 0;
+        for (int w = 0; w < warp; ++w) wbase += s_warp_tot[w];
+        const uint32_t excl = wbase + inc - count;
+        s_block_excl[d] = excl;
+
+        uint32_t prefix = 0;
+        if (tile > 0) {
+            int64_t t = (int64_t)tile - 1;
+            while (true) {
+                const uint32_t v = ld_volatile(lookback + (size_t)t * RADIX + d);
+                if ((v >> 30) == 0u) continue;           // predecessor not published yet
+                prefix += v & VALUE_MASK;
+                if (v & FLAG_INC) break;
+                --t;                                      // tile 0 always publishes FLAG_INC, so t stays >= 0
+            }
+            st_volatile(&lb[d], ((prefix + count) & VALUE_MASK) | FLAG_INC);
+        }
+        s_glob_base[d] = hist_excl[d] + prefix - excl;   // modulo-2^32 arithmetic
+    }
+    __syncthreads();
+
+    // ---- reorder through shared memory so that global writes are runs of equal digits ----
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+        const bool valid = (e0 + i * 32) < valid_count;
+        if (valid) {
+            const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
+            const uint32_t pos = s_block_excl[d] + s_warp_hist[warp][d] + rank[i];
+            s_keys[pos] = key[i];
+            s_vals[pos] = val[i];
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) {
+        const uint32_t sidx = tid + k * SORT_THREADS;
+        if (sidx < valid_count) {
+            const KeyT kk = s_keys[sidx];
+            const uint32_t d = (uint32_t)(kk >> shift) & digit_mask;
+            const uint32_t g = s_glob_base[d] + sidx;
+            keys_out[g] = kk;
+            vals_out[g] = s_vals[sidx];
+        }
+    }
+}
+
+}  // namespace
+
+template <typename KeyT>
+int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1, int64_t n_max,
+                     const uint32_t* n_dev, int begin_bit, int end_bit, uint32_t* hist, uint32_t* lookback,
+                     uint32_t* tile_counters, cudaStream_t s) {
+    if (n_max <= 0 || end_bit <= begin_bit) return GSR_OK;
+    if (n_max >= (int64_t)VALUE_MASK) return GSR_ERR_UNSUPPORTED;
+    const int passes = (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS;
+    if (passes > MAX_PASSES) return GSR_ERR_INVALID_ARGUMENT;
+    constexpr int TILE = SORT_THREADS * SortCfg<KeyT>::ITEMS;
+    const int tiles = (int)((n_max + TILE - 1) / TILE);
+    GSR_CUDA_TRY(cudaMemsetAsync(hist, 0, (size_t)passes * RADIX * 4, s));
+    GSR_CUDA_TRY(cudaMemsetAsync(lookback, 0, (size_t)passes * tiles * RADIX * 4, s));
+    GSR_CUDA_TRY(cudaMemsetAsync(tile_counters, 0, (size_t)passes * 4, s));
+    int64_t hb = (n_max + 256 * 16 - 1) / (256 * 16);
+    const int hist_blocks = (int)(hb < 148 * 8 ? hb : 148 * 8);
+    radix_histogram_kernel<KeyT><<<hist_blocks, 256, 0, s>>>(keys0, (uint32_t)n_max, n_dev, begin_bit, end_bit,
+                                                            passes, hist);
+    GSR_LAUNCH_CHECK();
+    radix_scan_hist_kernel<<<passes, RADIX, 0, s>>>(hist);
+    GSR_LAUNCH_CHECK();
+    const size_t dyn = (size_t)TILE * (sizeof(KeyT) + 4);
+    for (int p = 0; p < passes; ++p) {
+        const int shift = begin_bit + p * RADIX_BITS;
+        const int bits = (end_bit - shift) < RADIX_BITS ? (end_bit - shift) : RADIX_BITS;
+        const KeyT* kin = (p & 1) ? keys1 : keys0;
+        KeyT* kout = (p & 1) ? keys0 : keys1;
+        const uint32_t* vin = (p & 1) ? vals1 : vals0;
+        uint32_t* vout = (p & 1) ? vals0 : vals1;
+        onesweep_pass_kernel<KeyT><<<tiles, SORT_THREADS, dyn, s>>>(
+            kin, kout, vin, vout, (uint32_t)n_max, n_dev, shift, (1u << bits) - 1u, hist + p * RADIX,
+            lookback + (size_t)p * tiles * RADIX, tile_counters + p);
+        GSR_LAUNCH_CHECK();
+    }
+    return GSR_OK;
+}
+
+template int radix_sort_pairs<uint32_t>(uint32_t*, uint32_t*, uint32_t*, uint32_t*, int64_t, const uint32_t*, int, int,
+                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t);
+template int radix_sort_pairs<uint64_t>(uint64_t*, uint64_t*, uint32_t*, uint32_t*, int64_t, const uint32_t*, int, int,
+                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t);
+
+}  // namespace gsr

@@ -1,0 +1,180 @@
+/*
+ * gsr_b200.h -- C ABI of the B200-native (sm_100a) differentiable Gaussian-splatting rasterizer and kNN.
+ *
+ * This is the drop-in boundary for the hot path of ImNotPrepared/Dynamic3DGaussians.  Paths below are relative to
+ *   R/ = submodules_fsgs/diff-gaussian-rasterization-confidence/      K/ = submodules_fsgs/simple-knn/
+ *
+ * The reference's own boundary is C++ (std::function resize callbacks + pybind11), not a C ABI:
+ *   CudaRasterizer::Rasterizer::forward      R/cuda_rasterizer/rasterizer.h:35-63   (impl rasterizer_impl.cu:198-346)
+ *   CudaRasterizer::Rasterizer::backward     R/cuda_rasterizer/rasterizer.h:65-105  (impl rasterizer_impl.cu:350-467)
+ *   CudaRasterizer::Rasterizer::markVisible  R/cuda_rasterizer/rasterizer.h:28-33   (impl rasterizer_impl.cu:141-153)
+ *   RasterizeGaussiansCUDA / ...BackwardCUDA / markVisible (torch glue)  R/rasterize_points.cu:35-126,128-225,227-246
+ *   SimpleKNN::knn / distCUDA2               K/simple_knn.cu:192-228, K/spatial.cu:15-27
+ * The resize callbacks (R/rasterize_points.cu:27-33) are replaced by a query-then-run workspace protocol; the
+ * caller owns every buffer and the library never allocates, frees, synchronises the device or throws.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - all functions enqueue work on `stream` and return immediately (0 = ok, negative = GsrStatus);
+ *   - V views are processed in one batch; all views of a batch share width/height;
+ *   - per-view arrays are laid out [V][...]; images are planar [V][C][H][W] like the reference's [C,H,W];
+ *   - matrices are the reference's transposed (column-major) 4x4 floats: element i is what the reference kernels
+ *     call matrix[i] (R/cuda_rasterizer/auxiliary.h:58-77).
+ */
+#ifndef GSR_B200_H_INCLUDED
+#define GSR_B200_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* gsr_stream_t; /* a cudaStream_t */
+
+typedef enum GsrStatus {
+    GSR_OK = 0,
+    GSR_ERR_INVALID_ARGUMENT = -1,
+    GSR_ERR_WORKSPACE_TOO_SMALL = -2,
+    GSR_ERR_CUDA = -3,           /* a CUDA runtime call failed; see gsr_last_cuda_error() */
+    GSR_ERR_UNSUPPORTED = -4,
+    GSR_ERR_CAPACITY = -5        /* instance capacity exceeded (reported by gsr_check_overflow) */
+} GsrStatus;
+
+/* One camera == one GaussianRasterizationSettings (R/diff_gaussian_rasterization/__init__.py:176-191). Host struct. */
+typedef struct GsrCamera {
+    int32_t image_width;
+    int32_t image_height;
+    float tanfovx;
+    float tanfovy;
+    float c_x;
+    float c_y;
+    float scale_modifier;
+    int32_t sh_degree;
+    int32_t prefiltered;
+    float bg[8];          /* background per blended channel: [0..2] colour, [3..5] extra (segmentation) colours */
+    float viewmatrix[16];
+    float projmatrix[16];
+    float campos[3];
+} GsrCamera;
+
+/* Byte sizes of the three caller-owned workspaces (the reference's geomBuffer / binningBuffer / imgBuffer). */
+typedef struct GsrWorkspaceSizes {
+    size_t geom_bytes;     /* per (view, Gaussian) state + depth-sort scratch      */
+    size_t binning_bytes;  /* per (Gaussian, tile) instance state, for `capacity`  */
+    size_t image_bytes;    /* per pixel / per tile state                            */
+} GsrWorkspaceSizes;
+
+/* Offsets (bytes) of the arrays inside the workspaces, for tests / tools that want to look at intermediate state. */
+typedef struct GsrLayout {
+    /* geom workspace */
+    size_t cams, counters, depths, radii, means2D, conic_opacity, tiles_touched, cov3D, rgb, clamped;
+    size_t dkeys0, dkeys1, dvals0, dvals1, dhist, dlookback, block_sums, grad_rec;
+    /* binning workspace */
+    size_t ikeys0, ikeys1, ivals0, ivals1, ihist, ilookback, recA, recB, recC, recD;
+    /* image workspace */
+    size_t ranges, n_contrib, final_T;
+    /* derived integers */
+    int32_t tiles_x, tiles_y, tile_bits, depth_passes, tile_passes, sorted_keys_in, sorted_vals_in;
+} GsrLayout;
+
+/* Number of colour channels blended in the single pass: 3 (colour) or 6 (colour + fg/bg segmentation colours). */
+#define GSR_MAX_CHANNELS 6
+
+int gsr_abi_version(void);
+const char* gsr_strerror(int status);
+const char* gsr_last_cuda_error(void);
+
+/* Workspace protocol: query sizes for (P, V, W, H, channels, instance capacity). */
+int gsr_workspace_sizes(int P, int V, int W, int H, int channels, int sh_coeffs, int64_t capacity,
+                        GsrWorkspaceSizes* out);
+int gsr_workspace_layout(int P, int V, int W, int H, int channels, int sh_coeffs, int64_t capacity, GsrLayout* out);
+
+/*
+ * Forward, stage 1 of 2: per-Gaussian preprocess for all V views (projection, covariance, conic, radius, tile rect;
+ * replaces FORWARD::preprocess, R/cuda_rasterizer/forward.cu:166-269), per-view depth ordering, and the instance count.
+ *   num_rendered_dev[0]  <- total number of (Gaussian, tile) instances over all views (what the reference returns as
+ *                           `num_rendered`, rasterizer_impl.cu:285-287, summed over views).
+ * Exactly one of (scales+rotations | cov3D_precomp) and one of (colors_precomp | sh) must be non-null.
+ * radii is [V][P] int32.
+ */
+int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels, int sh_coeffs,
+                         const float* means3D, const float* opacities, const float* scales, const float* rotations,
+                         const float* cov3D_precomp, const float* sh,
+                         void* geom_ws, size_t geom_bytes,
+                         int32_t* radii, uint32_t* num_rendered_dev, gsr_stream_t stream);
+
+/*
+ * Forward, stage 2 of 2: instance emission, tile sort, tile ranges, record gather and the fused tile blend
+ * (replaces duplicateWithKeys / SortPairs / identifyTileRanges / FORWARD::render, rasterizer_impl.cu:295-343).
+ * `capacity` is the number of instances the binning workspace was sized for; if the true count exceeds it the
+ * surplus instances are dropped and the overflow flag (gsr_check_overflow) is raised.
+ * colors_precomp [P][3] (or null when SH colours were evaluated in stage 1); extra_colors [P][3] or null (channels==6).
+ * Outputs: out_color [V][3][H][W], out_extra [V][3][H][W] (channels==6), out_depth [V][1][H][W], out_alpha [V][1][H][W].
+ */
+int gsr_forward_render(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
+                       const float* colors_precomp, const float* extra_colors,
+                       void* geom_ws, void* binning_ws, void* image_ws,
+                       float* out_color, float* out_extra, float* out_depth, float* out_alpha,
+                       gsr_stream_t stream);
+
+/* Reads back (asynchronously, into host memory) the overflow flag and the instance count. Caller synchronises. */
+int gsr_read_counters(const void* geom_ws, uint32_t* counters_host /* [4]: num_rendered, overflow, 0, 0 */,
+                      gsr_stream_t stream);
+
+/*
+ * Backward (replaces BACKWARD::render + BACKWARD::preprocess, R/cuda_rasterizer/backward.cu:432-652,144-429).
+ * Image cotangents may be null (treated as zero).  Per-Gaussian gradients are SUMMED over the V views and written
+ * (not accumulated) to the outputs; any output may be null.  dL_dmeans2D is [V][P][3] in the reference's NDC-scaled
+ * units with z = 0 (backward.cu:520-521).  `label` ([P], nullable) is the per-Gaussian gradient mask the reference
+ * applies in Python (R/diff_gaussian_rasterization/__init__.py:159-170).
+ */
+int gsr_backward(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
+                 const float* means3D, const float* opacities, const float* scales, const float* rotations,
+                 const float* cov3D_precomp, const float* sh, const float* colors_precomp, const float* extra_colors,
+                 const int32_t* radii,
+                 void* geom_ws, void* binning_ws, void* image_ws,
+                 const float* dL_dcolor, const float* dL_dextra, const float* dL_ddepth, const float* dL_dalpha,
+                 const float* label,
+                 float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors, float* dL_dextra_colors,
+                 float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D, float* dL_dsh,
+                 gsr_stream_t stream);
+
+/* present[i] = (view * p_i).z > 0   (checkFrustum, rasterizer_impl.cu:54-66).  present is [P] bytes. */
+int gsr_mark_visible(const GsrCamera* cam_host, int P, const float* means3D, uint8_t* present, gsr_stream_t stream);
+
+/*
+ * Test / tool export of one view's binning state in the REFERENCE's format: point_list_keys (uint64:
+ * tile << 32 | depth bits) and point_list (uint32 Gaussian index) in sorted order, and ranges [T][2].
+ * keys_out / list_out must hold that view's instance count (ranges tell it).  Any output may be null.
+ */
+int gsr_export_view_binning(int view, int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
+                            const void* geom_ws, const void* binning_ws, const void* image_ws,
+                            uint64_t* keys_out, uint32_t* list_out, uint32_t* ranges_out, uint32_t* n_contrib_out,
+                            gsr_stream_t stream);
+
+/* Stable LSD radix sort of n (key, value) pairs on key bits [begin_bit, end_bit) -- the hand-written onesweep used
+ * for both sorts above, exposed for tests (replaces cub::DeviceRadixSort::SortPairs, rasterizer_impl.cu:309-314).
+ * Results land in keys_out/vals_out.  tmp must hold gsr_sort_temp_bytes(n, key_bytes). key_bytes is 4 or 8. */
+size_t gsr_sort_temp_bytes(int64_t n, int key_bytes);
+int gsr_sort_pairs(int key_bytes, const void* keys_in, void* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                   int64_t n, int begin_bit, int end_bit, void* tmp, size_t tmp_bytes, gsr_stream_t stream);
+
+/*
+ * k-nearest-neighbour search (replaces SimpleKNN::knn, K/simple_knn.cu:192-228; K = 3 is distCUDA2).
+ *   mean_dist2 [P]  mean of the squared distances to the K nearest other points
+ *   idx        [P][K] int32 their indices (ascending distance);  dist2 [P][K] (nullable) the squared distances
+ */
+size_t gsr_knn_temp_bytes(int64_t P);
+int gsr_knn(int64_t P, int K, const float* points, float* mean_dist2, int32_t* idx, float* dist2,
+            void* tmp, size_t tmp_bytes, gsr_stream_t stream);
+
+/* Utility kernels used by bench.py: dependent-free FFMA loop (measures the FP32-pipe peak) and an L2 flush. */
+int gsr_fp32_peak_probe(float* out, int iters, gsr_stream_t stream);   /* flops = blocks*threads*iters*2*8 */
+int gsr_probe_geometry(int* blocks, int* threads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSR_B200_H_INCLUDED */
