@@ -1,0 +1,105 @@
+"""ctypes binding of libgsr_b200.so (the C ABI declared in include/gsr_b200.h).
+
+There is deliberately no fallback: if the CUDA library is missing or a call fails, a RuntimeError is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libgsr_b200.so")
+
+EXPORTED_SYMBOLS = [
+    "gsr_abi_version", "gsr_strerror", "gsr_last_cuda_error", "gsr_workspace_sizes", "gsr_workspace_layout",
+    "gsr_forward_geometry", "gsr_forward_render", "gsr_read_counters", "gsr_backward", "gsr_mark_visible",
+    "gsr_export_view_binning", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_knn_temp_bytes", "gsr_knn",
+    "gsr_fp32_peak_probe", "gsr_probe_geometry",
+]
+
+
+class GsrCamera(C.Structure):
+    _fields_ = [
+        ("image_width", C.c_int32), ("image_height", C.c_int32),
+        ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("c_x", C.c_float), ("c_y", C.c_float),
+        ("scale_modifier", C.c_float), ("sh_degree", C.c_int32), ("prefiltered", C.c_int32),
+        ("bg", C.c_float * 8), ("viewmatrix", C.c_float * 16), ("projmatrix", C.c_float * 16),
+        ("campos", C.c_float * 3),
+    ]
+
+
+class GsrWorkspaceSizes(C.Structure):
+    _fields_ = [("geom_bytes", C.c_size_t), ("binning_bytes", C.c_size_t), ("image_bytes", C.c_size_t)]
+
+
+_LAYOUT_SIZE_T = ["cams", "counters", "depths", "radii", "means2D", "conic_opacity", "tiles_touched", "cov3D", "rgb",
+                  "clamped", "dkeys0", "dkeys1", "dvals0", "dvals1", "dhist", "dlookback", "block_sums", "grad_rec",
+                  "ikeys0", "ikeys1", "ivals0", "ivals1", "ihist", "ilookback", "recA", "recB", "recC", "recD",
+                  "ranges", "n_contrib", "final_T"]
+_LAYOUT_INT = ["tiles_x", "tiles_y", "tile_bits", "depth_passes", "tile_passes", "sorted_keys_in", "sorted_vals_in"]
+
+
+class GsrLayout(C.Structure):
+    _fields_ = [(n, C.c_size_t) for n in _LAYOUT_SIZE_T] + [(n, C.c_int32) for n in _LAYOUT_INT]
+
+
+_lib: Optional[C.CDLL] = None
+
+
+def load(build_if_missing: bool = True) -> C.CDLL:
+    """Loads (building first when the .so is absent and nvcc is available) the CUDA library."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH) and build_if_missing:
+        from . import build as _build
+        _build.build()
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python -m dynamic3dgaussians_b200.build` (no CPU fallback exists)")
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, i64, sz = C.c_void_p, C.c_int, C.c_int64, C.c_size_t
+    lib.gsr_abi_version.restype = C.c_int
+    lib.gsr_strerror.restype = C.c_char_p
+    lib.gsr_strerror.argtypes = [C.c_int]
+    lib.gsr_last_cuda_error.restype = C.c_char_p
+    lib.gsr_workspace_sizes.argtypes = [i32, i32, i32, i32, i32, i32, i64, C.POINTER(GsrWorkspaceSizes)]
+    lib.gsr_workspace_layout.argtypes = [i32, i32, i32, i32, i32, i32, i64, C.POINTER(GsrLayout)]
+    lib.gsr_forward_geometry.argtypes = [C.POINTER(GsrCamera), i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, sz,
+                                         vp, vp, vp]
+    lib.gsr_forward_render.argtypes = [i32, i32, i32, i32, i32, i32, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.gsr_read_counters.argtypes = [vp, vp, vp]
+    lib.gsr_backward.argtypes = [i32, i32, i32, i32, i32, i32, i64] + [vp] * 27
+    lib.gsr_mark_visible.argtypes = [C.POINTER(GsrCamera), i32, vp, vp, vp]
+    lib.gsr_export_view_binning.argtypes = [i32, i32, i32, i32, i32, i32, i32, i64, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.gsr_sort_temp_bytes.restype = sz
+    lib.gsr_sort_temp_bytes.argtypes = [i64, i32]
+    lib.gsr_sort_pairs.argtypes = [i32, vp, vp, vp, vp, i64, i32, i32, vp, sz, vp]
+    lib.gsr_knn_temp_bytes.restype = sz
+    lib.gsr_knn_temp_bytes.argtypes = [i64]
+    lib.gsr_knn.argtypes = [i64, i32, vp, vp, vp, vp, vp, sz, vp]
+    lib.gsr_fp32_peak_probe.argtypes = [vp, i32, vp]
+    lib.gsr_probe_geometry.argtypes = [C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    for name in EXPORTED_SYMBOLS:
+        fn = getattr(lib, name)
+        if fn.restype is C.c_int and name not in ("gsr_abi_version",):
+            pass
+    _lib = lib
+    return lib
+
+
+def check(status: int, what: str = "") -> None:
+    if status == 0:
+        return
+    lib = load()
+    msg = lib.gsr_strerror(status).decode()
+    if status == -3:
+        msg += ": " + lib.gsr_last_cuda_error().decode()
+    raise RuntimeError(f"gsr_b200 {what} failed: {msg}")
+
+
+def ptr(t) -> Optional[int]:
+    """Device pointer of a torch tensor (None -> NULL)."""
+    if t is None:
+        return None
+    return t.data_ptr()

@@ -13,7 +13,7 @@ LIB = os.path.join(HERE, "libgsr_b200.so")
 SOURCES = ["abi.cu", "preprocess.cu", "radix_sort.cu", "binning.cu", "blend_forward.cu", "blend_backward.cu",
            "preprocess_backward.cu", "knn.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr"]
+              "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
 
 def _nvcc() -> str:

@@ -26,9 +26,9 @@ __device__ __forceinline__ float3 eval_sh_pinned(int deg, int M, const float* __
         const float a = __fmul_rn(y, GSR_SH_C1), b = __fmul_rn(z, GSR_SH_C1), d = __fmul_rn(x, GSR_SH_C1);
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-            float r = __fsub_rn(res[c], __fmul_rn(a, SH(1, c)));
+            float r = __fmaf_rn(-a, SH(1, c), res[c]);
             r = __fmaf_rn(b, SH(2, c), r);
-            res[c] = __fsub_rn(r, __fmul_rn(d, SH(3, c)));
+            res[c] = __fmaf_rn(-d, SH(3, c), r);
         }
         if (deg > 1) {
             const float xx = __fmul_rn(x, x), yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
@@ -47,15 +47,15 @@ __device__ __forceinline__ float3 eval_sh_pinned(int deg, int M, const float* __
                 res[c] = __fmaf_rn(k8, SH(8, c), r);
             }
             if (deg > 2) {
-                const float xx3 = __fmul_rn(xx, 3.0f), yy3 = __fmul_rn(yy, 3.0f);
-                const float f401 = __fsub_rn(__fsub_rn(__fmul_rn(zz, 4.0f), xx), yy);
-                const float k9 = __fmul_rn(__fmul_rn(y, GSR_SH_C3_0), __fsub_rn(xx3, yy));
+                // 3xx, 3yy and 4zz only feed adds/subs, so they are fused there (single rounding)
+                const float f401 = __fsub_rn(__fmaf_rn(zz, 4.0f, -xx), yy);
+                const float k9 = __fmul_rn(__fmul_rn(y, GSR_SH_C3_0), __fmaf_rn(xx, 3.0f, -yy));
                 const float k10 = __fmul_rn(z, __fmul_rn(xy, GSR_SH_C3_1));
                 const float k11 = __fmul_rn(__fmul_rn(y, GSR_SH_C3_2), f401);
-                const float k12 = __fmul_rn(__fmul_rn(z, GSR_SH_C3_3), __fsub_rn(__fsub_rn(zz2, xx3), yy3));
+                const float k12 = __fmul_rn(__fmul_rn(z, GSR_SH_C3_3), __fmaf_rn(-yy, 3.0f, __fmaf_rn(-xx, 3.0f, zz2)));
                 const float k13 = __fmul_rn(__fmul_rn(x, GSR_SH_C3_4), f401);
                 const float k14 = __fmul_rn(__fmul_rn(z, GSR_SH_C3_5), xx_yy);
-                const float k15 = __fmul_rn(__fmul_rn(x, GSR_SH_C3_6), __fsub_rn(xx, yy3));
+                const float k15 = __fmul_rn(__fmul_rn(x, GSR_SH_C3_6), __fmaf_rn(-yy, 3.0f, xx));
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
                     float r = __fmaf_rn(k9, SH(9, c), res[c]);
@@ -126,14 +126,14 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
         }
         Cov2DInter ci;
         cov2d(cam, x, y, z, cv, ci);
-        const float det = __fsub_rn(__fmul_rn(ci.a, ci.c), __fmul_rn(ci.b, ci.b));
+        const float det = __fmaf_rn(ci.a, ci.c, -__fmul_rn(ci.b, ci.b));   // a*c - b*b as the reference SASS has it
         if (det != 0.0f) {
             const float det_inv = __frcp_rn(det);
             const float conic_x = __fmul_rn(ci.c, det_inv);
             const float conic_y = __fmul_rn(det_inv, -ci.b);
             const float conic_z = __fmul_rn(ci.a, det_inv);
             const float mid = __fmul_rn(__fadd_rn(ci.a, ci.c), 0.5f);
-            const float sq = __fsqrt_rn(fmaxf(__fsub_rn(__fmul_rn(mid, mid), det), 0.1f));
+            const float sq = __fsqrt_rn(fmaxf(__fmaf_rn(mid, mid, -det), 0.1f));
             const float lam = fmaxf(__fadd_rn(mid, sq), __fsub_rn(mid, sq));
             const float my_radius = ceilf(__fmul_rn(__fsqrt_rn(lam), 3.0f));
             const float2 pix = make_float2(ndc2pix(ndc_x, cam.width), ndc2pix(ndc_y, cam.height));

@@ -133,28 +133,30 @@ def compute_cov3d(A: _Arith, scales, rotations, mod):
     sy = mod * scales[:, 1]
     sz = mod * scales[:, 2]
     r, x, y, z = rotations[:, 0], rotations[:, 1], rotations[:, 2], rotations[:, 3]
+    # Besides the FMAs nvcc's front end forms, ptxas fuses a product into a following add/sub whenever all uses of
+    # the product are such adds/subs (read off the reference SASS): x*y, r*y and y*z are never rounded on their own.
     yy = y * y
     zz = z * z
-    xy = x * y
     rz = r * z
     xz = x * z
-    ry = r * y
-    yz = y * z
     rx = r * x
     xx_zz = A.fma(x, x, zz)
     xx_yy = A.fma(x, x, yy)
     yy_zz = yy + zz
     one = A.c(1.0)
+
+    def twice(a):
+        return a + a
     # R columns (GLM column-major constructor, forward.cu:145-149)
-    R00 = one - (yy_zz + yy_zz)
-    R01 = (xy - rz) + (xy - rz)
-    R02 = (ry + xz) + (ry + xz)
-    R10 = (xy + rz) + (xy + rz)
-    R11 = one - (xx_zz + xx_zz)
-    R12 = (yz - rx) + (yz - rx)
-    R20 = (xz - ry) + (xz - ry)
-    R21 = (rx + yz) + (rx + yz)
-    R22 = one - (xx_yy + xx_yy)
+    R00 = one - twice(yy_zz)
+    R01 = twice(A.fma(x, y, -rz))
+    R02 = twice(A.fma(r, y, xz))
+    R10 = twice(A.fma(x, y, rz))
+    R11 = one - twice(xx_zz)
+    R12 = twice(A.fma(y, z, -rx))
+    R20 = twice(A.fma(-r, y, xz))
+    R21 = twice(A.fma(y, z, rx))
+    R22 = one - twice(xx_yy)
     # M = S * R  (column j of M = S * column j of R)
     M00, M01, M02 = sx * R00, sy * R01, sz * R02
     M10, M11, M12 = sx * R10, sy * R11, sz * R12
@@ -186,11 +188,11 @@ def eval_sh(A: _Arith, deg, means3D, campos, shs):
     res = A.c(SH_C0) * sh[:, 0]
     if deg > 0:
         t = (y * A.c(SH_C1))[:, None]
-        res = res - t * sh[:, 1]
+        res = A.fma(-t, sh[:, 1], res)
         t = (z * A.c(SH_C1))[:, None]
         res = A.fma(t, sh[:, 2], res)
         t = (x * A.c(SH_C1))[:, None]
-        res = res - t * sh[:, 3]
+        res = A.fma(-t, sh[:, 3], res)
         if deg > 1:
             xx, yy, zz = x * x, y * y, z * z
             xy, yz, xz = x * y, y * z, x * z
@@ -202,16 +204,15 @@ def eval_sh(A: _Arith, deg, means3D, campos, shs):
             xx_yy = xx - yy
             res = A.fma((xx_yy * A.c(SH_C2[4]))[:, None], sh[:, 8], res)
             if deg > 2:
-                xx3 = xx * 3.0
-                yy3 = yy * 3.0
-                res = A.fma(((y * A.c(SH_C3[0])) * (xx3 - yy))[:, None], sh[:, 9], res)
+                three, four = A.c(3.0), A.c(4.0)
+                res = A.fma(((y * A.c(SH_C3[0])) * A.fma(xx, three, -yy))[:, None], sh[:, 9], res)
                 res = A.fma((z * (xy * A.c(SH_C3[1])))[:, None], sh[:, 10], res)
-                f401 = (zz * 4.0 - xx) - yy
+                f401 = A.fma(zz, four, -xx) - yy
                 res = A.fma(((y * A.c(SH_C3[2])) * f401)[:, None], sh[:, 11], res)
-                res = A.fma(((z * A.c(SH_C3[3])) * ((zz2 - xx3) - yy3))[:, None], sh[:, 12], res)
+                res = A.fma(((z * A.c(SH_C3[3])) * A.fma(-yy, three, A.fma(-xx, three, zz2)))[:, None], sh[:, 12], res)
                 res = A.fma(((x * A.c(SH_C3[4])) * f401)[:, None], sh[:, 13], res)
                 res = A.fma(((z * A.c(SH_C3[5])) * xx_yy)[:, None], sh[:, 14], res)
-                res = A.fma(((x * A.c(SH_C3[6])) * (xx - yy3))[:, None], sh[:, 15], res)
+                res = A.fma(((x * A.c(SH_C3[6])) * A.fma(-yy, three, xx))[:, None], sh[:, 15], res)
     res = res + 0.5
     clamped = res < 0
     return torch.where(clamped, torch.zeros_like(res), res), clamped
@@ -290,7 +291,7 @@ def preprocess(cam: Camera, means3D, opacities, scales=None, rotations=None, cov
     cov_b = A.dot3(T00, w0, T01, w1, T02, w2)
     cov_c = A.dot3(T10, w0, T11, w1, T12, w2) + A.c(0.3)
 
-    det = cov_a * cov_c - cov_b * cov_b
+    det = A.fma(cov_a, cov_c, -(cov_b * cov_b))
     det_ok = det.detach() != 0
     det_s = torch.where(det_ok, det, torch.ones_like(det))
     det_inv = torch.reciprocal(det_s)
@@ -299,7 +300,7 @@ def preprocess(cam: Camera, means3D, opacities, scales=None, rotations=None, cov
     conic_z = cov_a * det_inv
 
     mid = (cov_a + cov_c) * 0.5
-    disc = torch.clamp(mid * mid - det, min=A.c(0.1).item())
+    disc = torch.clamp(A.fma(mid, mid, -det), min=A.c(0.1).item())
     sq = torch.sqrt(disc)
     lam = torch.maximum(mid + sq, mid - sq)
     rad_f = torch.ceil(torch.sqrt(torch.clamp(lam, min=0.0)) * 3.0).detach()
@@ -444,7 +445,7 @@ def blend_forward(pre: dict, lists: dict, colors, bg, dtype=torch.float32, colle
         dy = xy[:, 1:2] - pyf
         t3 = dy * (dy * con[:, 2:3])
         q = A.fma(dx, dx * con[:, 0:1], t3)
-        power = q * (-0.5) - dy * (dx * con[:, 1:2])
+        power = A.fma(q, A.c(-0.5), -(dy * (dx * con[:, 1:2])))      # ptxas fuses the *(-0.5) into the subtraction
         skip1 = power.detach() > 0
         power_s = torch.where(skip1 | ~valid, torch.zeros_like(power), power)
         G = torch.exp(power_s)
