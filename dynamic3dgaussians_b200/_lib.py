@@ -15,7 +15,8 @@ EXPORTED_SYMBOLS = [
     "gsr_abi_version", "gsr_strerror", "gsr_last_cuda_error", "gsr_workspace_sizes", "gsr_workspace_layout",
     "gsr_forward_geometry", "gsr_forward_render", "gsr_read_counters", "gsr_backward", "gsr_mark_visible",
     "gsr_export_view_binning", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_knn_temp_bytes", "gsr_knn",
-    "gsr_fp32_peak_probe", "gsr_probe_geometry",
+    "gsr_fp32_peak_probe", "gsr_probe_geometry", "gsr_stage_timing_enable", "gsr_stage_timing_count", "gsr_stage_name",
+    "gsr_stage_timing_read",
 ]
 
 
@@ -79,6 +80,10 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.gsr_knn_temp_bytes.argtypes = [i64]
     lib.gsr_knn.argtypes = [i64, i32, vp, vp, vp, vp, vp, sz, vp]
     lib.gsr_fp32_peak_probe.argtypes = [vp, i32, vp]
+    lib.gsr_stage_timing_enable.argtypes = [i32]
+    lib.gsr_stage_name.restype = C.c_char_p
+    lib.gsr_stage_name.argtypes = [i32]
+    lib.gsr_stage_timing_read.argtypes = [vp, i32]
     lib.gsr_probe_geometry.argtypes = [C.POINTER(C.c_int), C.POINTER(C.c_int)]
     for name in EXPORTED_SYMBOLS:
         fn = getattr(lib, name)
@@ -103,3 +108,16 @@ def ptr(t) -> Optional[int]:
     if t is None:
         return None
     return t.data_ptr()
+
+
+def stage_timing(enable: bool) -> None:
+    check(load().gsr_stage_timing_enable(1 if enable else 0), "stage_timing_enable")
+
+
+def read_stage_timing() -> dict:
+    """{stage name: milliseconds} of the most recent forward/backward (waits for their events)."""
+    lib = load()
+    n = lib.gsr_stage_timing_count()
+    buf = (C.c_float * n)()
+    check(lib.gsr_stage_timing_read(buf, n), "stage_timing_read")
+    return {lib.gsr_stage_name(i).decode(): float(buf[i]) for i in range(n) if buf[i] >= 0}

@@ -14,6 +14,20 @@ void set_cuda_error(cudaError_t e, const char* where) {
     snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s (%s)", where, cudaGetErrorName(e), cudaGetErrorString(e));
 }
 
+static bool g_timing = false;
+static cudaEvent_t g_ev[ST_COUNT][2];
+static bool g_ev_made = false, g_ev_used[ST_COUNT];
+
+void stage_begin(int st, cudaStream_t s) {
+    if (!g_timing) return;
+    cudaEventRecord(g_ev[st][0], s);
+}
+void stage_end(int st, cudaStream_t s) {
+    if (!g_timing) return;
+    cudaEventRecord(g_ev[st][1], s);
+    g_ev_used[st] = true;
+}
+
 static void fill_cam(const GsrCamera& c, CamDev& d) {
     memset(&d, 0, sizeof(d));
     memcpy(d.view, c.viewmatrix, sizeof(d.view));
@@ -140,16 +154,25 @@ int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels,
     }
     uint32_t* counters = at<uint32_t>(geom_ws, L.counters);
     GSR_CUDA_TRY(cudaMemsetAsync(counters, 0, NUM_COUNTERS * sizeof(uint32_t), s));
-    rc = launch_preprocess(at<CamDev>(geom_ws, L.cams), V, P, sh_coeffs, means3D, opacities, scales, rotations,
-                           cov3D_precomp, sh, geom_ws, L, radii, s);
+    {
+        StageScope sc(ST_PREPROCESS, s);
+        rc = launch_preprocess(at<CamDev>(geom_ws, L.cams), V, P, sh_coeffs, means3D, opacities, scales, rotations,
+                               cov3D_precomp, sh, geom_ws, L, radii, s);
+    }
     if (rc) return rc;
     const int view_bits = V > 1 ? ceil_log2((uint32_t)V) : 0;
-    rc = radix_sort_pairs<uint64_t>(at<uint64_t>(geom_ws, L.dkeys0), at<uint64_t>(geom_ws, L.dkeys1),
-                                    at<uint32_t>(geom_ws, L.dvals0), at<uint32_t>(geom_ws, L.dvals1),
-                                    (int64_t)V * P, nullptr, 0, 32 + view_bits, at<uint32_t>(geom_ws, L.dhist),
-                                    at<uint32_t>(geom_ws, L.dlookback), counters + CNT_DEPTH_TILE, s);
+    {
+        StageScope sc(ST_DEPTH_SORT, s);
+        rc = radix_sort_pairs<uint64_t>(at<uint64_t>(geom_ws, L.dkeys0), at<uint64_t>(geom_ws, L.dkeys1),
+                                        at<uint32_t>(geom_ws, L.dvals0), at<uint32_t>(geom_ws, L.dvals1),
+                                        (int64_t)V * P, nullptr, 0, 32 + view_bits, at<uint32_t>(geom_ws, L.dhist),
+                                        at<uint32_t>(geom_ws, L.dlookback), counters + CNT_DEPTH_TILE, s);
+    }
     if (rc) return rc;
-    rc = launch_tile_scan(V, P, geom_ws, L, s);
+    {
+        StageScope sc(ST_TILE_SCAN, s);
+        rc = launch_tile_scan(V, P, geom_ws, L, s);
+    }
     if (rc) return rc;
     if (num_rendered_dev)
         GSR_CUDA_TRY(cudaMemcpyAsync(num_rendered_dev, counters + CNT_RENDERED, 4, cudaMemcpyDeviceToDevice, s));
@@ -172,6 +195,7 @@ int gsr_forward_render(int V, int P, int W, int H, int channels, int sh_coeffs, 
     rc = launch_binning(V, P, W, H, channels, sh_coeffs, capacity, colors_precomp, extra_colors, geom_ws, binning_ws,
                         image_ws, L, s);
     if (rc) return rc;
+    StageScope sc(ST_BLEND_FWD, s);
     return launch_blend_forward(V, W, H, channels, geom_ws, binning_ws, image_ws, L, out_color, out_extra, out_depth,
                                 out_alpha, s);
 }
@@ -203,6 +227,7 @@ int gsr_backward(int V, int P, int W, int H, int channels, int sh_coeffs, int64_
     rc = launch_blend_backward(V, P, W, H, channels, geom_ws, binning_ws, image_ws, L, dL_dcolor, dL_dextra, dL_ddepth,
                                dL_dalpha, s);
     if (rc) return rc;
+    StageScope sc(ST_PREPROCESS_BWD, s);
     return launch_preprocess_backward(V, P, W, H, channels, sh_coeffs, means3D, opacities, scales, rotations,
                                       cov3D_precomp, sh, radii, geom_ws, L, label, dL_dmeans3D, dL_dmeans2D,
                                       dL_dcolors, dL_dextra_colors, dL_dopacity, dL_dscales, dL_drotations, dL_dcov3D,
@@ -272,6 +297,37 @@ int gsr_sort_pairs(int key_bytes, const void* keys_in, void* keys_out, const uin
     const int res = passes & 1;
     GSR_CUDA_TRY(cudaMemcpyAsync(keys_out, t + off[res ? 1 : 0], (size_t)n * key_bytes, cudaMemcpyDeviceToDevice, s));
     GSR_CUDA_TRY(cudaMemcpyAsync(vals_out, t + off[res ? 3 : 2], (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+    return GSR_OK;
+}
+
+int gsr_stage_timing_enable(int on) {
+    if (on && !g_ev_made) {
+        for (int i = 0; i < ST_COUNT; ++i)
+            for (int j = 0; j < 2; ++j) GSR_CUDA_TRY(cudaEventCreate(&g_ev[i][j]));
+        g_ev_made = true;
+    }
+    for (int i = 0; i < ST_COUNT; ++i) g_ev_used[i] = false;
+    g_timing = on != 0;
+    return GSR_OK;
+}
+
+int gsr_stage_timing_count(void) { return ST_COUNT; }
+
+const char* gsr_stage_name(int stage) {
+    static const char* names[ST_COUNT] = {"preprocess", "depth_sort", "tile_scan", "emit_instances", "tile_sort",
+                                          "tile_ranges", "gather_records", "blend_forward", "grad_zero",
+                                          "blend_backward", "preprocess_backward"};
+    return stage >= 0 && stage < ST_COUNT ? names[stage] : "?";
+}
+
+int gsr_stage_timing_read(float* ms_out, int n) {
+    if (!ms_out || !g_ev_made) return GSR_ERR_INVALID_ARGUMENT;
+    for (int i = 0; i < n && i < ST_COUNT; ++i) {
+        ms_out[i] = -1.0f;
+        if (!g_ev_used[i]) continue;
+        GSR_CUDA_TRY(cudaEventSynchronize(g_ev[i][1]));
+        GSR_CUDA_TRY(cudaEventElapsedTime(&ms_out[i], g_ev[i][0], g_ev[i][1]));
+    }
     return GSR_OK;
 }
 

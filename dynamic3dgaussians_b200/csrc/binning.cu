@@ -237,21 +237,28 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     uint32_t* counters = at<uint32_t>(gws, L.counters);
     const uint32_t nblocks = (VP + SCAN_TILE - 1) / SCAN_TILE;
     const uint32_t* sorted_g = at<uint32_t>(gws, L.sorted_vals_in ? L.dvals1 : L.dvals0);
+    stage_begin(ST_EMIT, s);
     emit_instances_kernel<<<nblocks, SCAN_BLOCK, 0, s>>>(
         VP, P, L.tiles_x, L.tiles_y, sorted_g, at<uint32_t>(gws, L.tiles_touched), at<uint32_t>(gws, L.block_sums),
         at<float2>(gws, L.means2D), at<int32_t>(gws, L.radii), cap, at<uint32_t>(bws, L.ikeys0),
         at<uint32_t>(bws, L.ivals0), counters);
     GSR_LAUNCH_CHECK();
+    stage_end(ST_EMIT, s);
+    stage_begin(ST_TILE_SORT, s);
     int rc = radix_sort_pairs<uint32_t>(at<uint32_t>(bws, L.ikeys0), at<uint32_t>(bws, L.ikeys1),
                                         at<uint32_t>(bws, L.ivals0), at<uint32_t>(bws, L.ivals1), capacity,
                                         counters + CNT_RENDERED, 0, L.tile_bits, at<uint32_t>(bws, L.ihist),
                                         at<uint32_t>(bws, L.ilookback), counters + CNT_INST_TILE, s);
+    stage_end(ST_TILE_SORT, s);
     if (rc != GSR_OK) return rc;
     const uint32_t* skeys = at<uint32_t>(bws, L.sorted_keys_in ? L.ikeys1 : L.ikeys0);
     const uint32_t* svals = at<uint32_t>(bws, L.sorted_keys_in ? L.ivals1 : L.ivals0);
     const uint32_t gblocks = (cap + 255) / 256;
+    stage_begin(ST_RANGES, s);
     tile_ranges_kernel<<<gblocks, 256, 0, s>>>(counters, cap, skeys, at<uint2>(iws, L.ranges));
     GSR_LAUNCH_CHECK();
+    stage_end(ST_RANGES, s);
+    StageScope sc(ST_GATHER, s);
     gather_records_kernel<<<gblocks, 256, 0, s>>>(
         counters, cap, P, T, channels, skeys, svals, at<float2>(gws, L.means2D), at<float4>(gws, L.conic_opacity),
         at<float>(gws, L.depths), colors_precomp, sh_coeffs > 0 ? at<float>(gws, L.rgb) : nullptr, extra_colors,

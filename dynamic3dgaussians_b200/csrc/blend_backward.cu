@@ -261,8 +261,12 @@ int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, c
                           const float* dL_dalpha, cudaStream_t s) {
     const int T = L.tiles_x * L.tiles_y;
     const int blocks = V * T;
-    GSR_CUDA_TRY(cudaMemsetAsync(at<float>(gws, L.grad_rec), 0, (size_t)V * P * GRAD_REC * 4, s));
+    {
+        StageScope sc(ST_GRAD_ZERO, s);
+        GSR_CUDA_TRY(cudaMemsetAsync(at<float>(gws, L.grad_rec), 0, (size_t)V * P * GRAD_REC * 4, s));
+    }
     if (blocks == 0 || P == 0) return GSR_OK;
+    StageScope sc(ST_BLEND_BWD, s);
     const uint2* ranges = at<uint2>(iws, L.ranges);
     const float4* A = at<float4>(bws, L.recA);
     const float4* B = at<float4>(bws, L.recB);

@@ -134,6 +134,17 @@ __host__ __device__ inline const T* at(const void* base, size_t off) {
     return reinterpret_cast<const T*>(reinterpret_cast<const char*>(base) + off);
 }
 
+// optional per-stage device timing (bench.py's roofline numbers): events are recorded on the launching stream
+enum Stage : int { ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_TILE_SCAN, ST_EMIT, ST_TILE_SORT, ST_RANGES, ST_GATHER,
+                   ST_BLEND_FWD, ST_GRAD_ZERO, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_COUNT };
+void stage_begin(int stage, cudaStream_t s);
+void stage_end(int stage, cudaStream_t s);
+struct StageScope {
+    int st; cudaStream_t s;
+    StageScope(int stage, cudaStream_t stream) : st(stage), s(stream) { stage_begin(st, s); }
+    ~StageScope() { stage_end(st, s); }
+};
+
 // error plumbing (no exceptions across the C ABI)
 void set_cuda_error(cudaError_t e, const char* where);
 #define GSR_CUDA_TRY(expr)                                              \

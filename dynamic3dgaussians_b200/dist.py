@@ -1,0 +1,78 @@
+"""View-sharded data parallelism: the V camera views of a timestep are split over the ranks of one
+node, the Gaussians are replicated, every rank renders + back-propagates its views in one batch, and ONE all-reduce
+sums the per-Gaussian gradient slab.  The reference has no multi-GPU path; this is the only place the hot path
+partitions (views are independent given the parameters; their gradients add)."""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+
+GRAD_KEYS = ("means3D", "colors", "opacity", "scales", "rotations")     # 3 + 3 + 1 + 3 + 4 = 14 floats / Gaussian
+GRAD_WIDTH = 14
+
+
+def partition_views(costs: Sequence[float], world: int) -> List[List[int]]:
+    """Longest-processing-time-first assignment of views to ranks.  `costs[v]` is any per-view cost proxy (instance
+    count or last step's milliseconds); with equal costs this is a balanced round-robin.  Deterministic, so every rank
+    computes the same table without communicating."""
+    order = sorted(range(len(costs)), key=lambda v: (-float(costs[v]), v))
+    loads = [0.0] * world
+    counts = [0] * world
+    out: List[List[int]] = [[] for _ in range(world)]
+    for v in order:
+        r = min(range(world), key=lambda i: (loads[i], counts[i], i))
+        out[r].append(v)
+        loads[r] += float(costs[v])
+        counts[r] += 1
+    return [sorted(x) for x in out]
+
+
+def pack_grads(g: dict, P: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[P, 14] contiguous slab (means3D 3 | colours 3 | opacity 1 | scales 3 | rotations 4): one collective per step."""
+    dev = g["means3D"].device
+    if out is None:
+        out = torch.empty((P, GRAD_WIDTH), dtype=torch.float32, device=dev)
+    c = 0
+    for k in GRAD_KEYS:
+        t = g[k]
+        w = t.shape[1] if t.dim() > 1 else 1
+        out[:, c:c + w] = t.reshape(P, w)
+        c += w
+    return out
+
+
+def unpack_grads(slab: torch.Tensor) -> dict:
+    return dict(means3D=slab[:, 0:3], colors=slab[:, 3:6], opacity=slab[:, 6:7], scales=slab[:, 7:10],
+                rotations=slab[:, 10:14])
+
+
+def allreduce_grads(slab: torch.Tensor, group=None, async_op: bool = False):
+    """Sum of the gradient slab over the ranks (NCCL on GPUs, gloo in the CPU tests)."""
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return None
+    return dist.all_reduce(slab, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+
+
+def sharded_step(settings, my_views: Sequence[int], params: dict, cotangents: dict, group=None):
+    """forward + backward of this rank's views and the all-reduce.  params: means3D, opacities, colors_precomp, scales,
+    rotations (replicated).  cotangents: dict of [V_total, C, H, W] tensors or None for color / depth / alpha.
+    Returns (outputs of the local views, gradient slab [P,14] summed over ALL views)."""
+    from . import rasterizer as RZ
+    P = params["means3D"].shape[0]
+    my_views = list(my_views)
+    if my_views:
+        sets = [settings[v] for v in my_views]
+        out = RZ.forward_views(sets, params["means3D"], params["opacities"], params["colors_precomp"],
+                               params["scales"], params["rotations"])
+        sel = lambda t: None if t is None else t[my_views].contiguous()
+        g = RZ.backward_views(out[5], params["means3D"], params["opacities"], params["colors_precomp"],
+                              params["scales"], params["rotations"], None, None, None, sel(cotangents.get("color")),
+                              None, sel(cotangents.get("depth")), sel(cotangents.get("alpha")), want_means2D=False)
+        slab = pack_grads(g, P)
+    else:
+        out = None
+        slab = torch.zeros((P, GRAD_WIDTH), dtype=torch.float32, device=params["means3D"].device)
+    allreduce_grads(slab, group)
+    return out, slab

@@ -170,6 +170,14 @@ size_t gsr_knn_temp_bytes(int64_t P);
 int gsr_knn(int64_t P, int K, const float* points, float* mean_dist2, int32_t* idx, float* dist2,
             void* tmp, size_t tmp_bytes, gsr_stream_t stream);
 
+/* Optional per-stage device timing (used by bench.py for the roofline numbers): when enabled, the library records
+ * CUDA events on the launching stream around each stage of the forward/backward; gsr_stage_timing_read waits for the
+ * most recent events and returns milliseconds per stage (-1 for a stage that did not run). Not thread-safe. */
+int gsr_stage_timing_enable(int on);
+int gsr_stage_timing_count(void);
+const char* gsr_stage_name(int stage);
+int gsr_stage_timing_read(float* ms_out, int n);
+
 /* Utility kernels used by bench.py: dependent-free FFMA loop (measures the FP32-pipe peak) and an L2 flush. */
 int gsr_fp32_peak_probe(float* out, int iters, gsr_stream_t stream);   /* flops = blocks*threads*iters*2*8 */
 int gsr_probe_geometry(int* blocks, int* threads);

@@ -263,6 +263,30 @@ def diag_timing(P=300_000, V=27):
                   f"  Mpix/s={V * 640 * 360 / dt / 1e6:.1f}")
 
 
+@stage("C2 radii / images vs reference, every view")
+def diag_c2_exact(P=300_000, V=27):
+    sc = scenes.make_scene_c2(P)
+    cams = scenes.cameras_c2(V)
+    sets = [settings_from_spec(c)[0] for c in cams]
+    rv = {k: v.to(DEV) for k, v in sc.rendervar().items()}
+    out = RZ.forward_views(sets, rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"])
+    color, _, depth, alpha, radii, st = out
+    bad_r = bad_c = bad_d = 0
+    tot = 0
+    for v, s in enumerate(sets):
+        rr = ref_cuda.RefRasterizer(s)
+        ro = rr.forward(rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"])
+        tot += ro["num_rendered"]
+        br = int((radii[v] != ro["radii"]).sum())
+        bc = int((color[v] != ro["color"]).sum())
+        bd = int((depth[v] != ro["depth"]).sum())
+        if br or bc or bd:
+            print(f"   view {v}: radii diff {br}, colour values diff {bc}, depth diff {bd}")
+        bad_r += br; bad_c += bc; bad_d += bd
+    print(f"  total: radii mismatches {bad_r} / {V * P}; colour value mismatches {bad_c}; depth {bad_d};"
+          f" R mine {st.num_rendered} ref {tot}")
+
+
 if __name__ == "__main__":
     print(torch.cuda.get_device_name(0))
     diag_sort()
@@ -270,4 +294,5 @@ if __name__ == "__main__":
     diag_view(10_000, tag="C1")
     diag_batch()
     if "--big" in sys.argv:
+        diag_c2_exact()
         diag_timing()
