@@ -130,9 +130,11 @@ def forward_views(settings: Sequence[GaussianRasterizationSettings], means3D, op
     V = len(settings)
     if V == 0:
         raise ValueError("need at least one view")
-    means3D = _cuda_f32(means3D, "means3D", (3,))
-    if means3D is None:
-        raise ValueError("means3D must have dimensions (num_points, 3)")
+    if not torch.is_tensor(means3D) or means3D.dim() != 2 or means3D.shape[1] != 3:
+        raise ValueError("means3D must have dimensions (num_points, 3)")       # R/rasterize_points.cu:60-62
+    if not means3D.is_cuda or means3D.dtype != torch.float32:
+        raise ValueError("means3D must be a float32 CUDA tensor (this rasterizer has no CPU path)")
+    means3D = means3D.contiguous()
     dev = means3D.device
     P = means3D.shape[0]
     W, H = int(settings[0].image_width), int(settings[0].image_height)
