@@ -170,6 +170,21 @@ size_t gsr_knn_temp_bytes(int64_t P);
 int gsr_knn(int64_t P, int K, const float* points, float* mean_dist2, int32_t* idx, float* dist2,
             void* tmp, size_t tmp_bytes, gsr_stream_t stream);
 
+/*
+ * Fused local-rigidity / rotation-similarity / isometry losses over a fixed K-NN graph of F foreground Gaussians,
+ * forward and (optionally) backward: replaces the eager PyTorch code of REF/train.py:253-273 (== REF/cvpr_dyn.py:304-330).
+ *   pts [F][3], rot [F][4] (w,x,y,z; the normalised current rotations), prev_inv_rot [F][4] (REF/train.py:303-304),
+ *   nbr_idx [F][K] int32, nbr_weight [F][K], prev_offset [F][K][3] (:306), nbr_dist [F][K] (:323)
+ *   losses [3] <- (rigid, rot, iso), each the mean over the F*K edges as weighted_l2_loss_v2 / _v1 (REF/helpers.py:118-123)
+ * When dL_dpts [F][3] and dL_drot [F][4] are non-null they receive  sum_l upstream_dev[l] * d losses[l] / d(pts, rot);
+ * upstream_dev is a DEVICE pointer to 3 floats (the loss weights or autograd's cotangents), so no host sync is needed.
+ */
+size_t gsr_dyn_losses_temp_bytes(int64_t F);
+int gsr_dyn_losses(int64_t F, int K, const float* pts, const float* rot, const float* prev_inv_rot,
+                   const int32_t* nbr_idx, const float* nbr_weight, const float* prev_offset, const float* nbr_dist,
+                   const float* upstream_dev, float* losses, float* dL_dpts, float* dL_drot, void* tmp,
+                   size_t tmp_bytes, gsr_stream_t stream);
+
 /* Optional per-stage device timing (used by bench.py for the roofline numbers): when enabled, the library records
  * CUDA events on the launching stream around each stage of the forward/backward; gsr_stage_timing_read waits for the
  * most recent events and returns milliseconds per stage (-1 for a stage that did not run). Not thread-safe. */

@@ -1,0 +1,43 @@
+"""Condenses `ncu -i X.ncu-rep --page raw --csv` into the handful of metrics the roofline discussion uses.
+usage: python profiles/ncu_summary.py raw.csv"""
+import csv
+import sys
+
+WANT = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum',
+        'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed', 'sm__throughput.avg.pct_of_peak_sustained_elapsed',
+        'launch__registers_per_thread', 'launch__grid_size', 'launch__block_size',
+        'launch__shared_mem_per_block_static', 'launch__occupancy_limit_registers',
+        'launch__occupancy_limit_shared_mem', 'sm__warps_active.avg.pct_of_peak_sustained_active',
+        'smsp__issue_active.avg.pct_of_peak_sustained_active', 'smsp__inst_executed.sum',
+        'smsp__thread_inst_executed_per_inst_executed.ratio',
+        'sm__inst_executed_pipe_fma.sum', 'sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active',
+        'sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_active',
+        'sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active',
+        'sm__inst_executed_pipe_xu.sum', 'sm__pipe_xu_cycles_active.avg.pct_of_peak_sustained_active',
+        'sm__inst_executed_pipe_lsu.sum', 'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum',
+        'l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed',
+        'l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum',
+        'lts__t_sectors_op_red.sum', 'lts__t_sectors_op_atom.sum', 'lts__t_bytes.sum',
+        'lts__throughput.avg.pct_of_peak_sustained_elapsed', 'l1tex__throughput.avg.pct_of_peak_sustained_elapsed']
+
+
+def main(path):
+    rows = list(csv.reader(open(path)))
+    hdr, units = rows[0], rows[1]
+    col = {h: i for i, h in enumerate(hdr)}
+    for r in rows[2:]:
+        print('-----', r[col['Kernel Name']][:100], ' id', r[col['ID']])
+        for w in WANT:
+            if w in col:
+                print(f"  {w:72s} {r[col[w]]} {units[col[w]]}")
+        for h, i in col.items():
+            if 'issue_stalled' in h and h.endswith('_per_warp_active.pct'):
+                try:
+                    if float(r[i]) > 4:
+                        print(f"    stall {h[len('smsp__average_warps_issue_stalled_'):-len('_per_warp_active.pct')]:40s} {r[i]}")
+                except ValueError:
+                    pass
+
+
+if __name__ == '__main__':
+    main(sys.argv[1])
