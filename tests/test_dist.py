@@ -1,0 +1,76 @@
+"""View-sharded data parallelism: host logic on CPU with the gloo backend, world_size 2."""
+import os
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import helpers  # noqa: E402,F401
+from dynamic3dgaussians_b200 import dist as D  # noqa: E402
+
+
+def test_partition_views_balances_counts_and_costs():
+    for world in (1, 2, 4, 8):
+        parts = D.partition_views([1.0] * 27, world)
+        sizes = sorted(len(p) for p in parts)
+        assert sum(sizes) == 27 and sizes[-1] - sizes[0] <= 1
+        assert sorted(v for p in parts for v in p) == list(range(27))
+    # cost-aware: one heavy view gets a rank (almost) to itself
+    costs = [10.0] + [1.0] * 9
+    parts = D.partition_views(costs, 2)
+    heavy = next(p for p in parts if 0 in p)
+    assert sum(costs[v] for v in heavy) <= 10.0 + 1e-9
+    assert D.partition_views(costs, 2) == parts                     # deterministic
+
+
+def test_pack_unpack_roundtrip():
+    P = 17
+    g = dict(means3D=torch.randn(P, 3), colors=torch.randn(P, 3), opacity=torch.randn(P, 1), scales=torch.randn(P, 3),
+             rotations=torch.randn(P, 4))
+    slab = D.pack_grads(g, P)
+    assert slab.shape == (P, D.GRAD_WIDTH) and slab.is_contiguous()
+    u = D.unpack_grads(slab)
+    for k in D.GRAD_KEYS:
+        assert torch.equal(u[k], g[k])
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        V, P = 7, 50
+        g = torch.Generator().manual_seed(0)
+        per_view = torch.randn(V, P, D.GRAD_WIDTH, generator=g)       # stand-in for each view's per-Gaussian gradients
+        parts = D.partition_views([float(v + 1) for v in range(V)], world)
+        mine = parts[rank]
+        slab = per_view[mine].sum(dim=0) if mine else torch.zeros(P, D.GRAD_WIDTH)
+        D.allreduce_grads(slab)
+        ok = torch.allclose(slab, per_view.sum(dim=0), atol=1e-5)
+        # an async handle works too, and a rank with no views contributes zeros
+        z = torch.zeros(P, D.GRAD_WIDTH) if rank else per_view[0].clone()
+        h = D.allreduce_grads(z, async_op=True)
+        h.wait()
+        ok = ok and torch.allclose(z, per_view[0], atol=1e-6)
+        out[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_gloo_allreduce_equals_single_process_sum():
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(2, port, out), nprocs=2, join=True)
+    assert out[0] and out[1]
+
+
+def test_allreduce_is_a_noop_without_a_process_group():
+    t = torch.ones(3, D.GRAD_WIDTH)
+    assert D.allreduce_grads(t) is None and torch.equal(t, torch.ones(3, D.GRAD_WIDTH))
