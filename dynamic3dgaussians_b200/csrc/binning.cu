@@ -141,8 +141,8 @@ tile_ranges_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, con
 }
 
 // Gathers the per-instance records the blend kernels stream with TMA bulk copies:
-//   A = (mean.x, mean.y, conic.x, conic.y)   B = (conic.z, opacity, depth, bits(view*P + g))
-//   C = (r, g, b, 0)                         D = (extra colour r, g, b, 0)   [channels == 6]
+//   A = (mean.x, mean.y, conic.x, conic.y)   B = (conic.z, opacity, depth, skip threshold [blend_skip_threshold])
+//   C = (r, g, b, bits(view*P + g))          D = (extra colour r, g, b, 0)   [channels == 6]
 __global__ void __launch_bounds__(256)
 gather_records_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, int P, uint32_t T, int channels,
                       const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
@@ -160,9 +160,9 @@ gather_records_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, 
     const float2 m = means2D[gi];
     const float4 co = conic_opacity[gi];
     recA[i] = make_float4(m.x, m.y, co.x, co.y);
-    recB[i] = make_float4(co.z, co.w, depths[gi], __uint_as_float(gi));
+    recB[i] = make_float4(co.z, co.w, depths[gi], blend_skip_threshold(co.w));
     const float* c = colors_precomp ? colors_precomp + 3 * (size_t)g : rgb_sh + 3 * (size_t)gi;
-    recC[i] = make_float4(c[0], c[1], c[2], 0.0f);
+    recC[i] = make_float4(c[0], c[1], c[2], __uint_as_float(gi));
     if (channels > 3) {
         const float* e = extra_colors + 3 * (size_t)g;
         recD[i] = make_float4(e[0], e[1], e[2], 0.0f);

@@ -83,7 +83,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     __shared__ __align__(8) uint64_t full[2];
     __shared__ float s_part[TILE_PIX / 32][SUB][GRAD_REC];
     __shared__ uint32_t s_mask[TILE_PIX / 32];
+    __shared__ uint32_t s_wmask[TILE_PIX / 32][BATCH / SUB];
     __shared__ uint32_t s_max;
+    static_assert(SUB == 32 && BATCH <= TILE_PIX, "work lists are one 32-bit word per (warp, sub-batch)");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int vt = blockIdx.x;
@@ -166,25 +168,54 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     const unsigned slot_peers = __match_any_sync(FULL, my_slot);
     const bool writer = lane == (__ffs(slot_peers) - 1);
 
+    const float tile_x0 = (float)(tile_xi * TILE_X), tile_y0 = (float)(tile_yi * TILE_Y);
+    const uint32_t warp_last = __reduce_max_sync(FULL, last_contributor);   // nothing at or past it matters to this warp
+
     for (int r = 0; r < rounds; ++r) {
         const int buf = r & 1;
         const int c = rounds - 1 - r;
         const int nb = min(BATCH, n_proc - c * BATCH);
         mbar_wait(&full[buf], (uint32_t)((r >> 1) & 1));
+        // ---- pre-pass: per-warp work lists (see blend_forward.cu): Gaussian j x warp patch intersection ----
+        if (tid < BATCH) {
+            uint32_t m8 = 0u;
+            if (tid < nb) {
+                const float4 a = sA[buf][tid];
+                const float4 b = sB[buf][tid];
+                m8 = blend_patch_mask(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
+            }
+#pragma unroll
+            for (int w = 0; w < TILE_PIX / 32; ++w) {
+                const uint32_t bal = __ballot_sync(FULL, (m8 >> w) & 1u);
+                if (lane == 0) s_wmask[w][warp] = bal;
+            }
+        }
+        __syncthreads();
         for (int sub = (nb - 1) / SUB; sub >= 0; --sub) {
             const int lo = sub * SUB;
             const int hi = min(lo + SUB, nb);
             uint32_t hit_mask = 0;
-            for (int j = hi - 1; j >= lo; --j) {
+            uint32_t m = s_wmask[warp][sub];
+            {   // drop positions no pixel of this warp blended (pos >= warp_last)
+                const uint32_t base = (uint32_t)(c * BATCH + lo);
+                if (warp_last <= base) m = 0u;
+                else if (warp_last - base < 32u) m &= (1u << (warp_last - base)) - 1u;
+            }
+            while (m != 0u) {                                       // warp-uniform, back to front
+                const int jl = 31 - __clz(m);
+                m &= ~(1u << jl);
+                const int j = lo + jl;
                 const float4 a = sA[buf][j];
                 const float4 b = sB[buf][j];
                 const uint32_t pos = (uint32_t)(c * BATCH + j);
                 const float dx = __fsub_rn(a.x, pxf), dy = __fsub_rn(a.y, pyf);
                 const float power = blend_power(dx, dy, a.z, a.w, b.x);
+                const bool pre = (pos < last_contributor) && !(power > 0.0f) && !(power < b.w);
+                if (!__any_sync(FULL, pre)) continue;                // warp-uniform
                 const float G = expf(fminf(power, 0.0f));
                 const float alpha = fminf(0.99f, __fmul_rn(b.y, G));
-                const bool valid = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                if (__ballot_sync(FULL, valid) == 0u) continue;      // warp-uniform
+                const bool valid = pre && !(alpha < 1.0f / 255.0f);
+                if (!__any_sync(FULL, valid)) continue;              // warp-uniform
 
                 float v[K];
 #pragma unroll
@@ -221,8 +252,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                     v[GR_DEPTH] = w * gD;
                 }
                 PackedReduce<K>::run(v, lane);
-                if (writer) s_part[warp][j - lo][my_slot] = v[0];
-                hit_mask |= 1u << (j - lo);
+                if (writer) s_part[warp][jl][my_slot] = v[0];
+                hit_mask |= 1u << jl;
             }
             if (lane == 0) s_mask[warp] = hit_mask;
             __syncthreads();
@@ -240,7 +271,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                         }
                     }
                     if (any) {
-                        const uint32_t gi = __float_as_uint(sB[buf][lo + jl].w);
+                        const uint32_t gi = __float_as_uint(sC[buf][lo + jl].w);
                         float* rec = grad_rec + (size_t)gi * GRAD_REC;
                         atomicAdd(rec + kk, s0);
                         if (kk + 8 < K) atomicAdd(rec + kk + 8, s1);

@@ -6,8 +6,12 @@
 //   (the reference fetches colour/depth/semantics from global memory for every contributing pair, forward.cu:375-383);
 // * colour, fg/bg segmentation colours, depth and accumulated alpha are blended in ONE pass over the list
 //   (the reference renders colour and segmentation with two full rasterizer calls, REF/train.py:142,249);
-// * a warp covers an 8x4 pixel patch, leaves the inner loop as soon as all of its pixels are saturated (the loop
-//   condition is warp-uniform once every lane is done) and the CTA stops fetching when all 256 pixels are done;
+// * a warp covers an 8x4 pixel patch.  Per staged batch a pre-pass (one thread per Gaussian) intersects the Gaussian's
+//   opacity-aware extent (the ellipse outside of which alpha < 1/255) with the 8 patches and warp ballots turn that into
+//   a 128-bit work list per warp: a warp only iterates over Gaussians that can reach its patch (2-3x fewer
+//   iterations than walking the tile's whole list as the reference does), and each lane tests `power < threshold`
+//   before paying for the exp.  Both filters are conservative, so the set of blended pairs is unchanged;
+// * a warp leaves the loop as soon as all of its pixels are saturated and the CTA stops fetching when all 256 are;
 // * arithmetic per pair follows the reference binary exactly (see geom_math.cuh), so n_contrib and the images agree
 //   with the reference bit for bit.
 #include "geom_math.cuh"
@@ -32,6 +36,8 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
     __shared__ __align__(128) float4 sC[2][BATCH];
     __shared__ __align__(128) float4 sD[EXTRA ? 2 : 1][EXTRA ? BATCH : 1];
     __shared__ __align__(8) uint64_t full[2];
+    __shared__ uint32_t s_wmask[TILE_PIX / 32][BATCH / 32];
+    static_assert(BATCH <= TILE_PIX && BATCH % 32 == 0, "one pre-pass thread per staged Gaussian");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int vt = blockIdx.x;
@@ -78,38 +84,61 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
     uint32_t last_contributor = 0;
     bool done = !inside;
 
+    const float tile_x0 = (float)(tile_xi * TILE_X), tile_y0 = (float)(tile_yi * TILE_Y);
     for (int r = 0; r < rounds; ++r) {
         const int buf = r & 1;
         mbar_wait(&full[buf], (uint32_t)((r >> 1) & 1));
         const int nb = min(BATCH, n_total - r * BATCH);
         const uint32_t contrib_base = (uint32_t)r * BATCH;
-        for (int j = 0; !done && j < nb; ++j) {
-            const float4 a = sA[buf][j];
-            const float4 b = sB[buf][j];
-            const float dx = __fsub_rn(a.x, pxf), dy = __fsub_rn(a.y, pyf);
-            const float power = blend_power(dx, dy, a.z, a.w, b.x);
-            if (power > 0.0f) continue;
-            const float alpha = fminf(0.99f, __fmul_rn(b.y, expf(power)));
-            if (alpha < 1.0f / 255.0f) continue;
-            const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
-            if (test_T < 0.0001f) {
-                done = true;
-                continue;
+        // ---- pre-pass: thread j decides which of the 8 warp patches Gaussian j can reach; the ballots turn that
+        //      into one 128-bit "work list" per warp, so a warp never touches a Gaussian that misses its patch ----
+        if (tid < BATCH) {
+            uint32_t m8 = 0u;
+            if (tid < nb) {
+                const float4 a = sA[buf][tid];
+                const float4 b = sB[buf][tid];
+                m8 = blend_patch_mask(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
             }
-            const float4 c = sC[buf][j];
-            C[0] = __fmaf_rn(T, __fmul_rn(alpha, c.x), C[0]);
-            C[1] = __fmaf_rn(T, __fmul_rn(alpha, c.y), C[1]);
-            C[2] = __fmaf_rn(T, __fmul_rn(alpha, c.z), C[2]);
-            if (EXTRA) {
-                const float4 e = sD[buf][j];
-                C[NCH - 3] = __fmaf_rn(T, __fmul_rn(alpha, e.x), C[NCH - 3]);
-                C[NCH - 2] = __fmaf_rn(T, __fmul_rn(alpha, e.y), C[NCH - 2]);
-                C[NCH - 1] = __fmaf_rn(T, __fmul_rn(alpha, e.z), C[NCH - 1]);
+#pragma unroll
+            for (int w = 0; w < TILE_PIX / 32; ++w) {
+                const uint32_t bal = __ballot_sync(0xffffffffu, (m8 >> w) & 1u);
+                if (lane == 0) s_wmask[w][warp] = bal;
             }
-            D = __fmaf_rn(T, __fmul_rn(alpha, b.z), D);
-            Wsum = __fmaf_rn(alpha, T, Wsum);
-            T = test_T;
-            last_contributor = contrib_base + (uint32_t)j + 1u;
+        }
+        __syncthreads();
+#pragma unroll 1
+        for (int q = 0; q < BATCH / 32; ++q) {
+            uint32_t m = s_wmask[warp][q];
+            while (m != 0u && !done) {
+                const int j = q * 32 + __ffs(m) - 1;
+                m &= m - 1u;
+                const float4 a = sA[buf][j];
+                const float4 b = sB[buf][j];
+                const float dx = __fsub_rn(a.x, pxf), dy = __fsub_rn(a.y, pyf);
+                const float power = blend_power(dx, dy, a.z, a.w, b.x);
+                if (power > 0.0f || power < b.w) continue;      // b.w: conservative skip threshold (no exp needed)
+                const float alpha = fminf(0.99f, __fmul_rn(b.y, expf(power)));
+                if (alpha < 1.0f / 255.0f) continue;
+                const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
+                if (test_T < 0.0001f) {
+                    done = true;
+                    continue;
+                }
+                const float4 c = sC[buf][j];
+                C[0] = __fmaf_rn(T, __fmul_rn(alpha, c.x), C[0]);
+                C[1] = __fmaf_rn(T, __fmul_rn(alpha, c.y), C[1]);
+                C[2] = __fmaf_rn(T, __fmul_rn(alpha, c.z), C[2]);
+                if (EXTRA) {
+                    const float4 e = sD[buf][j];
+                    C[NCH - 3] = __fmaf_rn(T, __fmul_rn(alpha, e.x), C[NCH - 3]);
+                    C[NCH - 2] = __fmaf_rn(T, __fmul_rn(alpha, e.y), C[NCH - 2]);
+                    C[NCH - 1] = __fmaf_rn(T, __fmul_rn(alpha, e.z), C[NCH - 1]);
+                }
+                D = __fmaf_rn(T, __fmul_rn(alpha, b.z), D);
+                Wsum = __fmaf_rn(alpha, T, Wsum);
+                T = test_T;
+                last_contributor = contrib_base + (uint32_t)j + 1u;
+            }
         }
         // everyone is finished with `buf`; stop fetching once the whole tile is saturated
         const int num_done = __syncthreads_count(done);
