@@ -178,8 +178,10 @@ def run_ours(args, world, rank, local):
     parts = D.partition_views([1.0] * V, world)
     mine = parts[rank]
 
+    cap = [None]
+
     def step():
-        return D.sharded_step(sets, mine, rv, cot)
+        return D.sharded_step(sets, mine, rv, cot, capacity=cap[0])
 
     # first pass: per-view instance counts -> cost-aware partition (deterministic on every rank)
     out, _ = step()
@@ -193,6 +195,11 @@ def run_ours(args, world, rank, local):
         dist.all_reduce(costs)
         parts = D.partition_views(costs.tolist(), world)
         mine = parts[rank]
+    # one synchronising step with the final partition tells the instance count; from then on the binning workspace is
+    # sized for 1.05x that count and no step touches the host (overflow is checked after the timed region)
+    out, _ = step()
+    if out is not None:
+        cap[0] = int(out[5].num_rendered * 1.05) + 4096
     for _ in range(args.warmup):
         step()
     barrier(world)
@@ -223,11 +230,14 @@ def run_ours(args, world, rank, local):
     pairs = 0
     R = 0
     if st is not None:
+        n_now, overflowed = RZ.read_counters(st)
+        assert not overflowed, "instance capacity exceeded inside the timed region"
+        st.num_rendered = n_now
         L = RZ.workspace_layout(st.P, st.V, st.W, st.H, st.channels, 0, st.capacity)
         ncon = st.image[L.n_contrib: L.n_contrib + st.V * st.W * st.H * 4].view(torch.int32)
         pairs = int(ncon.sum(dtype=torch.int64).item())
         R = st.num_rendered
-    res = dict(ms=ms, stages=stages, pairs=pairs, R=R, clocks=clocks, views_per_rank=[len(p) for p in parts],
+    res = dict(ms=ms, stages=stages, pairs=pairs, R=R, clocks=clocks, views_per_rank=[len(p) for p in parts], parts=parts,
                launches=kernels_per_step(L, world > 1) * args.steps if st is not None else 0, state=st, dev=dev,
                rv=rv, sets=sets, sc=sc, lib=lib)
     return res
@@ -239,7 +249,7 @@ def run_e2e(args, res, world, rank):
     targets, back-propagates, all-reduces the gradients and reads the loss and the gradient slab back to the host."""
     from dynamic3dgaussians_b200 import dist as D, rasterizer as RZ
     dev, sets, sc = res["dev"], res["sets"], res["sc"]
-    parts = D.partition_views([1.0] * len(sets), world)
+    parts = res["parts"]
     mine = parts[rank]
     my_sets = [sets[v] for v in mine]
     rv_host = sc.rendervar()
@@ -253,11 +263,16 @@ def run_e2e(args, res, world, rank):
     h2d = slab_host.numel() * 4 + tgt_host.numel()
     d2h = grad_host.numel() * 4 + 4
 
+    states = []
+    cap_e2e = int(res["R"] * 1.05) + 4096 if mine else None
+
     def step():
         slab = slab_host.to(dev, non_blocking=True).requires_grad_(True)
         tgt = tgt_host.to(dev, non_blocking=True)
         m, c, o, s, r = slab[:, 0:3], slab[:, 3:6], slab[:, 6:7], slab[:, 7:10], slab[:, 10:14]
-        color, _, depth, alpha, radii = RZ.rasterize_views(my_sets, m, o, colors_precomp=c, scales=s, rotations=r)
+        color, _, depth, alpha, radii = RZ.rasterize_views(my_sets, m, o, colors_precomp=c, scales=s, rotations=r,
+                                                           capacity=cap_e2e, state_out=states)
+        del states[:-1]
         loss = (color - tgt.float() * (1.0 / 255.0)).abs().mean()
         loss.backward()
         D.allreduce_grads(slab.grad)
@@ -275,6 +290,8 @@ def run_e2e(args, res, world, rank):
     e1.record()
     barrier(world)
     ms = max_over_ranks(e0.elapsed_time(e1), world)
+    if states and cap_e2e is not None:
+        assert not RZ.read_counters(states[-1])[1], "instance capacity exceeded inside the e2e region"
     mpix = args.views * IMG_W * IMG_H * n / (ms * 1e-3) / 1e6
     return {"value": round(mpix, 2), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
             "steps": n, "ms_per_step": round(ms / n, 3), "loss": float(loss_host.item())}

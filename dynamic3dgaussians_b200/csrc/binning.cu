@@ -78,12 +78,20 @@ block_sums_scan_kernel(uint32_t nblocks, uint32_t* __restrict__ block_sums, uint
 
 // Emits the (view*T + tile, Gaussian) pairs of every visible (view, Gaussian) in depth order.
 // Row-major tile order inside a Gaussian (y outer, x inner) as duplicateWithKeys, rasterizer_impl.cu:98-109.
+// The reference (and the first version of this kernel) lets one thread write all instances of its Gaussian, so the
+// lanes of a warp write to addresses `tiles_touched` apart: every store is its own 32-byte sector.  Here a CTA first
+// scans its 2048 slots into shared memory, then walks its OUTPUT range with one thread per instance (binary search
+// of the owning slot), so stores are fully coalesced.
 __global__ void __launch_bounds__(SCAN_BLOCK)
 emit_instances_kernel(uint32_t VP, int P, int tiles_x, int tiles_y, const uint32_t* __restrict__ sorted_g,
                       const uint32_t* __restrict__ tiles_touched, const uint32_t* __restrict__ block_sums,
                       const float2* __restrict__ means2D, const int32_t* __restrict__ radii, uint32_t capacity,
                       uint32_t* __restrict__ ikeys, uint32_t* __restrict__ ivals, uint32_t* __restrict__ counters) {
     __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
+    __shared__ uint32_t s_off[SCAN_TILE + 1];     // exclusive offset of every slot inside this CTA's output range
+    __shared__ uint32_t s_key0[SCAN_TILE];        // key of the slot's first tile: view*T + min.y*tiles_x + min.x
+    __shared__ uint32_t s_g[SCAN_TILE];           // Gaussian index
+    __shared__ uint16_t s_w[SCAN_TILE];           // rect width in tiles
     const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
     uint32_t cnt[SCAN_ITEMS], gidx[SCAN_ITEMS];
     uint32_t sum = 0;
@@ -93,28 +101,45 @@ emit_instances_kernel(uint32_t VP, int P, int tiles_x, int tiles_y, const uint32
         sum += cnt[k];
     }
     uint32_t total;
-    uint32_t off = block_sums[blockIdx.x] + block_exclusive_scan_256(sum, s_warp, total);
+    uint32_t off = block_exclusive_scan_256(sum, s_warp, total);
     const uint32_t T = (uint32_t)tiles_x * (uint32_t)tiles_y;
-    bool overflow = false;
-#pragma unroll 1
+#pragma unroll
     for (int k = 0; k < SCAN_ITEMS; ++k) {
-        if (cnt[k] == 0) continue;
-        const uint32_t gi = gidx[k];
-        const uint32_t view = gi / (uint32_t)P;
-        const uint32_t g = gi - view * (uint32_t)P;
-        uint2 mn, mx;
-        tile_rect(means2D[gi], radii[gi], tiles_x, tiles_y, mn, mx);
-        const uint32_t key_base = view * T;
-        for (uint32_t ty = mn.y; ty < mx.y; ++ty) {
-            for (uint32_t tx = mn.x; tx < mx.x; ++tx) {
-                if (off < capacity) {
-                    ikeys[off] = key_base + ty * (uint32_t)tiles_x + tx;
-                    ivals[off] = g;
-                } else {
-                    overflow = true;
-                }
-                ++off;
-            }
+        const int slot = threadIdx.x * SCAN_ITEMS + k;
+        s_off[slot] = off;
+        off += cnt[k];
+        if (cnt[k] != 0) {
+            const uint32_t gi = gidx[k];
+            const uint32_t view = gi / (uint32_t)P;
+            uint2 mn, mx;
+            tile_rect(means2D[gi], radii[gi], tiles_x, tiles_y, mn, mx);
+            s_key0[slot] = view * T + mn.y * (uint32_t)tiles_x + mn.x;
+            s_g[slot] = gi - view * (uint32_t)P;
+            s_w[slot] = (uint16_t)(mx.x - mn.x);
+        }
+    }
+    if (threadIdx.x == 0) s_off[SCAN_TILE] = total;
+    __syncthreads();
+    const uint32_t out0 = block_sums[blockIdx.x];
+    bool overflow = false;
+    for (uint32_t o = threadIdx.x; o < total; o += SCAN_BLOCK) {
+        // last slot with s_off <= o (empty slots share their successor's offset and are skipped by construction)
+        uint32_t lo = 0, hi = SCAN_TILE;
+#pragma unroll
+        for (int step = 0; step < 11; ++step) {           // SCAN_TILE == 2^11
+            const uint32_t mid = (lo + hi) >> 1;
+            if (s_off[mid] <= o) lo = mid; else hi = mid;
+        }
+        const uint32_t l = o - s_off[lo];
+        const uint32_t w = s_w[lo];
+        const uint32_t ty = l / w;
+        const uint32_t key = s_key0[lo] + ty * (uint32_t)tiles_x + (l - ty * w);
+        const uint32_t dst = out0 + o;
+        if (dst < capacity) {
+            ikeys[dst] = key;
+            ivals[dst] = s_g[lo];
+        } else {
+            overflow = true;
         }
     }
     if (overflow) counters[CNT_OVERFLOW] = 1;
@@ -143,8 +168,14 @@ tile_ranges_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, con
 // Gathers the per-instance records the blend kernels stream with TMA bulk copies:
 //   A = (mean.x, mean.y, conic.x, conic.y)   B = (conic.z, opacity, depth, skip threshold [blend_skip_threshold])
 //   C = (r, g, b, bits(view*P + g))          D = (extra colour r, g, b, 0)   [channels == 6]
+// Four instances per thread, all loads of a stage issued before the first use: the kernel is bound by the latency of
+// the key -> geometry -> store chain, so what matters is bytes in flight per thread.  key / T is a multiply-high by a
+// host-computed reciprocal (exact for key < 2^31).
+constexpr int GATHER_ITEMS = 4;
+
 __global__ void __launch_bounds__(256)
-gather_records_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, int P, uint32_t T, int channels,
+gather_records_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, int P, uint32_t T, uint32_t T_magic,
+                      int T_shift, int channels,
                       const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
                       const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
                       const float* __restrict__ depths, const float* __restrict__ colors_precomp,
@@ -152,20 +183,46 @@ gather_records_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, 
                       float4* __restrict__ recA, float4* __restrict__ recB, float4* __restrict__ recC,
                       float4* __restrict__ recD) {
     const uint32_t n = min(counters[CNT_RENDERED], capacity);
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t view = keys[i] / T;
-    const uint32_t g = vals[i];
-    const uint32_t gi = view * (uint32_t)P + g;
-    const float2 m = means2D[gi];
-    const float4 co = conic_opacity[gi];
-    recA[i] = make_float4(m.x, m.y, co.x, co.y);
-    recB[i] = make_float4(co.z, co.w, depths[gi], blend_skip_threshold(co.w));
-    const float* c = colors_precomp ? colors_precomp + 3 * (size_t)g : rgb_sh + 3 * (size_t)gi;
-    recC[i] = make_float4(c[0], c[1], c[2], __uint_as_float(gi));
+    const uint32_t i0 = blockIdx.x * (256 * GATHER_ITEMS) + threadIdx.x;
+    if (i0 >= n) return;
+    uint32_t g[GATHER_ITEMS], gi[GATHER_ITEMS];
+    bool ok[GATHER_ITEMS];
+#pragma unroll
+    for (int k = 0; k < GATHER_ITEMS; ++k) {
+        const uint32_t i = i0 + k * 256;
+        ok[k] = i < n;
+        const uint32_t key = ok[k] ? keys[i] : 0u;
+        g[k] = ok[k] ? vals[i] : 0u;
+        const uint32_t view = T == 1u ? key : (__umulhi(key, T_magic) >> T_shift);
+        gi[k] = view * (uint32_t)P + g[k];
+    }
+    float2 m[GATHER_ITEMS];
+    float4 co[GATHER_ITEMS];
+    float dep[GATHER_ITEMS];
+    float c[GATHER_ITEMS][3];
+#pragma unroll
+    for (int k = 0; k < GATHER_ITEMS; ++k) {
+        m[k] = means2D[gi[k]];
+        co[k] = conic_opacity[gi[k]];
+        dep[k] = depths[gi[k]];
+        const float* cp = colors_precomp ? colors_precomp + 3 * (size_t)g[k] : rgb_sh + 3 * (size_t)gi[k];
+        c[k][0] = cp[0]; c[k][1] = cp[1]; c[k][2] = cp[2];
+    }
+#pragma unroll
+    for (int k = 0; k < GATHER_ITEMS; ++k) {
+        if (!ok[k]) continue;
+        const uint32_t i = i0 + k * 256;
+        recA[i] = make_float4(m[k].x, m[k].y, co[k].x, co[k].y);
+        recB[i] = make_float4(co[k].z, co[k].w, dep[k], blend_skip_threshold(co[k].w));
+        recC[i] = make_float4(c[k][0], c[k][1], c[k][2], __uint_as_float(gi[k]));
+    }
     if (channels > 3) {
-        const float* e = extra_colors + 3 * (size_t)g;
-        recD[i] = make_float4(e[0], e[1], e[2], 0.0f);
+#pragma unroll
+        for (int k = 0; k < GATHER_ITEMS; ++k) {
+            if (!ok[k]) continue;
+            const float* e = extra_colors + 3 * (size_t)g[k];
+            recD[i0 + k * 256] = make_float4(e[0], e[1], e[2], 0.0f);
+        }
     }
 }
 
@@ -259,8 +316,14 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     GSR_LAUNCH_CHECK();
     stage_end(ST_RANGES, s);
     StageScope sc(ST_GATHER, s);
-    gather_records_kernel<<<gblocks, 256, 0, s>>>(
-        counters, cap, P, T, channels, skeys, svals, at<float2>(gws, L.means2D), at<float4>(gws, L.conic_opacity),
+    // floor(key / T) == umulhi(key, magic) >> shift for every key < 2^31 (V*T < 2^31 is checked at the ABI)
+    int lg = 1;                                   // T == 1 is special-cased in the kernel (magic would need 33 bits)
+    while ((1u << lg) < T) ++lg;
+    const int sh = 31 + lg;
+    const uint32_t magic = (uint32_t)((((uint64_t)1 << sh) + T - 1) / T);
+    const uint32_t rblocks = (cap + 256 * GATHER_ITEMS - 1) / (256 * GATHER_ITEMS);
+    gather_records_kernel<<<rblocks, 256, 0, s>>>(
+        counters, cap, P, T, magic, sh - 32, channels, skeys, svals, at<float2>(gws, L.means2D), at<float4>(gws, L.conic_opacity),
         at<float>(gws, L.depths), colors_precomp, sh_coeffs > 0 ? at<float>(gws, L.rgb) : nullptr, extra_colors,
         at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC),
         channels > 3 ? at<float4>(bws, L.recD) : nullptr);

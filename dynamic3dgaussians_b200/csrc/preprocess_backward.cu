@@ -160,8 +160,15 @@ preprocess_backward_kernel(const CamDev* __restrict__ cams, int V, int P, int sh
         // ---- conic -> 2D covariance (a, b, c) ----
         const float a = ci.a, b = ci.b, c = ci.c;
         const float det = a * c - b * b;
-        const float dA = rec[GR_CA], dB = rec[GR_CB], dC = rec[GR_CC];
-        const float d2 = 1.0f / (det * det);
+        // the blend backward hands over raw moments (S1 = sum a d, S2 = sum a d d^T, a = opacity G dL/dalpha):
+        //   dL/dconic = (-S2xx/2, -S2xy, -S2yy/2)   [the true d/d(conic.y), no 0.5]         backward.cu:644-646
+        //   dL/dmean2D = -conic S1, scaled to the reference's NDC units (0.5 W, 0.5 H)         backward.cu:520-521,640-641
+        const float dA = -0.5f * rec[GR_CA], dB = -rec[GR_CB], dC = -0.5f * rec[GR_CC];
+        const float idet = 1.0f / det;
+        const float conA = c * idet, conB = -b * idet, conC = a * idet;
+        const float gx = -0.5f * (float)cam.width * (conA * rec[GR_MX] + conB * rec[GR_MY]);
+        const float gy = -0.5f * (float)cam.height * (conC * rec[GR_MY] + conB * rec[GR_MX]);
+        const float d2 = idet * idet;
         const float da = d2 * (-c * c * dA + b * c * dB - b * b * dC);
         const float dc = d2 * (-a * a * dC + a * b * dB - b * b * dA);
         const float db = d2 * (2.f * b * c * dA - (det + 2.f * b * b) * dB + 2.f * a * b * dC);
@@ -215,7 +222,6 @@ preprocess_backward_kernel(const CamDev* __restrict__ cams, int V, int P, int sh
         const float hw = Pm[3] * x + Pm[7] * y + Pm[11] * z + Pm[15];
         const float mw = 1.0f / (hw + 0.0000001f);
         const float mul1 = hx * mw * mw, mul2 = hy * mw * mw;
-        const float gx = rec[GR_MX], gy = rec[GR_MY];
         dmean[0] += (Pm[0] * mw - Pm[3] * mul1) * gx + (Pm[1] * mw - Pm[3] * mul2) * gy;
         dmean[1] += (Pm[4] * mw - Pm[7] * mul1) * gx + (Pm[5] * mw - Pm[7] * mul2) * gy;
         dmean[2] += (Pm[8] * mw - Pm[11] * mul1) * gx + (Pm[9] * mw - Pm[11] * mul2) * gy;

@@ -73,7 +73,7 @@ __global__ void __launch_bounds__(RADIX) radix_scan_hist_kernel(uint32_t* __rest
 }
 
 template <typename KeyT>
-__global__ void __launch_bounds__(SORT_THREADS)
+__global__ void __launch_bounds__(SORT_THREADS, 4)
 onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                      const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                      uint32_t n_max, const uint32_t* __restrict__ n_dev, int shift, uint32_t digit_mask,
@@ -103,17 +103,15 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     const uint32_t base = (uint32_t)base64;
     const uint32_t valid_count = min((uint32_t)TILE, n - base);
 
-    // ---- load (warp-striped: element e = warp*32*ITEMS + i*32 + lane) ----
+    // ---- load keys (warp-striped: element e = warp*32*ITEMS + i*32 + lane); values are loaded only after the keys
+    //      have left the registers (two-phase scatter), which keeps the kernel at <= 64 registers = 4 CTAs / SM ----
     KeyT key[ITEMS];
-    uint32_t val[ITEMS];
     uint32_t rank[ITEMS];
     const uint32_t e0 = warp * 32 * ITEMS + lane;
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) {
         const uint32_t e = e0 + i * 32;
-        const bool valid = e < valid_count;
-        key[i] = valid ? keys_in[base + e] : (KeyT)0;
-        val[i] = valid ? vals_in[base + e] : 0u;
+        key[i] = e < valid_count ? keys_in[base + e] : (KeyT)0;
     }
 
     // ---- stable in-warp ranking, one item row at a time ----
@@ -178,16 +176,12 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     }
     __syncthreads();
 
-    // ---- reorder through shared memory so that global writes are runs of equal digits ----
+    // ---- phase 1: keys through shared memory so that global writes are runs of equal digits ----
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) {
-        const bool valid = (e0 + i * 32) < valid_count;
-        if (valid) {
-            const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
-            const uint32_t pos = s_block_excl[d] + s_warp_hist[warp][d] + rank[i];
-            s_keys[pos] = key[i];
-            s_vals[pos] = val[i];
-        }
+        const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
+        rank[i] += s_block_excl[d] + s_warp_hist[warp][d];      // rank[] becomes the tile-local sorted position
+        if ((e0 + i * 32) < valid_count) s_keys[rank[i]] = key[i];
     }
     __syncthreads();
 #pragma unroll
@@ -196,9 +190,28 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
         if (sidx < valid_count) {
             const KeyT kk = s_keys[sidx];
             const uint32_t d = (uint32_t)(kk >> shift) & digit_mask;
-            const uint32_t g = s_glob_base[d] + sidx;
-            keys_out[g] = kk;
-            vals_out[g] = s_vals[sidx];
+            keys_out[s_glob_base[d] + sidx] = kk;
+        }
+    }
+    // ---- phase 2: values follow the same permutation (digits are re-read from the staged keys) ----
+    {
+        uint32_t val[ITEMS];
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const uint32_t e = e0 + i * 32;
+            val[i] = e < valid_count ? vals_in[base + e] : 0u;
+        }
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+            if ((e0 + i * 32) < valid_count) s_vals[rank[i]] = val[i];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) {
+        const uint32_t sidx = tid + k * SORT_THREADS;
+        if (sidx < valid_count) {
+            const uint32_t d = (uint32_t)(s_keys[sidx] >> shift) & digit_mask;
+            vals_out[s_glob_base[d] + sidx] = s_vals[sidx];
         }
     }
 }

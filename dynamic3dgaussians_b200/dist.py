@@ -55,9 +55,11 @@ def allreduce_grads(slab: torch.Tensor, group=None, async_op: bool = False):
     return dist.all_reduce(slab, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
 
 
-def sharded_step(settings, my_views: Sequence[int], params: dict, cotangents: dict, group=None):
+def sharded_step(settings, my_views: Sequence[int], params: dict, cotangents: dict, group=None,
+                 capacity: Optional[int] = None):
     """forward + backward of this rank's views and the all-reduce.  params: means3D, opacities, colors_precomp, scales,
     rotations (replicated).  cotangents: dict of [V_total, C, H, W] tensors or None for color / depth / alpha.
+    `capacity`: instance capacity of the binning workspace (None = read the count back, one host sync per step).
     Returns (outputs of the local views, gradient slab [P,14] summed over ALL views)."""
     from . import rasterizer as RZ
     P = params["means3D"].shape[0]
@@ -65,7 +67,7 @@ def sharded_step(settings, my_views: Sequence[int], params: dict, cotangents: di
     if my_views:
         sets = [settings[v] for v in my_views]
         out = RZ.forward_views(sets, params["means3D"], params["opacities"], params["colors_precomp"],
-                               params["scales"], params["rotations"])
+                               params["scales"], params["rotations"], capacity=capacity)
         sel = lambda t: None if t is None else t[my_views].contiguous()
         g = RZ.backward_views(out[5], params["means3D"], params["opacities"], params["colors_precomp"],
                               params["scales"], params["rotations"], None, None, None, sel(cotangents.get("color")),

@@ -254,11 +254,13 @@ class _RasterizeViews(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, extra_colors, opacities, scales, rotations, cov3Ds_precomp,
-                settings, label, bg_extra):
+                settings, label, bg_extra, capacity, state_out):
         color, extra, depth, alpha, radii, st = forward_views(
             settings, means3D, opacities, _opt(colors_precomp), _opt(scales), _opt(rotations), _opt(cov3Ds_precomp),
-            _opt(sh), _opt(extra_colors), bg_extra)
+            _opt(sh), _opt(extra_colors), bg_extra, capacity=capacity)
         ctx.state = st
+        if state_out is not None:
+            state_out.append(st)
         ctx.has = [_opt(t) is not None for t in (sh, colors_precomp, extra_colors, scales, rotations, cov3Ds_precomp)]
         ctx.means2D_shape = None if means2D is None else tuple(means2D.shape)
         ctx.label = label if torch.is_tensor(label) else None
@@ -286,17 +288,21 @@ class _RasterizeViews(torch.autograd.Function):
             g_means2D = g_means2D.reshape(ctx.means2D_shape)
         g_op = g["opacity"].reshape(opacities.shape)
         return (g["means3D"], g_means2D, g["sh"], g["colors"], g["extra"], g_op, g["scales"], g["rotations"],
-                g["cov3D"], None, None, None)
+                g["cov3D"], None, None, None, None, None)
 
 
 def rasterize_views(settings: Sequence[GaussianRasterizationSettings], means3D, opacities, means2D=None, shs=None,
                     colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None, extra_colors=None,
-                    label=None, bg_extra=None):
+                    label=None, bg_extra=None, capacity: Optional[int] = None, state_out: Optional[list] = None):
     """Renders all `settings` (V cameras of equal resolution) in one batch.
 
     Returns (color [V,3,H,W], extra [V,3,H,W] or None, depth [V,1,H,W], alpha [V,1,H,W], radii [V,P]).
     `extra_colors` ([P,3], e.g. the fg/bg segmentation colours of REF/train.py:100,247-249) are blended in the same
     pass.  Gradients of the per-Gaussian inputs are summed over the views.
+
+    `capacity` (instances the binning workspace is sized for) removes the reference's one host sync per call
+    (rasterizer_impl.cu:287): pass e.g. 1.1x the previous step's count; append-only `state_out` receives the
+    RasterState, whose `read_counters` tells afterwards whether the capacity was exceeded (surplus instances dropped).
     """
     if (shs is None) == (colors_precomp is None):
         raise Exception('Please provide excatly one of either SHs or precomputed colors!')
@@ -308,7 +314,7 @@ def rasterize_views(settings: Sequence[GaussianRasterizationSettings], means3D, 
         means3D, means2D, e if shs is None else shs, e if colors_precomp is None else colors_precomp,
         e if extra_colors is None else extra_colors, opacities, e if scales is None else scales,
         e if rotations is None else rotations, e if cov3D_precomp is None else cov3D_precomp, list(settings), label,
-        bg_extra)
+        bg_extra, capacity, state_out)
     return color, (extra if extra.numel() else None), depth, alpha, radii
 
 
