@@ -409,7 +409,7 @@ def main():
         L = RZ.workspace_layout(P, max(Vl, 1), IMG_W, IMG_H, 3, 0, max(R, 1))
         work = {
             "blend_backward": ("fp32", 80.0 * pairs), "blend_forward": ("fp32", 27.0 * pairs),
-            "tile_sort": ("hbm", (4.0 + 16.0 * L.tile_passes) * R), "depth_sort": ("hbm", (8.0 + 24.0 * L.depth_passes) * Vl * P),
+            "tile_sort": ("hbm", (4.0 + 16.0 * L.tile_passes) * R), "depth_sort": ("hbm", (4.0 + 16.0 * L.depth_passes) * Vl * P),
             "preprocess": ("hbm", (44.0 + 48.0 * Vl) * P), "gather_records": ("hbm", (8.0 + 40.0 + 48.0) * R),
             "emit_instances": ("hbm", 20.0 * Vl * P + 8.0 * R), "tile_ranges": ("hbm", 4.0 * R),
             "grad_zero": ("hbm", 64.0 * Vl * P), "preprocess_backward": ("hbm", (44.0 + 56.0) * P + 68.0 * Vl * P),

@@ -160,13 +160,13 @@ int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels,
                                cov3D_precomp, sh, geom_ws, L, radii, s);
     }
     if (rc) return rc;
-    const int view_bits = V > 1 ? ceil_log2((uint32_t)V) : 0;
     {
+        // every view's Gaussians by depth: V segments of P (depth bits, Gaussian index) pairs, 4 passes of 32-bit keys
         StageScope sc(ST_DEPTH_SORT, s);
-        rc = radix_sort_pairs<uint64_t>(at<uint64_t>(geom_ws, L.dkeys0), at<uint64_t>(geom_ws, L.dkeys1),
-                                        at<uint32_t>(geom_ws, L.dvals0), at<uint32_t>(geom_ws, L.dvals1),
-                                        (int64_t)V * P, nullptr, 0, 32 + view_bits, at<uint32_t>(geom_ws, L.dhist),
-                                        at<uint32_t>(geom_ws, L.dlookback), counters + CNT_DEPTH_TILE, s);
+        rc = radix_sort_pairs<uint32_t>(at<uint32_t>(geom_ws, L.dkeys0), at<uint32_t>(geom_ws, L.dkeys1),
+                                        at<uint32_t>(geom_ws, L.dvals0), at<uint32_t>(geom_ws, L.dvals1), P, nullptr,
+                                        0, 32, at<uint32_t>(geom_ws, L.dhist), at<uint32_t>(geom_ws, L.dlookback),
+                                        at<uint32_t>(geom_ws, L.dcounters), s, V, false);
     }
     if (rc) return rc;
     {

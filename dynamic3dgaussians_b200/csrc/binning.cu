@@ -6,12 +6,14 @@
 // (sort of P entries per view), so instances are emitted in that order with a 32-bit (view*T + tile) key and a stable
 // sort on the tile bits alone produces exactly the reference's order: (tile, depth bits, Gaussian index).
 #include "geom_math.cuh"
+#include "radix_rank.cuh"
 
 namespace gsr {
 
 namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
+constexpr int EMIT_HIST_PASSES = 2;      // tile sorts of up to 16 key bits get their histograms from the emit kernel
 
 __device__ __forceinline__ uint32_t block_exclusive_scan_256(uint32_t v, uint32_t* s_warp /*[8]*/, uint32_t& total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -86,8 +88,10 @@ __global__ void __launch_bounds__(SCAN_BLOCK)
 emit_instances_kernel(uint32_t VP, int P, int tiles_x, int tiles_y, const uint32_t* __restrict__ sorted_g,
                       const uint32_t* __restrict__ tiles_touched, const uint32_t* __restrict__ block_sums,
                       const float2* __restrict__ means2D, const int32_t* __restrict__ radii, uint32_t capacity,
-                      uint32_t* __restrict__ ikeys, uint32_t* __restrict__ ivals, uint32_t* __restrict__ counters) {
+                      uint32_t* __restrict__ ikeys, uint32_t* __restrict__ ivals, uint32_t* __restrict__ counters,
+                      int hist_passes, int tile_bits, uint32_t* __restrict__ sort_hist) {
     __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
+    __shared__ uint32_t s_hist[SCAN_BLOCK / 32][EMIT_HIST_PASSES][RADIX];   // warp-private digit histograms of the keys
     __shared__ uint32_t s_off[SCAN_TILE + 1];     // exclusive offset of every slot inside this CTA's output range
     __shared__ uint32_t s_key0[SCAN_TILE];        // key of the slot's first tile: view*T + min.y*tiles_x + min.x
     __shared__ uint32_t s_g[SCAN_TILE];           // Gaussian index
@@ -119,30 +123,59 @@ emit_instances_kernel(uint32_t VP, int P, int tiles_x, int tiles_y, const uint32
         }
     }
     if (threadIdx.x == 0) s_off[SCAN_TILE] = total;
+    if (hist_passes > 0)
+        for (int i = threadIdx.x; i < (SCAN_BLOCK / 32) * EMIT_HIST_PASSES * RADIX; i += SCAN_BLOCK) (&s_hist[0][0][0])[i] = 0;
     __syncthreads();
     const uint32_t out0 = block_sums[blockIdx.x];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     bool overflow = false;
-    for (uint32_t o = threadIdx.x; o < total; o += SCAN_BLOCK) {
-        // last slot with s_off <= o (empty slots share their successor's offset and are skipped by construction)
-        uint32_t lo = 0, hi = SCAN_TILE;
+    for (uint32_t o0 = 0; o0 < total; o0 += SCAN_BLOCK) {     // warp-uniform trip count (the histogram uses ballots)
+        const uint32_t o = o0 + threadIdx.x;
+        bool stored = false;
+        uint32_t key = 0;
+        if (o < total) {
+            // last slot with s_off <= o (empty slots share their successor's offset and are skipped by construction)
+            uint32_t lo = 0, hi = SCAN_TILE;
 #pragma unroll
-        for (int step = 0; step < 11; ++step) {           // SCAN_TILE == 2^11
-            const uint32_t mid = (lo + hi) >> 1;
-            if (s_off[mid] <= o) lo = mid; else hi = mid;
+            for (int step = 0; step < 11; ++step) {           // SCAN_TILE == 2^11
+                const uint32_t mid = (lo + hi) >> 1;
+                if (s_off[mid] <= o) lo = mid; else hi = mid;
+            }
+            const uint32_t l = o - s_off[lo];
+            const uint32_t w = s_w[lo];
+            const uint32_t ty = l / w;
+            key = s_key0[lo] + ty * (uint32_t)tiles_x + (l - ty * w);
+            const uint32_t dst = out0 + o;
+            if (dst < capacity) {
+                ikeys[dst] = key;
+                ivals[dst] = s_g[lo];
+                stored = true;
+            } else {
+                overflow = true;
+            }
         }
-        const uint32_t l = o - s_off[lo];
-        const uint32_t w = s_w[lo];
-        const uint32_t ty = l / w;
-        const uint32_t key = s_key0[lo] + ty * (uint32_t)tiles_x + (l - ty * w);
-        const uint32_t dst = out0 + o;
-        if (dst < capacity) {
-            ikeys[dst] = key;
-            ivals[dst] = s_g[lo];
-        } else {
-            overflow = true;
+        // the tile sort's digit histograms, taken while the keys are in registers (saves a pass over the keys)
+#pragma unroll
+        for (int p = 0; p < EMIT_HIST_PASSES; ++p) {
+            if (p < hist_passes) {
+                const int shift = p * RADIX_BITS;
+                const int bits = min(RADIX_BITS, tile_bits - shift);
+                uint32_t peers;
+                warp_hist_add(s_hist[warp][p], (key >> shift) & ((1u << bits) - 1u), stored, lane, peers);
+            }
         }
     }
     if (overflow) counters[CNT_OVERFLOW] = 1;
+    if (hist_passes > 0) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < hist_passes * RADIX; i += SCAN_BLOCK) {
+            const int p = i / RADIX, d = i - p * RADIX;
+            uint32_t c = 0;
+#pragma unroll
+            for (int w = 0; w < SCAN_BLOCK / 32; ++w) c += s_hist[w][p][d];
+            if (c) atomicAdd(&sort_hist[i], c);
+        }
+    }
 }
 
 // identifyTileRanges, rasterizer_impl.cu:116-138, on the 32-bit (view*T + tile) keys
@@ -168,62 +201,67 @@ tile_ranges_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, con
 // Gathers the per-instance records the blend kernels stream with TMA bulk copies:
 //   A = (mean.x, mean.y, conic.x, conic.y)   B = (conic.z, opacity, depth, skip threshold [blend_skip_threshold])
 //   C = (r, g, b, bits(view*P + g))          D = (extra colour r, g, b, 0)   [channels == 6]
-// Four instances per thread, all loads of a stage issued before the first use: the kernel is bound by the latency of
-// the key -> geometry -> store chain, so what matters is bytes in flight per thread.  key / T is a multiply-high by a
-// host-computed reciprocal (exact for key < 2^31).
+// Two threads per instance: the per-(view, Gaussian) geometry is already stored as the 32-byte pair (recA | recB) by
+// the preprocess kernel, so the even thread moves the first 16 bytes and the odd thread the second 16 bytes of ONE
+// 32-byte sector; colours come from float4-packed per-Gaussian arrays.  A warp instruction therefore touches 16 sectors
+// for 16 instances.  (The first version read five separate arrays with 4/8/12/16-byte gathers: six divergent load
+// instructions = ~190 L1 tag cycles per 32 instances, which -- not DRAM -- bounded the kernel at 0.94 ms.)
+// key / T is a multiply-high by a host-computed reciprocal (exact for key < 2^31).
 constexpr int GATHER_ITEMS = 4;
 
 __global__ void __launch_bounds__(256)
 gather_records_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, int P, uint32_t T, uint32_t T_magic,
                       int T_shift, int channels,
                       const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
-                      const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
-                      const float* __restrict__ depths, const float* __restrict__ colors_precomp,
-                      const float* __restrict__ rgb_sh, const float* __restrict__ extra_colors,
+                      const float4* __restrict__ geomrec, const float4* __restrict__ col4,
+                      const float4* __restrict__ rgb_sh4, const float4* __restrict__ ext4,
                       float4* __restrict__ recA, float4* __restrict__ recB, float4* __restrict__ recC,
                       float4* __restrict__ recD) {
     const uint32_t n = min(counters[CNT_RENDERED], capacity);
-    const uint32_t i0 = blockIdx.x * (256 * GATHER_ITEMS) + threadIdx.x;
+    const uint32_t half = threadIdx.x & 1u;
+    const uint32_t i0 = blockIdx.x * (128 * GATHER_ITEMS) + (threadIdx.x >> 1);
     if (i0 >= n) return;
     uint32_t g[GATHER_ITEMS], gi[GATHER_ITEMS];
     bool ok[GATHER_ITEMS];
 #pragma unroll
     for (int k = 0; k < GATHER_ITEMS; ++k) {
-        const uint32_t i = i0 + k * 256;
+        const uint32_t i = i0 + k * 128;
         ok[k] = i < n;
         const uint32_t key = ok[k] ? keys[i] : 0u;
         g[k] = ok[k] ? vals[i] : 0u;
         const uint32_t view = T == 1u ? key : (__umulhi(key, T_magic) >> T_shift);
         gi[k] = view * (uint32_t)P + g[k];
     }
-    float2 m[GATHER_ITEMS];
-    float4 co[GATHER_ITEMS];
-    float dep[GATHER_ITEMS];
-    float c[GATHER_ITEMS][3];
+    float4 geo[GATHER_ITEMS], col[GATHER_ITEMS];
+    const bool want_col = half == 0u || channels > 3;
 #pragma unroll
     for (int k = 0; k < GATHER_ITEMS; ++k) {
-        m[k] = means2D[gi[k]];
-        co[k] = conic_opacity[gi[k]];
-        dep[k] = depths[gi[k]];
-        const float* cp = colors_precomp ? colors_precomp + 3 * (size_t)g[k] : rgb_sh + 3 * (size_t)gi[k];
-        c[k][0] = cp[0]; c[k][1] = cp[1]; c[k][2] = cp[2];
+        geo[k] = geomrec[2 * (size_t)gi[k] + half];
+        if (want_col)
+            col[k] = half == 0u ? (col4 ? col4[g[k]] : rgb_sh4[gi[k]]) : ext4[g[k]];
     }
+    float4* __restrict__ dst_geo = half == 0u ? recA : recB;
+    float4* __restrict__ dst_col = half == 0u ? recC : recD;
 #pragma unroll
     for (int k = 0; k < GATHER_ITEMS; ++k) {
         if (!ok[k]) continue;
-        const uint32_t i = i0 + k * 256;
-        recA[i] = make_float4(m[k].x, m[k].y, co[k].x, co[k].y);
-        recB[i] = make_float4(co[k].z, co[k].w, dep[k], blend_skip_threshold(co[k].w));
-        recC[i] = make_float4(c[k][0], c[k][1], c[k][2], __uint_as_float(gi[k]));
-    }
-    if (channels > 3) {
-#pragma unroll
-        for (int k = 0; k < GATHER_ITEMS; ++k) {
-            if (!ok[k]) continue;
-            const float* e = extra_colors + 3 * (size_t)g[k];
-            recD[i0 + k * 256] = make_float4(e[0], e[1], e[2], 0.0f);
+        const uint32_t i = i0 + k * 128;
+        dst_geo[i] = geo[k];
+        if (want_col) {
+            if (half == 0u) col[k].w = __uint_as_float(gi[k]);
+            dst_col[i] = col[k];
         }
     }
+}
+
+// float4 packing of the per-Gaussian colours handed to gsr_forward_render ([P][3] AoS in the reference's layout)
+__global__ void __launch_bounds__(256)
+pack_colors_kernel(int P, const float* __restrict__ colors, const float* __restrict__ extra,
+                   float4* __restrict__ col4, float4* __restrict__ ext4) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= P) return;
+    if (colors) col4[g] = make_float4(colors[3 * g], colors[3 * g + 1], colors[3 * g + 2], 0.0f);
+    if (extra) ext4[g] = make_float4(extra[3 * g], extra[3 * g + 1], extra[3 * g + 2], 0.0f);
 }
 
 // ---- export of one view in the reference's format (tests / tools) ----
@@ -294,18 +332,21 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     uint32_t* counters = at<uint32_t>(gws, L.counters);
     const uint32_t nblocks = (VP + SCAN_TILE - 1) / SCAN_TILE;
     const uint32_t* sorted_g = at<uint32_t>(gws, L.sorted_vals_in ? L.dvals1 : L.dvals0);
+    const bool fused_hist = L.tile_passes <= EMIT_HIST_PASSES;
     stage_begin(ST_EMIT, s);
+    if (fused_hist) GSR_CUDA_TRY(cudaMemsetAsync(at<uint32_t>(bws, L.ihist), 0, (size_t)L.tile_passes * RADIX * 4, s));
     emit_instances_kernel<<<nblocks, SCAN_BLOCK, 0, s>>>(
         VP, P, L.tiles_x, L.tiles_y, sorted_g, at<uint32_t>(gws, L.tiles_touched), at<uint32_t>(gws, L.block_sums),
         at<float2>(gws, L.means2D), at<int32_t>(gws, L.radii), cap, at<uint32_t>(bws, L.ikeys0),
-        at<uint32_t>(bws, L.ivals0), counters);
+        at<uint32_t>(bws, L.ivals0), counters, fused_hist ? L.tile_passes : 0, L.tile_bits,
+        at<uint32_t>(bws, L.ihist));
     GSR_LAUNCH_CHECK();
     stage_end(ST_EMIT, s);
     stage_begin(ST_TILE_SORT, s);
     int rc = radix_sort_pairs<uint32_t>(at<uint32_t>(bws, L.ikeys0), at<uint32_t>(bws, L.ikeys1),
                                         at<uint32_t>(bws, L.ivals0), at<uint32_t>(bws, L.ivals1), capacity,
                                         counters + CNT_RENDERED, 0, L.tile_bits, at<uint32_t>(bws, L.ihist),
-                                        at<uint32_t>(bws, L.ilookback), counters + CNT_INST_TILE, s);
+                                        at<uint32_t>(bws, L.ilookback), counters + CNT_INST_TILE, s, 1, fused_hist);
     stage_end(ST_TILE_SORT, s);
     if (rc != GSR_OK) return rc;
     const uint32_t* skeys = at<uint32_t>(bws, L.sorted_keys_in ? L.ikeys1 : L.ikeys0);
@@ -321,11 +362,16 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     while ((1u << lg) < T) ++lg;
     const int sh = 31 + lg;
     const uint32_t magic = (uint32_t)((((uint64_t)1 << sh) + T - 1) / T);
-    const uint32_t rblocks = (cap + 256 * GATHER_ITEMS - 1) / (256 * GATHER_ITEMS);
+    const uint32_t rblocks = (cap + 128 * GATHER_ITEMS - 1) / (128 * GATHER_ITEMS);
+    if (colors_precomp || extra_colors) {
+        pack_colors_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, colors_precomp, extra_colors, at<float4>(gws, L.col4),
+                                                           at<float4>(gws, L.ext4));
+        GSR_LAUNCH_CHECK();
+    }
     gather_records_kernel<<<rblocks, 256, 0, s>>>(
-        counters, cap, P, T, magic, sh - 32, channels, skeys, svals, at<float2>(gws, L.means2D), at<float4>(gws, L.conic_opacity),
-        at<float>(gws, L.depths), colors_precomp, sh_coeffs > 0 ? at<float>(gws, L.rgb) : nullptr, extra_colors,
-        at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC),
+        counters, cap, P, T, magic, sh - 32, channels, skeys, svals, at<float4>(gws, L.geomrec),
+        colors_precomp ? at<float4>(gws, L.col4) : nullptr, sh_coeffs > 0 ? at<float4>(gws, L.rgb) : nullptr,
+        at<float4>(gws, L.ext4), at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC),
         channels > 3 ? at<float4>(bws, L.recD) : nullptr);
     GSR_LAUNCH_CHECK();
     return GSR_OK;

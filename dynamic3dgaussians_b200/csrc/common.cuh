@@ -78,8 +78,7 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     L.tiles_x = tx;
     L.tiles_y = ty;
     L.tile_bits = ceil_log2((uint32_t)VT);
-    const int view_bits = V > 1 ? ceil_log2((uint32_t)V) : 0;
-    L.depth_passes = (32 + view_bits + RADIX_BITS - 1) / RADIX_BITS;
+    L.depth_passes = 32 / RADIX_BITS;         // per-view segmented sort of the 32 depth bits
     L.tile_passes = (L.tile_bits + RADIX_BITS - 1) / RADIX_BITS;
     L.sorted_keys_in = (L.tile_passes & 1);   // which ping-pong buffer holds the result of the instance sort
     L.sorted_vals_in = (L.depth_passes & 1);  // ... and of the depth sort
@@ -91,17 +90,20 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     L.depths = take(VP * 4);
     L.radii = take(VP * 4);
     L.means2D = take(VP * 8);
-    L.conic_opacity = take(VP * 16);
+    L.geomrec = take(VP * 32);            // (mean.x, mean.y, conic.a, conic.b | conic.c, opacity, depth, skip threshold)
     L.tiles_touched = take(VP * 4);
     L.cov3D = take((size_t)P * 24);
-    L.rgb = take(sh_coeffs > 0 ? VP * 12 : 0);
+    L.rgb = take(sh_coeffs > 0 ? VP * 16 : 0);     // float4 per (view, Gaussian): SH colours
+    L.col4 = take((size_t)P * 16);                 // float4-packed colors_precomp / extra colours (per Gaussian)
+    L.ext4 = take(channels > 3 ? (size_t)P * 16 : 0);
     L.clamped = take(sh_coeffs > 0 ? VP * 3 : 0);
-    L.dkeys0 = take(VP * 8);
-    L.dkeys1 = take(VP * 8);
+    L.dkeys0 = take(VP * 4);
+    L.dkeys1 = take(VP * 4);
     L.dvals0 = take(VP * 4);
     L.dvals1 = take(VP * 4);
-    L.dhist = take((size_t)MAX_PASSES * RADIX * 4);
-    L.dlookback = take((size_t)MAX_PASSES * sort_num_tiles((int64_t)VP, 8) * RADIX * 4);
+    L.dhist = take((size_t)V * MAX_PASSES * RADIX * 4);
+    L.dlookback = take((size_t)MAX_PASSES * V * (sort_num_tiles((int64_t)P, 4) + 1) * RADIX * 4);
+    L.dcounters = take((size_t)MAX_PASSES * V * 4);
     L.block_sums = take(((VP + SCAN_TILE - 1) / SCAN_TILE + 2) * 4);
     L.grad_rec = take(VP * GRAD_REC * 4);
     L.geom_bytes = o;
@@ -166,7 +168,7 @@ int launch_mark_visible(const float* view, int P, const float* means3D, uint8_t*
 template <typename KeyT>
 int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1, int64_t n_max,
                      const uint32_t* n_dev, int begin_bit, int end_bit, uint32_t* hist, uint32_t* lookback,
-                     uint32_t* tile_counters, cudaStream_t s);
+                     uint32_t* tile_counters, cudaStream_t s, int segments = 1, bool hist_ready = false);
 
 int launch_tile_scan(int V, int P, void* geom_ws, const Layout& L, cudaStream_t s);
 int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,

@@ -87,9 +87,9 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
                   const float* __restrict__ cov3D_precomp, const float* __restrict__ sh,
                   int tiles_x, int tiles_y,
                   float* __restrict__ depths, int32_t* __restrict__ radii, float2* __restrict__ means2D,
-                  float4* __restrict__ conic_opacity, uint32_t* __restrict__ tiles_touched,
+                  float4* __restrict__ geomrec, uint32_t* __restrict__ tiles_touched,
                   float* __restrict__ rgb, uint8_t* __restrict__ clamped,
-                  uint64_t* __restrict__ dkeys, uint32_t* __restrict__ dvals, int32_t* __restrict__ radii_out) {
+                  uint32_t* __restrict__ dkeys, uint32_t* __restrict__ dvals, int32_t* __restrict__ radii_out) {
     __shared__ CamDev cam;
     const int v = blockIdx.y;
     {
@@ -146,16 +146,16 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
                     bool cl[3];
                     const float3 c = eval_sh_pinned(cam.sh_degree, sh_coeffs, sh + (size_t)g * sh_coeffs * 3,
                                                     make_float3(x, y, z), cam.campos, cl);
-                    rgb[3 * idx] = c.x;
-                    rgb[3 * idx + 1] = c.y;
-                    rgb[3 * idx + 2] = c.z;
+                    reinterpret_cast<float4*>(rgb)[idx] = make_float4(c.x, c.y, c.z, 0.0f);
                     clamped[3 * idx] = cl[0];
                     clamped[3 * idx + 1] = cl[1];
                     clamped[3 * idx + 2] = cl[2];
                 }
                 depths[idx] = depth;
                 means2D[idx] = pix;
-                conic_opacity[idx] = make_float4(conic_x, conic_y, conic_z, opacities[g]);
+                const float op = opacities[g];
+                geomrec[2 * idx] = make_float4(pix.x, pix.y, conic_x, conic_y);          // the blend kernels' recA
+                geomrec[2 * idx + 1] = make_float4(conic_z, op, depth, blend_skip_threshold(op));   // ... and recB
                 radius = r_i;
                 tiles = area;
                 depth_key = __float_as_uint(depth);
@@ -165,7 +165,7 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
     radii[idx] = radius;
     if (radii_out) radii_out[idx] = radius;
     tiles_touched[idx] = tiles;
-    dkeys[idx] = ((uint64_t)(uint32_t)v << 32) | depth_key;
+    dkeys[idx] = depth_key;                // sorted per view (segmented sort), so the key is the depth alone
     dvals[idx] = (uint32_t)g;
 }
 
@@ -188,8 +188,8 @@ int launch_preprocess(const CamDev* cams, int V, int P, int sh_coeffs, const flo
     preprocess_kernel<<<grid, 256, 0, s>>>(
         cams, P, sh_coeffs, means3D, opacities, scales, rotations, cov3D_precomp, sh, L.tiles_x, L.tiles_y,
         at<float>(ws, L.depths), at<int32_t>(ws, L.radii), at<float2>(ws, L.means2D),
-        at<float4>(ws, L.conic_opacity), at<uint32_t>(ws, L.tiles_touched), at<float>(ws, L.rgb),
-        at<uint8_t>(ws, L.clamped), at<uint64_t>(ws, L.dkeys0), at<uint32_t>(ws, L.dvals0), radii_out);
+        at<float4>(ws, L.geomrec), at<uint32_t>(ws, L.tiles_touched), at<float>(ws, L.rgb),
+        at<uint8_t>(ws, L.clamped), at<uint32_t>(ws, L.dkeys0), at<uint32_t>(ws, L.dvals0), radii_out);
     GSR_LAUNCH_CHECK();
     return GSR_OK;
 }

@@ -9,7 +9,11 @@
 //
 // HBM traffic per pass: read (key,value) once, write once.  The look-back state is one 32-bit word per
 // (tile, digit): 2 flag bits + 30-bit count, so a single volatile load carries flag and value together.
-#include "common.cuh"
+//
+// SEGMENTED mode (segments > 1): `segments` independent arrays of n_max elements each, laid out back to back, are
+// sorted by one set of launches (grid.y = segment).  The rasterizer sorts every view's Gaussians by depth this way
+// with 32-bit keys (4 passes) instead of one (view << 32 | depth) 64-bit sort (5 passes of 12-byte pairs).
+#include "radix_rank.cuh"
 
 namespace gsr {
 
@@ -19,41 +23,57 @@ constexpr uint32_t FLAG_AGG = 1u << 30;     // tile-local count published
 constexpr uint32_t FLAG_INC = 1u << 31;     // inclusive prefix (all tiles <= this one) published
 constexpr uint32_t VALUE_MASK = (1u << 30) - 1u;
 constexpr unsigned FULL = 0xffffffffu;
+constexpr int HIST_PASSES = 4;              // digit passes histogrammed per launch (warp-private bins in smem)
+constexpr int HIST_ITEMS = 16;
 
 __device__ __forceinline__ uint32_t ld_volatile(const uint32_t* p) { return *reinterpret_cast<const volatile uint32_t*>(p); }
 __device__ __forceinline__ void st_volatile(uint32_t* p, uint32_t v) { *reinterpret_cast<volatile uint32_t*>(p) = v; }
 
+// Global digit histograms of passes [p0, p0 + np).  Warp-private bins, no shared-memory atomics (radix_rank.cuh).
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
 radix_histogram_kernel(const KeyT* __restrict__ keys, uint32_t n_max, const uint32_t* __restrict__ n_dev,
-                       int begin_bit, int end_bit, int passes, uint32_t* __restrict__ hist) {
-    __shared__ uint32_t sh[MAX_PASSES * RADIX];
-    for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) sh[i] = 0;
+                       int begin_bit, int end_bit, int p0, int np, int passes_total, uint32_t* __restrict__ hist) {
+    __shared__ uint32_t sh[8][HIST_PASSES][RADIX];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < 8 * HIST_PASSES * RADIX; i += 256) (&sh[0][0][0])[i] = 0;
     __syncthreads();
+    const int seg = blockIdx.y;
+    keys += (size_t)seg * n_max;
+    hist += (size_t)seg * passes_total * RADIX;
     const uint32_t n = n_dev ? min(*n_dev, n_max) : n_max;
-    const uint32_t stride = gridDim.x * blockDim.x;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const KeyT key = keys[i];
+    const uint32_t chunk = 256 * HIST_ITEMS;
+    for (uint32_t base = blockIdx.x * chunk; base < n; base += gridDim.x * chunk) {
+        const uint32_t e0 = base + warp * 32 * HIST_ITEMS + lane;
+        KeyT key[HIST_ITEMS];
 #pragma unroll
-        for (int p = 0; p < MAX_PASSES; ++p) {
-            if (p < passes) {
-                const int shift = begin_bit + p * RADIX_BITS;
-                const int bits = min(RADIX_BITS, end_bit - shift);
-                const uint32_t d = (uint32_t)(key >> shift) & ((1u << bits) - 1u);
-                // warp-aggregate equal digits so that near-constant high digits do not serialise on one bank
-                const unsigned peers = __match_any_sync(__activemask(), d);
-                if ((int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&sh[p * RADIX + d], __popc(peers));
+        for (int i = 0; i < HIST_ITEMS; ++i) key[i] = (e0 + i * 32) < n ? keys[e0 + i * 32] : (KeyT)0;
+#pragma unroll
+        for (int i = 0; i < HIST_ITEMS; ++i) {
+            const bool valid = (e0 + i * 32) < n;
+#pragma unroll
+            for (int p = 0; p < HIST_PASSES; ++p) {
+                if (p < np) {
+                    const int shift = begin_bit + (p0 + p) * RADIX_BITS;
+                    const int bits = min(RADIX_BITS, end_bit - shift);
+                    const uint32_t d = (uint32_t)(key[i] >> shift) & ((1u << bits) - 1u);
+                    uint32_t peers;
+                    warp_hist_add(sh[warp][p], d, valid, lane, peers);
+                }
             }
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) {
-        const uint32_t c = sh[i];
-        if (c) atomicAdd(&hist[i], c);
+    for (int i = tid; i < np * RADIX; i += 256) {
+        const int p = i / RADIX, d = i - p * RADIX;
+        uint32_t c = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) c += sh[w][p][d];
+        if (c) atomicAdd(&hist[(p0 + p) * RADIX + d], c);
     }
 }
 
-// exclusive scan of each pass's 256 bins, in place (one block of 256 threads per pass)
+// exclusive scan of each (segment, pass)'s 256 bins, in place (one block of 256 threads each)
 __global__ void __launch_bounds__(RADIX) radix_scan_hist_kernel(uint32_t* __restrict__ hist) {
     __shared__ uint32_t warp_tot[RADIX / 32];
     uint32_t* h = hist + blockIdx.x * RADIX;
@@ -77,8 +97,8 @@ __global__ void __launch_bounds__(SORT_THREADS, 4)
 onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                      const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                      uint32_t n_max, const uint32_t* __restrict__ n_dev, int shift, uint32_t digit_mask,
-                     const uint32_t* __restrict__ hist_excl, uint32_t* __restrict__ lookback,
-                     uint32_t* __restrict__ tile_counter) {
+                     const uint32_t* __restrict__ hist_excl, size_t hist_seg_stride, uint32_t* __restrict__ lookback,
+                     size_t lookback_seg_stride, uint32_t* __restrict__ tile_counter) {
     constexpr int ITEMS = SortCfg<KeyT>::ITEMS;
     constexpr int TILE = SORT_THREADS * ITEMS;
     constexpr int WARPS = SORT_THREADS / 32;
@@ -90,6 +110,15 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     extern __shared__ __align__(16) unsigned char s_dyn[];
     KeyT* s_keys = reinterpret_cast<KeyT*>(s_dyn);
     uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_dyn + sizeof(KeyT) * TILE);
+
+    const int seg = blockIdx.y;
+    keys_in += (size_t)seg * n_max;
+    keys_out += (size_t)seg * n_max;
+    vals_in += (size_t)seg * n_max;
+    vals_out += (size_t)seg * n_max;
+    hist_excl += (size_t)seg * hist_seg_stride;
+    lookback += (size_t)seg * lookback_seg_stride;
+    tile_counter += seg;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
@@ -120,15 +149,9 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     for (int i = 0; i < ITEMS; ++i) {
         const bool valid = (e0 + i * 32) < valid_count;
         const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
-        const uint32_t dm = valid ? d : (RADIX + lane);         // invalid lanes match nobody
-        const unsigned peers = __match_any_sync(FULL, dm);
-        const int leader = __ffs(peers) - 1;
-        uint32_t prev = 0;
-        if (valid && lane == leader) prev = s_warp_hist[warp][d];
-        prev = __shfl_sync(FULL, prev, leader);
+        uint32_t peers;
+        const uint32_t prev = warp_hist_add(s_warp_hist[warp], d, valid, lane, peers);
         rank[i] = prev + __popc(peers & lt_mask);
-        if (valid && lane == leader) s_warp_hist[warp][d] = prev + __popc(peers);
-        __syncwarp();
     }
     __syncthreads();
 
@@ -221,22 +244,32 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
 template <typename KeyT>
 int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1, int64_t n_max,
                      const uint32_t* n_dev, int begin_bit, int end_bit, uint32_t* hist, uint32_t* lookback,
-                     uint32_t* tile_counters, cudaStream_t s) {
-    if (n_max <= 0 || end_bit <= begin_bit) return GSR_OK;
+                     uint32_t* tile_counters, cudaStream_t s, int segments, bool hist_ready) {
+    if (n_max <= 0 || end_bit <= begin_bit || segments <= 0) return GSR_OK;
     if (n_max >= (int64_t)VALUE_MASK) return GSR_ERR_UNSUPPORTED;
+    if (segments > 1 && n_dev != nullptr) return GSR_ERR_INVALID_ARGUMENT;
+    if (segments > 65535) return GSR_ERR_UNSUPPORTED;
     const int passes = (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS;
     if (passes > MAX_PASSES) return GSR_ERR_INVALID_ARGUMENT;
     constexpr int TILE = SORT_THREADS * SortCfg<KeyT>::ITEMS;
     const int tiles = (int)((n_max + TILE - 1) / TILE);
-    GSR_CUDA_TRY(cudaMemsetAsync(hist, 0, (size_t)passes * RADIX * 4, s));
-    GSR_CUDA_TRY(cudaMemsetAsync(lookback, 0, (size_t)passes * tiles * RADIX * 4, s));
-    GSR_CUDA_TRY(cudaMemsetAsync(tile_counters, 0, (size_t)passes * 4, s));
-    int64_t hb = (n_max + 256 * 16 - 1) / (256 * 16);
-    const int hist_blocks = (int)(hb < 148 * 8 ? hb : 148 * 8);
-    radix_histogram_kernel<KeyT><<<hist_blocks, 256, 0, s>>>(keys0, (uint32_t)n_max, n_dev, begin_bit, end_bit,
-                                                            passes, hist);
-    GSR_LAUNCH_CHECK();
-    radix_scan_hist_kernel<<<passes, RADIX, 0, s>>>(hist);
+    const size_t hist_seg = (size_t)passes * RADIX;
+    const size_t lb_seg = (size_t)tiles * RADIX;
+    if (!hist_ready) GSR_CUDA_TRY(cudaMemsetAsync(hist, 0, (size_t)segments * hist_seg * 4, s));
+    GSR_CUDA_TRY(cudaMemsetAsync(lookback, 0, (size_t)passes * segments * lb_seg * 4, s));
+    GSR_CUDA_TRY(cudaMemsetAsync(tile_counters, 0, (size_t)passes * segments * 4, s));
+    if (!hist_ready) {
+        int64_t hb = (n_max + 256 * HIST_ITEMS - 1) / (256 * HIST_ITEMS);
+        const int64_t cap = (148 * 8 + segments - 1) / segments;
+        const int hist_blocks = (int)(hb < cap ? hb : (cap > 1 ? cap : 1));
+        for (int p0 = 0; p0 < passes; p0 += HIST_PASSES) {
+            const int np = passes - p0 < HIST_PASSES ? passes - p0 : HIST_PASSES;
+            radix_histogram_kernel<KeyT><<<dim3(hist_blocks, segments), 256, 0, s>>>(
+                keys0, (uint32_t)n_max, n_dev, begin_bit, end_bit, p0, np, passes, hist);
+            GSR_LAUNCH_CHECK();
+        }
+    }
+    radix_scan_hist_kernel<<<passes * segments, RADIX, 0, s>>>(hist);
     GSR_LAUNCH_CHECK();
     const size_t dyn = (size_t)TILE * (sizeof(KeyT) + 4);
     for (int p = 0; p < passes; ++p) {
@@ -246,17 +279,17 @@ int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1,
         KeyT* kout = (p & 1) ? keys0 : keys1;
         const uint32_t* vin = (p & 1) ? vals1 : vals0;
         uint32_t* vout = (p & 1) ? vals0 : vals1;
-        onesweep_pass_kernel<KeyT><<<tiles, SORT_THREADS, dyn, s>>>(
-            kin, kout, vin, vout, (uint32_t)n_max, n_dev, shift, (1u << bits) - 1u, hist + p * RADIX,
-            lookback + (size_t)p * tiles * RADIX, tile_counters + p);
+        onesweep_pass_kernel<KeyT><<<dim3(tiles, segments), SORT_THREADS, dyn, s>>>(
+            kin, kout, vin, vout, (uint32_t)n_max, n_dev, shift, (1u << bits) - 1u, hist + p * RADIX, hist_seg,
+            lookback + (size_t)p * segments * lb_seg, lb_seg, tile_counters + (size_t)p * segments);
         GSR_LAUNCH_CHECK();
     }
     return GSR_OK;
 }
 
 template int radix_sort_pairs<uint32_t>(uint32_t*, uint32_t*, uint32_t*, uint32_t*, int64_t, const uint32_t*, int, int,
-                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t);
+                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t, int, bool);
 template int radix_sort_pairs<uint64_t>(uint64_t*, uint64_t*, uint32_t*, uint32_t*, int64_t, const uint32_t*, int, int,
-                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t);
+                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t, int, bool);
 
 }  // namespace gsr

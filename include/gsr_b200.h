@@ -69,8 +69,8 @@ typedef struct GsrWorkspaceSizes {
 /* Offsets (bytes) of the arrays inside the workspaces, for tests / tools that want to look at intermediate state. */
 typedef struct GsrLayout {
     /* geom workspace */
-    size_t cams, counters, depths, radii, means2D, conic_opacity, tiles_touched, cov3D, rgb, clamped;
-    size_t dkeys0, dkeys1, dvals0, dvals1, dhist, dlookback, block_sums, grad_rec;
+    size_t cams, counters, depths, radii, means2D, geomrec, tiles_touched, cov3D, rgb, col4, ext4, clamped;
+    size_t dkeys0, dkeys1, dvals0, dvals1, dhist, dlookback, dcounters, block_sums, grad_rec;
     /* binning workspace */
     size_t ikeys0, ikeys1, ivals0, ivals1, ihist, ilookback, recA, recB, recC, recD;
     /* image workspace */
