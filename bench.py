@@ -179,9 +179,11 @@ def run_ours(args, world, rank, local):
     mine = parts[rank]
 
     cap = [None]
+    slab = D.GradSlab(P, dev)
+    local = [D.select_views(cot, mine)]       # the loss side hands each rank the cotangents of its own views
 
     def step():
-        return D.sharded_step(sets, mine, rv, cot, capacity=cap[0])
+        return D.sharded_step(sets, mine, rv, local[0], capacity=cap[0], slab=slab, local_cotangents=True)
 
     # first pass: per-view instance counts -> cost-aware partition (deterministic on every rank)
     out, _ = step()
@@ -195,6 +197,7 @@ def run_ours(args, world, rank, local):
         dist.all_reduce(costs)
         parts = D.partition_views(costs.tolist(), world)
         mine = parts[rank]
+        local[0] = D.select_views(cot, mine)
     # one synchronising step with the final partition tells the instance count; from then on the binning workspace is
     # sized for 1.05x that count and no step touches the host (overflow is checked after the timed region)
     out, _ = step()
@@ -211,7 +214,7 @@ def run_ours(args, world, rank, local):
     barrier(world)
     e0.record()
     for _ in range(args.steps):
-        out, slab = step()
+        out, _ = step()
     e1.record()
     barrier(world)
     ms = max_over_ranks(e0.elapsed_time(e1), world)
@@ -221,7 +224,7 @@ def run_ours(args, world, rank, local):
     stages = {}
     nrep = 5
     for _ in range(nrep):
-        out, slab = step()
+        out, _ = step()
         torch.cuda.synchronize()
         for k, v in _lib.read_stage_timing().items():
             stages[k] = stages.get(k, 0.0) + v / nrep

@@ -47,6 +47,28 @@ def unpack_grads(slab: torch.Tensor) -> dict:
                 rotations=slab[:, 10:14])
 
 
+class GradSlab:
+    """One flat float32 buffer of 14*P elements holding the per-Gaussian gradients as back-to-back contiguous regions
+    (means3D [P,3] | colours [P,3] | opacity [P,1] | scales [P,3] | rotations [P,4]).  The backward kernels write
+    straight into the regions (rasterizer.backward_views(out=...)), so the single all-reduce needs no packing pass."""
+
+    WIDTHS = dict(means3D=3, colors=3, opacity=1, scales=3, rotations=4)
+
+    def __init__(self, P: int, device):
+        self.P = P
+        self.flat = torch.zeros(P * GRAD_WIDTH, dtype=torch.float32, device=device)
+        self.views = {}
+        o = 0
+        for k in GRAD_KEYS:
+            w = self.WIDTHS[k]
+            self.views[k] = self.flat[o:o + P * w].view(P, w)
+            o += P * w
+
+    def as_rows(self) -> torch.Tensor:
+        """[P,14] copy in the pack_grads() column order (for callers that want one row per Gaussian)."""
+        return torch.cat([self.views[k] for k in GRAD_KEYS], dim=1)
+
+
 def allreduce_grads(slab: torch.Tensor, group=None, async_op: bool = False):
     """Sum of the gradient slab over the ranks (NCCL on GPUs, gloo in the CPU tests)."""
     import torch.distributed as dist
@@ -55,26 +77,35 @@ def allreduce_grads(slab: torch.Tensor, group=None, async_op: bool = False):
     return dist.all_reduce(slab, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
 
 
+def select_views(cotangents: dict, my_views: Sequence[int]) -> dict:
+    """The local views' slices of [V_total, C, H, W] cotangent tensors (contiguous copies; done once per partition)."""
+    idx = list(my_views)
+    return {k: (None if t is None else t[idx].contiguous()) for k, t in cotangents.items()}
+
+
 def sharded_step(settings, my_views: Sequence[int], params: dict, cotangents: dict, group=None,
-                 capacity: Optional[int] = None):
+                 capacity: Optional[int] = None, slab: Optional[GradSlab] = None, local_cotangents: bool = False):
     """forward + backward of this rank's views and the all-reduce.  params: means3D, opacities, colors_precomp, scales,
-    rotations (replicated).  cotangents: dict of [V_total, C, H, W] tensors or None for color / depth / alpha.
+    rotations (replicated).  cotangents: dict of [V_total, C, H, W] tensors or None for color / depth / alpha (or, with
+    local_cotangents=True, already restricted to this rank's views by select_views()).
     `capacity`: instance capacity of the binning workspace (None = read the count back, one host sync per step).
-    Returns (outputs of the local views, gradient slab [P,14] summed over ALL views)."""
+    `slab`: a reusable GradSlab the gradients are written into (allocated when omitted).
+    Returns (outputs of the local views, GradSlab summed over ALL views)."""
     from . import rasterizer as RZ
     P = params["means3D"].shape[0]
     my_views = list(my_views)
+    if slab is None:
+        slab = GradSlab(P, params["means3D"].device)
     if my_views:
         sets = [settings[v] for v in my_views]
         out = RZ.forward_views(sets, params["means3D"], params["opacities"], params["colors_precomp"],
                                params["scales"], params["rotations"], capacity=capacity)
-        sel = lambda t: None if t is None else t[my_views].contiguous()
-        g = RZ.backward_views(out[5], params["means3D"], params["opacities"], params["colors_precomp"],
-                              params["scales"], params["rotations"], None, None, None, sel(cotangents.get("color")),
-                              None, sel(cotangents.get("depth")), sel(cotangents.get("alpha")), want_means2D=False)
-        slab = pack_grads(g, P)
+        cot = cotangents if local_cotangents else select_views(cotangents, my_views)
+        RZ.backward_views(out[5], params["means3D"], params["opacities"], params["colors_precomp"],
+                          params["scales"], params["rotations"], None, None, None, cot.get("color"),
+                          None, cot.get("depth"), cot.get("alpha"), want_means2D=False, out=slab.views)
     else:
         out = None
-        slab = torch.zeros((P, GRAD_WIDTH), dtype=torch.float32, device=params["means3D"].device)
-    allreduce_grads(slab, group)
+        slab.flat.zero_()
+    allreduce_grads(slab.flat, group)
     return out, slab

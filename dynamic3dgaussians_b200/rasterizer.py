@@ -195,8 +195,10 @@ def read_counters(st: RasterState):
 
 
 def backward_views(st: RasterState, means3D, opacities, colors_precomp, scales, rotations, cov3D_precomp, shs,
-                   extra_colors, dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, label=None, want_means2D=True):
-    """Returns dict of gradients summed over the views of the batch (means2D: [V,P,3])."""
+                   extra_colors, dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, label=None, want_means2D=True, out=None):
+    """Returns dict of gradients summed over the views of the batch (means2D: [V,P,3]).  `out` may carry preallocated
+    contiguous float32 tensors for means3D / colors / opacity / scales / rotations (e.g. views into one all-reduce
+    slab, dist.GradSlab); every gradient is written, never accumulated."""
     lib = _lib.load()
     dev = st.geom.device
     V, P = st.V, st.P
@@ -215,14 +217,24 @@ def backward_views(st: RasterState, means3D, opacities, colors_precomp, scales, 
     dL_dextra = cot(dL_dextra, (V, 3, H, W)) if st.channels == 6 else None
     dL_ddepth = cot(dL_ddepth, (V, 1, H, W))
     dL_dalpha = cot(dL_dalpha, (V, 1, H, W))
+    out = out or {}
+
+    def buf(key, shape):
+        t = out.get(key)
+        if t is None:
+            return torch.empty(shape, **f32)
+        if tuple(t.shape) != tuple(shape) or t.dtype != torch.float32 or not t.is_contiguous() or t.device != dev:
+            raise ValueError(f"out[{key!r}] must be a contiguous float32 {tuple(shape)} tensor on {dev}")
+        return t
+
     g = dict(
-        means3D=torch.empty((P, 3), **f32),
+        means3D=buf("means3D", (P, 3)),
         means2D=torch.empty((V, P, 3), **f32) if want_means2D else None,
-        colors=torch.empty((P, 3), **f32) if colors_precomp is not None else None,
+        colors=buf("colors", (P, 3)) if colors_precomp is not None else None,
         extra=torch.empty((P, 3), **f32) if st.channels == 6 else None,
-        opacity=torch.empty((P, 1), **f32),
-        scales=torch.empty((P, 3), **f32) if scales is not None else None,
-        rotations=torch.empty((P, 4), **f32) if rotations is not None else None,
+        opacity=buf("opacity", (P, 1)),
+        scales=buf("scales", (P, 3)) if scales is not None else None,
+        rotations=buf("rotations", (P, 4)) if rotations is not None else None,
         cov3D=torch.empty((P, 6), **f32) if cov3D_precomp is not None else None,
         sh=torch.empty((P, st.sh_coeffs, 3), **f32) if shs is not None else None,
     )

@@ -31,10 +31,10 @@ def main(path):
             if w in col:
                 print(f"  {w:72s} {r[col[w]]} {units[col[w]]}")
         for h, i in col.items():
-            if 'issue_stalled' in h and h.endswith('_per_warp_active.pct'):
+            if h.startswith('smsp__average_warps_issue_stalled_') and h.endswith('_per_issue_active.ratio'):
                 try:
-                    if float(r[i]) > 4:
-                        print(f"    stall {h[len('smsp__average_warps_issue_stalled_'):-len('_per_warp_active.pct')]:40s} {r[i]}")
+                    if float(r[i]) > 0.3:      # warps stalled for this reason per issued instruction
+                        print(f"    stall {h[len('smsp__average_warps_issue_stalled_'):-len('_per_issue_active.ratio')]:28s} {r[i]}")
                 except ValueError:
                     pass
 

@@ -37,6 +37,19 @@ def test_pack_unpack_roundtrip():
         assert torch.equal(u[k], g[k])
 
 
+def test_grad_slab_regions_are_contiguous_views_of_one_buffer():
+    P = 11
+    slab = D.GradSlab(P, "cpu")
+    assert slab.flat.numel() == P * D.GRAD_WIDTH
+    for k in D.GRAD_KEYS:
+        v = slab.views[k]
+        assert v.is_contiguous() and v.shape == (P, D.GradSlab.WIDTHS[k])
+        v.fill_(float(D.GRAD_KEYS.index(k) + 1))
+    assert slab.flat.sum().item() == P * (3 * 1 + 3 * 2 + 1 * 3 + 3 * 4 + 4 * 5)       # writes landed in the flat buffer
+    rows = slab.as_rows()
+    assert rows.shape == (P, D.GRAD_WIDTH) and rows[0].tolist() == [1, 1, 1, 2, 2, 2, 3, 4, 4, 4, 5, 5, 5, 5]
+
+
 def _worker(rank, world, port, out):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     dist.init_process_group("gloo", rank=rank, world_size=world)
