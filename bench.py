@@ -130,7 +130,9 @@ def build_workload(args, device):
 
 def kernels_per_step(L, with_allreduce: bool) -> int:
     """Launches of OUR kernels in one forward+backward (memsets/memcpys not counted)."""
-    fwd = 1 + (2 + L.depth_passes) + 2 + 1 + (2 + L.tile_passes) + 1 + 1 + 1
+    # preprocess | depth sort (hist, scan, passes) | count + scan | emit | supertile sort (scan, passes) |
+    # st ranges, chunk table, chunk count, tile offsets, tile scan | pack colours, scatter records | blend
+    fwd = 1 + (2 + L.depth_passes) + 2 + 1 + (1 + L.tile_passes) + 5 + 2 + 1
     bwd = 1 + 1
     return fwd + bwd
 
@@ -236,11 +238,12 @@ def run_ours(args, world, rank, local):
         n_now, overflowed = RZ.read_counters(st)
         assert not overflowed, "instance capacity exceeded inside the timed region"
         st.num_rendered = n_now
+        R1 = int(st.geom[12:16].view(torch.int32).item())          # counters[3]: supertile instances
         L = RZ.workspace_layout(st.P, st.V, st.W, st.H, st.channels, 0, st.capacity)
         ncon = st.image[L.n_contrib: L.n_contrib + st.V * st.W * st.H * 4].view(torch.int32)
         pairs = int(ncon.sum(dtype=torch.int64).item())
         R = st.num_rendered
-    res = dict(ms=ms, stages=stages, pairs=pairs, R=R, clocks=clocks, views_per_rank=[len(p) for p in parts], parts=parts,
+    res = dict(ms=ms, stages=stages, pairs=pairs, R=R, R1=R1 if st is not None else 0, clocks=clocks, views_per_rank=[len(p) for p in parts], parts=parts,
                launches=kernels_per_step(L, world > 1) * args.steps if st is not None else 0, state=st, dev=dev,
                rv=rv, sets=sets, sc=sc, lib=lib)
     return res
@@ -410,13 +413,15 @@ def main():
         # algorithmic work per launch of each stage on THIS rank (SURVEY.md 8d constants)
         from dynamic3dgaussians_b200 import rasterizer as RZ
         L = RZ.workspace_layout(P, max(Vl, 1), IMG_W, IMG_H, 3, 0, max(R, 1))
+        R1 = res.get("R1", 0)
         work = {
             "blend_backward": ("fp32", 80.0 * pairs), "blend_forward": ("fp32", 27.0 * pairs),
-            "tile_sort": ("hbm", (4.0 + 16.0 * L.tile_passes) * R), "depth_sort": ("hbm", (4.0 + 16.0 * L.depth_passes) * Vl * P),
-            "preprocess": ("hbm", (44.0 + 48.0 * Vl) * P), "gather_records": ("hbm", (8.0 + 40.0 + 48.0) * R),
-            "emit_instances": ("hbm", 20.0 * Vl * P + 8.0 * R), "tile_ranges": ("hbm", 4.0 * R),
+            "supertile_sort": ("hbm", 16.0 * L.tile_passes * R1),
+            "depth_sort": ("hbm", (4.0 + 16.0 * L.depth_passes) * Vl * P),
+            "preprocess": ("hbm", (44.0 + 56.0 * Vl) * P), "scatter_records": ("hbm", (4.0 + 8.0 + 48.0) * R1 + 48.0 * R),
+            "emit_supertile_instances": ("hbm", 12.0 * Vl * P + 8.0 * R1), "tile_offsets": ("hbm", (4.0 + 4.0 + 8.0) * R1),
             "grad_zero": ("hbm", 64.0 * Vl * P), "preprocess_backward": ("hbm", (44.0 + 56.0) * P + 68.0 * Vl * P),
-            "tile_scan": ("hbm", 16.0 * Vl * P),
+            "instance_count": ("hbm", 12.0 * Vl * P),
         }
         roof = None
         if dom in work:
@@ -438,7 +443,7 @@ def main():
             "config": {"workload": f"C2: {P} Gaussians, {V} views {IMG_W}x{IMG_H}, fwd+bwd, colour+depth cotangents",
                        "views_per_rank": res["views_per_rank"], "parallelism": f"view-sharded dp{world}",
                        "l2": "per-step working set (>1 GB of per-view state and instance records) exceeds the 126 MB L2",
-                       "num_rendered_rank0": R, "pairs_rank0": pairs},
+                       "num_rendered_rank0": R, "supertile_instances_rank0": res.get("R1", 0), "pairs_rank0": pairs},
             "clocks": res["clocks"], "e2e": e2e, "gpu_launches": res["launches"],
             "roofline": roof,
             "stage_ms_rank0": {k: round(v, 4) for k, v in stages.items()},

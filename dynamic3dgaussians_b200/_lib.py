@@ -35,11 +35,13 @@ class GsrWorkspaceSizes(C.Structure):
     _fields_ = [("geom_bytes", C.c_size_t), ("binning_bytes", C.c_size_t), ("image_bytes", C.c_size_t)]
 
 
-_LAYOUT_SIZE_T = ["cams", "counters", "depths", "radii", "means2D", "geomrec", "tiles_touched", "cov3D", "rgb",
-                  "col4", "ext4", "clamped", "dkeys0", "dkeys1", "dvals0", "dvals1", "dhist", "dlookback", "dcounters", "block_sums", "grad_rec",
-                  "ikeys0", "ikeys1", "ivals0", "ivals1", "ihist", "ilookback", "recA", "recB", "recC", "recD",
-                  "ranges", "n_contrib", "final_T"]
-_LAYOUT_INT = ["tiles_x", "tiles_y", "tile_bits", "depth_passes", "tile_passes", "sorted_keys_in", "sorted_vals_in"]
+_LAYOUT_SIZE_T = ["cams", "counters", "radii", "rects", "geomrec", "cov3D", "rgb", "col4", "ext4", "clamped",
+                  "dkeys0", "dkeys1", "dvals0", "dvals1", "dhist", "dlookback", "dcounters", "block_sums", "grad_rec",
+                  "ikeys0", "ikeys1", "ivals0", "ivals1", "ihist", "ilookback", "st_ranges", "chunk_base", "chunk_key",
+                  "chunk_counts", "recA", "recB", "recC", "recD",
+                  "ranges", "tile_start", "n_contrib", "final_T"]
+_LAYOUT_INT = ["tiles_x", "tiles_y", "stiles_x", "stiles_y", "tile_bits", "depth_passes", "tile_passes", "sorted_keys_in",
+               "sorted_vals_in", "max_chunks"]
 
 
 class GsrLayout(C.Structure):

@@ -93,7 +93,7 @@ static int check_dims(int P, int V, int W, int H, int channels, int sh_coeffs, i
     if (channels != 3 && channels != 6) return GSR_ERR_UNSUPPORTED;
     if ((int64_t)V * P >= (1ll << 30) || capacity >= (1ll << 30)) return GSR_ERR_UNSUPPORTED;
     const int64_t VT = (int64_t)V * ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
-    if (VT >= (1ll << 31)) return GSR_ERR_UNSUPPORTED;
+    if (VT >= (1ll << 28) || W >= (1 << 20) || H >= (1 << 20)) return GSR_ERR_UNSUPPORTED;   // tile rects are ushort4
     return GSR_OK;
 }
 
@@ -314,8 +314,8 @@ int gsr_stage_timing_enable(int on) {
 int gsr_stage_timing_count(void) { return ST_COUNT; }
 
 const char* gsr_stage_name(int stage) {
-    static const char* names[ST_COUNT] = {"preprocess", "depth_sort", "tile_scan", "emit_instances", "tile_sort",
-                                          "tile_ranges", "gather_records", "blend_forward", "grad_zero",
+    static const char* names[ST_COUNT] = {"preprocess", "depth_sort", "instance_count", "emit_supertile_instances",
+                                          "supertile_sort", "tile_offsets", "scatter_records", "blend_forward", "grad_zero",
                                           "blend_backward", "preprocess_backward"};
     return stage >= 0 && stage < ST_COUNT ? names[stage] : "?";
 }

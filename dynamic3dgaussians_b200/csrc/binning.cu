@@ -1,10 +1,21 @@
-// (b) binning: instance counting, instance emission in depth order, stable tile sort, tile ranges, record gather.
+// (b) binning: from depth-ordered Gaussians to per-tile, depth-ordered record lists.
 // Replaces cub::DeviceScan::InclusiveSum + duplicateWithKeys + SortPairs + identifyTileRanges
-// (R/cuda_rasterizer/rasterizer_impl.cu:70-138,283-323).
+// (R/cuda_rasterizer/rasterizer_impl.cu:70-138,283-323); the result -- for every tile the list of Gaussians whose
+// rectangle covers it, ordered by (depth bits, Gaussian index) -- is identical to the reference's sorted list.
 //
-// The reference sorts R instances on a 64-bit (tile | depth) key.  Here Gaussians are already in per-view depth order
-// (sort of P entries per view), so instances are emitted in that order with a 32-bit (view*T + tile) key and a stable
-// sort on the tile bits alone produces exactly the reference's order: (tile, depth bits, Gaussian index).
+// The reference sorts R = sum(tiles touched) instances on a 64-bit (tile | depth) key: 6 radix passes over 12-byte pairs.
+// Here the ordering is built hierarchically, and the only radix-sorted instance set is 3-4x smaller than R:
+//   1. Gaussians are already in per-view depth order (segmented 32-bit sort, abi.cu).
+//   2. In that order every Gaussian emits one instance per SUPERTILE (4x4 tiles) it touches, key = view*S + supertile;
+//      a stable onesweep sort on those ~11 key bits (2 passes, histograms taken while emitting) groups them per
+//      supertile, still in depth order.
+//   3. Each supertile list is cut into chunks of 256 instances.  A counting kernel finds, per chunk, how many
+//      instances hit each of the 16 tiles (warp ballots on a 16-bit hit mask); a per-supertile prefix over its chunks
+//      and one scan over all tiles give every tile's range and every (chunk, tile) output offset.
+//   4. A scatter kernel recomputes the hit masks and writes the instances' 48-byte blend records (recA|recB|recC[|recD])
+//      straight into the tile lists -- order-preserving compaction, so depth order survives -- with the per-Gaussian
+//      data fetched once per supertile instance instead of once per tile instance, and coalesced stores.
+// No R-sized key/value arrays exist any more; `ranges` fall out of the scan (no identifyTileRanges pass).
 #include "geom_math.cuh"
 #include "radix_rank.cuh"
 
@@ -13,7 +24,7 @@ namespace gsr {
 namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
-constexpr int EMIT_HIST_PASSES = 2;      // tile sorts of up to 16 key bits get their histograms from the emit kernel
+constexpr int EMIT_HIST_PASSES = 2;      // instance sorts of up to 16 key bits get their histograms from the emit kernel
 
 __device__ __forceinline__ uint32_t block_exclusive_scan_256(uint32_t v, uint32_t* s_warp /*[8]*/, uint32_t& total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -37,29 +48,49 @@ __device__ __forceinline__ uint32_t block_exclusive_scan_256(uint32_t v, uint32_
     return base + inc - v;
 }
 
+// supertile rectangle of a tile rectangle (max exclusive); empty rect -> zero supertiles
+__device__ __forceinline__ uint32_t st_rect(ushort4 r, uint32_t& sx0, uint32_t& sy0, uint32_t& sw) {
+    if (r.z <= r.x || r.w <= r.y) { sx0 = sy0 = sw = 0; return 0u; }
+    sx0 = r.x / ST;
+    sy0 = r.y / ST;
+    sw = (r.z - 1u) / ST - sx0 + 1u;
+    return sw * ((r.w - 1u) / ST - sy0 + 1u);
+}
+
 // slot i of the depth-sorted list: view = i / P, Gaussian = sorted_g[i]
-__device__ __forceinline__ uint32_t slot_tiles(uint32_t i, uint32_t VP, int P, const uint32_t* __restrict__ sorted_g,
-                                               const uint32_t* __restrict__ tiles_touched, uint32_t& gidx) {
-    if (i >= VP) { gidx = 0; return 0; }
+__device__ __forceinline__ ushort4 slot_rect(uint32_t i, uint32_t VP, int P, const uint32_t* __restrict__ sorted_g,
+                                             const ushort4* __restrict__ rects, uint32_t& gidx) {
+    if (i >= VP) { gidx = 0; return make_ushort4(0, 0, 0, 0); }
     const uint32_t view = i / (uint32_t)P;
     gidx = view * (uint32_t)P + sorted_g[i];
-    return tiles_touched[gidx];
+    return rects[gidx];
 }
 
+// per block of 2048 slots: number of supertile instances (for the emit offsets); the tile-instance total
+// (the reference's num_rendered) is accumulated on the side
 __global__ void __launch_bounds__(SCAN_BLOCK)
-tile_count_reduce_kernel(uint32_t VP, int P, const uint32_t* __restrict__ sorted_g,
-                         const uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ block_sums) {
+st_count_reduce_kernel(uint32_t VP, int P, const uint32_t* __restrict__ sorted_g, const ushort4* __restrict__ rects,
+                       uint32_t* __restrict__ block_sums, uint32_t* __restrict__ counters) {
     __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
     const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
-    uint32_t sum = 0, gidx;
+    uint32_t sum = 0, tiles = 0, gidx;
 #pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; ++k) sum += slot_tiles(base + k, VP, P, sorted_g, tiles_touched, gidx);
-    uint32_t total;
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        const ushort4 r = slot_rect(base + k, VP, P, sorted_g, rects, gidx);
+        uint32_t a, b, c;
+        sum += st_rect(r, a, b, c);
+        tiles += (uint32_t)(r.z - r.x) * (uint32_t)(r.w - r.y);
+    }
+    uint32_t total, total_tiles;
     block_exclusive_scan_256(sum, s_warp, total);
-    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+    block_exclusive_scan_256(tiles, s_warp, total_tiles);
+    if (threadIdx.x == 0) {
+        block_sums[blockIdx.x] = total;
+        if (total_tiles) atomicAdd(&counters[CNT_RENDERED], total_tiles);
+    }
 }
 
-// single block: exclusive scan of the per-block sums in place; total -> counters[CNT_RENDERED]
+// single block: exclusive scan of the per-block sums in place; total -> counters[CNT_ST_RENDERED]
 __global__ void __launch_bounds__(SCAN_BLOCK)
 block_sums_scan_kernel(uint32_t nblocks, uint32_t* __restrict__ block_sums, uint32_t* __restrict__ counters) {
     __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
@@ -73,54 +104,47 @@ block_sums_scan_kernel(uint32_t nblocks, uint32_t* __restrict__ block_sums, uint
         carry += total;
     }
     if (threadIdx.x == 0) {
-        counters[CNT_RENDERED] = carry;
+        counters[CNT_ST_RENDERED] = carry;
         counters[CNT_OVERFLOW] = 0;
     }
 }
 
-// Emits the (view*T + tile, Gaussian) pairs of every visible (view, Gaussian) in depth order.
-// Row-major tile order inside a Gaussian (y outer, x inner) as duplicateWithKeys, rasterizer_impl.cu:98-109.
-// The reference (and the first version of this kernel) lets one thread write all instances of its Gaussian, so the
-// lanes of a warp write to addresses `tiles_touched` apart: every store is its own 32-byte sector.  Here a CTA first
-// scans its 2048 slots into shared memory, then walks its OUTPUT range with one thread per instance (binary search
-// of the owning slot), so stores are fully coalesced.
+// Emits the (view*S + supertile, view*P + Gaussian) pairs of every visible (view, Gaussian) in depth order.
+// A CTA first scans its 2048 slots into shared memory, then walks its OUTPUT range with one thread per instance
+// (binary search of the owning slot), so stores are fully coalesced; the digit histograms of the following sort are
+// taken on the way (warp-private bins, radix_rank.cuh), which saves that sort's pass over the keys.
 __global__ void __launch_bounds__(SCAN_BLOCK)
-emit_instances_kernel(uint32_t VP, int P, int tiles_x, int tiles_y, const uint32_t* __restrict__ sorted_g,
-                      const uint32_t* __restrict__ tiles_touched, const uint32_t* __restrict__ block_sums,
-                      const float2* __restrict__ means2D, const int32_t* __restrict__ radii, uint32_t capacity,
-                      uint32_t* __restrict__ ikeys, uint32_t* __restrict__ ivals, uint32_t* __restrict__ counters,
-                      int hist_passes, int tile_bits, uint32_t* __restrict__ sort_hist) {
+emit_st_instances_kernel(uint32_t VP, int P, int stiles_x, uint32_t S, const uint32_t* __restrict__ sorted_g,
+                         const ushort4* __restrict__ rects, const uint32_t* __restrict__ block_sums, uint32_t capacity,
+                         uint32_t* __restrict__ ikeys, uint32_t* __restrict__ ivals, uint32_t* __restrict__ counters,
+                         int hist_passes, int key_bits, uint32_t* __restrict__ sort_hist) {
     __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
-    __shared__ uint32_t s_hist[SCAN_BLOCK / 32][EMIT_HIST_PASSES][RADIX];   // warp-private digit histograms of the keys
+    __shared__ uint32_t s_hist[SCAN_BLOCK / 32][EMIT_HIST_PASSES][RADIX];
     __shared__ uint32_t s_off[SCAN_TILE + 1];     // exclusive offset of every slot inside this CTA's output range
-    __shared__ uint32_t s_key0[SCAN_TILE];        // key of the slot's first tile: view*T + min.y*tiles_x + min.x
-    __shared__ uint32_t s_g[SCAN_TILE];           // Gaussian index
-    __shared__ uint16_t s_w[SCAN_TILE];           // rect width in tiles
+    __shared__ uint32_t s_key0[SCAN_TILE];        // key of the slot's first supertile
+    __shared__ uint32_t s_gi[SCAN_TILE];          // view*P + Gaussian
+    __shared__ uint16_t s_w[SCAN_TILE];           // supertile-rect width
     const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
-    uint32_t cnt[SCAN_ITEMS], gidx[SCAN_ITEMS];
+    uint32_t cnt[SCAN_ITEMS], gidx[SCAN_ITEMS], key0[SCAN_ITEMS], wid[SCAN_ITEMS];
     uint32_t sum = 0;
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; ++k) {
-        cnt[k] = slot_tiles(base + k, VP, P, sorted_g, tiles_touched, gidx[k]);
+        const ushort4 r = slot_rect(base + k, VP, P, sorted_g, rects, gidx[k]);
+        uint32_t sx0, sy0;
+        cnt[k] = st_rect(r, sx0, sy0, wid[k]);
+        key0[k] = (gidx[k] / (uint32_t)P) * S + sy0 * (uint32_t)stiles_x + sx0;
         sum += cnt[k];
     }
     uint32_t total;
     uint32_t off = block_exclusive_scan_256(sum, s_warp, total);
-    const uint32_t T = (uint32_t)tiles_x * (uint32_t)tiles_y;
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; ++k) {
         const int slot = threadIdx.x * SCAN_ITEMS + k;
         s_off[slot] = off;
         off += cnt[k];
-        if (cnt[k] != 0) {
-            const uint32_t gi = gidx[k];
-            const uint32_t view = gi / (uint32_t)P;
-            uint2 mn, mx;
-            tile_rect(means2D[gi], radii[gi], tiles_x, tiles_y, mn, mx);
-            s_key0[slot] = view * T + mn.y * (uint32_t)tiles_x + mn.x;
-            s_g[slot] = gi - view * (uint32_t)P;
-            s_w[slot] = (uint16_t)(mx.x - mn.x);
-        }
+        s_key0[slot] = key0[k];
+        s_gi[slot] = gidx[k];
+        s_w[slot] = (uint16_t)wid[k];
     }
     if (threadIdx.x == 0) s_off[SCAN_TILE] = total;
     if (hist_passes > 0)
@@ -144,22 +168,21 @@ emit_instances_kernel(uint32_t VP, int P, int tiles_x, int tiles_y, const uint32
             const uint32_t l = o - s_off[lo];
             const uint32_t w = s_w[lo];
             const uint32_t ty = l / w;
-            key = s_key0[lo] + ty * (uint32_t)tiles_x + (l - ty * w);
+            key = s_key0[lo] + ty * (uint32_t)stiles_x + (l - ty * w);
             const uint32_t dst = out0 + o;
             if (dst < capacity) {
                 ikeys[dst] = key;
-                ivals[dst] = s_g[lo];
+                ivals[dst] = s_gi[lo];
                 stored = true;
             } else {
                 overflow = true;
             }
         }
-        // the tile sort's digit histograms, taken while the keys are in registers (saves a pass over the keys)
 #pragma unroll
         for (int p = 0; p < EMIT_HIST_PASSES; ++p) {
             if (p < hist_passes) {
                 const int shift = p * RADIX_BITS;
-                const int bits = min(RADIX_BITS, tile_bits - shift);
+                const int bits = min(RADIX_BITS, key_bits - shift);
                 uint32_t peers;
                 warp_hist_add(s_hist[warp][p], (key >> shift) & ((1u << bits) - 1u), stored, lane, peers);
             }
@@ -178,79 +201,265 @@ emit_instances_kernel(uint32_t VP, int P, int tiles_x, int tiles_y, const uint32
     }
 }
 
-// identifyTileRanges, rasterizer_impl.cu:116-138, on the 32-bit (view*T + tile) keys
+// boundary detection on the sorted supertile keys (the reference's identifyTileRanges, rasterizer_impl.cu:116-138, one
+// level up): st_ranges[key] = [first, last+1) ; st_ranges is zeroed before
 __global__ void __launch_bounds__(256)
-tile_ranges_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, const uint32_t* __restrict__ keys,
-                   uint2* __restrict__ ranges) {
-    const uint32_t n = min(counters[CNT_RENDERED], capacity);
+st_ranges_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, const uint32_t* __restrict__ keys,
+                 uint2* __restrict__ st_ranges) {
+    const uint32_t n = min(counters[CNT_ST_RENDERED], capacity);
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t cur = keys[i];
     if (i == 0) {
-        ranges[cur].x = 0;
+        st_ranges[cur].x = 0;
     } else {
         const uint32_t prev = keys[i - 1];
         if (cur != prev) {
-            ranges[prev].y = i;
-            ranges[cur].x = i;
+            st_ranges[prev].y = i;
+            st_ranges[cur].x = i;
         }
     }
-    if (i == n - 1) ranges[cur].y = n;
+    if (i == n - 1) st_ranges[cur].y = n;
 }
 
-// Gathers the per-instance records the blend kernels stream with TMA bulk copies:
-//   A = (mean.x, mean.y, conic.x, conic.y)   B = (conic.z, opacity, depth, skip threshold [blend_skip_threshold])
-//   C = (r, g, b, bits(view*P + g))          D = (extra colour r, g, b, 0)   [channels == 6]
-// Two threads per instance: the per-(view, Gaussian) geometry is already stored as the 32-byte pair (recA | recB) by
-// the preprocess kernel, so the even thread moves the first 16 bytes and the odd thread the second 16 bytes of ONE
-// 32-byte sector; colours come from float4-packed per-Gaussian arrays.  A warp instruction therefore touches 16 sectors
-// for 16 instances.  (The first version read five separate arrays with 4/8/12/16-byte gathers: six divergent load
-// instructions = ~190 L1 tag cycles per 32 instances, which -- not DRAM -- bounded the kernel at 0.94 ms.)
-// key / T is a multiply-high by a host-computed reciprocal (exact for key < 2^31).
-constexpr int GATHER_ITEMS = 4;
-
-__global__ void __launch_bounds__(256)
-gather_records_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, int P, uint32_t T, uint32_t T_magic,
-                      int T_shift, int channels,
-                      const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
-                      const float4* __restrict__ geomrec, const float4* __restrict__ col4,
-                      const float4* __restrict__ rgb_sh4, const float4* __restrict__ ext4,
-                      float4* __restrict__ recA, float4* __restrict__ recB, float4* __restrict__ recC,
-                      float4* __restrict__ recD) {
-    const uint32_t n = min(counters[CNT_RENDERED], capacity);
-    const uint32_t half = threadIdx.x & 1u;
-    const uint32_t i0 = blockIdx.x * (128 * GATHER_ITEMS) + (threadIdx.x >> 1);
-    if (i0 >= n) return;
-    uint32_t g[GATHER_ITEMS], gi[GATHER_ITEMS];
-    bool ok[GATHER_ITEMS];
-#pragma unroll
-    for (int k = 0; k < GATHER_ITEMS; ++k) {
-        const uint32_t i = i0 + k * 128;
-        ok[k] = i < n;
-        const uint32_t key = ok[k] ? keys[i] : 0u;
-        g[k] = ok[k] ? vals[i] : 0u;
-        const uint32_t view = T == 1u ? key : (__umulhi(key, T_magic) >> T_shift);
-        gi[k] = view * (uint32_t)P + g[k];
-    }
-    float4 geo[GATHER_ITEMS], col[GATHER_ITEMS];
-    const bool want_col = half == 0u || channels > 3;
-#pragma unroll
-    for (int k = 0; k < GATHER_ITEMS; ++k) {
-        geo[k] = geomrec[2 * (size_t)gi[k] + half];
-        if (want_col)
-            col[k] = half == 0u ? (col4 ? col4[g[k]] : rgb_sh4[gi[k]]) : ext4[g[k]];
-    }
-    float4* __restrict__ dst_geo = half == 0u ? recA : recB;
-    float4* __restrict__ dst_col = half == 0u ? recC : recD;
-#pragma unroll
-    for (int k = 0; k < GATHER_ITEMS; ++k) {
-        if (!ok[k]) continue;
-        const uint32_t i = i0 + k * 128;
-        dst_geo[i] = geo[k];
-        if (want_col) {
-            if (half == 0u) col[k].w = __uint_as_float(gi[k]);
-            dst_col[i] = col[k];
+// single block: chunk_base[k] = exclusive scan of ceil(len_k / CHUNK) over the V*S supertile keys, chunk_base[VS] and
+// counters[CNT_NCHUNKS] = number of chunks; chunk_key[c] = owning key of chunk c
+__global__ void __launch_bounds__(SCAN_BLOCK)
+chunk_table_kernel(uint32_t VS, const uint2* __restrict__ st_ranges, uint32_t* __restrict__ chunk_base,
+                   uint32_t* __restrict__ chunk_key, uint32_t max_chunks, uint32_t* __restrict__ counters) {
+    __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
+    uint32_t carry = 0;
+    for (uint32_t start = 0; start < VS; start += SCAN_BLOCK) {
+        const uint32_t k = start + threadIdx.x;
+        uint32_t nch = 0;
+        if (k < VS) {
+            const uint2 r = st_ranges[k];
+            nch = (r.y - r.x + CHUNK - 1) / CHUNK;
         }
+        uint32_t total;
+        const uint32_t cb = carry + block_exclusive_scan_256(nch, s_warp, total);
+        if (k < VS) {
+            chunk_base[k] = cb;
+            for (uint32_t j = 0; j < nch; ++j)
+                if (cb + j < max_chunks) chunk_key[cb + j] = k;
+        }
+        carry += total;
+    }
+    if (threadIdx.x == 0) {
+        chunk_base[VS] = carry;
+        counters[CNT_NCHUNKS] = min(carry, max_chunks);
+    }
+}
+
+// 16-bit hit mask of a tile rectangle inside the supertile whose first tile is (ox, oy): bit ty*4+tx
+__device__ __forceinline__ uint32_t st_hit_mask(ushort4 r, uint32_t ox, uint32_t oy) {
+    const int xlo = max((int)r.x - (int)ox, 0), xhi = min((int)r.z - (int)ox, ST);
+    const int ylo = max((int)r.y - (int)oy, 0), yhi = min((int)r.w - (int)oy, ST);
+    if (xhi <= xlo || yhi <= ylo) return 0u;
+    const uint32_t xb = ((1u << xhi) - 1u) & ~((1u << xlo) - 1u);
+    const uint32_t yb = ((1u << yhi) - 1u) & ~((1u << ylo) - 1u);
+    const uint32_t ys = (yb & 1u) | ((yb & 2u) << 3) | ((yb & 4u) << 6) | ((yb & 8u) << 9);
+    return xb * ys;
+}
+
+struct ChunkInfo {
+    uint32_t key, first, count;      // supertile key, first sorted instance, instances in this chunk
+    uint32_t view, ox, oy;           // view and first tile of the supertile
+};
+
+__device__ __forceinline__ bool chunk_info(uint32_t cid, const uint32_t* __restrict__ counters,
+                                           const uint32_t* __restrict__ chunk_key, const uint32_t* __restrict__ chunk_base,
+                                           const uint2* __restrict__ st_ranges, uint32_t S, int stiles_x, ChunkInfo& c) {
+    if (cid >= counters[CNT_NCHUNKS]) return false;
+    c.key = chunk_key[cid];
+    const uint2 r = st_ranges[c.key];
+    c.first = r.x + (cid - chunk_base[c.key]) * CHUNK;
+    c.count = min((uint32_t)CHUNK, r.y - c.first);
+    c.view = c.key / S;
+    const uint32_t s = c.key - c.view * S;
+    const uint32_t sy = s / (uint32_t)stiles_x;
+    c.ox = (s - sy * (uint32_t)stiles_x) * ST;
+    c.oy = sy * ST;
+    return true;
+}
+
+// per chunk: how many of its instances hit each of the supertile's 16 tiles
+__global__ void __launch_bounds__(CHUNK)
+chunk_count_kernel(const uint32_t* __restrict__ counters, const uint32_t* __restrict__ chunk_key,
+                   const uint32_t* __restrict__ chunk_base, const uint2* __restrict__ st_ranges, uint32_t S,
+                   int stiles_x, const uint32_t* __restrict__ vals, const ushort4* __restrict__ rects,
+                   uint32_t* __restrict__ chunk_counts) {
+    __shared__ uint32_t s_cnt[ST_TILES][CHUNK / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    ChunkInfo c;
+    // persistent CTAs: the chunk count is only known on the device, so the grid is sized for the SMs, not the chunks
+    for (uint32_t cid = blockIdx.x; chunk_info(cid, counters, chunk_key, chunk_base, st_ranges, S, stiles_x, c);
+         cid += gridDim.x) {
+        uint32_t mask = 0;
+        if ((uint32_t)tid < c.count) mask = st_hit_mask(rects[vals[c.first + tid]], c.ox, c.oy);
+#pragma unroll
+        for (int t = 0; t < ST_TILES; ++t) {
+            const uint32_t bal = __ballot_sync(FULL, (mask >> t) & 1u);
+            if (lane == 0) s_cnt[t][warp] = __popc(bal);
+        }
+        __syncthreads();
+        if (tid < ST_TILES) {
+            uint32_t n = 0;
+#pragma unroll
+            for (int w = 0; w < CHUNK / 32; ++w) n += s_cnt[tid][w];
+            chunk_counts[(size_t)cid * ST_TILES + tid] = n;
+        }
+        __syncthreads();
+    }
+}
+
+// one warp per supertile key: per tile, exclusive prefix of the chunk counts over the key's chunks (in place), and the
+// tile's total -> tile_start[view*T + tile] (scanned by tile_scan_kernel)
+__global__ void __launch_bounds__(128)
+tile_offsets_kernel(uint32_t VS, uint32_t S, int stiles_x, int tiles_x, int tiles_y,
+                    const uint32_t* __restrict__ chunk_base, uint32_t max_chunks, uint32_t* __restrict__ chunk_counts,
+                    uint32_t* __restrict__ tile_start) {
+    const uint32_t k = blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int t = threadIdx.x & 31;
+    if (k >= VS || t >= ST_TILES) return;
+    const uint32_t c0 = min(chunk_base[k], max_chunks), c1 = min(chunk_base[k + 1], max_chunks);
+    uint32_t run = 0;
+    for (uint32_t c = c0; c < c1; ++c) {
+        const uint32_t n = chunk_counts[(size_t)c * ST_TILES + t];
+        chunk_counts[(size_t)c * ST_TILES + t] = run;
+        run += n;
+    }
+    const uint32_t view = k / S, s = k - view * S;
+    const uint32_t sy = s / (uint32_t)stiles_x, sx = s - sy * (uint32_t)stiles_x;
+    const uint32_t gx = sx * ST + (t & 3), gy = sy * ST + (t >> 2);
+    if (gx < (uint32_t)tiles_x && gy < (uint32_t)tiles_y)
+        tile_start[(size_t)view * tiles_x * tiles_y + gy * (uint32_t)tiles_x + gx] = run;
+}
+
+// single block: exclusive scan of the per-tile counts in place (tile_start), ranges clamped to the capacity
+__global__ void __launch_bounds__(SCAN_BLOCK)
+tile_scan_kernel(uint32_t VT, uint32_t capacity, uint32_t* __restrict__ tile_start, uint2* __restrict__ ranges,
+                 uint32_t* __restrict__ counters) {
+    __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
+    uint32_t carry = 0;
+    for (uint32_t start = 0; start < VT; start += SCAN_BLOCK * 4) {
+        const uint32_t i0 = start + threadIdx.x * 4;
+        uint32_t v[4], sum = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { v[k] = i0 + k < VT ? tile_start[i0 + k] : 0u; sum += v[k]; }
+        uint32_t total;
+        uint32_t ex = carry + block_exclusive_scan_256(sum, s_warp, total);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (i0 + k < VT) {
+                tile_start[i0 + k] = ex;
+                ranges[i0 + k] = make_uint2(min(ex, capacity), min(ex + v[k], capacity));
+            }
+            ex += v[k];
+        }
+        carry += total;
+    }
+    if (threadIdx.x == 0) {
+        tile_start[VT] = carry;
+        if (carry > capacity) counters[CNT_OVERFLOW] = 1;
+    }
+}
+
+// Per chunk: order-preserving compaction of its instances into the 16 tile lists, writing the blend records.
+// Thread i stages instance i's records in shared memory (geometry: two float4 of one 32-byte sector written by the
+// preprocess kernel; colour: one float4), ballots give every hit its position, and the records are then copied out by
+// flattened (tile, position) index so that consecutive threads store to consecutive list slots.
+template <bool EXTRA>
+__global__ void __launch_bounds__(CHUNK)
+scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __restrict__ chunk_key,
+                       const uint32_t* __restrict__ chunk_base, const uint2* __restrict__ st_ranges, uint32_t S,
+                       int stiles_x, int tiles_x, int tiles_y, int P, uint32_t capacity,
+                       const uint32_t* __restrict__ vals, const ushort4* __restrict__ rects,
+                       const uint32_t* __restrict__ chunk_offs, const uint32_t* __restrict__ tile_start,
+                       const float4* __restrict__ geomrec, const float4* __restrict__ col4,
+                       const float4* __restrict__ rgb_sh4, const float4* __restrict__ ext4,
+                       float4* __restrict__ recA, float4* __restrict__ recB, float4* __restrict__ recC,
+                       float4* __restrict__ recD) {
+    __shared__ float4 s_recA[CHUNK], s_recB[CHUNK], s_recC[CHUNK];
+    __shared__ float4 s_recD[EXTRA ? CHUNK : 1];
+    __shared__ uint8_t s_list[ST_TILES][CHUNK];
+    __shared__ uint32_t s_wcnt[ST_TILES][CHUNK / 32];
+    __shared__ uint32_t s_tbase[ST_TILES];            // list position of this chunk's first hit, per tile
+    __shared__ uint32_t s_tpre[ST_TILES + 1];         // prefix of the per-tile hit counts of this chunk
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    ChunkInfo c;
+    for (uint32_t cid = blockIdx.x; chunk_info(cid, counters, chunk_key, chunk_base, st_ranges, S, stiles_x, c);
+         cid += gridDim.x) {
+        uint32_t mask = 0;
+        if ((uint32_t)tid < c.count) {
+            const uint32_t gi = vals[c.first + tid];
+            mask = st_hit_mask(rects[gi], c.ox, c.oy);
+            if (mask) {
+                const uint32_t g = gi - c.view * (uint32_t)P;
+                s_recA[tid] = geomrec[2 * (size_t)gi];
+                s_recB[tid] = geomrec[2 * (size_t)gi + 1];
+                float4 col = col4 ? col4[g] : rgb_sh4[gi];
+                col.w = __uint_as_float(gi);
+                s_recC[tid] = col;
+                if (EXTRA) s_recD[tid] = ext4[g];
+            }
+        }
+        if (tid < ST_TILES) {
+            const uint32_t gx = c.ox + (tid & 3), gy = c.oy + (tid >> 2);
+            uint32_t b = 0;
+            if (gx < (uint32_t)tiles_x && gy < (uint32_t)tiles_y)
+                b = tile_start[(size_t)c.view * tiles_x * tiles_y + gy * (uint32_t)tiles_x + gx] +
+                    chunk_offs[(size_t)cid * ST_TILES + tid];
+            s_tbase[tid] = b;
+        }
+#pragma unroll
+        for (int t = 0; t < ST_TILES; ++t) {
+            const uint32_t bal = __ballot_sync(FULL, (mask >> t) & 1u);
+            if (lane == 0) s_wcnt[t][warp] = __popc(bal);
+        }
+        __syncthreads();
+        if (tid < ST_TILES) {                             // per tile: exclusive prefix over the 8 warps, total
+            uint32_t run = 0;
+#pragma unroll
+            for (int w = 0; w < CHUNK / 32; ++w) {
+                const uint32_t n = s_wcnt[tid][w];
+                s_wcnt[tid][w] = run;
+                run += n;
+            }
+            // exclusive prefix of the totals over the 16 tiles (threads 0..15 are one half-warp)
+            uint32_t inc = run;
+#pragma unroll
+            for (int o = 1; o < ST_TILES; o <<= 1) {
+                const uint32_t v = __shfl_up_sync(0x0000ffffu, inc, o, ST_TILES);
+                if (tid >= o) inc += v;
+            }
+            s_tpre[tid] = inc - run;
+            if (tid == ST_TILES - 1) s_tpre[ST_TILES] = inc;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int t = 0; t < ST_TILES; ++t) {
+            const uint32_t bal = __ballot_sync(FULL, (mask >> t) & 1u);
+            if ((mask >> t) & 1u) s_list[t][s_wcnt[t][warp] + __popc(bal & lt)] = (uint8_t)tid;
+        }
+        __syncthreads();
+        const uint32_t hits = s_tpre[ST_TILES];
+        for (uint32_t h = tid; h < hits; h += CHUNK) {
+            uint32_t t = 0;
+#pragma unroll
+            for (int k = 1; k < ST_TILES; ++k) t += (h >= s_tpre[k]) ? 1u : 0u;
+            const uint32_t p = h - s_tpre[t];
+            const uint32_t e = s_list[t][p];
+            const uint32_t dst = s_tbase[t] + p;
+            if (dst < capacity) {
+                recA[dst] = s_recA[e];
+                recB[dst] = s_recB[e];
+                recC[dst] = s_recC[e];
+                if (EXTRA) recD[dst] = s_recD[e];
+            }
+        }
+        __syncthreads();                              // shared staging is reused by the next chunk
     }
 }
 
@@ -264,44 +473,24 @@ pack_colors_kernel(int P, const float* __restrict__ colors, const float* __restr
     if (extra) ext4[g] = make_float4(extra[3 * g], extra[3 * g + 1], extra[3 * g + 2], 0.0f);
 }
 
-// ---- export of one view in the reference's format (tests / tools) ----
-__global__ void find_view_start_kernel(const uint32_t* __restrict__ counters, uint32_t capacity,
-                                       const uint32_t* __restrict__ keys, uint32_t first_key,
-                                       uint32_t* __restrict__ out) {
-    const uint32_t n = min(counters[CNT_RENDERED], capacity);
-    uint32_t lo = 0, hi = n;
-    while (lo < hi) {
-        const uint32_t mid = lo + (hi - lo) / 2;
-        if (keys[mid] < first_key) lo = mid + 1; else hi = mid;
+// ---- export of one view in the reference's format (tests / tools): one CTA per tile ----
+__global__ void __launch_bounds__(128)
+export_view_kernel(int view, int P, uint32_t T, const uint2* __restrict__ ranges, const float4* __restrict__ recB,
+                   const float4* __restrict__ recC, uint64_t* __restrict__ keys_out, uint32_t* __restrict__ list_out,
+                   uint32_t* __restrict__ ranges_out) {
+    const uint32_t tile = blockIdx.x;
+    const uint32_t vs = ranges[(size_t)view * T].x;                 // first instance of the view (tile 0 may be empty:
+    const uint2 r = ranges[(size_t)view * T + tile];                // its range is then [start, start))
+    if (ranges_out && threadIdx.x == 0) {
+        const bool empty = r.y == r.x;
+        ranges_out[2 * tile] = empty ? 0u : r.x - vs;
+        ranges_out[2 * tile + 1] = empty ? 0u : r.y - vs;
     }
-    out[0] = lo;
-}
-
-__global__ void export_view_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, int view, int P,
-                                   uint32_t T, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
-                                   const float* __restrict__ depths, const uint32_t* __restrict__ view_start,
-                                   uint64_t* __restrict__ keys_out, uint32_t* __restrict__ list_out) {
-    const uint32_t n = min(counters[CNT_RENDERED], capacity);
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x + view_start[0];
-    if (i >= n) return;
-    const uint32_t k = keys[i];
-    if (k / T != (uint32_t)view) return;
-    const uint32_t local = i - view_start[0];
-    const uint32_t g = vals[i];
-    if (keys_out)
-        keys_out[local] = ((uint64_t)(k - (uint32_t)view * T) << 32) |
-                          (uint64_t)__float_as_uint(depths[(size_t)view * P + g]);
-    if (list_out) list_out[local] = g;
-}
-
-__global__ void export_ranges_kernel(int view, uint32_t T, const uint2* __restrict__ ranges,
-                                     const uint32_t* __restrict__ view_start, uint32_t* __restrict__ ranges_out) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= T) return;
-    const uint2 r = ranges[(size_t)view * T + t];
-    const bool empty = r.y == r.x;
-    ranges_out[2 * t] = empty ? 0u : r.x - view_start[0];
-    ranges_out[2 * t + 1] = empty ? 0u : r.y - view_start[0];
+    for (uint32_t i = r.x + threadIdx.x; i < r.y; i += blockDim.x) {
+        const uint32_t gi = __float_as_uint(recC[i].w);
+        if (keys_out) keys_out[i - vs] = ((uint64_t)tile << 32) | (uint64_t)__float_as_uint(recB[i].z);
+        if (list_out) list_out[i - vs] = gi - (uint32_t)view * (uint32_t)P;
+    }
 }
 
 }  // namespace
@@ -311,8 +500,8 @@ int launch_tile_scan(int V, int P, void* ws, const Layout& L, cudaStream_t s) {
     if (VP == 0) return GSR_OK;
     const uint32_t nblocks = (VP + SCAN_TILE - 1) / SCAN_TILE;
     const uint32_t* sorted_g = at<uint32_t>(ws, L.sorted_vals_in ? L.dvals1 : L.dvals0);
-    tile_count_reduce_kernel<<<nblocks, SCAN_BLOCK, 0, s>>>(VP, P, sorted_g, at<uint32_t>(ws, L.tiles_touched),
-                                                           at<uint32_t>(ws, L.block_sums));
+    st_count_reduce_kernel<<<nblocks, SCAN_BLOCK, 0, s>>>(VP, P, sorted_g, at<ushort4>(ws, L.rects),
+                                                         at<uint32_t>(ws, L.block_sums), at<uint32_t>(ws, L.counters));
     GSR_LAUNCH_CHECK();
     block_sums_scan_kernel<<<1, SCAN_BLOCK, 0, s>>>(nblocks, at<uint32_t>(ws, L.block_sums),
                                                     at<uint32_t>(ws, L.counters));
@@ -325,54 +514,75 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
                    const Layout& L, cudaStream_t s) {
     const uint32_t VP = (uint32_t)((size_t)V * P);
     const uint32_t T = (uint32_t)L.tiles_x * (uint32_t)L.tiles_y;
-    const size_t VT = (size_t)V * T;
-    GSR_CUDA_TRY(cudaMemsetAsync(at<uint2>(iws, L.ranges), 0, VT * sizeof(uint2), s));
-    if (VP == 0 || capacity <= 0) return GSR_OK;
+    const uint32_t S = (uint32_t)L.stiles_x * (uint32_t)L.stiles_y;
+    const uint32_t VT = (uint32_t)V * T, VS = (uint32_t)V * S;
+    if (VP == 0 || capacity <= 0) {
+        GSR_CUDA_TRY(cudaMemsetAsync(at<uint2>(iws, L.ranges), 0, (size_t)VT * sizeof(uint2), s));
+        return GSR_OK;
+    }
     const uint32_t cap = (uint32_t)capacity;
     uint32_t* counters = at<uint32_t>(gws, L.counters);
     const uint32_t nblocks = (VP + SCAN_TILE - 1) / SCAN_TILE;
     const uint32_t* sorted_g = at<uint32_t>(gws, L.sorted_vals_in ? L.dvals1 : L.dvals0);
+    const ushort4* rects = at<ushort4>(gws, L.rects);
     const bool fused_hist = L.tile_passes <= EMIT_HIST_PASSES;
     stage_begin(ST_EMIT, s);
     if (fused_hist) GSR_CUDA_TRY(cudaMemsetAsync(at<uint32_t>(bws, L.ihist), 0, (size_t)L.tile_passes * RADIX * 4, s));
-    emit_instances_kernel<<<nblocks, SCAN_BLOCK, 0, s>>>(
-        VP, P, L.tiles_x, L.tiles_y, sorted_g, at<uint32_t>(gws, L.tiles_touched), at<uint32_t>(gws, L.block_sums),
-        at<float2>(gws, L.means2D), at<int32_t>(gws, L.radii), cap, at<uint32_t>(bws, L.ikeys0),
-        at<uint32_t>(bws, L.ivals0), counters, fused_hist ? L.tile_passes : 0, L.tile_bits,
-        at<uint32_t>(bws, L.ihist));
+    emit_st_instances_kernel<<<nblocks, SCAN_BLOCK, 0, s>>>(
+        VP, P, L.stiles_x, S, sorted_g, rects, at<uint32_t>(gws, L.block_sums), cap, at<uint32_t>(bws, L.ikeys0),
+        at<uint32_t>(bws, L.ivals0), counters, fused_hist ? L.tile_passes : 0, L.tile_bits, at<uint32_t>(bws, L.ihist));
     GSR_LAUNCH_CHECK();
     stage_end(ST_EMIT, s);
     stage_begin(ST_TILE_SORT, s);
     int rc = radix_sort_pairs<uint32_t>(at<uint32_t>(bws, L.ikeys0), at<uint32_t>(bws, L.ikeys1),
                                         at<uint32_t>(bws, L.ivals0), at<uint32_t>(bws, L.ivals1), capacity,
-                                        counters + CNT_RENDERED, 0, L.tile_bits, at<uint32_t>(bws, L.ihist),
+                                        counters + CNT_ST_RENDERED, 0, L.tile_bits, at<uint32_t>(bws, L.ihist),
                                         at<uint32_t>(bws, L.ilookback), counters + CNT_INST_TILE, s, 1, fused_hist);
     stage_end(ST_TILE_SORT, s);
     if (rc != GSR_OK) return rc;
     const uint32_t* skeys = at<uint32_t>(bws, L.sorted_keys_in ? L.ikeys1 : L.ikeys0);
     const uint32_t* svals = at<uint32_t>(bws, L.sorted_keys_in ? L.ivals1 : L.ivals0);
-    const uint32_t gblocks = (cap + 255) / 256;
+    uint2* st_ranges = at<uint2>(bws, L.st_ranges);
+    uint32_t* chunk_base = at<uint32_t>(bws, L.chunk_base);
+    uint32_t* chunk_key = at<uint32_t>(bws, L.chunk_key);
+    uint32_t* chunk_counts = at<uint32_t>(bws, L.chunk_counts);
+    uint32_t* tile_start = at<uint32_t>(iws, L.tile_start);
+    const uint32_t max_chunks = (uint32_t)L.max_chunks;
+    const uint32_t chunk_grid = max_chunks < 148u * 8u ? max_chunks : 148u * 8u;   // persistent CTAs, 8 per SM
     stage_begin(ST_RANGES, s);
-    tile_ranges_kernel<<<gblocks, 256, 0, s>>>(counters, cap, skeys, at<uint2>(iws, L.ranges));
+    GSR_CUDA_TRY(cudaMemsetAsync(st_ranges, 0, (size_t)VS * sizeof(uint2), s));
+    st_ranges_kernel<<<(cap + 255) / 256, 256, 0, s>>>(counters, cap, skeys, st_ranges);
+    GSR_LAUNCH_CHECK();
+    chunk_table_kernel<<<1, SCAN_BLOCK, 0, s>>>(VS, st_ranges, chunk_base, chunk_key, max_chunks, counters);
+    GSR_LAUNCH_CHECK();
+    chunk_count_kernel<<<chunk_grid, CHUNK, 0, s>>>(counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, svals,
+                                                   rects, chunk_counts);
+    GSR_LAUNCH_CHECK();
+    tile_offsets_kernel<<<(VS + 3) / 4, 128, 0, s>>>(VS, S, L.stiles_x, L.tiles_x, L.tiles_y, chunk_base, max_chunks,
+                                                    chunk_counts, tile_start);
+    GSR_LAUNCH_CHECK();
+    tile_scan_kernel<<<1, SCAN_BLOCK, 0, s>>>(VT, cap, tile_start, at<uint2>(iws, L.ranges), counters);
     GSR_LAUNCH_CHECK();
     stage_end(ST_RANGES, s);
     StageScope sc(ST_GATHER, s);
-    // floor(key / T) == umulhi(key, magic) >> shift for every key < 2^31 (V*T < 2^31 is checked at the ABI)
-    int lg = 1;                                   // T == 1 is special-cased in the kernel (magic would need 33 bits)
-    while ((1u << lg) < T) ++lg;
-    const int sh = 31 + lg;
-    const uint32_t magic = (uint32_t)((((uint64_t)1 << sh) + T - 1) / T);
-    const uint32_t rblocks = (cap + 128 * GATHER_ITEMS - 1) / (128 * GATHER_ITEMS);
     if (colors_precomp || extra_colors) {
         pack_colors_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, colors_precomp, extra_colors, at<float4>(gws, L.col4),
                                                            at<float4>(gws, L.ext4));
         GSR_LAUNCH_CHECK();
     }
-    gather_records_kernel<<<rblocks, 256, 0, s>>>(
-        counters, cap, P, T, magic, sh - 32, channels, skeys, svals, at<float4>(gws, L.geomrec),
-        colors_precomp ? at<float4>(gws, L.col4) : nullptr, sh_coeffs > 0 ? at<float4>(gws, L.rgb) : nullptr,
-        at<float4>(gws, L.ext4), at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC),
-        channels > 3 ? at<float4>(bws, L.recD) : nullptr);
+    const float4* col4 = colors_precomp ? at<float4>(gws, L.col4) : nullptr;
+    const float4* rgb4 = sh_coeffs > 0 ? at<float4>(gws, L.rgb) : nullptr;
+    if (channels > 3) {
+        scatter_records_kernel<true><<<chunk_grid, CHUNK, 0, s>>>(
+            counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals, rects,
+            chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, at<float4>(gws, L.ext4),
+            at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC), at<float4>(bws, L.recD));
+    } else {
+        scatter_records_kernel<false><<<chunk_grid, CHUNK, 0, s>>>(
+            counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals, rects,
+            chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, nullptr, at<float4>(bws, L.recA),
+            at<float4>(bws, L.recB), at<float4>(bws, L.recC), nullptr);
+    }
     GSR_LAUNCH_CHECK();
     return GSR_OK;
 }
@@ -381,29 +591,9 @@ int launch_export_view(int view, int V, int P, int W, int H, const void* gws, co
                        const Layout& L, uint64_t* keys_out, uint32_t* list_out, uint32_t* ranges_out,
                        uint32_t* n_contrib_out, cudaStream_t s) {
     const uint32_t T = (uint32_t)L.tiles_x * (uint32_t)L.tiles_y;
-    // scratch slot for the view's first sorted position: counters[2]
-    uint32_t* counters = const_cast<uint32_t*>(at<uint32_t>(gws, L.counters));
-    const uint32_t* skeys = at<uint32_t>(bws, L.sorted_keys_in ? L.ikeys1 : L.ikeys0);
-    const uint32_t* svals = at<uint32_t>(bws, L.sorted_keys_in ? L.ivals1 : L.ivals0);
-    // capacity is not needed beyond clamping; counters[CNT_RENDERED] <= capacity is enforced by the caller's check
-    const uint32_t cap = 0xffffffffu;
-    find_view_start_kernel<<<1, 1, 0, s>>>(counters, cap, skeys, (uint32_t)view * T, counters + 2);
-    GSR_LAUNCH_CHECK();
-    if (keys_out || list_out) {
-        // upper bound on this view's instances: everything after its start; threads past the view return early
-        uint32_t host_n = 0;
-        GSR_CUDA_TRY(cudaMemcpyAsync(&host_n, counters + CNT_RENDERED, 4, cudaMemcpyDeviceToHost, s));
-        GSR_CUDA_TRY(cudaStreamSynchronize(s));
-        if (host_n > 0) {
-            export_view_kernel<<<(host_n + 255) / 256, 256, 0, s>>>(counters, cap, view, P, T, skeys, svals,
-                                                                    at<float>(gws, L.depths), counters + 2, keys_out,
-                                                                    list_out);
-            GSR_LAUNCH_CHECK();
-        }
-    }
-    if (ranges_out) {
-        export_ranges_kernel<<<(T + 255) / 256, 256, 0, s>>>(view, T, at<uint2>(iws, L.ranges), counters + 2,
-                                                             ranges_out);
+    if (keys_out || list_out || ranges_out) {
+        export_view_kernel<<<T, 128, 0, s>>>(view, P, T, at<uint2>(iws, L.ranges), at<float4>(bws, L.recB),
+                                             at<float4>(bws, L.recC), keys_out, list_out, ranges_out);
         GSR_LAUNCH_CHECK();
     }
     if (n_contrib_out) {

@@ -18,7 +18,7 @@ constexpr int NUM_COUNTERS = 64;
 // gradient-record slots
 enum : int { GR_MX = 0, GR_MY = 1, GR_CA = 2, GR_CB = 3, GR_CC = 4, GR_OP = 5, GR_DEPTH = 6, GR_COL = 7 };
 // counter slots
-enum : int { CNT_RENDERED = 0, CNT_OVERFLOW = 1, CNT_DEPTH_TILE = 8, CNT_INST_TILE = 24 };
+enum : int { CNT_RENDERED = 0, CNT_OVERFLOW = 1, CNT_SCRATCH = 2, CNT_ST_RENDERED = 3, CNT_NCHUNKS = 4, CNT_INST_TILE = 24 };
 
 // Device-side camera: GsrCamera plus the per-view constants the reference derives on the host
 // (focal lengths, rasterizer_impl.cu:227-228) or in every thread (clamp limits, forward.cu:87-99).
@@ -71,13 +71,21 @@ struct Layout : GsrLayout {
 
 inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
+// hierarchical binning geometry: a supertile is ST x ST tiles; its sorted instance list is cut into chunks of CHUNK
+constexpr int ST = 4;
+constexpr int ST_TILES = ST * ST;
+constexpr int CHUNK = 256;
+
 inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coeffs, int64_t capacity, Layout& L) {
     const size_t VP = (size_t)V * (size_t)P;
     const int tx = (W + TILE_X - 1) / TILE_X, ty = (H + TILE_Y - 1) / TILE_Y;
     const size_t VT = (size_t)V * tx * ty;
     L.tiles_x = tx;
     L.tiles_y = ty;
-    L.tile_bits = ceil_log2((uint32_t)VT);
+    L.stiles_x = (tx + ST - 1) / ST;
+    L.stiles_y = (ty + ST - 1) / ST;
+    const size_t VS = (size_t)V * L.stiles_x * L.stiles_y;
+    L.tile_bits = ceil_log2((uint32_t)VS);    // key bits of the instance sort: view * S + supertile
     L.depth_passes = 32 / RADIX_BITS;         // per-view segmented sort of the 32 depth bits
     L.tile_passes = (L.tile_bits + RADIX_BITS - 1) / RADIX_BITS;
     L.sorted_keys_in = (L.tile_passes & 1);   // which ping-pong buffer holds the result of the instance sort
@@ -87,11 +95,9 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     // geom
     L.counters = take(NUM_COUNTERS * sizeof(uint32_t));   // always at offset 0 (gsr_read_counters relies on it)
     L.cams = take((size_t)V * sizeof(CamDev));
-    L.depths = take(VP * 4);
     L.radii = take(VP * 4);
-    L.means2D = take(VP * 8);
+    L.rects = take(VP * 8);               // ushort4 tile rectangle (min.x, min.y, max.x, max.y), all zero when culled
     L.geomrec = take(VP * 32);            // (mean.x, mean.y, conic.a, conic.b | conic.c, opacity, depth, skip threshold)
-    L.tiles_touched = take(VP * 4);
     L.cov3D = take((size_t)P * 24);
     L.rgb = take(sh_coeffs > 0 ? VP * 16 : 0);     // float4 per (view, Gaussian): SH colours
     L.col4 = take((size_t)P * 16);                 // float4-packed colors_precomp / extra colours (per Gaussian)
@@ -110,12 +116,18 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     // binning
     o = 0;
     const size_t cap = (size_t)(capacity > 0 ? capacity : 0);
-    L.ikeys0 = take(cap * 4);
+    const size_t max_chunks = cap / CHUNK + VS + 1;
+    L.max_chunks = (int32_t)max_chunks;
+    L.ikeys0 = take(cap * 4);             // supertile instances: at most one per (Gaussian, tile) instance
     L.ikeys1 = take(cap * 4);
     L.ivals0 = take(cap * 4);
     L.ivals1 = take(cap * 4);
     L.ihist = take((size_t)MAX_PASSES * RADIX * 4);
     L.ilookback = take((size_t)MAX_PASSES * (sort_num_tiles((int64_t)cap, 4) + 1) * RADIX * 4);
+    L.st_ranges = take(VS * 8);
+    L.chunk_base = take((VS + 1) * 4);
+    L.chunk_key = take(max_chunks * 4);
+    L.chunk_counts = take(max_chunks * ST_TILES * 4);
     L.recA = take(cap * 16);
     L.recB = take(cap * 16);
     L.recC = take(cap * 16);
@@ -124,6 +136,7 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     // image
     o = 0;
     L.ranges = take(VT * 8);
+    L.tile_start = take((VT + 1) * 4);
     L.n_contrib = take((size_t)V * W * H * 4);
     L.final_T = take((size_t)V * W * H * 4);
     L.image_bytes = o;

@@ -86,8 +86,7 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
                   const float* __restrict__ scales, const float* __restrict__ rotations,
                   const float* __restrict__ cov3D_precomp, const float* __restrict__ sh,
                   int tiles_x, int tiles_y,
-                  float* __restrict__ depths, int32_t* __restrict__ radii, float2* __restrict__ means2D,
-                  float4* __restrict__ geomrec, uint32_t* __restrict__ tiles_touched,
+                  int32_t* __restrict__ radii, ushort4* __restrict__ rects, float4* __restrict__ geomrec,
                   float* __restrict__ rgb, uint8_t* __restrict__ clamped,
                   uint32_t* __restrict__ dkeys, uint32_t* __restrict__ dvals, int32_t* __restrict__ radii_out) {
     __shared__ CamDev cam;
@@ -103,7 +102,7 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
     const size_t idx = (size_t)v * P + g;
 
     int radius = 0;
-    uint32_t tiles = 0;
+    ushort4 rect = make_ushort4(0, 0, 0, 0);
     uint32_t depth_key = 0xffffffffu;      // culled Gaussians sort behind every visible one of their view
 
     const float x = means3D[3 * g], y = means3D[3 * g + 1], z = means3D[3 * g + 2];
@@ -151,20 +150,18 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
                     clamped[3 * idx + 1] = cl[1];
                     clamped[3 * idx + 2] = cl[2];
                 }
-                depths[idx] = depth;
-                means2D[idx] = pix;
                 const float op = opacities[g];
                 geomrec[2 * idx] = make_float4(pix.x, pix.y, conic_x, conic_y);          // the blend kernels' recA
                 geomrec[2 * idx + 1] = make_float4(conic_z, op, depth, blend_skip_threshold(op));   // ... and recB
                 radius = r_i;
-                tiles = area;
+                rect = make_ushort4((unsigned short)mn.x, (unsigned short)mn.y, (unsigned short)mx.x, (unsigned short)mx.y);
                 depth_key = __float_as_uint(depth);
             }
         }
     }
     radii[idx] = radius;
     if (radii_out) radii_out[idx] = radius;
-    tiles_touched[idx] = tiles;
+    rects[idx] = rect;
     dkeys[idx] = depth_key;                // sorted per view (segmented sort), so the key is the depth alone
     dvals[idx] = (uint32_t)g;
 }
@@ -187,8 +184,7 @@ int launch_preprocess(const CamDev* cams, int V, int P, int sh_coeffs, const flo
     dim3 grid((P + 255) / 256, V);
     preprocess_kernel<<<grid, 256, 0, s>>>(
         cams, P, sh_coeffs, means3D, opacities, scales, rotations, cov3D_precomp, sh, L.tiles_x, L.tiles_y,
-        at<float>(ws, L.depths), at<int32_t>(ws, L.radii), at<float2>(ws, L.means2D),
-        at<float4>(ws, L.geomrec), at<uint32_t>(ws, L.tiles_touched), at<float>(ws, L.rgb),
+        at<int32_t>(ws, L.radii), at<ushort4>(ws, L.rects), at<float4>(ws, L.geomrec), at<float>(ws, L.rgb),
         at<uint8_t>(ws, L.clamped), at<uint32_t>(ws, L.dkeys0), at<uint32_t>(ws, L.dvals0), radii_out);
     GSR_LAUNCH_CHECK();
     return GSR_OK;

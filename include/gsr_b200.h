@@ -69,14 +69,16 @@ typedef struct GsrWorkspaceSizes {
 /* Offsets (bytes) of the arrays inside the workspaces, for tests / tools that want to look at intermediate state. */
 typedef struct GsrLayout {
     /* geom workspace */
-    size_t cams, counters, depths, radii, means2D, geomrec, tiles_touched, cov3D, rgb, col4, ext4, clamped;
+    size_t cams, counters, radii, rects, geomrec, cov3D, rgb, col4, ext4, clamped;
     size_t dkeys0, dkeys1, dvals0, dvals1, dhist, dlookback, dcounters, block_sums, grad_rec;
-    /* binning workspace */
-    size_t ikeys0, ikeys1, ivals0, ivals1, ihist, ilookback, recA, recB, recC, recD;
+    /* binning workspace: supertile-instance sort arrays, chunk tables, per-instance records */
+    size_t ikeys0, ikeys1, ivals0, ivals1, ihist, ilookback, st_ranges, chunk_base, chunk_key, chunk_counts;
+    size_t recA, recB, recC, recD;
     /* image workspace */
-    size_t ranges, n_contrib, final_T;
-    /* derived integers */
-    int32_t tiles_x, tiles_y, tile_bits, depth_passes, tile_passes, sorted_keys_in, sorted_vals_in;
+    size_t ranges, tile_start, n_contrib, final_T;
+    /* derived integers: tiles per view, supertiles (4x4 tiles) per view, key bits / passes of the two sorts */
+    int32_t tiles_x, tiles_y, stiles_x, stiles_y, tile_bits, depth_passes, tile_passes, sorted_keys_in, sorted_vals_in;
+    int32_t max_chunks;
 } GsrLayout;
 
 /* Number of colour channels blended in the single pass: 3 (colour) or 6 (colour + fg/bg segmentation colours). */
