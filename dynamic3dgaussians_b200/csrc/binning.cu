@@ -207,19 +207,20 @@ __global__ void __launch_bounds__(256)
 st_ranges_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, const uint32_t* __restrict__ keys,
                  uint2* __restrict__ st_ranges) {
     const uint32_t n = min(counters[CNT_ST_RENDERED], capacity);
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t cur = keys[i];
-    if (i == 0) {
-        st_ranges[cur].x = 0;
-    } else {
-        const uint32_t prev = keys[i - 1];
-        if (cur != prev) {
-            st_ranges[prev].y = i;
-            st_ranges[cur].x = i;
+    // grid-stride: the count lives on the device, so the grid is sized for the SMs rather than for the capacity
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t cur = keys[i];
+        if (i == 0) {
+            st_ranges[cur].x = 0;
+        } else {
+            const uint32_t prev = keys[i - 1];
+            if (cur != prev) {
+                st_ranges[prev].y = i;
+                st_ranges[cur].x = i;
+            }
         }
+        if (i == n - 1) st_ranges[cur].y = n;
     }
-    if (i == n - 1) st_ranges[cur].y = n;
 }
 
 // single block: chunk_base[k] = exclusive scan of ceil(len_k / CHUNK) over the V*S supertile keys, chunk_base[VS] and
@@ -342,15 +343,16 @@ tile_scan_kernel(uint32_t VT, uint32_t capacity, uint32_t* __restrict__ tile_sta
                  uint32_t* __restrict__ counters) {
     __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
     uint32_t carry = 0;
-    for (uint32_t start = 0; start < VT; start += SCAN_BLOCK * 4) {
-        const uint32_t i0 = start + threadIdx.x * 4;
-        uint32_t v[4], sum = 0;
+    constexpr int IT = 16;
+    for (uint32_t start = 0; start < VT; start += SCAN_BLOCK * IT) {
+        const uint32_t i0 = start + threadIdx.x * IT;
+        uint32_t v[IT], sum = 0;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) { v[k] = i0 + k < VT ? tile_start[i0 + k] : 0u; sum += v[k]; }
+        for (int k = 0; k < IT; ++k) { v[k] = i0 + k < VT ? tile_start[i0 + k] : 0u; sum += v[k]; }
         uint32_t total;
         uint32_t ex = carry + block_exclusive_scan_256(sum, s_warp, total);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < IT; ++k) {
             if (i0 + k < VT) {
                 tile_start[i0 + k] = ex;
                 ranges[i0 + k] = make_uint2(min(ex, capacity), min(ex + v[k], capacity));
@@ -366,9 +368,9 @@ tile_scan_kernel(uint32_t VT, uint32_t capacity, uint32_t* __restrict__ tile_sta
 }
 
 // Per chunk: order-preserving compaction of its instances into the 16 tile lists, writing the blend records.
-// Thread i stages instance i's records in shared memory (geometry: two float4 of one 32-byte sector written by the
-// preprocess kernel; colour: one float4), ballots give every hit its position, and the records are then copied out by
-// flattened (tile, position) index so that consecutive threads store to consecutive list slots.
+// Thread i holds instance i's records in registers (geometry: two float4 of one 32-byte sector written by the
+// preprocess kernel; colour: one float4); ballots give every hit its list position (per tile: chunk offset + hits of
+// the earlier warps + hits of the lower lanes), and every thread stores its records once per tile it hits.
 template <bool EXTRA>
 __global__ void __launch_bounds__(CHUNK)
 scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __restrict__ chunk_key,
@@ -380,29 +382,25 @@ scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __
                        const float4* __restrict__ rgb_sh4, const float4* __restrict__ ext4,
                        float4* __restrict__ recA, float4* __restrict__ recB, float4* __restrict__ recC,
                        float4* __restrict__ recD) {
-    __shared__ float4 s_recA[CHUNK], s_recB[CHUNK], s_recC[CHUNK];
-    __shared__ float4 s_recD[EXTRA ? CHUNK : 1];
-    __shared__ uint8_t s_list[ST_TILES][CHUNK];
     __shared__ uint32_t s_wcnt[ST_TILES][CHUNK / 32];
     __shared__ uint32_t s_tbase[ST_TILES];            // list position of this chunk's first hit, per tile
-    __shared__ uint32_t s_tpre[ST_TILES + 1];         // prefix of the per-tile hit counts of this chunk
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t lt = (1u << lane) - 1u;
     ChunkInfo c;
     for (uint32_t cid = blockIdx.x; chunk_info(cid, counters, chunk_key, chunk_base, st_ranges, S, stiles_x, c);
          cid += gridDim.x) {
         uint32_t mask = 0;
+        float4 rA, rB, rC, rD;
         if ((uint32_t)tid < c.count) {
             const uint32_t gi = vals[c.first + tid];
             mask = st_hit_mask(rects[gi], c.ox, c.oy);
             if (mask) {
                 const uint32_t g = gi - c.view * (uint32_t)P;
-                s_recA[tid] = geomrec[2 * (size_t)gi];
-                s_recB[tid] = geomrec[2 * (size_t)gi + 1];
-                float4 col = col4 ? col4[g] : rgb_sh4[gi];
-                col.w = __uint_as_float(gi);
-                s_recC[tid] = col;
-                if (EXTRA) s_recD[tid] = ext4[g];
+                rA = geomrec[2 * (size_t)gi];
+                rB = geomrec[2 * (size_t)gi + 1];
+                rC = col4 ? col4[g] : rgb_sh4[gi];
+                rC.w = __uint_as_float(gi);
+                if (EXTRA) rD = ext4[g];
             }
         }
         if (tid < ST_TILES) {
@@ -413,13 +411,14 @@ scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __
                     chunk_offs[(size_t)cid * ST_TILES + tid];
             s_tbase[tid] = b;
         }
+        uint32_t bal[ST_TILES];
 #pragma unroll
         for (int t = 0; t < ST_TILES; ++t) {
-            const uint32_t bal = __ballot_sync(FULL, (mask >> t) & 1u);
-            if (lane == 0) s_wcnt[t][warp] = __popc(bal);
+            bal[t] = __ballot_sync(FULL, (mask >> t) & 1u);
+            if (lane == 0) s_wcnt[t][warp] = __popc(bal[t]);
         }
         __syncthreads();
-        if (tid < ST_TILES) {                             // per tile: exclusive prefix over the 8 warps, total
+        if (tid < ST_TILES) {                             // per tile: exclusive prefix over the 8 warps
             uint32_t run = 0;
 #pragma unroll
             for (int w = 0; w < CHUNK / 32; ++w) {
@@ -427,39 +426,22 @@ scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __
                 s_wcnt[tid][w] = run;
                 run += n;
             }
-            // exclusive prefix of the totals over the 16 tiles (threads 0..15 are one half-warp)
-            uint32_t inc = run;
-#pragma unroll
-            for (int o = 1; o < ST_TILES; o <<= 1) {
-                const uint32_t v = __shfl_up_sync(0x0000ffffu, inc, o, ST_TILES);
-                if (tid >= o) inc += v;
-            }
-            s_tpre[tid] = inc - run;
-            if (tid == ST_TILES - 1) s_tpre[ST_TILES] = inc;
         }
         __syncthreads();
+        // the hits of a warp on one tile occupy consecutive list slots: each store instruction writes one contiguous run
 #pragma unroll
         for (int t = 0; t < ST_TILES; ++t) {
-            const uint32_t bal = __ballot_sync(FULL, (mask >> t) & 1u);
-            if ((mask >> t) & 1u) s_list[t][s_wcnt[t][warp] + __popc(bal & lt)] = (uint8_t)tid;
-        }
-        __syncthreads();
-        const uint32_t hits = s_tpre[ST_TILES];
-        for (uint32_t h = tid; h < hits; h += CHUNK) {
-            uint32_t t = 0;
-#pragma unroll
-            for (int k = 1; k < ST_TILES; ++k) t += (h >= s_tpre[k]) ? 1u : 0u;
-            const uint32_t p = h - s_tpre[t];
-            const uint32_t e = s_list[t][p];
-            const uint32_t dst = s_tbase[t] + p;
-            if (dst < capacity) {
-                recA[dst] = s_recA[e];
-                recB[dst] = s_recB[e];
-                recC[dst] = s_recC[e];
-                if (EXTRA) recD[dst] = s_recD[e];
+            if ((mask >> t) & 1u) {
+                const uint32_t dst = s_tbase[t] + s_wcnt[t][warp] + __popc(bal[t] & lt);
+                if (dst < capacity) {
+                    recA[dst] = rA;
+                    recB[dst] = rB;
+                    recC[dst] = rC;
+                    if (EXTRA) recD[dst] = rD;
+                }
             }
         }
-        __syncthreads();                              // shared staging is reused by the next chunk
+        __syncthreads();                              // shared counters are reused by the next chunk
     }
 }
 
@@ -551,7 +533,7 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     const uint32_t chunk_grid = max_chunks < 148u * 8u ? max_chunks : 148u * 8u;   // persistent CTAs, 8 per SM
     stage_begin(ST_RANGES, s);
     GSR_CUDA_TRY(cudaMemsetAsync(st_ranges, 0, (size_t)VS * sizeof(uint2), s));
-    st_ranges_kernel<<<(cap + 255) / 256, 256, 0, s>>>(counters, cap, skeys, st_ranges);
+    st_ranges_kernel<<<min((cap + 255u) / 256u, 148u * 16u), 256, 0, s>>>(counters, cap, skeys, st_ranges);
     GSR_LAUNCH_CHECK();
     chunk_table_kernel<<<1, SCAN_BLOCK, 0, s>>>(VS, st_ranges, chunk_base, chunk_key, max_chunks, counters);
     GSR_LAUNCH_CHECK();
