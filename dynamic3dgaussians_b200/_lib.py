@@ -71,9 +71,9 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.gsr_workspace_layout.argtypes = [i32, i32, i32, i32, i32, i32, i64, C.POINTER(GsrLayout)]
     lib.gsr_forward_geometry.argtypes = [C.POINTER(GsrCamera), i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, sz,
                                          vp, vp, vp]
-    lib.gsr_forward_render.argtypes = [i32, i32, i32, i32, i32, i32, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.gsr_forward_render.argtypes = [i32, i32, i32, i32, i32, i32, i64, vp, vp, vp, i32] + [vp] * 9
     lib.gsr_read_counters.argtypes = [vp, vp, vp]
-    lib.gsr_backward.argtypes = [i32, i32, i32, i32, i32, i32, i64] + [vp] * 27
+    lib.gsr_backward.argtypes = [i32, i32, i32, i32, i32, i32, i64] + [vp] * 9 + [i32] + [vp] * 21
     lib.gsr_mark_visible.argtypes = [C.POINTER(GsrCamera), i32, vp, vp, vp]
     lib.gsr_export_view_binning.argtypes = [i32, i32, i32, i32, i32, i32, i32, i64, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.gsr_sort_temp_bytes.restype = sz

@@ -71,7 +71,7 @@ using namespace gsr;
 
 extern "C" {
 
-int gsr_abi_version(void) { return 1; }
+int gsr_abi_version(void) { return 2; }
 
 const char* gsr_strerror(int status) {
     switch (status) {
@@ -180,8 +180,9 @@ int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels,
 }
 
 int gsr_forward_render(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
-                       const float* colors_precomp, const float* extra_colors, void* geom_ws, void* binning_ws,
-                       void* image_ws, float* out_color, float* out_extra, float* out_depth, float* out_alpha,
+                       const float* colors_precomp, const float* extra_colors, const float* features,
+                       int num_features, void* geom_ws, void* binning_ws, void* image_ws, float* out_color,
+                       float* out_extra, float* out_depth, float* out_alpha, float* out_features,
                        gsr_stream_t stream) {
     cudaStream_t s = (cudaStream_t)stream;
     int rc = check_dims(P, V, W, H, channels, sh_coeffs, capacity);
@@ -190,14 +191,19 @@ int gsr_forward_render(int V, int P, int W, int H, int channels, int sh_coeffs, 
     if (capacity > 0 && !binning_ws) return GSR_ERR_INVALID_ARGUMENT;
     if (channels == 6 && (!extra_colors || !out_extra)) return GSR_ERR_INVALID_ARGUMENT;
     if ((sh_coeffs > 0) == (colors_precomp != nullptr) && P > 0) return GSR_ERR_INVALID_ARGUMENT;
+    if (features && (num_features != GSR_NUM_SEMANTIC_CHANNELS || !out_features)) return GSR_ERR_INVALID_ARGUMENT;
     Layout L;
     compute_layout(P, V, W, H, channels, sh_coeffs, capacity, L);
     rc = launch_binning(V, P, W, H, channels, sh_coeffs, capacity, colors_precomp, extra_colors, geom_ws, binning_ws,
                         image_ws, L, s);
     if (rc) return rc;
-    StageScope sc(ST_BLEND_FWD, s);
-    return launch_blend_forward(V, W, H, channels, geom_ws, binning_ws, image_ws, L, out_color, out_extra, out_depth,
-                                out_alpha, s);
+    {
+        StageScope sc(ST_BLEND_FWD, s);
+        rc = launch_blend_forward(V, W, H, channels, geom_ws, binning_ws, image_ws, L, out_color, out_extra, out_depth,
+                                  out_alpha, s);
+    }
+    if (rc || !features) return rc;
+    return launch_feature_forward(V, P, W, H, geom_ws, binning_ws, image_ws, L, features, out_features, s);
 }
 
 int gsr_read_counters(const void* geom_ws, uint32_t* counters_host, gsr_stream_t stream) {
@@ -210,11 +216,12 @@ int gsr_read_counters(const void* geom_ws, uint32_t* counters_host, gsr_stream_t
 
 int gsr_backward(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity, const float* means3D,
                  const float* opacities, const float* scales, const float* rotations, const float* cov3D_precomp,
-                 const float* sh, const float* colors_precomp, const float* extra_colors, const int32_t* radii,
-                 void* geom_ws, void* binning_ws, void* image_ws, const float* dL_dcolor, const float* dL_dextra,
-                 const float* dL_ddepth, const float* dL_dalpha, const float* label, float* dL_dmeans3D,
-                 float* dL_dmeans2D, float* dL_dcolors, float* dL_dextra_colors, float* dL_dopacity,
-                 float* dL_dscales, float* dL_drotations, float* dL_dcov3D, float* dL_dsh, gsr_stream_t stream) {
+                 const float* sh, const float* colors_precomp, const float* extra_colors, const float* features,
+                 int num_features, const int32_t* radii, void* geom_ws, void* binning_ws, void* image_ws,
+                 const float* dL_dcolor, const float* dL_dextra, const float* dL_ddepth, const float* dL_dalpha,
+                 const float* dL_dfeatures_img, const float* label, float* dL_dmeans3D, float* dL_dmeans2D,
+                 float* dL_dcolors, float* dL_dextra_colors, float* dL_dopacity, float* dL_dscales,
+                 float* dL_drotations, float* dL_dcov3D, float* dL_dsh, float* dL_dfeatures, gsr_stream_t stream) {
     cudaStream_t s = (cudaStream_t)stream;
     int rc = check_dims(P, V, W, H, channels, sh_coeffs, capacity);
     if (rc) return rc;
@@ -222,11 +229,21 @@ int gsr_backward(int V, int P, int W, int H, int channels, int sh_coeffs, int64_
     if (capacity > 0 && !binning_ws) return GSR_ERR_INVALID_ARGUMENT;
     if (P > 0 && !means3D) return GSR_ERR_INVALID_ARGUMENT;
     (void)opacities; (void)colors_precomp; (void)extra_colors;
+    if (features && num_features != GSR_NUM_SEMANTIC_CHANNELS) return GSR_ERR_INVALID_ARGUMENT;
     Layout L;
     compute_layout(P, V, W, H, channels, sh_coeffs, capacity, L);
     rc = launch_blend_backward(V, P, W, H, channels, geom_ws, binning_ws, image_ws, L, dL_dcolor, dL_dextra, dL_ddepth,
                                dL_dalpha, s);
     if (rc) return rc;
+    if (features && dL_dfeatures) {
+        if (dL_dfeatures_img)
+            rc = launch_feature_backward(V, P, W, H, geom_ws, binning_ws, image_ws, L, features, dL_dfeatures_img,
+                                         dL_dfeatures, s);
+        else
+            rc = cudaMemsetAsync(dL_dfeatures, 0, (size_t)P * GSR_NUM_SEMANTIC_CHANNELS * sizeof(float), s) == cudaSuccess
+                     ? GSR_OK : GSR_ERR_CUDA;
+        if (rc) return rc;
+    }
     StageScope sc(ST_PREPROCESS_BWD, s);
     return launch_preprocess_backward(V, P, W, H, channels, sh_coeffs, means3D, opacities, scales, rotations,
                                       cov3D_precomp, sh, radii, geom_ws, L, label, dL_dmeans3D, dL_dmeans2D,

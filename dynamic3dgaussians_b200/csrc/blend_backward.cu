@@ -14,6 +14,7 @@
 //    of 50), the 8 warps of the CTA are combined through shared memory, and ONE set of global atomics per
 //    (tile, Gaussian) is issued: the reference issues one set per (pixel, Gaussian) pair (backward.cu:586-649).
 #include "geom_math.cuh"
+#include "packed_reduce.cuh"
 
 namespace gsr {
 
@@ -22,47 +23,6 @@ namespace {
 constexpr int BATCH = 128;
 constexpr int SUB = 32;
 constexpr unsigned FULL = 0xffffffffu;
-
-// Packed butterfly: after run(), v[0] of lane l holds the warp-wide sum of the original v[slot(l)].
-template <int K>
-struct PackedReduce {
-    template <int KC, int OFF>
-    __device__ __forceinline__ static void step(float (&v)[K], int lane) {
-        if constexpr (OFF >= 1) {
-            constexpr int H = (KC + 1) / 2;
-            constexpr int PAIRS = KC / 2;
-            const bool up = (lane & OFF) != 0;
-#pragma unroll
-            for (int i = 0; i < PAIRS; ++i) {
-                const float send = up ? v[i] : v[i + H];
-                const float keep = up ? v[i + H] : v[i];
-                v[i] = keep + __shfl_xor_sync(FULL, send, OFF);
-            }
-            if constexpr ((KC & 1) != 0) v[H - 1] += __shfl_xor_sync(FULL, v[H - 1], OFF);
-            step<H, OFF / 2>(v, lane);
-        }
-    }
-    __device__ __forceinline__ static void run(float (&v)[K], int lane) { step<K, 16>(v, lane); }
-
-    template <int KC, int OFF>
-    __device__ __forceinline__ static void slot_step(int (&idx)[K], int lane) {
-        if constexpr (OFF >= 1) {
-            constexpr int H = (KC + 1) / 2;
-            constexpr int PAIRS = KC / 2;
-            const bool up = (lane & OFF) != 0;
-#pragma unroll
-            for (int i = 0; i < PAIRS; ++i) idx[i] = up ? idx[i + H] : idx[i];
-            slot_step<H, OFF / 2>(idx, lane);
-        }
-    }
-    __device__ __forceinline__ static int slot(int lane) {
-        int idx[K];
-#pragma unroll
-        for (int i = 0; i < K; ++i) idx[i] = i;
-        slot_step<K, 16>(idx, lane);
-        return idx[0];
-    }
-};
 
 template <int NCH>
 __global__ void __launch_bounds__(TILE_PIX)

@@ -193,6 +193,12 @@ int launch_blend_forward(int V, int W, int H, int channels, const void* geom_ws,
 int launch_blend_backward(int V, int P, int W, int H, int channels, void* geom_ws, const void* binning_ws,
                           const void* image_ws, const Layout& L, const float* dL_dcolor, const float* dL_dextra,
                           const float* dL_ddepth, const float* dL_dalpha, cudaStream_t s);
+int launch_feature_forward(int V, int P, int W, int H, const void* geom_ws, const void* binning_ws,
+                           const void* image_ws, const Layout& L, const float* features, float* out_features,
+                           cudaStream_t s);
+int launch_feature_backward(int V, int P, int W, int H, void* geom_ws, const void* binning_ws, const void* image_ws,
+                            const Layout& L, const float* features, const float* dL_dfeat_img, float* dL_dfeatures,
+                            cudaStream_t s);
 int launch_preprocess_backward(int V, int P, int W, int H, int channels, int sh_coeffs,
                                const float* means3D, const float* opacities, const float* scales,
                                const float* rotations, const float* cov3D_precomp, const float* sh,

@@ -21,6 +21,8 @@ import torch.nn as nn
 
 from . import _lib
 
+NUM_SEMANTIC_CHANNELS = 32          # R/cuda_rasterizer/config.h:17
+
 
 class GaussianRasterizationSettings(NamedTuple):
     image_height: int
@@ -109,7 +111,7 @@ def _stream_ptr(device) -> int:
 class RasterState:
     """Everything the backward needs from the forward (the reference keeps geomBuffer/binningBuffer/imgBuffer on ctx)."""
     __slots__ = ("V", "P", "W", "H", "channels", "sh_coeffs", "capacity", "num_rendered", "geom", "binning", "image",
-                 "radii", "layout")
+                 "radii", "layout", "feature_map")
 
 
 def workspace_layout(P, V, W, H, channels, sh_coeffs, capacity) -> _lib.GsrLayout:
@@ -120,9 +122,11 @@ def workspace_layout(P, V, W, H, channels, sh_coeffs, capacity) -> _lib.GsrLayou
 
 def forward_views(settings: Sequence[GaussianRasterizationSettings], means3D, opacities, colors_precomp=None,
                   scales=None, rotations=None, cov3D_precomp=None, shs=None, extra_colors=None, bg_extra=None,
-                  capacity: Optional[int] = None):
+                  capacity: Optional[int] = None, semantic_feature=None):
     """Runs the forward for V views.  Returns (color [V,3,H,W], extra [V,3,H,W] | None, depth [V,1,H,W],
-    alpha [V,1,H,W], radii [V,P] int32, RasterState).  With capacity=None the instance count is read back from the
+    alpha [V,1,H,W], radii [V,P] int32, RasterState).  With `semantic_feature` ([P,32] or the reference's [P,1,32],
+    R/diff_gaussian_rasterization/__init__.py:215) the 32-channel feature map [V,32,H,W] is left in
+    RasterState.feature_map.  With capacity=None the instance count is read back from the
     device once (the reference's one host sync, rasterizer_impl.cu:287); otherwise no sync happens and the caller
     checks `read_counters` later.
     """
@@ -153,6 +157,12 @@ def forward_views(settings: Sequence[GaussianRasterizationSettings], means3D, op
     if P > 0 and opacities is None:
         raise ValueError("opacities are required")
     channels = 6 if extra_colors is not None else 3
+    semantic_feature = _cuda_f32(semantic_feature, "semantic_feature")
+    if semantic_feature is not None:
+        if semantic_feature.numel() != P * NUM_SEMANTIC_CHANNELS:
+            raise ValueError(f"semantic_feature must hold {NUM_SEMANTIC_CHANNELS} channels per Gaussian "
+                             f"(R/cuda_rasterizer/config.h:17), got {tuple(semantic_feature.shape)}")
+        semantic_feature = semantic_feature.reshape(P, NUM_SEMANTIC_CHANNELS)
 
     cams = (_lib.GsrCamera * V)(*[camera_struct(s, bg_extra) for s in settings])
     sizes = _lib.GsrWorkspaceSizes()
@@ -176,15 +186,20 @@ def forward_views(settings: Sequence[GaussianRasterizationSettings], means3D, op
         extra = torch.empty((V, 3, H, W), dtype=torch.float32, device=dev) if channels == 6 else None
         depth = torch.empty((V, 1, H, W), dtype=torch.float32, device=dev)
         alpha = torch.empty((V, 1, H, W), dtype=torch.float32, device=dev)
+        feature_map = None
+        if semantic_feature is not None:
+            feature_map = torch.empty((V, NUM_SEMANTIC_CHANNELS, H, W), dtype=torch.float32, device=dev)
         _lib.check(lib.gsr_forward_render(V, P, W, H, channels, sh_coeffs, capacity, _lib.ptr(colors_precomp),
-                                          _lib.ptr(extra_colors), geom.data_ptr(), binning.data_ptr(),
-                                          image.data_ptr(), color.data_ptr(), _lib.ptr(extra), depth.data_ptr(),
-                                          alpha.data_ptr(), stream), "forward_render")
+                                          _lib.ptr(extra_colors), _lib.ptr(semantic_feature), NUM_SEMANTIC_CHANNELS,
+                                          geom.data_ptr(), binning.data_ptr(), image.data_ptr(), color.data_ptr(),
+                                          _lib.ptr(extra), depth.data_ptr(), alpha.data_ptr(), _lib.ptr(feature_map),
+                                          stream), "forward_render")
     st = RasterState()
     st.V, st.P, st.W, st.H, st.channels, st.sh_coeffs = V, P, W, H, channels, sh_coeffs
     st.capacity, st.num_rendered = int(capacity), num_rendered
     st.geom, st.binning, st.image, st.radii = geom, binning, image, radii
     st.layout = None
+    st.feature_map = feature_map
     return color, extra, depth, alpha, radii, st
 
 
@@ -195,8 +210,10 @@ def read_counters(st: RasterState):
 
 
 def backward_views(st: RasterState, means3D, opacities, colors_precomp, scales, rotations, cov3D_precomp, shs,
-                   extra_colors, dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, label=None, want_means2D=True, out=None):
-    """Returns dict of gradients summed over the views of the batch (means2D: [V,P,3]).  `out` may carry preallocated
+                   extra_colors, dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, label=None, want_means2D=True, out=None,
+                   semantic_feature=None, dL_dfeature=None):
+    """Returns dict of gradients summed over the views of the batch (means2D: [V,P,3]; features: [P,32] when
+    `semantic_feature` is given, with `dL_dfeature` [V,32,H,W] the cotangent of the feature map).  `out` may carry preallocated
     contiguous float32 tensors for means3D / colors / opacity / scales / rotations (e.g. views into one all-reduce
     slab, dist.GradSlab); every gradient is written, never accumulated."""
     lib = _lib.load()
@@ -217,6 +234,9 @@ def backward_views(st: RasterState, means3D, opacities, colors_precomp, scales, 
     dL_dextra = cot(dL_dextra, (V, 3, H, W)) if st.channels == 6 else None
     dL_ddepth = cot(dL_ddepth, (V, 1, H, W))
     dL_dalpha = cot(dL_dalpha, (V, 1, H, W))
+    if semantic_feature is not None:
+        semantic_feature = semantic_feature.reshape(P, NUM_SEMANTIC_CHANNELS).contiguous()
+        dL_dfeature = cot(dL_dfeature, (V, NUM_SEMANTIC_CHANNELS, H, W))
     out = out or {}
 
     def buf(key, shape):
@@ -237,6 +257,7 @@ def backward_views(st: RasterState, means3D, opacities, colors_precomp, scales, 
         rotations=buf("rotations", (P, 4)) if rotations is not None else None,
         cov3D=torch.empty((P, 6), **f32) if cov3D_precomp is not None else None,
         sh=torch.empty((P, st.sh_coeffs, 3), **f32) if shs is not None else None,
+        features=torch.empty((P, NUM_SEMANTIC_CHANNELS), **f32) if semantic_feature is not None else None,
     )
     if label is not None:
         label = label.to(torch.float32).reshape(-1).contiguous()
@@ -246,10 +267,11 @@ def backward_views(st: RasterState, means3D, opacities, colors_precomp, scales, 
     with torch.cuda.device(dev):
         _lib.check(lib.gsr_backward(V, P, W, H, st.channels, st.sh_coeffs, st.capacity, p(means3D), p(opacities),
                                     p(scales), p(rotations), p(cov3D_precomp), p(shs), p(colors_precomp),
-                                    p(extra_colors), p(st.radii), st.geom.data_ptr(), st.binning.data_ptr(),
-                                    st.image.data_ptr(), p(dL_dcolor), p(dL_dextra), p(dL_ddepth), p(dL_dalpha),
-                                    p(label), p(g["means3D"]), p(g["means2D"]), p(g["colors"]), p(g["extra"]),
-                                    p(g["opacity"]), p(g["scales"]), p(g["rotations"]), p(g["cov3D"]), p(g["sh"]),
+                                    p(extra_colors), p(semantic_feature), NUM_SEMANTIC_CHANNELS, p(st.radii),
+                                    st.geom.data_ptr(), st.binning.data_ptr(), st.image.data_ptr(), p(dL_dcolor),
+                                    p(dL_dextra), p(dL_ddepth), p(dL_dalpha), p(dL_dfeature), p(label),
+                                    p(g["means3D"]), p(g["means2D"]), p(g["colors"]), p(g["extra"]), p(g["opacity"]),
+                                    p(g["scales"]), p(g["rotations"]), p(g["cov3D"]), p(g["sh"]), p(g["features"]),
                                     _stream_ptr(dev)), "backward")
     return g
 
@@ -337,14 +359,13 @@ class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, semantic_feature, opacities, scales, rotations,
                 cov3Ds_precomp, raster_settings, label):
-        if semantic_feature is not None and torch.is_tensor(semantic_feature) and semantic_feature.numel() > 0:
-            raise NotImplementedError("32-channel semantic_feature rendering is not built yet (see DESIGN.md, scope)")
+        feat = _opt(semantic_feature) if torch.is_tensor(semantic_feature) else None
         if raster_settings.debug:
             cpu_args = tuple(a.detach().cpu().clone() if torch.is_tensor(a) else a for a in
                              (means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp))
             try:
                 out = forward_views([raster_settings], means3D, opacities, _opt(colors_precomp), _opt(scales),
-                                    _opt(rotations), _opt(cov3Ds_precomp), _opt(sh))
+                                    _opt(rotations), _opt(cov3Ds_precomp), _opt(sh), semantic_feature=feat)
                 torch.cuda.synchronize(means3D.device)
             except Exception:
                 torch.save(cpu_args, "snapshot_fw.dump")
@@ -352,28 +373,37 @@ class _RasterizeGaussians(torch.autograd.Function):
                 raise
         else:
             out = forward_views([raster_settings], means3D, opacities, _opt(colors_precomp), _opt(scales),
-                                _opt(rotations), _opt(cov3Ds_precomp), _opt(sh))
+                                _opt(rotations), _opt(cov3Ds_precomp), _opt(sh), semantic_feature=feat)
         color, _extra, depth, alpha, radii, st = out
         ctx.state = st
         ctx.raster_settings = raster_settings
         ctx.label = label if torch.is_tensor(label) else None
-        ctx.save_for_backward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
+        ctx.has_feat = feat is not None
+        ctx.save_for_backward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                              feat if feat is not None else means3D.new_empty(0))
         radii = radii[0]
-        feature_map = color.new_empty(0)
-        ctx.mark_non_differentiable(radii, feature_map)
+        if feat is not None:
+            feature_map = st.feature_map[0]
+            st.feature_map = None
+            ctx.mark_non_differentiable(radii)
+        else:
+            feature_map = color.new_empty(0)
+            ctx.mark_non_differentiable(radii, feature_map)
         return color[0], radii, feature_map, depth[0], alpha[0]
 
     @staticmethod
-    def backward(ctx, grad_color, _grad_radii, _grad_feature, grad_depth, grad_alpha):
-        means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp = ctx.saved_tensors
+    def backward(ctx, grad_color, _grad_radii, grad_feature, grad_depth, grad_alpha):
+        means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, feat = ctx.saved_tensors
         st = ctx.state
+        feat = feat if ctx.has_feat else None
 
         def run():
             return backward_views(st, means3D.contiguous(), opacities.contiguous(),
                                   _cuda_f32(_opt(colors_precomp), "colors_precomp"),
                                   _cuda_f32(_opt(scales), "scales"), _cuda_f32(_opt(rotations), "rotations"),
                                   _cuda_f32(_opt(cov3Ds_precomp), "cov3D_precomp"), _cuda_f32(_opt(sh), "shs"), None,
-                                  grad_color, None, grad_depth, grad_alpha, label=ctx.label)
+                                  grad_color, None, grad_depth, grad_alpha, label=ctx.label,
+                                  semantic_feature=feat, dL_dfeature=grad_feature if feat is not None else None)
         if ctx.raster_settings.debug:
             try:
                 g = run()
@@ -386,7 +416,10 @@ class _RasterizeGaussians(torch.autograd.Function):
             g = run()
         g_op = g["opacity"].reshape(opacities.shape)
         # order: means3D, means2D, sh, colors_precomp, semantic_feature, opacities, scales, rotations, cov3Ds, settings, label
-        return (g["means3D"], g["means2D"][0], g["sh"], g["colors"], None, g_op, g["scales"], g["rotations"],
+        g_feat = None
+        if feat is not None:
+            g_feat = g["features"].reshape(ctx.saved_tensors[7].shape)
+        return (g["means3D"], g["means2D"][0], g["sh"], g["colors"], g_feat, g_op, g["scales"], g["rotations"],
                 g["cov3D"], None, None)
 
 

@@ -114,11 +114,16 @@ int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels,
  * surplus instances are dropped and the overflow flag (gsr_check_overflow) is raised.
  * colors_precomp [P][3] (or null when SH colours were evaluated in stage 1); extra_colors [P][3] or null (channels==6).
  * Outputs: out_color [V][3][H][W], out_extra [V][3][H][W] (channels==6), out_depth [V][1][H][W], out_alpha [V][1][H][W].
+ * Semantic features (the vendored variant's 32-channel map, R/cuda_rasterizer/config.h:17, forward.cu:381-383,405-406):
+ * features [P][num_features] (nullable), num_features must be GSR_NUM_SEMANTIC_CHANNELS when features is given;
+ * out_features [V][32][H][W].  Channels 0..2 are composited over bg[0..2], the others over 0.
  */
+#define GSR_NUM_SEMANTIC_CHANNELS 32
 int gsr_forward_render(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
                        const float* colors_precomp, const float* extra_colors,
+                       const float* features, int num_features,
                        void* geom_ws, void* binning_ws, void* image_ws,
-                       float* out_color, float* out_extra, float* out_depth, float* out_alpha,
+                       float* out_color, float* out_extra, float* out_depth, float* out_alpha, float* out_features,
                        gsr_stream_t stream);
 
 /* Reads back (asynchronously, into host memory) the overflow flag and the instance count. Caller synchronises. */
@@ -130,18 +135,20 @@ int gsr_read_counters(const void* geom_ws, uint32_t* counters_host /* [4]: num_r
  * Image cotangents may be null (treated as zero).  Per-Gaussian gradients are SUMMED over the V views and written
  * (not accumulated) to the outputs; any output may be null.  dL_dmeans2D is [V][P][3] in the reference's NDC-scaled
  * units with z = 0 (backward.cu:520-521).  `label` ([P], nullable) is the per-Gaussian gradient mask the reference
- * applies in Python (R/diff_gaussian_rasterization/__init__.py:159-170).
+ * applies in Python (R/diff_gaussian_rasterization/__init__.py:159-170); it is not applied to dL_dfeatures (:164).
+ * features / dL_dfeatures_img [V][32][H][W] / dL_dfeatures [P][32]: the semantic-feature branch (backward.cu:594-611),
+ * all three null when the forward had no features.
  */
 int gsr_backward(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
                  const float* means3D, const float* opacities, const float* scales, const float* rotations,
                  const float* cov3D_precomp, const float* sh, const float* colors_precomp, const float* extra_colors,
-                 const int32_t* radii,
+                 const float* features, int num_features, const int32_t* radii,
                  void* geom_ws, void* binning_ws, void* image_ws,
                  const float* dL_dcolor, const float* dL_dextra, const float* dL_ddepth, const float* dL_dalpha,
-                 const float* label,
+                 const float* dL_dfeatures_img, const float* label,
                  float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors, float* dL_dextra_colors,
                  float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D, float* dL_dsh,
-                 gsr_stream_t stream);
+                 float* dL_dfeatures, gsr_stream_t stream);
 
 /* present[i] = (view * p_i).z > 0   (checkFrustum, rasterizer_impl.cu:54-66).  present is [P] bytes. */
 int gsr_mark_visible(const GsrCamera* cam_host, int P, const float* means3D, uint8_t* present, gsr_stream_t stream);

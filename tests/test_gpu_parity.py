@@ -229,3 +229,100 @@ def test_drop_in_module_autograd_and_label_mask():
     assert float(leaves["means3D"].grad[:1500].abs().max()) == 0 and float(leaves["means3D"].grad[1500:].abs().max()) > 0
     vis = Renderer(raster_settings=cam).markVisible(params['means3D'].detach())
     assert vis.dtype == torch.bool and bool(vis.all())
+
+
+def test_semantic_feature_map_forward_and_backward():
+    """The vendored variant's 32-channel feature map (forward.cu:381-383,405-406; backward.cu:594-611): bit-exact
+    against the reference's own CUDA forward, <= 1e-5 against the oracle (features ride along as extra channels there),
+    gradients (incl. dL/dfeature and the feature term in the geometry gradients) <= 1e-4 against the oracle's autograd;
+    several views at once equal the views one at a time."""
+    sc = scenes.make_scene_c1(8_000)
+    cs = scenes.camera_c1()
+    bg = (0.1, 0.2, 0.3)
+    st_, oc = settings_from_spec(cs, bg=bg)
+    rv = _rv(sc)
+    P = rv["means3D"].shape[0]
+    gen = torch.Generator().manual_seed(5)
+    feat = torch.rand(P, 32, generator=gen)
+    color, _, depth, alpha, radii, st = _fwd([st_], rv, semantic_feature=feat.cuda()[:, None, :])
+    fmap = st.feature_map
+    assert fmap.shape == (1, 32, cs.h, cs.w)
+    if ref_cuda.available():
+        rr = ref_cuda.RefRasterizer(st_)
+        ro = rr.forward(rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"],
+                        semantic=feat.cuda())
+        assert torch.equal(color[0], ro["color"])
+        assert torch.equal(fmap[0], ro["feature"])
+    leaves = {k: v.detach().cpu().clone().requires_grad_(True) for k, v in rv.items()}
+    fleaf = feat.clone().requires_grad_(True)
+    oc35 = oc._replace(bg=torch.cat([oc.bg.reshape(-1)[:3], oc.bg.reshape(-1)[:3], torch.zeros(29)]))
+    out = O.rasterize(oc35, leaves["means3D"], leaves["opacities"], colors_precomp=leaves["colors_precomp"],
+                      scales=leaves["scales"], rotations=leaves["rotations"], extra_colors=fleaf, collect_fragile=True)
+    ok = ~out["fragile"]
+    assert float((color[0].cpu() - out["color"][:3]).abs()[:, ok].max()) <= IMG_TOL
+    assert float((fmap[0].cpu() - out["color"][3:]).abs()[:, ok].max()) <= IMG_TOL
+    okf = ok.float()
+    gc, gf, gd, ga = [torch.randn(c, cs.h, cs.w, generator=gen) * okf for c in (3, 32, 1, 1)]
+    ((out["color"][:3] * gc).sum() + (out["color"][3:] * gf).sum() + (out["depth"] * gd).sum()
+     + (out["alpha"] * ga).sum()).backward()
+    g = RZ.backward_views(st, rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"], None,
+                          None, None, gc.cuda()[None], None, gd.cuda()[None], ga.cuda()[None],
+                          semantic_feature=feat.cuda(), dL_dfeature=gf.cuda()[None])
+    assert rel_err(g["features"], fleaf.grad) <= GRAD_TOL
+    assert rel_err(g["means3D"], leaves["means3D"].grad) <= GRAD_TOL
+    assert rel_err(g["colors"], leaves["colors_precomp"].grad) <= GRAD_TOL
+    assert rel_err(g["opacity"], leaves["opacities"].grad) <= GRAD_TOL
+    assert rel_err(g["scales"], leaves["scales"].grad) <= GRAD_TOL
+    assert rel_err(g["rotations"], leaves["rotations"].grad) <= GRAD_TOL
+    assert rel_err(g["means2D"][0], O.means2D_grad_ndc(out["pre"])) <= GRAD_TOL
+    # feature-only cotangent: the colour kernels contribute nothing, the geometry gradient is the feature term alone
+    g0 = RZ.backward_views(st, rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"], None,
+                           None, None, None, None, None, None, semantic_feature=feat.cuda(), dL_dfeature=gf.cuda()[None])
+    assert float(g0["colors"].abs().max()) == 0.0
+    assert float(g0["means3D"].abs().max()) > 0.0
+
+    # batched views == single views (forward exactly; feature gradients to summation order)
+    sc2 = scenes.make_scene_c2(20_000, seed=4)
+    cams = scenes.cameras_c2(3, w=320, h=180, f=233.0)
+    sets = [settings_from_spec(c, bg=bg)[0] for c in cams]
+    rv2 = _rv(sc2)
+    f2 = torch.rand(rv2["means3D"].shape[0], 32, generator=gen).cuda()
+    *_, stb = _fwd(sets, rv2, semantic_feature=f2)
+    gfs = torch.randn(3, 32, 180, 320, generator=gen).cuda()
+    gb = RZ.backward_views(stb, rv2["means3D"], rv2["opacities"], rv2["colors_precomp"], rv2["scales"], rv2["rotations"],
+                           None, None, None, None, None, None, None, semantic_feature=f2, dL_dfeature=gfs)
+    acc_f = torch.zeros_like(gb["features"])
+    acc_m = torch.zeros_like(gb["means3D"])
+    for v, s in enumerate(sets):
+        *_, s1 = _fwd([s], rv2, semantic_feature=f2)
+        assert torch.equal(s1.feature_map[0], stb.feature_map[v])
+        g1 = RZ.backward_views(s1, rv2["means3D"], rv2["opacities"], rv2["colors_precomp"], rv2["scales"],
+                               rv2["rotations"], None, None, None, None, None, None, None, semantic_feature=f2,
+                               dL_dfeature=gfs[v:v + 1])
+        acc_f += g1["features"]
+        acc_m += g1["means3D"]
+    assert rel_err(gb["features"], acc_f) <= GRAD_TOL
+    assert rel_err(gb["means3D"], acc_m) <= GRAD_TOL
+
+
+def test_drop_in_module_semantic_feature_autograd():
+    """GaussianRasterizer(...)(semantic_feature=[P,1,32]) returns the 5-tuple of the vendored variant
+    (R/diff_gaussian_rasterization/__init__.py:108) and routes dL/dfeature_map to gradient slot 5 (:166)."""
+    sc = scenes.make_scene_c1(3_000)
+    st_, _ = settings_from_spec(scenes.camera_c1(), bg=(0.0, 0.0, 0.0))
+    rv = {k: v.requires_grad_(True) for k, v in _rv(sc).items()}
+    P = rv["means3D"].shape[0]
+    feat = torch.rand(P, 1, 32, device="cuda", requires_grad=True)
+    rast = RZ.GaussianRasterizer(st_, returns=5)
+    means2D = torch.zeros_like(rv["means3D"], requires_grad=True)
+    color, radii, fmap, depth, alpha = rast(means3D=rv["means3D"], means2D=means2D, opacities=rv["opacities"],
+                                            semantic_feature=feat, colors_precomp=rv["colors_precomp"],
+                                            scales=rv["scales"], rotations=rv["rotations"])
+    assert fmap.shape == (32, st_.image_height, st_.image_width)
+    (fmap.square().sum() + color.sum()).backward()
+    assert feat.grad.shape == feat.shape and float(feat.grad.abs().max()) > 0
+    assert torch.isfinite(rv["means3D"].grad).all() and torch.isfinite(means2D.grad).all()
+    # no semantic_feature: empty feature map, as before
+    out = rast(means3D=rv["means3D"], means2D=means2D, opacities=rv["opacities"], colors_precomp=rv["colors_precomp"],
+               scales=rv["scales"], rotations=rv["rotations"])
+    assert out[2].numel() == 0
