@@ -215,8 +215,10 @@ def run_ours(args, world, rank, local):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier(world)
     e0.record()
+    t_host = time.perf_counter()
     for _ in range(args.steps):
         out, _ = step()
+    t_host = (time.perf_counter() - t_host) * 1e3 / max(args.steps, 1)       # host enqueue time per step (diagnostic)
     e1.record()
     barrier(world)
     ms = max_over_ranks(e0.elapsed_time(e1), world)
@@ -243,7 +245,7 @@ def run_ours(args, world, rank, local):
         ncon = st.image[L.n_contrib: L.n_contrib + st.V * st.W * st.H * 4].view(torch.int32)
         pairs = int(ncon.sum(dtype=torch.int64).item())
         R = st.num_rendered
-    res = dict(ms=ms, stages=stages, pairs=pairs, R=R, R1=R1 if st is not None else 0, clocks=clocks, views_per_rank=[len(p) for p in parts], parts=parts,
+    res = dict(ms=ms, host_ms=t_host, stages=stages, pairs=pairs, R=R, R1=R1 if st is not None else 0, clocks=clocks, views_per_rank=[len(p) for p in parts], parts=parts,
                launches=kernels_per_step(L, world > 1) * args.steps if st is not None else 0, state=st, dev=dev,
                rv=rv, sets=sets, sc=sc, lib=lib)
     return res
@@ -447,6 +449,7 @@ def main():
             "clocks": res["clocks"], "e2e": e2e, "gpu_launches": res["launches"],
             "roofline": roof,
             "stage_ms_rank0": {k: round(v, 4) for k, v in stages.items()},
+            "host_enqueue_ms_per_step_rank0": round(res["host_ms"], 3),
             "train_it_per_s_equiv": round(V * steps / (ms * 1e-3), 1),
         }
         if world == 1 and not args.no_cpu_baseline:

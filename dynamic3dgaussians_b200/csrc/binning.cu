@@ -337,18 +337,27 @@ tile_offsets_kernel(uint32_t VS, uint32_t S, int stiles_x, int tiles_x, int tile
         tile_start[(size_t)view * tiles_x * tiles_y + gy * (uint32_t)tiles_x + gx] = run;
 }
 
-// single block: exclusive scan of the per-tile counts in place (tile_start), ranges clamped to the capacity
+// single block: exclusive scan of the per-tile counts in place (tile_start), ranges clamped to the capacity; then a
+// counting sort of the (view, tile) indices by list length, longest first -> tile_order.  The blend kernels launch
+// their CTAs in that order, so the longest sequential chains start first and the short tiles fill in behind them
+// (the hardware dispatches CTAs in blockIdx order).
+constexpr int ORDER_BUCKETS = 1024;
 __global__ void __launch_bounds__(SCAN_BLOCK)
 tile_scan_kernel(uint32_t VT, uint32_t capacity, uint32_t* __restrict__ tile_start, uint2* __restrict__ ranges,
-                 uint32_t* __restrict__ counters) {
+                 uint32_t* __restrict__ tile_order, uint32_t* __restrict__ counters) {
     __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
-    uint32_t carry = 0;
+    __shared__ uint32_t s_bucket[ORDER_BUCKETS];
+    __shared__ uint32_t s_maxlen;
+    if (threadIdx.x == 0) s_maxlen = 0;
+    for (int b = threadIdx.x; b < ORDER_BUCKETS; b += SCAN_BLOCK) s_bucket[b] = 0;
+    __syncthreads();
+    uint32_t carry = 0, vmax = 0;
     constexpr int IT = 16;
     for (uint32_t start = 0; start < VT; start += SCAN_BLOCK * IT) {
         const uint32_t i0 = start + threadIdx.x * IT;
         uint32_t v[IT], sum = 0;
 #pragma unroll
-        for (int k = 0; k < IT; ++k) { v[k] = i0 + k < VT ? tile_start[i0 + k] : 0u; sum += v[k]; }
+        for (int k = 0; k < IT; ++k) { v[k] = i0 + k < VT ? tile_start[i0 + k] : 0u; sum += v[k]; vmax = max(vmax, v[k]); }
         uint32_t total;
         uint32_t ex = carry + block_exclusive_scan_256(sum, s_warp, total);
 #pragma unroll
@@ -364,6 +373,32 @@ tile_scan_kernel(uint32_t VT, uint32_t capacity, uint32_t* __restrict__ tile_sta
     if (threadIdx.x == 0) {
         tile_start[VT] = carry;
         if (carry > capacity) counters[CNT_OVERFLOW] = 1;
+    }
+    vmax = __reduce_max_sync(0xffffffffu, vmax);
+    if ((threadIdx.x & 31) == 0 && vmax > 0) atomicMax(&s_maxlen, vmax);
+    __syncthreads();
+    // bucket = ORDER_BUCKETS-1 for the longest lists ... 0 for the empty ones; sorted descending by bucket
+    const uint32_t q = s_maxlen / (ORDER_BUCKETS - 1) + 1;
+    for (uint32_t i = threadIdx.x; i < VT; i += SCAN_BLOCK) {
+        const uint2 r = ranges[i];
+        atomicAdd(&s_bucket[(ORDER_BUCKETS - 1) - min((r.y - r.x) / q, (uint32_t)ORDER_BUCKETS - 1)], 1u);
+    }
+    __syncthreads();
+    {   // exclusive scan of the bucket counts (4 per thread)
+        constexpr int BT = ORDER_BUCKETS / SCAN_BLOCK;
+        uint32_t c[BT], sum = 0;
+#pragma unroll
+        for (int k = 0; k < BT; ++k) { c[k] = s_bucket[threadIdx.x * BT + k]; sum += c[k]; }
+        uint32_t total;
+        uint32_t ex = block_exclusive_scan_256(sum, s_warp, total);
+#pragma unroll
+        for (int k = 0; k < BT; ++k) { s_bucket[threadIdx.x * BT + k] = ex; ex += c[k]; }
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < VT; i += SCAN_BLOCK) {
+        const uint2 r = ranges[i];
+        const uint32_t pos = atomicAdd(&s_bucket[(ORDER_BUCKETS - 1) - min((r.y - r.x) / q, (uint32_t)ORDER_BUCKETS - 1)], 1u);
+        tile_order[pos] = i;
     }
 }
 
@@ -498,8 +533,12 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     const uint32_t T = (uint32_t)L.tiles_x * (uint32_t)L.tiles_y;
     const uint32_t S = (uint32_t)L.stiles_x * (uint32_t)L.stiles_y;
     const uint32_t VT = (uint32_t)V * T, VS = (uint32_t)V * S;
-    if (VP == 0 || capacity <= 0) {
-        GSR_CUDA_TRY(cudaMemsetAsync(at<uint2>(iws, L.ranges), 0, (size_t)VT * sizeof(uint2), s));
+    if (VP == 0 || capacity <= 0) {     // every tile list empty: zero counts through the same scan (ranges, launch order)
+        if (VT == 0) return GSR_OK;
+        GSR_CUDA_TRY(cudaMemsetAsync(at<uint32_t>(iws, L.tile_start), 0, ((size_t)VT + 1) * sizeof(uint32_t), s));
+        tile_scan_kernel<<<1, SCAN_BLOCK, 0, s>>>(VT, 0u, at<uint32_t>(iws, L.tile_start), at<uint2>(iws, L.ranges),
+                                                  at<uint32_t>(iws, L.tile_order), at<uint32_t>(gws, L.counters));
+        GSR_LAUNCH_CHECK();
         return GSR_OK;
     }
     const uint32_t cap = (uint32_t)capacity;
@@ -543,7 +582,8 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     tile_offsets_kernel<<<(VS + 3) / 4, 128, 0, s>>>(VS, S, L.stiles_x, L.tiles_x, L.tiles_y, chunk_base, max_chunks,
                                                     chunk_counts, tile_start);
     GSR_LAUNCH_CHECK();
-    tile_scan_kernel<<<1, SCAN_BLOCK, 0, s>>>(VT, cap, tile_start, at<uint2>(iws, L.ranges), counters);
+    tile_scan_kernel<<<1, SCAN_BLOCK, 0, s>>>(VT, cap, tile_start, at<uint2>(iws, L.ranges),
+                                              at<uint32_t>(iws, L.tile_order), counters);
     GSR_LAUNCH_CHECK();
     stage_end(ST_RANGES, s);
     StageScope sc(ST_GATHER, s);

@@ -26,7 +26,7 @@ constexpr unsigned FULL = 0xffffffffu;
 
 template <int NCH>
 __global__ void __launch_bounds__(TILE_PIX)
-blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ recA,
+blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const float4* __restrict__ recA,
                       const float4* __restrict__ recB, const float4* __restrict__ recC,
                       const float4* __restrict__ recD, const CamDev* __restrict__ cams, int W, int H, int tiles_x,
                       int tiles_per_view, const uint32_t* __restrict__ n_contrib, const float* __restrict__ final_T,
@@ -48,7 +48,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     static_assert(SUB == 32 && BATCH <= TILE_PIX, "work lists are one 32-bit word per (warp, sub-batch)");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int vt = blockIdx.x;
+    const int vt = (int)tile_order[blockIdx.x];
     const int view = vt / tiles_per_view;
     const int tile = vt - view * tiles_per_view;
     const int tile_yi = tile / tiles_x, tile_xi = tile - tile_yi * tiles_x;
@@ -268,10 +268,10 @@ int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, c
     const float* fT = at<float>(iws, L.final_T);
     float* rec = at<float>(gws, L.grad_rec);
     if (channels == 3) {
-        blend_backward_kernel<3><<<blocks, TILE_PIX, 0, s>>>(ranges, A, B, C, D, cams, W, H, L.tiles_x, T, nc, fT,
+        blend_backward_kernel<3><<<blocks, TILE_PIX, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H, L.tiles_x, T, nc, fT,
                                                             dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, rec);
     } else if (channels == 6) {
-        blend_backward_kernel<6><<<blocks, TILE_PIX, 0, s>>>(ranges, A, B, C, D, cams, W, H, L.tiles_x, T, nc, fT,
+        blend_backward_kernel<6><<<blocks, TILE_PIX, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H, L.tiles_x, T, nc, fT,
                                                             dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, rec);
     } else {
         return GSR_ERR_UNSUPPORTED;

@@ -58,7 +58,7 @@ __device__ __forceinline__ void stage_batch(int tid, int lane, int warp, int nb,
 }
 
 __global__ void __launch_bounds__(TILE_PIX, 2)
-feature_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ recA,
+feature_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const float4* __restrict__ recA,
                        const float4* __restrict__ recB, const float4* __restrict__ recC,
                        const float* __restrict__ feat, int P, const CamDev* __restrict__ cams, int W, int H,
                        int tiles_x, int tiles_per_view, const uint32_t* __restrict__ n_contrib,
@@ -70,7 +70,7 @@ feature_forward_kernel(const uint2* __restrict__ ranges, const float4* __restric
     __shared__ uint32_t s_wmask[TILE_PIX / 32][FB / 32];
     __shared__ uint32_t s_max;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int vt = blockIdx.x;
+    const int vt = (int)tile_order[blockIdx.x];
     const int view = vt / tiles_per_view;
     const int tile = vt - view * tiles_per_view;
     const int tile_yi = tile / tiles_x, tile_xi = tile - tile_yi * tiles_x;
@@ -138,7 +138,7 @@ constexpr int KT = 6 + NF;          // values per (warp, Gaussian)
 constexpr int SUBF = 32;
 
 __global__ void __launch_bounds__(TILE_PIX)
-feature_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ recA,
+feature_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const float4* __restrict__ recA,
                         const float4* __restrict__ recB, const float4* __restrict__ recC,
                         const float* __restrict__ feat, int P, const CamDev* __restrict__ cams, int W, int H,
                         int tiles_x, int tiles_per_view, const uint32_t* __restrict__ n_contrib,
@@ -154,7 +154,7 @@ feature_backward_kernel(const uint2* __restrict__ ranges, const float4* __restri
     extern __shared__ float s_part_dyn[];             // [8 warps][SUBF][KT]
     float (*s_part)[SUBF][KT] = reinterpret_cast<float (*)[SUBF][KT]>(s_part_dyn);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int vt = blockIdx.x;
+    const int vt = (int)tile_order[blockIdx.x];
     const int view = vt / tiles_per_view;
     const int tile = vt - view * tiles_per_view;
     const int tile_yi = tile / tiles_x, tile_xi = tile - tile_yi * tiles_x;
@@ -288,7 +288,7 @@ int launch_feature_forward(int V, int P, int W, int H, const void* gws, const vo
     const int T = L.tiles_x * L.tiles_y;
     if (V * T == 0) return GSR_OK;
     feature_forward_kernel<<<V * T, TILE_PIX, 0, s>>>(
-        at<uint2>(iws, L.ranges), at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC), features,
+        at<uint2>(iws, L.ranges), at<uint32_t>(iws, L.tile_order), at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC), features,
         P, at<CamDev>(gws, L.cams), W, H, L.tiles_x, T, at<uint32_t>(iws, L.n_contrib), at<float>(iws, L.final_T),
         out_features);
     GSR_LAUNCH_CHECK();
@@ -307,7 +307,7 @@ int launch_feature_backward(int V, int P, int W, int H, void* gws, const void* b
         attr_set = true;
     }
     feature_backward_kernel<<<V * T, TILE_PIX, dyn, s>>>(
-        at<uint2>(iws, L.ranges), at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC), features,
+        at<uint2>(iws, L.ranges), at<uint32_t>(iws, L.tile_order), at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC), features,
         P, at<CamDev>(gws, L.cams), W, H, L.tiles_x, T, at<uint32_t>(iws, L.n_contrib), at<float>(iws, L.final_T),
         dL_dfeat_img, at<float>(gws, L.grad_rec), dL_dfeatures);
     GSR_LAUNCH_CHECK();

@@ -24,7 +24,7 @@ constexpr int BATCH = 128;
 
 template <int NCH>
 __global__ void __launch_bounds__(TILE_PIX)
-blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ recA,
+blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const float4* __restrict__ recA,
                      const float4* __restrict__ recB, const float4* __restrict__ recC,
                      const float4* __restrict__ recD, const CamDev* __restrict__ cams, int W, int H, int tiles_x,
                      int tiles_per_view, float* __restrict__ out_color, float* __restrict__ out_extra,
@@ -40,7 +40,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
     static_assert(BATCH <= TILE_PIX && BATCH % 32 == 0, "one pre-pass thread per staged Gaussian");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int vt = blockIdx.x;
+    const int vt = (int)tile_order[blockIdx.x];
     const int view = vt / tiles_per_view;
     const int tile = vt - view * tiles_per_view;
     const int tile_yi = tile / tiles_x, tile_xi = tile - tile_yi * tiles_x;
@@ -187,10 +187,10 @@ int launch_blend_forward(int V, int W, int H, int channels, const void* gws, con
     uint32_t* nc = at<uint32_t>(iws, L.n_contrib);
     float* fT = at<float>(iws, L.final_T);
     if (channels == 3) {
-        blend_forward_kernel<3><<<blocks, TILE_PIX, 0, s>>>(ranges, A, B, C, D, cams, W, H, L.tiles_x, T, out_color,
+        blend_forward_kernel<3><<<blocks, TILE_PIX, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H, L.tiles_x, T, out_color,
                                                            out_extra, out_depth, out_alpha, nc, fT);
     } else if (channels == 6) {
-        blend_forward_kernel<6><<<blocks, TILE_PIX, 0, s>>>(ranges, A, B, C, D, cams, W, H, L.tiles_x, T, out_color,
+        blend_forward_kernel<6><<<blocks, TILE_PIX, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H, L.tiles_x, T, out_color,
                                                            out_extra, out_depth, out_alpha, nc, fT);
     } else {
         return GSR_ERR_UNSUPPORTED;

@@ -137,6 +137,7 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     o = 0;
     L.ranges = take(VT * 8);
     L.tile_start = take((VT + 1) * 4);
+    L.tile_order = take(VT * 4);          // (view, tile) indices, longest list first: the blend kernels' launch order
     L.n_contrib = take((size_t)V * W * H * 4);
     L.final_T = take((size_t)V * W * H * 4);
     L.image_bytes = o;

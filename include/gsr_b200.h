@@ -75,7 +75,7 @@ typedef struct GsrLayout {
     size_t ikeys0, ikeys1, ivals0, ivals1, ihist, ilookback, st_ranges, chunk_base, chunk_key, chunk_counts;
     size_t recA, recB, recC, recD;
     /* image workspace */
-    size_t ranges, tile_start, n_contrib, final_T;
+    size_t ranges, tile_start, tile_order, n_contrib, final_T;
     /* derived integers: tiles per view, supertiles (4x4 tiles) per view, key bits / passes of the two sorts */
     int32_t tiles_x, tiles_y, stiles_x, stiles_y, tile_bits, depth_passes, tile_passes, sorted_keys_in, sorted_vals_in;
     int32_t max_chunks;
