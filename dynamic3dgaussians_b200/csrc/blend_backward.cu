@@ -13,6 +13,8 @@
 //  * the 7+C per-Gaussian partial sums of a warp are reduced with a packed butterfly (12 shuffles for 10 values instead
 //    of 50), the 8 warps of the CTA are combined through shared memory, and ONE set of global atomics per
 //    (tile, Gaussian) is issued: the reference issues one set per (pixel, Gaussian) pair (backward.cu:586-649).
+#include <cstdlib>
+
 #include "geom_math.cuh"
 #include "packed_reduce.cuh"
 
@@ -245,6 +247,253 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     }
 }
 
+
+// ---- two pixels per thread ------------------------------------------------------------------------------------------
+// CTA = 128 threads = 4 warps; a warp owns an 8x8 pixel patch, a lane the two pixels (x, y) and (x, y + 4) of it, so
+// dx is shared by the pair and the per-(warp, Gaussian) costs (record loads, loop control, the packed butterfly, the
+// partial-sum store) are paid once per 64 pixels instead of once per 32.  The pair's arithmetic is issued as packed
+// fp32x2 instructions (FFMA2 / FMUL2 / FADD2, sm_100) where both pixels do the same operation; the kernel is bound by
+// instruction issue, not by the FMA pipe.  Invalid pixels run the same instructions with alpha = 0 and a zeroed
+// dL/dalpha, which leaves T, the recurrence and every sum unchanged (no divergent region).
+__device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
+__device__ __forceinline__ float2 splat(float a) { return make_float2(a, a); }
+
+constexpr int NT2 = 128;
+constexpr int NW2 = NT2 / 32;
+
+template <int NCH>
+__global__ void __launch_bounds__(NT2, 8)
+blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
+                       const float4* __restrict__ recA, const float4* __restrict__ recB,
+                       const float4* __restrict__ recC, const float4* __restrict__ recD,
+                       const CamDev* __restrict__ cams, int W, int H, int tiles_x, int tiles_per_view,
+                       const uint32_t* __restrict__ n_contrib, const float* __restrict__ final_T,
+                       const float* __restrict__ dL_dcolor, const float* __restrict__ dL_dextra,
+                       const float* __restrict__ dL_ddepth, const float* __restrict__ dL_dalpha,
+                       float* __restrict__ grad_rec) {
+    constexpr bool EXTRA = NCH > 3;
+    constexpr int K = GR_COL + NCH;
+    __shared__ __align__(128) float4 sA[2][BATCH];
+    __shared__ __align__(128) float4 sB[2][BATCH];
+    __shared__ __align__(128) float4 sC[2][BATCH];
+    __shared__ __align__(128) float4 sD[EXTRA ? 2 : 1][EXTRA ? BATCH : 1];
+    __shared__ __align__(8) uint64_t full[2];
+    __shared__ float s_part[NW2][SUB][GRAD_REC];
+    __shared__ uint32_t s_mask[NW2];
+    __shared__ uint32_t s_wmask[NW2][BATCH / SUB];
+    __shared__ uint32_t s_max;
+    static_assert(BATCH == NT2, "one pre-pass thread per staged Gaussian");
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int vt = (int)tile_order[blockIdx.x];
+    const int view = vt / tiles_per_view;
+    const int tile = vt - view * tiles_per_view;
+    const int tile_yi = tile / tiles_x, tile_xi = tile - tile_yi * tiles_x;
+    const int px = tile_xi * TILE_X + (warp & 1) * 8 + (lane & 7);
+    const int py0 = tile_yi * TILE_Y + (warp >> 1) * 8 + (lane >> 3);
+    const int py1 = py0 + 4;
+    const bool in0 = px < W && py0 < H, in1 = px < W && py1 < H;
+    const float npx = -(float)px;
+    const float2 npy = f2(-(float)py0, -(float)py1);
+    const size_t HW = (size_t)H * W;
+    const size_t pix0 = (size_t)view * HW + (size_t)py0 * W + px, pix1 = pix0 + 4 * (size_t)W;
+
+    const uint2 range = ranges[vt];
+    const uint32_t lc0 = in0 ? n_contrib[pix0] : 0u, lc1 = in1 ? n_contrib[pix1] : 0u;
+    float2 T = f2(in0 ? final_T[pix0] : 0.0f, in1 ? final_T[pix1] : 0.0f);
+
+    if (tid == 0) {
+        s_max = 0;
+        mbar_init(&full[0], 1);
+        mbar_init(&full[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    const uint32_t warp_last = __reduce_max_sync(FULL, max(lc0, lc1));   // nothing at or past it matters to this warp
+    if (lane == 0 && warp_last > 0) atomicMax(&s_max, warp_last);
+    __syncthreads();
+    const int n_proc = (int)min(s_max, range.y - range.x);
+    const int rounds = (n_proc + BATCH - 1) / BATCH;
+    if (rounds == 0) return;
+
+    auto issue = [&](int r) {   // thread 0 only; round r walks chunk (rounds-1-r)
+        const int buf = r & 1;
+        const int c = rounds - 1 - r;
+        const int nb = min(BATCH, n_proc - c * BATCH);
+        const uint32_t bytes = (uint32_t)nb * 16u;
+        const size_t src = (size_t)range.x + (size_t)c * BATCH;
+        mbar_expect_tx(&full[buf], bytes * (EXTRA ? 4u : 3u));
+        tma_load_1d(sA[buf], recA + src, bytes, &full[buf]);
+        tma_load_1d(sB[buf], recB + src, bytes, &full[buf]);
+        tma_load_1d(sC[buf], recC + src, bytes, &full[buf]);
+        if (EXTRA) tma_load_1d(sD[buf], recD + src, bytes, &full[buf]);
+    };
+    if (tid == 0) {
+        issue(0);
+        if (rounds > 1) issue(1);
+    }
+
+    // pixel cotangents (x: first pixel, y: second)
+    float2 gC[NCH];
+    float2 gD = splat(0.0f), gA = splat(0.0f);
+#pragma unroll
+    for (int k = 0; k < NCH; ++k) gC[k] = splat(0.0f);
+    const CamDev& cam = cams[view];
+    float2 acc = splat(0.0f);
+    {
+        const size_t o0 = pix0 - (size_t)view * HW, o1 = pix1 - (size_t)view * HW;
+        if (dL_dcolor) {
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) {
+                const float* g = dL_dcolor + ((size_t)view * 3 + ch) * HW;
+                gC[ch] = f2(in0 ? g[o0] : 0.0f, in1 ? g[o1] : 0.0f);
+                acc.x += cam.bg[ch] * gC[ch].x;
+                acc.y += cam.bg[ch] * gC[ch].y;
+            }
+        }
+        if (EXTRA && dL_dextra) {
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) {
+                const float* g = dL_dextra + ((size_t)view * 3 + ch) * HW;
+                gC[NCH - 3 + ch] = f2(in0 ? g[o0] : 0.0f, in1 ? g[o1] : 0.0f);
+                acc.x += cam.bg[3 + ch] * gC[NCH - 3 + ch].x;
+                acc.y += cam.bg[3 + ch] * gC[NCH - 3 + ch].y;
+            }
+        }
+        if (dL_ddepth) gD = f2(in0 ? dL_ddepth[pix0] : 0.0f, in1 ? dL_ddepth[pix1] : 0.0f);
+        if (dL_dalpha) gA = f2(in0 ? dL_dalpha[pix0] : 0.0f, in1 ? dL_dalpha[pix1] : 0.0f);
+    }
+    float2 last_alpha = splat(0.0f), last_s = splat(0.0f);
+
+    const int my_slot = PackedReduce<K>::slot(lane);
+    const unsigned slot_peers = __match_any_sync(FULL, my_slot);
+    const bool writer = lane == (__ffs(slot_peers) - 1);
+    const float tile_x0 = (float)(tile_xi * TILE_X), tile_y0 = (float)(tile_yi * TILE_Y);
+
+    for (int r = 0; r < rounds; ++r) {
+        const int buf = r & 1;
+        const int c = rounds - 1 - r;
+        const int nb = min(BATCH, n_proc - c * BATCH);
+        mbar_wait(&full[buf], (uint32_t)((r >> 1) & 1));
+        {   // pre-pass: per-warp work lists, Gaussian `tid` x the four 8x8 patches
+            uint32_t m4 = 0u;
+            if (tid < nb) {
+                const float4 a = sA[buf][tid];
+                const float4 b = sB[buf][tid];
+                const uint32_t m8 = blend_patch_mask(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
+                const uint32_t t = m8 | (m8 >> 2);
+                m4 = (t & 3u) | ((t >> 2) & 0xcu);
+            }
+#pragma unroll
+            for (int w = 0; w < NW2; ++w) {
+                const uint32_t bal = __ballot_sync(FULL, (m4 >> w) & 1u);
+                if (lane == 0) s_wmask[w][warp] = bal;
+            }
+        }
+        __syncthreads();
+        for (int sub = (nb - 1) / SUB; sub >= 0; --sub) {
+            const int lo = sub * SUB;
+            const int hi = min(lo + SUB, nb);
+            uint32_t hit_mask = 0;
+            uint32_t m = s_wmask[warp][sub];
+            {
+                const uint32_t base = (uint32_t)(c * BATCH + lo);
+                if (warp_last <= base) m = 0u;
+                else if (warp_last - base < 32u) m &= (1u << (warp_last - base)) - 1u;
+            }
+            while (m != 0u) {                                       // warp-uniform, back to front
+                const int jl = 31 - __clz(m);
+                m &= ~(1u << jl);
+                const int j = lo + jl;
+                const float4 a = sA[buf][j];
+                const float4 b = sB[buf][j];
+                const uint32_t pos = (uint32_t)(c * BATCH + j);
+                // blend_power (geom_math.cuh) on the pixel pair; identical roundings per component
+                const float dx = __fadd_rn(a.x, npx);
+                const float2 dy = __fadd2_rn(splat(a.y), npy);
+                const float dxca = __fmul_rn(dx, a.z), ndxcb = __fmul_rn(dx, -a.w);
+                const float2 t3 = __fmul2_rn(dy, __fmul2_rn(dy, splat(b.x)));
+                const float2 q = __ffma2_rn(splat(dx), splat(dxca), t3);
+                const float2 power = __ffma2_rn(q, splat(-0.5f), __fmul2_rn(dy, splat(ndxcb)));
+                const bool pre0 = (pos < lc0) && !(power.x > 0.0f) && !(power.x < b.w);
+                const bool pre1 = (pos < lc1) && !(power.y > 0.0f) && !(power.y < b.w);
+                if (!__any_sync(FULL, pre0 || pre1)) continue;      // warp-uniform
+                const float2 G = f2(expf(fminf(power.x, 0.0f)), expf(fminf(power.y, 0.0f)));
+                const float2 og = __fmul2_rn(splat(b.y), G);
+                float2 alpha = f2(fminf(0.99f, og.x), fminf(0.99f, og.y));
+                const bool valid0 = pre0 && !(alpha.x < 1.0f / 255.0f);
+                const bool valid1 = pre1 && !(alpha.y < 1.0f / 255.0f);
+                alpha.x = valid0 ? alpha.x : 0.0f;
+                alpha.y = valid1 ? alpha.y : 0.0f;
+                const float2 om = __fadd2_rn(splat(1.0f), f2(-alpha.x, -alpha.y));
+                T = f2(__fdividef(T.x, om.x), __fdividef(T.y, om.y));     // transmittance in front of this Gaussian
+                const float2 w = __fmul2_rn(alpha, T);
+                const float4 col = sC[buf][j];
+                float2 s = __ffma2_rn(splat(col.x), gC[0],
+                           __ffma2_rn(splat(col.y), gC[1],
+                           __ffma2_rn(splat(col.z), gC[2], __ffma2_rn(splat(b.z), gD, gA))));
+                float v[K];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) v[GR_COL + k] = fmaf(w.y, gC[k].y, w.x * gC[k].x);
+                if (EXTRA) {
+                    const float4 e = sD[buf][j];
+                    s = __ffma2_rn(splat(e.x), gC[NCH - 3],
+                        __ffma2_rn(splat(e.y), gC[NCH - 2], __ffma2_rn(splat(e.z), gC[NCH - 1], s)));
+#pragma unroll
+                    for (int k = NCH - 3; k < NCH; ++k) v[GR_COL + k] = fmaf(w.y, gC[k].y, w.x * gC[k].x);
+                }
+                v[GR_DEPTH] = fmaf(w.y, gD.y, w.x * gD.x);
+                // colour-behind recurrence (see header); with alpha = 0 it only flushes the pending term
+                acc = __ffma2_rn(last_alpha, __fadd2_rn(last_s, f2(-acc.x, -acc.y)), acc);
+                last_s = s;
+                last_alpha = alpha;
+                float2 gq = __fmul2_rn(G, __fmul2_rn(__fadd2_rn(s, f2(-acc.x, -acc.y)), T));   // G * dL/dalpha
+                gq.x = valid0 ? gq.x : 0.0f;
+                gq.y = valid1 ? gq.y : 0.0f;
+                const float2 am = __fmul2_rn(splat(b.y), gq);
+                const float2 uy = __fmul2_rn(am, dy);
+                const float sam = am.x + am.y;
+                v[GR_MX] = sam * dx;
+                v[GR_MY] = uy.x + uy.y;
+                v[GR_CA] = v[GR_MX] * dx;
+                v[GR_CB] = v[GR_MY] * dx;
+                v[GR_CC] = fmaf(uy.y, dy.y, uy.x * dy.x);
+                v[GR_OP] = gq.x + gq.y;
+                PackedReduce<K>::run(v, lane);
+                if (writer) s_part[warp][jl][my_slot] = v[0];
+                hit_mask |= 1u << jl;
+            }
+            if (lane == 0) s_mask[warp] = hit_mask;
+            __syncthreads();
+            {   // combine the 4 warps; one atomic set per (tile, Gaussian)
+                const int jl = tid >> 2, kk = tid & 3;
+                if (lo + jl < hi) {
+                    uint32_t any = 0;
+#pragma unroll
+                    for (int w = 0; w < NW2; ++w) any |= ((s_mask[w] >> jl) & 1u) << w;
+                    if (any) {
+                        const uint32_t gi = __float_as_uint(sC[buf][lo + jl].w);
+                        float* rec = grad_rec + (size_t)gi * GRAD_REC;
+#pragma unroll
+                        for (int k = 0; k < (K + 3) / 4; ++k) {
+                            const int kx = kk + 4 * k;
+                            if (kx < K) {
+                                float sum = 0.0f;
+#pragma unroll
+                                for (int w = 0; w < NW2; ++w)
+                                    if ((any >> w) & 1u) sum += s_part[w][jl][kx];
+                                atomicAdd(rec + kx, sum);
+                            }
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        if (tid == 0 && r + 2 < rounds) issue(r + 2);
+    }
+}
+
 }  // namespace
 
 int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, const void* bws, const void* iws,
@@ -267,6 +516,21 @@ int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, c
     const uint32_t* nc = at<uint32_t>(iws, L.n_contrib);
     const float* fT = at<float>(iws, L.final_T);
     float* rec = at<float>(gws, L.grad_rec);
+    static const bool two_px = []() { const char* e = getenv("GSR_BLEND_PPT"); return !(e && e[0] == '1'); }();
+    if (two_px) {
+        if (channels == 3)
+            blend_backward2_kernel<3><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams,
+                                                            W, H, L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra,
+                                                            dL_ddepth, dL_dalpha, rec);
+        else if (channels == 6)
+            blend_backward2_kernel<6><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams,
+                                                            W, H, L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra,
+                                                            dL_ddepth, dL_dalpha, rec);
+        else
+            return GSR_ERR_UNSUPPORTED;
+        GSR_LAUNCH_CHECK();
+        return GSR_OK;
+    }
     if (channels == 3) {
         blend_backward_kernel<3><<<blocks, TILE_PIX, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H, L.tiles_x, T, nc, fT,
                                                             dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, rec);

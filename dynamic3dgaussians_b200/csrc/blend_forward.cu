@@ -14,6 +14,8 @@
 // * a warp leaves the loop as soon as all of its pixels are saturated and the CTA stops fetching when all 256 are;
 // * arithmetic per pair follows the reference binary exactly (see geom_math.cuh), so n_contrib and the images agree
 //   with the reference bit for bit.
+#include <cstdlib>
+
 #include "geom_math.cuh"
 
 namespace gsr {
@@ -170,6 +172,188 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     }
 }
 
+
+// ---- two pixels per thread ------------------------------------------------------------------------------------------
+// CTA = 128 threads = 4 warps; a warp owns an 8x8 patch, a lane the pixels (x, y) and (x, y + 4).  Record loads, loop
+// control and dx are shared by the pair and the pair's arithmetic is issued as packed fp32x2 instructions (FFMA2 /
+// FMUL2 / FADD2, sm_100): the kernel is bound by instruction issue, so halving the instructions per pixel pair is what
+// counts.  Each component goes through exactly the roundings of the one-pixel kernel above (and of the reference
+// binary): a pixel that does not blend a Gaussian runs the same instructions with alpha = 0, which leaves C, D, W and
+// T bit-for-bit unchanged.
+__device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
+__device__ __forceinline__ float2 splat(float a) { return make_float2(a, a); }
+
+constexpr int NT2 = 128;
+constexpr int NW2 = NT2 / 32;
+
+template <int NCH>
+__global__ void __launch_bounds__(NT2, 8)
+blend_forward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
+                      const float4* __restrict__ recA, const float4* __restrict__ recB,
+                      const float4* __restrict__ recC, const float4* __restrict__ recD,
+                      const CamDev* __restrict__ cams, int W, int H, int tiles_x, int tiles_per_view,
+                      float* __restrict__ out_color, float* __restrict__ out_extra, float* __restrict__ out_depth,
+                      float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib, float* __restrict__ final_T) {
+    constexpr bool EXTRA = NCH > 3;
+    __shared__ __align__(128) float4 sA[2][BATCH];
+    __shared__ __align__(128) float4 sB[2][BATCH];
+    __shared__ __align__(128) float4 sC[2][BATCH];
+    __shared__ __align__(128) float4 sD[EXTRA ? 2 : 1][EXTRA ? BATCH : 1];
+    __shared__ __align__(8) uint64_t full[2];
+    __shared__ uint32_t s_wmask[NW2][BATCH / 32];
+    static_assert(BATCH == NT2, "one pre-pass thread per staged Gaussian");
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int vt = (int)tile_order[blockIdx.x];
+    const int view = vt / tiles_per_view;
+    const int tile = vt - view * tiles_per_view;
+    const int tile_yi = tile / tiles_x, tile_xi = tile - tile_yi * tiles_x;
+    const int px = tile_xi * TILE_X + (warp & 1) * 8 + (lane & 7);
+    const int py0 = tile_yi * TILE_Y + (warp >> 1) * 8 + (lane >> 3);
+    const int py1 = py0 + 4;
+    const bool in0 = px < W && py0 < H, in1 = px < W && py1 < H;
+    const float npx = -(float)px;
+    const float2 npy = f2(-(float)py0, -(float)py1);
+
+    const uint2 range = ranges[vt];
+    const int n_total = (int)(range.y - range.x);
+    const int rounds = (n_total + BATCH - 1) / BATCH;
+
+    if (tid == 0) {
+        mbar_init(&full[0], 1);
+        mbar_init(&full[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    auto issue = [&](int r) {   // thread 0 only
+        const int buf = r & 1;
+        const int nb = min(BATCH, n_total - r * BATCH);
+        const uint32_t bytes = (uint32_t)nb * 16u;
+        const size_t src = (size_t)range.x + (size_t)r * BATCH;
+        mbar_expect_tx(&full[buf], bytes * (EXTRA ? 4u : 3u));
+        tma_load_1d(sA[buf], recA + src, bytes, &full[buf]);
+        tma_load_1d(sB[buf], recB + src, bytes, &full[buf]);
+        tma_load_1d(sC[buf], recC + src, bytes, &full[buf]);
+        if (EXTRA) tma_load_1d(sD[buf], recD + src, bytes, &full[buf]);
+    };
+    if (tid == 0) {
+        if (rounds > 0) issue(0);
+        if (rounds > 1) issue(1);
+    }
+
+    float2 T = splat(1.0f);
+    float2 C[NCH];
+#pragma unroll
+    for (int k = 0; k < NCH; ++k) C[k] = splat(0.0f);
+    float2 D = splat(0.0f), Wsum = splat(0.0f);
+    uint32_t lc0 = 0, lc1 = 0;
+    bool done0 = !in0, done1 = !in1;
+
+    const float tile_x0 = (float)(tile_xi * TILE_X), tile_y0 = (float)(tile_yi * TILE_Y);
+    for (int r = 0; r < rounds; ++r) {
+        const int buf = r & 1;
+        mbar_wait(&full[buf], (uint32_t)((r >> 1) & 1));
+        const int nb = min(BATCH, n_total - r * BATCH);
+        const uint32_t contrib_base = (uint32_t)r * BATCH;
+        {   // pre-pass: Gaussian `tid` x the four 8x8 patches -> one 128-bit work list per warp
+            uint32_t m4 = 0u;
+            if (tid < nb) {
+                const float4 a = sA[buf][tid];
+                const float4 b = sB[buf][tid];
+                const uint32_t m8 = blend_patch_mask(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
+                const uint32_t t = m8 | (m8 >> 2);
+                m4 = (t & 3u) | ((t >> 2) & 0xcu);
+            }
+#pragma unroll
+            for (int w = 0; w < NW2; ++w) {
+                const uint32_t bal = __ballot_sync(0xffffffffu, (m4 >> w) & 1u);
+                if (lane == 0) s_wmask[w][warp] = bal;
+            }
+        }
+        __syncthreads();
+#pragma unroll 1
+        for (int q = 0; q < BATCH / 32; ++q) {
+            uint32_t m = s_wmask[warp][q];
+            while (m != 0u && !(done0 && done1)) {
+                const int j = q * 32 + __ffs(m) - 1;
+                m &= m - 1u;
+                const float4 a = sA[buf][j];
+                const float4 b = sB[buf][j];
+                // blend_power (geom_math.cuh) on the pixel pair, component-wise the same roundings
+                const float dx = __fadd_rn(a.x, npx);
+                const float2 dy = __fadd2_rn(splat(a.y), npy);
+                const float dxca = __fmul_rn(dx, a.z), ndxcb = __fmul_rn(dx, -a.w);
+                const float2 t3 = __fmul2_rn(dy, __fmul2_rn(dy, splat(b.x)));
+                const float2 q2 = __ffma2_rn(splat(dx), splat(dxca), t3);
+                const float2 power = __ffma2_rn(q2, splat(-0.5f), __fmul2_rn(dy, splat(ndxcb)));
+                bool live0 = !done0 && !(power.x > 0.0f || power.x < b.w);
+                bool live1 = !done1 && !(power.y > 0.0f || power.y < b.w);
+                if (!(live0 || live1)) continue;
+                const float2 og = __fmul2_rn(splat(b.y), f2(expf(power.x), expf(power.y)));
+                float2 alpha = f2(fminf(0.99f, og.x), fminf(0.99f, og.y));
+                live0 = live0 && !(alpha.x < 1.0f / 255.0f);
+                live1 = live1 && !(alpha.y < 1.0f / 255.0f);
+                const float2 test_T = __fmul2_rn(T, __fadd2_rn(splat(1.0f), f2(-alpha.x, -alpha.y)));
+                const bool term0 = live0 && test_T.x < 0.0001f, term1 = live1 && test_T.y < 0.0001f;
+                done0 = done0 || term0;
+                done1 = done1 || term1;
+                const bool c0 = live0 && !term0, c1 = live1 && !term1;
+                if (!(c0 || c1)) continue;
+                alpha.x = c0 ? alpha.x : 0.0f;
+                alpha.y = c1 ? alpha.y : 0.0f;
+                const float4 c = sC[buf][j];
+                C[0] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.x)), C[0]);
+                C[1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.y)), C[1]);
+                C[2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.z)), C[2]);
+                if (EXTRA) {
+                    const float4 e = sD[buf][j];
+                    C[NCH - 3] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.x)), C[NCH - 3]);
+                    C[NCH - 2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.y)), C[NCH - 2]);
+                    C[NCH - 1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.z)), C[NCH - 1]);
+                }
+                D = __ffma2_rn(T, __fmul2_rn(alpha, splat(b.z)), D);
+                Wsum = __ffma2_rn(alpha, T, Wsum);
+                T.x = c0 ? test_T.x : T.x;
+                T.y = c1 ? test_T.y : T.y;
+                const uint32_t pos1 = contrib_base + (uint32_t)j + 1u;
+                lc0 = c0 ? pos1 : lc0;
+                lc1 = c1 ? pos1 : lc1;
+            }
+        }
+        // everyone is finished with `buf`; stop fetching once the whole tile is saturated
+        const int num_done = __syncthreads_count(done0 && done1);
+        if (num_done == NT2) {
+            // batch r+1 may still be in flight: the CTA must not retire under it
+            if (tid == 0 && r + 1 < rounds) mbar_wait(&full[(r + 1) & 1], (uint32_t)(((r + 1) >> 1) & 1));
+            break;
+        }
+        if (tid == 0 && r + 2 < rounds) issue(r + 2);
+    }
+
+    const CamDev& cam = cams[view];
+    const size_t HW = (size_t)H * W;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        if (!(i == 0 ? in0 : in1)) continue;
+        const size_t pix = (size_t)(i == 0 ? py0 : py1) * W + px;
+        const float Ti = i == 0 ? T.x : T.y;
+        n_contrib[(size_t)view * HW + pix] = i == 0 ? lc0 : lc1;
+        final_T[(size_t)view * HW + pix] = Ti;
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch)
+            out_color[((size_t)view * 3 + ch) * HW + pix] = __fmaf_rn(Ti, cam.bg[ch], i == 0 ? C[ch].x : C[ch].y);
+        if (EXTRA) {
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch)
+                out_extra[((size_t)view * 3 + ch) * HW + pix] =
+                    __fmaf_rn(Ti, cam.bg[3 + ch], i == 0 ? C[NCH - 3 + ch].x : C[NCH - 3 + ch].y);
+        }
+        out_depth[(size_t)view * HW + pix] = i == 0 ? D.x : D.y;
+        out_alpha[(size_t)view * HW + pix] = i == 0 ? Wsum.x : Wsum.y;
+    }
+}
+
 }  // namespace
 
 int launch_blend_forward(int V, int W, int H, int channels, const void* gws, const void* bws, void* iws,
@@ -186,6 +370,21 @@ int launch_blend_forward(int V, int W, int H, int channels, const void* gws, con
     const CamDev* cams = at<CamDev>(gws, L.cams);
     uint32_t* nc = at<uint32_t>(iws, L.n_contrib);
     float* fT = at<float>(iws, L.final_T);
+    static const bool two_px = []() { const char* e = getenv("GSR_BLEND_PPT"); return !(e && e[0] == '1'); }();
+    if (two_px) {
+        if (channels == 3)
+            blend_forward2_kernel<3><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W,
+                                                           H, L.tiles_x, T, out_color, out_extra, out_depth, out_alpha,
+                                                           nc, fT);
+        else if (channels == 6)
+            blend_forward2_kernel<6><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W,
+                                                           H, L.tiles_x, T, out_color, out_extra, out_depth, out_alpha,
+                                                           nc, fT);
+        else
+            return GSR_ERR_UNSUPPORTED;
+        GSR_LAUNCH_CHECK();
+        return GSR_OK;
+    }
     if (channels == 3) {
         blend_forward_kernel<3><<<blocks, TILE_PIX, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H, L.tiles_x, T, out_color,
                                                            out_extra, out_depth, out_alpha, nc, fT);
