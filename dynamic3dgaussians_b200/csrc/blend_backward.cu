@@ -10,11 +10,13 @@
 //        acc_j = alpha_{j+1} * s_{j+1} + (1 - alpha_{j+1}) * acc_{j+1},   acc_last = <bg, dL/dC>
 //        dL/dalpha_j = T_j * (s_j - acc_j)
 //    which removes ~3 registers and ~3 flops per blended channel per pair (the reference kernel needs 198 registers);
-//  * the 7+C per-Gaussian partial sums of a warp are reduced with a packed butterfly (12 shuffles for 10 values instead
-//    of 50), the 8 warps of the CTA are combined through shared memory, and ONE set of global atomics per
-//    (tile, Gaussian) is issued: the reference issues one set per (pixel, Gaussian) pair (backward.cu:586-649).
-#include <cstdlib>
-
+//  * what is reduced over the pixels are raw moments of a = opacity * G * dL/dalpha about d = mean - pixel (S1 = sum a d,
+//    S2 = sum a d d^T, sum G dL/dalpha, and the colour / depth weights); preprocess_backward applies the chain rule
+//    through the conic once per Gaussian;
+//  * the 7+C partial sums of a warp (an 8x8 pixel patch) are reduced with a packed butterfly (12 shuffles for 10 values
+//    instead of 50) and land in the per-(view, Gaussian) gradient record with ONE reduction per (patch, Gaussian,
+//    value): the reference issues one atomic per (pixel, Gaussian, value) (backward.cu:586-649).  The warps of a CTA
+//    only meet once per 128-instance batch.
 #include "geom_math.cuh"
 #include "packed_reduce.cuh"
 
@@ -26,232 +28,9 @@ constexpr int BATCH = 128;
 constexpr int SUB = 32;
 constexpr unsigned FULL = 0xffffffffu;
 
-template <int NCH>
-__global__ void __launch_bounds__(TILE_PIX)
-blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const float4* __restrict__ recA,
-                      const float4* __restrict__ recB, const float4* __restrict__ recC,
-                      const float4* __restrict__ recD, const CamDev* __restrict__ cams, int W, int H, int tiles_x,
-                      int tiles_per_view, const uint32_t* __restrict__ n_contrib, const float* __restrict__ final_T,
-                      const float* __restrict__ dL_dcolor, const float* __restrict__ dL_dextra,
-                      const float* __restrict__ dL_ddepth, const float* __restrict__ dL_dalpha,
-                      float* __restrict__ grad_rec) {
-    constexpr bool EXTRA = NCH > 3;
-    constexpr int K = GR_COL + NCH;
-    static_assert(K <= GRAD_REC, "gradient record too small");
-    __shared__ __align__(128) float4 sA[2][BATCH];
-    __shared__ __align__(128) float4 sB[2][BATCH];
-    __shared__ __align__(128) float4 sC[2][BATCH];
-    __shared__ __align__(128) float4 sD[EXTRA ? 2 : 1][EXTRA ? BATCH : 1];
-    __shared__ __align__(8) uint64_t full[2];
-    __shared__ float s_part[TILE_PIX / 32][SUB][GRAD_REC];
-    __shared__ uint32_t s_mask[TILE_PIX / 32];
-    __shared__ uint32_t s_wmask[TILE_PIX / 32][BATCH / SUB];
-    __shared__ uint32_t s_max;
-    static_assert(SUB == 32 && BATCH <= TILE_PIX, "work lists are one 32-bit word per (warp, sub-batch)");
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int vt = (int)tile_order[blockIdx.x];
-    const int view = vt / tiles_per_view;
-    const int tile = vt - view * tiles_per_view;
-    const int tile_yi = tile / tiles_x, tile_xi = tile - tile_yi * tiles_x;
-    const int px = tile_xi * TILE_X + (warp & 1) * 8 + (lane & 7);
-    const int py = tile_yi * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
-    const bool inside = px < W && py < H;
-    const float pxf = (float)px, pyf = (float)py;
-    const size_t HW = (size_t)H * W;
-    const size_t pix = (size_t)py * W + px;
-
-    const uint2 range = ranges[vt];
-    const uint32_t last_contributor = inside ? n_contrib[(size_t)view * HW + pix] : 0u;
-    float T = inside ? final_T[(size_t)view * HW + pix] : 0.0f;
-
-    if (tid == 0) {
-        s_max = 0;
-        mbar_init(&full[0], 1);
-        mbar_init(&full[1], 1);
-        mbar_fence_init();
-    }
-    __syncthreads();
-    {
-        const uint32_t wmax = __reduce_max_sync(FULL, last_contributor);
-        if (lane == 0 && wmax > 0) atomicMax(&s_max, wmax);
-    }
-    __syncthreads();
-    const int n_proc = (int)min(s_max, range.y - range.x);   // positions [0, n_proc) can contribute to some pixel
-    const int rounds = (n_proc + BATCH - 1) / BATCH;
-    if (rounds == 0) return;
-
-    auto issue = [&](int r) {   // thread 0 only; round r walks chunk (rounds-1-r)
-        const int buf = r & 1;
-        const int c = rounds - 1 - r;
-        const int nb = min(BATCH, n_proc - c * BATCH);
-        const uint32_t bytes = (uint32_t)nb * 16u;
-        const size_t src = (size_t)range.x + (size_t)c * BATCH;
-        mbar_expect_tx(&full[buf], bytes * (EXTRA ? 4u : 3u));
-        tma_load_1d(sA[buf], recA + src, bytes, &full[buf]);
-        tma_load_1d(sB[buf], recB + src, bytes, &full[buf]);
-        tma_load_1d(sC[buf], recC + src, bytes, &full[buf]);
-        if (EXTRA) tma_load_1d(sD[buf], recD + src, bytes, &full[buf]);
-    };
-    if (tid == 0) {
-        issue(0);
-        if (rounds > 1) issue(1);
-    }
-
-    // pixel cotangents
-    float gC[NCH];
-    float gD = 0.0f, gA = 0.0f;
-#pragma unroll
-    for (int k = 0; k < NCH; ++k) gC[k] = 0.0f;
-    const CamDev& cam = cams[view];
-    float acc = 0.0f;   // "extended colour behind me" dotted with the cotangent; starts as the background term
-    if (inside) {
-        if (dL_dcolor) {
-#pragma unroll
-            for (int ch = 0; ch < 3; ++ch) {
-                gC[ch] = dL_dcolor[((size_t)view * 3 + ch) * HW + pix];
-                acc += cam.bg[ch] * gC[ch];
-            }
-        }
-        if (EXTRA && dL_dextra) {
-#pragma unroll
-            for (int ch = 0; ch < 3; ++ch) {
-                gC[NCH - 3 + ch] = dL_dextra[((size_t)view * 3 + ch) * HW + pix];
-                acc += cam.bg[3 + ch] * gC[NCH - 3 + ch];
-            }
-        }
-        if (dL_ddepth) gD = dL_ddepth[(size_t)view * HW + pix];
-        if (dL_dalpha) gA = dL_dalpha[(size_t)view * HW + pix];
-    }
-    float last_alpha = 0.0f, last_s = 0.0f;
-
-    const int my_slot = PackedReduce<K>::slot(lane);
-    const unsigned slot_peers = __match_any_sync(FULL, my_slot);
-    const bool writer = lane == (__ffs(slot_peers) - 1);
-
-    const float tile_x0 = (float)(tile_xi * TILE_X), tile_y0 = (float)(tile_yi * TILE_Y);
-    const uint32_t warp_last = __reduce_max_sync(FULL, last_contributor);   // nothing at or past it matters to this warp
-
-    for (int r = 0; r < rounds; ++r) {
-        const int buf = r & 1;
-        const int c = rounds - 1 - r;
-        const int nb = min(BATCH, n_proc - c * BATCH);
-        mbar_wait(&full[buf], (uint32_t)((r >> 1) & 1));
-        // ---- pre-pass: per-warp work lists (see blend_forward.cu): Gaussian j x warp patch intersection ----
-        if (tid < BATCH) {
-            uint32_t m8 = 0u;
-            if (tid < nb) {
-                const float4 a = sA[buf][tid];
-                const float4 b = sB[buf][tid];
-                m8 = blend_patch_mask(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
-            }
-#pragma unroll
-            for (int w = 0; w < TILE_PIX / 32; ++w) {
-                const uint32_t bal = __ballot_sync(FULL, (m8 >> w) & 1u);
-                if (lane == 0) s_wmask[w][warp] = bal;
-            }
-        }
-        __syncthreads();
-        for (int sub = (nb - 1) / SUB; sub >= 0; --sub) {
-            const int lo = sub * SUB;
-            const int hi = min(lo + SUB, nb);
-            uint32_t hit_mask = 0;
-            uint32_t m = s_wmask[warp][sub];
-            {   // drop positions no pixel of this warp blended (pos >= warp_last)
-                const uint32_t base = (uint32_t)(c * BATCH + lo);
-                if (warp_last <= base) m = 0u;
-                else if (warp_last - base < 32u) m &= (1u << (warp_last - base)) - 1u;
-            }
-            while (m != 0u) {                                       // warp-uniform, back to front
-                const int jl = 31 - __clz(m);
-                m &= ~(1u << jl);
-                const int j = lo + jl;
-                const float4 a = sA[buf][j];
-                const float4 b = sB[buf][j];
-                const uint32_t pos = (uint32_t)(c * BATCH + j);
-                const float dx = __fsub_rn(a.x, pxf), dy = __fsub_rn(a.y, pyf);
-                const float power = blend_power(dx, dy, a.z, a.w, b.x);
-                const bool pre = (pos < last_contributor) && !(power > 0.0f) && !(power < b.w);
-                if (!__any_sync(FULL, pre)) continue;                // warp-uniform
-                const float G = expf(fminf(power, 0.0f));
-                const float alpha = fminf(0.99f, __fmul_rn(b.y, G));
-                const bool valid = pre && !(alpha < 1.0f / 255.0f);
-                // (no second vote: ncu shows 99.98 % of the warps that pass the first one have a valid lane)
-
-                // What is reduced over the pixels are raw moments of a = opacity * G * dL/dalpha about the pixel offset
-                // d = mean - pixel; preprocess_backward turns them into dL/dmean2D and dL/dconic:
-                //   S1 = sum a d,  S2 = sum a d d^T,  OP = sum G dL/dalpha,  plus sum w g for depth and colours.
-                float v[K];
-#pragma unroll
-                for (int k = 0; k < K; ++k) v[k] = 0.0f;
-                if (valid) {
-                    T = __fdividef(T, 1.0f - alpha);                 // transmittance in front of this Gaussian
-                    const float w = alpha * T;
-                    const float4 col = sC[buf][j];
-                    float s = fmaf(col.x, gC[0], fmaf(col.y, gC[1], fmaf(col.z, gC[2], fmaf(b.z, gD, gA))));
-                    v[GR_COL + 0] = w * gC[0];
-                    v[GR_COL + 1] = w * gC[1];
-                    v[GR_COL + 2] = w * gC[2];
-                    if (EXTRA) {
-                        const float4 e = sD[buf][j];
-                        s = fmaf(e.x, gC[NCH - 3], fmaf(e.y, gC[NCH - 2], fmaf(e.z, gC[NCH - 1], s)));
-                        v[GR_COL + NCH - 3] = w * gC[NCH - 3];
-                        v[GR_COL + NCH - 2] = w * gC[NCH - 2];
-                        v[GR_COL + NCH - 1] = w * gC[NCH - 1];
-                    }
-                    acc = fmaf(last_alpha, last_s - acc, acc);        // colour-behind recurrence (see header)
-                    last_s = s;
-                    last_alpha = alpha;
-                    const float gq = G * ((s - acc) * T);             // G * dL/dalpha (straight through the 0.99 clamp)
-                    const float am = b.y * gq;
-                    const float ux = am * dx, uy = am * dy;
-                    v[GR_MX] = ux;
-                    v[GR_MY] = uy;
-                    v[GR_CA] = ux * dx;
-                    v[GR_CB] = ux * dy;
-                    v[GR_CC] = uy * dy;
-                    v[GR_OP] = gq;
-                    v[GR_DEPTH] = w * gD;
-                }
-                PackedReduce<K>::run(v, lane);
-                if (writer) s_part[warp][jl][my_slot] = v[0];
-                hit_mask |= 1u << jl;
-            }
-            if (lane == 0) s_mask[warp] = hit_mask;
-            __syncthreads();
-            {   // combine the 8 warps; one atomic set per (tile, Gaussian)
-                const int jl = tid >> 3, kk = tid & 7;
-                if (lo + jl < hi) {
-                    float s0 = 0.0f, s1 = 0.0f;
-                    bool any = false;
-#pragma unroll
-                    for (int w = 0; w < TILE_PIX / 32; ++w) {
-                        if ((s_mask[w] >> jl) & 1u) {
-                            s0 += s_part[w][jl][kk];
-                            if (kk + 8 < K) s1 += s_part[w][jl][kk + 8];
-                            any = true;
-                        }
-                    }
-                    if (any) {
-                        const uint32_t gi = __float_as_uint(sC[buf][lo + jl].w);
-                        float* rec = grad_rec + (size_t)gi * GRAD_REC;
-                        atomicAdd(rec + kk, s0);
-                        if (kk + 8 < K) atomicAdd(rec + kk + 8, s1);
-                    }
-                }
-            }
-            __syncthreads();
-        }
-        // all threads are past the last read of `buf` (barrier above)
-        if (tid == 0 && r + 2 < rounds) issue(r + 2);
-    }
-}
-
-
-// ---- two pixels per thread ------------------------------------------------------------------------------------------
 // CTA = 128 threads = 4 warps; a warp owns an 8x8 pixel patch, a lane the two pixels (x, y) and (x, y + 4) of it, so
 // dx is shared by the pair and the per-(warp, Gaussian) costs (record loads, loop control, the packed butterfly, the
-// partial-sum store) are paid once per 64 pixels instead of once per 32.  The pair's arithmetic is issued as packed
+// atomics) are paid once per 64 pixels.  The pair's arithmetic is issued as packed
 // fp32x2 instructions (FFMA2 / FMUL2 / FADD2, sm_100) where both pixels do the same operation; the kernel is bound by
 // instruction issue, not by the FMA pipe.  Invalid pixels run the same instructions with alpha = 0 and a zeroed
 // dL/dalpha, which leaves T, the recurrence and every sum unchanged (no divergent region).
@@ -263,7 +42,7 @@ constexpr int NW2 = NT2 / 32;
 
 template <int NCH>
 __global__ void __launch_bounds__(NT2, 8)
-blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
+blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                        const float4* __restrict__ recA, const float4* __restrict__ recB,
                        const float4* __restrict__ recC, const float4* __restrict__ recD,
                        const CamDev* __restrict__ cams, int W, int H, int tiles_x, int tiles_per_view,
@@ -278,8 +57,6 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
     __shared__ __align__(128) float4 sC[2][BATCH];
     __shared__ __align__(128) float4 sD[EXTRA ? 2 : 1][EXTRA ? BATCH : 1];
     __shared__ __align__(8) uint64_t full[2];
-    __shared__ float s_part[NW2][SUB][GRAD_REC];
-    __shared__ uint32_t s_mask[NW2];
     __shared__ uint32_t s_wmask[NW2][BATCH / SUB];
     __shared__ uint32_t s_max;
     static_assert(BATCH == NT2, "one pre-pass thread per staged Gaussian");
@@ -393,8 +170,6 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
         __syncthreads();
         for (int sub = (nb - 1) / SUB; sub >= 0; --sub) {
             const int lo = sub * SUB;
-            const int hi = min(lo + SUB, nb);
-            uint32_t hit_mask = 0;
             uint32_t m = s_wmask[warp][sub];
             {
                 const uint32_t base = (uint32_t)(c * BATCH + lo);
@@ -418,7 +193,7 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
                 const bool pre0 = (pos < lc0) && !(power.x > 0.0f) && !(power.x < b.w);
                 const bool pre1 = (pos < lc1) && !(power.y > 0.0f) && !(power.y < b.w);
                 if (!__any_sync(FULL, pre0 || pre1)) continue;      // warp-uniform
-                const float2 G = f2(expf(fminf(power.x, 0.0f)), expf(fminf(power.y, 0.0f)));
+                const float2 G = expf2_pinned(power);        // garbage where !pre: masked by the selects below
                 const float2 og = __fmul2_rn(splat(b.y), G);
                 float2 alpha = f2(fminf(0.99f, og.x), fminf(0.99f, og.y));
                 const bool valid0 = pre0 && !(alpha.x < 1.0f / 255.0f);
@@ -460,36 +235,12 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
                 v[GR_CC] = fmaf(uy.y, dy.y, uy.x * dy.x);
                 v[GR_OP] = gq.x + gq.y;
                 PackedReduce<K>::run(v, lane);
-                if (writer) s_part[warp][jl][my_slot] = v[0];
-                hit_mask |= 1u << jl;
+                // one reduction (RED) per (warp patch, Gaussian, value): the K sums sit in K different lanes and land in
+                // one 64-byte gradient record
+                if (writer) atomicAdd(grad_rec + (size_t)__float_as_uint(col.w) * GRAD_REC + my_slot, v[0]);
             }
-            if (lane == 0) s_mask[warp] = hit_mask;
-            __syncthreads();
-            {   // combine the 4 warps; one atomic set per (tile, Gaussian)
-                const int jl = tid >> 2, kk = tid & 3;
-                if (lo + jl < hi) {
-                    uint32_t any = 0;
-#pragma unroll
-                    for (int w = 0; w < NW2; ++w) any |= ((s_mask[w] >> jl) & 1u) << w;
-                    if (any) {
-                        const uint32_t gi = __float_as_uint(sC[buf][lo + jl].w);
-                        float* rec = grad_rec + (size_t)gi * GRAD_REC;
-#pragma unroll
-                        for (int k = 0; k < (K + 3) / 4; ++k) {
-                            const int kx = kk + 4 * k;
-                            if (kx < K) {
-                                float sum = 0.0f;
-#pragma unroll
-                                for (int w = 0; w < NW2; ++w)
-                                    if ((any >> w) & 1u) sum += s_part[w][jl][kx];
-                                atomicAdd(rec + kx, sum);
-                            }
-                        }
-                    }
-                }
-            }
-            __syncthreads();
         }
+        __syncthreads();        // every warp is done with `buf`
         if (tid == 0 && r + 2 < rounds) issue(r + 2);
     }
 }
@@ -516,30 +267,16 @@ int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, c
     const uint32_t* nc = at<uint32_t>(iws, L.n_contrib);
     const float* fT = at<float>(iws, L.final_T);
     float* rec = at<float>(gws, L.grad_rec);
-    static const bool two_px = []() { const char* e = getenv("GSR_BLEND_PPT"); return !(e && e[0] == '1'); }();
-    if (two_px) {
-        if (channels == 3)
-            blend_backward2_kernel<3><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams,
-                                                            W, H, L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra,
-                                                            dL_ddepth, dL_dalpha, rec);
-        else if (channels == 6)
-            blend_backward2_kernel<6><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams,
-                                                            W, H, L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra,
-                                                            dL_ddepth, dL_dalpha, rec);
-        else
-            return GSR_ERR_UNSUPPORTED;
-        GSR_LAUNCH_CHECK();
-        return GSR_OK;
-    }
-    if (channels == 3) {
-        blend_backward_kernel<3><<<blocks, TILE_PIX, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H, L.tiles_x, T, nc, fT,
-                                                            dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, rec);
-    } else if (channels == 6) {
-        blend_backward_kernel<6><<<blocks, TILE_PIX, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H, L.tiles_x, T, nc, fT,
-                                                            dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, rec);
-    } else {
+    if (channels == 3)
+        blend_backward_kernel<3><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H,
+                                                        L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
+                                                        dL_dalpha, rec);
+    else if (channels == 6)
+        blend_backward_kernel<6><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H,
+                                                        L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
+                                                        dL_dalpha, rec);
+    else
         return GSR_ERR_UNSUPPORTED;
-    }
     GSR_LAUNCH_CHECK();
     return GSR_OK;
 }
