@@ -42,51 +42,102 @@ def parse():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe).  NVML is used in-process
+    (nvidia_ml_py) and initialised before the warm-up: spawning nvidia-smi next to the timed region stalls CUDA launches
+    of this process for as long as its driver initialisation takes (seen as 7 ms of host time per step on some boxes).
+    Falls back to an `nvidia-smi -lms` child started equally early."""
 
     def __init__(self, index: int):
         self.index = index
+        self.samples = []          # (sm_mhz, max_mhz, reasons bitmask or list)
+        self.active = False
+        self.stop_flag = False
+        self.thread = None
+        self.nvml = None
         self.proc = None
-        self.lines = []
-
-    def start(self):
-        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-             "clocks_event_reasons.sw_power_cap")
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
+            import pynvml
+            pynvml.nvmlInit()
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+            self.thread = threading.Thread(target=self._poll_nvml, daemon=True)
+            self.thread.start()
         except Exception:
-            self.proc = None
+            self.nvml = None
+            q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+                 "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+                 "clocks_event_reasons.sw_power_cap")
+            try:
+                self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={q}",
+                                              "--format=csv,noheader,nounits", "-lms", "50"],
+                                             stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                self.thread = threading.Thread(target=self._read_smi, daemon=True)
+                self.thread.start()
+            except Exception:
+                self.proc = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
+    def _poll_nvml(self):
+        n = self.nvml
+        while not self.stop_flag:
+            if self.active:
+                try:
+                    sm = float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
+                    try:
+                        r = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+                    except Exception:
+                        r = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+                    self.samples.append((sm, self.max_mhz, r))
+                except Exception:
+                    pass
+            time.sleep(0.01)
 
-    def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        sm, mx, reasons = [], [], set()
+    def _read_smi(self):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
+        for line in self.proc.stdout:
+            if not self.active:
+                continue
+            f = [x.strip() for x in line.split(",")]
             if len(f) < 7:
                 continue
             try:
-                sm.append(float(f[0]))
-                mx.append(float(f[1]))
+                self.samples.append((float(f[0]), float(f[1]),
+                                     [n for n, v in zip(names, f[3:7]) if v.lower().startswith("active")]))
             except ValueError:
                 continue
-            for n, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        sm.sort()
+
+    def start(self):
+        self.samples = []
+        self.active = True
+
+    def stop(self):
+        if self.nvml is None and self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml and nvidia-smi unavailable"]}
+        if not self.samples:
+            time.sleep(0.12)           # a very short timed region: take one sample right behind it
+        self.active = False
+        self.stop_flag = True
+        if self.proc is not None:
+            self.proc.terminate()
+        reasons = set()
+        if self.nvml is not None:
+            n = self.nvml
+            bits = {"hw_slowdown": getattr(n, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                    "hw_thermal_slowdown": getattr(n, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                    "sw_thermal_slowdown": getattr(n, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                    "sw_power_cap": getattr(n, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+            for _, _, r in self.samples:
+                for name, bit in bits.items():
+                    if r & bit:
+                        reasons.add(name)
+        else:
+            for _, _, r in self.samples:
+                reasons.update(r)
+        sm = sorted(x[0] for x in self.samples)
+        mx = [x[1] for x in self.samples]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": sorted(reasons),
+                "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 def dist_setup(args):
@@ -205,10 +256,10 @@ def run_ours(args, world, rank, local):
     out, _ = step()
     if out is not None:
         cap[0] = int(out[5].num_rendered * 1.05) + 4096
+    sampler = ClockSampler(dev.index or 0) if rank == 0 else None      # NVML initialised before the warm-up
     for _ in range(args.warmup):
         step()
     barrier(world)
-    sampler = ClockSampler(dev.index or 0)
     if rank == 0:
         sampler.start()
     _lib.stage_timing(True)

@@ -237,7 +237,7 @@ int gsr_backward(int V, int P, int W, int H, int channels, int sh_coeffs, int64_
     if (rc) return rc;
     if (features && dL_dfeatures) {
         if (dL_dfeatures_img)
-            rc = launch_feature_backward(V, P, W, H, geom_ws, binning_ws, image_ws, L, features, dL_dfeatures_img,
+            rc = launch_feature_backward(V, P, W, H, channels, geom_ws, binning_ws, image_ws, L, features, dL_dfeatures_img,
                                          dL_dfeatures, s);
         else
             rc = cudaMemsetAsync(dL_dfeatures, 0, (size_t)P * GSR_NUM_SEMANTIC_CHANNELS * sizeof(float), s) == cudaSuccess

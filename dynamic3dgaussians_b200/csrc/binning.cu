@@ -342,24 +342,49 @@ tile_offsets_kernel(uint32_t VS, uint32_t S, int stiles_x, int tiles_x, int tile
 // their CTAs in that order, so the longest sequential chains start first and the short tiles fill in behind them
 // (the hardware dispatches CTAs in blockIdx order).
 constexpr int ORDER_BUCKETS = 1024;
-__global__ void __launch_bounds__(SCAN_BLOCK)
+constexpr int TSCAN_THREADS = 1024;          // one CTA on the critical path: as many loads in flight as one CTA can have
+
+__device__ __forceinline__ uint32_t block_exclusive_scan_1024(uint32_t v, uint32_t* s_warp /*[32]*/, uint32_t& total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(FULL, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t w = s_warp[lane], winc = w;                 // every warp scans the 32 warp totals
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(FULL, winc, o);
+        if (lane >= o) winc += t;
+    }
+    total = __shfl_sync(FULL, winc, 31);
+    const uint32_t base = __shfl_sync(FULL, winc - w, warp);
+    __syncthreads();
+    return base + inc - v;
+}
+
+__global__ void __launch_bounds__(TSCAN_THREADS)
 tile_scan_kernel(uint32_t VT, uint32_t capacity, uint32_t* __restrict__ tile_start, uint2* __restrict__ ranges,
                  uint32_t* __restrict__ tile_order, uint32_t* __restrict__ counters) {
-    __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
+    __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_bucket[ORDER_BUCKETS];
     __shared__ uint32_t s_maxlen;
+    static_assert(ORDER_BUCKETS == TSCAN_THREADS, "one bucket per thread in the bucket scan");
     if (threadIdx.x == 0) s_maxlen = 0;
-    for (int b = threadIdx.x; b < ORDER_BUCKETS; b += SCAN_BLOCK) s_bucket[b] = 0;
+    s_bucket[threadIdx.x] = 0;
     __syncthreads();
     uint32_t carry = 0, vmax = 0;
-    constexpr int IT = 16;
-    for (uint32_t start = 0; start < VT; start += SCAN_BLOCK * IT) {
+    constexpr int IT = 8;
+    for (uint32_t start = 0; start < VT; start += TSCAN_THREADS * IT) {
         const uint32_t i0 = start + threadIdx.x * IT;
         uint32_t v[IT], sum = 0;
 #pragma unroll
         for (int k = 0; k < IT; ++k) { v[k] = i0 + k < VT ? tile_start[i0 + k] : 0u; sum += v[k]; vmax = max(vmax, v[k]); }
         uint32_t total;
-        uint32_t ex = carry + block_exclusive_scan_256(sum, s_warp, total);
+        uint32_t ex = carry + block_exclusive_scan_1024(sum, s_warp, total);
 #pragma unroll
         for (int k = 0; k < IT; ++k) {
             if (i0 + k < VT) {
@@ -374,31 +399,48 @@ tile_scan_kernel(uint32_t VT, uint32_t capacity, uint32_t* __restrict__ tile_sta
         tile_start[VT] = carry;
         if (carry > capacity) counters[CNT_OVERFLOW] = 1;
     }
-    vmax = __reduce_max_sync(0xffffffffu, vmax);
+    vmax = __reduce_max_sync(FULL, vmax);
     if ((threadIdx.x & 31) == 0 && vmax > 0) atomicMax(&s_maxlen, vmax);
     __syncthreads();
-    // bucket = ORDER_BUCKETS-1 for the longest lists ... 0 for the empty ones; sorted descending by bucket
+    // bucket 0 holds the longest lists ... ORDER_BUCKETS-1 the empty ones
     const uint32_t q = s_maxlen / (ORDER_BUCKETS - 1) + 1;
-    for (uint32_t i = threadIdx.x; i < VT; i += SCAN_BLOCK) {
-        const uint2 r = ranges[i];
-        atomicAdd(&s_bucket[(ORDER_BUCKETS - 1) - min((r.y - r.x) / q, (uint32_t)ORDER_BUCKETS - 1)], 1u);
+    constexpr int OT = 4;
+    for (uint32_t start = 0; start < VT; start += TSCAN_THREADS * OT) {
+        uint2 r[OT];
+#pragma unroll
+        for (int k = 0; k < OT; ++k) {
+            const uint32_t i = start + k * TSCAN_THREADS + threadIdx.x;
+            r[k] = i < VT ? ranges[i] : make_uint2(0u, 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < OT; ++k)
+            if (start + k * TSCAN_THREADS + threadIdx.x < VT)
+                atomicAdd(&s_bucket[(ORDER_BUCKETS - 1) - min((r[k].y - r[k].x) / q, (uint32_t)ORDER_BUCKETS - 1)], 1u);
     }
     __syncthreads();
-    {   // exclusive scan of the bucket counts (4 per thread)
-        constexpr int BT = ORDER_BUCKETS / SCAN_BLOCK;
-        uint32_t c[BT], sum = 0;
-#pragma unroll
-        for (int k = 0; k < BT; ++k) { c[k] = s_bucket[threadIdx.x * BT + k]; sum += c[k]; }
+    {
+        const uint32_t c = s_bucket[threadIdx.x];
         uint32_t total;
-        uint32_t ex = block_exclusive_scan_256(sum, s_warp, total);
-#pragma unroll
-        for (int k = 0; k < BT; ++k) { s_bucket[threadIdx.x * BT + k] = ex; ex += c[k]; }
+        const uint32_t ex = block_exclusive_scan_1024(c, s_warp, total);
+        s_bucket[threadIdx.x] = ex;
     }
     __syncthreads();
-    for (uint32_t i = threadIdx.x; i < VT; i += SCAN_BLOCK) {
-        const uint2 r = ranges[i];
-        const uint32_t pos = atomicAdd(&s_bucket[(ORDER_BUCKETS - 1) - min((r.y - r.x) / q, (uint32_t)ORDER_BUCKETS - 1)], 1u);
-        tile_order[pos] = i;
+    for (uint32_t start = 0; start < VT; start += TSCAN_THREADS * OT) {
+        uint2 r[OT];
+#pragma unroll
+        for (int k = 0; k < OT; ++k) {
+            const uint32_t i = start + k * TSCAN_THREADS + threadIdx.x;
+            r[k] = i < VT ? ranges[i] : make_uint2(0u, 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < OT; ++k) {
+            const uint32_t i = start + k * TSCAN_THREADS + threadIdx.x;
+            if (i < VT) {
+                const uint32_t pos =
+                    atomicAdd(&s_bucket[(ORDER_BUCKETS - 1) - min((r[k].y - r[k].x) / q, (uint32_t)ORDER_BUCKETS - 1)], 1u);
+                tile_order[pos] = i;
+            }
+        }
     }
 }
 
@@ -536,7 +578,7 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     if (VP == 0 || capacity <= 0) {     // every tile list empty: zero counts through the same scan (ranges, launch order)
         if (VT == 0) return GSR_OK;
         GSR_CUDA_TRY(cudaMemsetAsync(at<uint32_t>(iws, L.tile_start), 0, ((size_t)VT + 1) * sizeof(uint32_t), s));
-        tile_scan_kernel<<<1, SCAN_BLOCK, 0, s>>>(VT, 0u, at<uint32_t>(iws, L.tile_start), at<uint2>(iws, L.ranges),
+        tile_scan_kernel<<<1, TSCAN_THREADS, 0, s>>>(VT, 0u, at<uint32_t>(iws, L.tile_start), at<uint2>(iws, L.ranges),
                                                   at<uint32_t>(iws, L.tile_order), at<uint32_t>(gws, L.counters));
         GSR_LAUNCH_CHECK();
         return GSR_OK;
@@ -582,7 +624,7 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     tile_offsets_kernel<<<(VS + 3) / 4, 128, 0, s>>>(VS, S, L.stiles_x, L.tiles_x, L.tiles_y, chunk_base, max_chunks,
                                                     chunk_counts, tile_start);
     GSR_LAUNCH_CHECK();
-    tile_scan_kernel<<<1, SCAN_BLOCK, 0, s>>>(VT, cap, tile_start, at<uint2>(iws, L.ranges),
+    tile_scan_kernel<<<1, TSCAN_THREADS, 0, s>>>(VT, cap, tile_start, at<uint2>(iws, L.ranges),
                                               at<uint32_t>(iws, L.tile_order), counters);
     GSR_LAUNCH_CHECK();
     stage_end(ST_RANGES, s);

@@ -59,7 +59,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     __shared__ __align__(8) uint64_t full[2];
     __shared__ uint32_t s_wmask[NW2][BATCH / SUB];
     __shared__ uint32_t s_max;
-    static_assert(BATCH == NT2, "one pre-pass thread per staged Gaussian");
+    static_assert(BATCH % NT2 == 0, "pre-pass: BATCH / NT2 staged Gaussians per thread");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int vt = (int)tile_order[blockIdx.x];
@@ -153,18 +153,22 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         const int nb = min(BATCH, n_proc - c * BATCH);
         mbar_wait(&full[buf], (uint32_t)((r >> 1) & 1));
         {   // pre-pass: per-warp work lists, Gaussian `tid` x the four 8x8 patches
-            uint32_t m4 = 0u;
-            if (tid < nb) {
-                const float4 a = sA[buf][tid];
-                const float4 b = sB[buf][tid];
-                const uint32_t m8 = blend_patch_mask(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
-                const uint32_t t = m8 | (m8 >> 2);
-                m4 = (t & 3u) | ((t >> 2) & 0xcu);
-            }
 #pragma unroll
-            for (int w = 0; w < NW2; ++w) {
-                const uint32_t bal = __ballot_sync(FULL, (m4 >> w) & 1u);
-                if (lane == 0) s_wmask[w][warp] = bal;
+            for (int g0 = 0; g0 < BATCH; g0 += NT2) {
+                const int g = g0 + tid;
+                uint32_t m4 = 0u;
+                if (g < nb) {
+                    const float4 a = sA[buf][g];
+                    const float4 b = sB[buf][g];
+                    const uint32_t m8 = blend_patch_mask(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
+                    const uint32_t t = m8 | (m8 >> 2);
+                    m4 = (t & 3u) | ((t >> 2) & 0xcu);
+                }
+#pragma unroll
+                for (int w = 0; w < NW2; ++w) {
+                    const uint32_t bal = __ballot_sync(FULL, (m4 >> w) & 1u);
+                    if (lane == 0) s_wmask[w][g0 / 32 + warp] = bal;
+                }
             }
         }
         __syncthreads();
@@ -237,7 +241,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 PackedReduce<K>::run(v, lane);
                 // one reduction (RED) per (warp patch, Gaussian, value): the K sums sit in K different lanes and land in
                 // one 64-byte gradient record
-                if (writer) atomicAdd(grad_rec + (size_t)__float_as_uint(col.w) * GRAD_REC + my_slot, v[0]);
+                if (writer) atomicAdd(grad_rec + (size_t)__float_as_uint(col.w) * grad_rec_stride(NCH) + my_slot, v[0]);
             }
         }
         __syncthreads();        // every warp is done with `buf`
@@ -254,7 +258,7 @@ int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, c
     const int blocks = V * T;
     {
         StageScope sc(ST_GRAD_ZERO, s);
-        GSR_CUDA_TRY(cudaMemsetAsync(at<float>(gws, L.grad_rec), 0, (size_t)V * P * GRAD_REC * 4, s));
+        GSR_CUDA_TRY(cudaMemsetAsync(at<float>(gws, L.grad_rec), 0, (size_t)V * P * grad_rec_stride(channels) * 4, s));
     }
     if (blocks == 0 || P == 0) return GSR_OK;
     StageScope sc(ST_BLEND_BWD, s);

@@ -143,7 +143,7 @@ feature_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __rest
                         const float* __restrict__ feat, int P, const CamDev* __restrict__ cams, int W, int H,
                         int tiles_x, int tiles_per_view, const uint32_t* __restrict__ n_contrib,
                         const float* __restrict__ final_T, const float* __restrict__ dL_dfeat_img,
-                        float* __restrict__ grad_rec, float* __restrict__ dL_dfeat) {
+                        float* __restrict__ grad_rec, int rec_stride, float* __restrict__ dL_dfeat) {
     __shared__ __align__(16) float4 sA[FB];
     __shared__ __align__(16) float4 sB[FB];
     __shared__ uint32_t s_gi[FB];
@@ -270,7 +270,7 @@ feature_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __rest
 #pragma unroll
                             for (int w = 0; w < TILE_PIX / 32; ++w)
                                 if ((s_mask[w] >> jl) & 1u) sum += s_part[w][jl][k];
-                            if (k < 6) atomicAdd(grad_rec + (size_t)gi * GRAD_REC + k, sum);
+                            if (k < 6) atomicAdd(grad_rec + (size_t)gi * rec_stride + k, sum);
                             else atomicAdd(dL_dfeat + (size_t)g * NF + (k - 6), sum);
                         }
                     }
@@ -295,7 +295,7 @@ int launch_feature_forward(int V, int P, int W, int H, const void* gws, const vo
     return GSR_OK;
 }
 
-int launch_feature_backward(int V, int P, int W, int H, void* gws, const void* bws, const void* iws, const Layout& L,
+int launch_feature_backward(int V, int P, int W, int H, int channels, void* gws, const void* bws, const void* iws, const Layout& L,
                             const float* features, const float* dL_dfeat_img, float* dL_dfeatures, cudaStream_t s) {
     const int T = L.tiles_x * L.tiles_y;
     GSR_CUDA_TRY(cudaMemsetAsync(dL_dfeatures, 0, (size_t)P * NF * sizeof(float), s));
@@ -309,7 +309,7 @@ int launch_feature_backward(int V, int P, int W, int H, void* gws, const void* b
     feature_backward_kernel<<<V * T, TILE_PIX, dyn, s>>>(
         at<uint2>(iws, L.ranges), at<uint32_t>(iws, L.tile_order), at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC), features,
         P, at<CamDev>(gws, L.cams), W, H, L.tiles_x, T, at<uint32_t>(iws, L.n_contrib), at<float>(iws, L.final_T),
-        dL_dfeat_img, at<float>(gws, L.grad_rec), dL_dfeatures);
+        dL_dfeat_img, at<float>(gws, L.grad_rec), grad_rec_stride(channels), dL_dfeatures);
     GSR_LAUNCH_CHECK();
     return GSR_OK;
 }

@@ -20,7 +20,7 @@ namespace gsr {
 
 namespace {
 
-constexpr int BATCH = 128;
+constexpr int BATCH = 256;
 
 // CTA = 128 threads = 4 warps; a warp owns an 8x8 patch, a lane the pixels (x, y) and (x, y + 4).  Record loads, loop
 // control and dx are shared by the pair and the pair's arithmetic is issued as packed fp32x2 instructions (FFMA2 /
@@ -48,7 +48,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     __shared__ __align__(128) float4 sD[EXTRA ? 2 : 1][EXTRA ? BATCH : 1];
     __shared__ __align__(8) uint64_t full[2];
     __shared__ uint32_t s_wmask[NW2][BATCH / 32];
-    static_assert(BATCH == NT2, "one pre-pass thread per staged Gaussian");
+    static_assert(BATCH % NT2 == 0, "pre-pass: BATCH / NT2 staged Gaussians per thread");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int vt = (int)tile_order[blockIdx.x];
@@ -104,18 +104,22 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         const int nb = min(BATCH, n_total - r * BATCH);
         const uint32_t contrib_base = (uint32_t)r * BATCH;
         {   // pre-pass: Gaussian `tid` x the four 8x8 patches -> one 128-bit work list per warp
-            uint32_t m4 = 0u;
-            if (tid < nb) {
-                const float4 a = sA[buf][tid];
-                const float4 b = sB[buf][tid];
-                const uint32_t m8 = blend_patch_mask(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
-                const uint32_t t = m8 | (m8 >> 2);
-                m4 = (t & 3u) | ((t >> 2) & 0xcu);
-            }
 #pragma unroll
-            for (int w = 0; w < NW2; ++w) {
-                const uint32_t bal = __ballot_sync(0xffffffffu, (m4 >> w) & 1u);
-                if (lane == 0) s_wmask[w][warp] = bal;
+            for (int g0 = 0; g0 < BATCH; g0 += NT2) {
+                const int g = g0 + tid;
+                uint32_t m4 = 0u;
+                if (g < nb) {
+                    const float4 a = sA[buf][g];
+                    const float4 b = sB[buf][g];
+                    const uint32_t m8 = blend_patch_mask(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
+                    const uint32_t t = m8 | (m8 >> 2);
+                    m4 = (t & 3u) | ((t >> 2) & 0xcu);
+                }
+#pragma unroll
+                for (int w = 0; w < NW2; ++w) {
+                    const uint32_t bal = __ballot_sync(0xffffffffu, (m4 >> w) & 1u);
+                    if (lane == 0) s_wmask[w][g0 / 32 + warp] = bal;
+                }
             }
         }
         __syncthreads();

@@ -12,7 +12,10 @@ namespace gsr {
 constexpr int TILE_X = 16;            // R/cuda_rasterizer/config.h:18-19
 constexpr int TILE_Y = 16;
 constexpr int TILE_PIX = TILE_X * TILE_Y;
-constexpr int GRAD_REC = 16;          // floats per (view, Gaussian) gradient record written by the blend backward
+constexpr int GRAD_REC = 16;          // upper bound on the floats per (view, Gaussian) gradient record
+// floats per (view, Gaussian) gradient record written by the blend backward: 7 geometry / opacity / depth sums + one per
+// blended channel, rounded up to whole float4s (12 for colour only, 16 with the fused extra colours)
+constexpr int grad_rec_stride(int channels) { return (7 + channels + 3) / 4 * 4; }
 constexpr int NUM_COUNTERS = 64;
 
 // gradient-record slots
@@ -111,7 +114,7 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     L.dlookback = take((size_t)MAX_PASSES * V * (sort_num_tiles((int64_t)P, 4) + 1) * RADIX * 4);
     L.dcounters = take((size_t)MAX_PASSES * V * 4);
     L.block_sums = take(((VP + SCAN_TILE - 1) / SCAN_TILE + 2) * 4);
-    L.grad_rec = take(VP * GRAD_REC * 4);
+    L.grad_rec = take(VP * grad_rec_stride(channels) * 4);
     L.geom_bytes = o;
     // binning
     o = 0;
@@ -197,7 +200,7 @@ int launch_blend_backward(int V, int P, int W, int H, int channels, void* geom_w
 int launch_feature_forward(int V, int P, int W, int H, const void* geom_ws, const void* binning_ws,
                            const void* image_ws, const Layout& L, const float* features, float* out_features,
                            cudaStream_t s);
-int launch_feature_backward(int V, int P, int W, int H, void* geom_ws, const void* binning_ws, const void* image_ws,
+int launch_feature_backward(int V, int P, int W, int H, int channels, void* geom_ws, const void* binning_ws, const void* image_ws,
                             const Layout& L, const float* features, const float* dL_dfeat_img, float* dL_dfeatures,
                             cudaStream_t s);
 int launch_preprocess_backward(int V, int P, int W, int H, int channels, int sh_coeffs,

@@ -146,10 +146,11 @@ preprocess_backward_kernel(const CamDev* __restrict__ cams, int V, int P, int sh
             }
             continue;
         }
-        const float4* rp = reinterpret_cast<const float4*>(grad_rec + idx * GRAD_REC);
-        float rec[GRAD_REC];
+        constexpr int REC = grad_rec_stride(NCH);
+        const float4* rp = reinterpret_cast<const float4*>(grad_rec + idx * REC);
+        float rec[REC];
 #pragma unroll
-        for (int i = 0; i < GRAD_REC / 4; ++i) {
+        for (int i = 0; i < REC / 4; ++i) {
             const float4 t = rp[i];
             rec[4 * i] = t.x; rec[4 * i + 1] = t.y; rec[4 * i + 2] = t.z; rec[4 * i + 3] = t.w;
         }

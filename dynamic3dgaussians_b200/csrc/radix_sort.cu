@@ -23,54 +23,89 @@ constexpr uint32_t FLAG_AGG = 1u << 30;     // tile-local count published
 constexpr uint32_t FLAG_INC = 1u << 31;     // inclusive prefix (all tiles <= this one) published
 constexpr uint32_t VALUE_MASK = (1u << 30) - 1u;
 constexpr unsigned FULL = 0xffffffffu;
-constexpr int HIST_PASSES = 4;              // digit passes histogrammed per launch (warp-private bins in smem)
-constexpr int HIST_ITEMS = 16;
 
 __device__ __forceinline__ uint32_t ld_volatile(const uint32_t* p) { return *reinterpret_cast<const volatile uint32_t*>(p); }
 __device__ __forceinline__ void st_volatile(uint32_t* p, uint32_t v) { *reinterpret_cast<volatile uint32_t*>(p) = v; }
 
-// Global digit histograms of passes [p0, p0 + np).  Warp-private bins, no shared-memory atomics (radix_rank.cuh).
+// Global digit histogram of one pass (blockIdx.z) of one segment (blockIdx.y).
+// Every LANE owns a private byte counter per bin (8 warps x 256 bins x 32 lanes = 64 KB), so counting a key is a plain
+// byte load / add / store: no atomics (shared-memory atomics cost ~2 cycles per lane on this part) and no digit matching
+// (9 ballots + bit logic per row, which is what the ballot-based version spent its time on: 127 us for 8.1 M keys x 4
+// digits, ncu launch list r01 v4).  A warp flushes its counters into the block's 256 totals before any of them can
+// exceed 255 rows.
+constexpr int HIST_ROWS_PER_BLOCK = 1024;   // rows of 32 keys per block (128 per warp)
+constexpr int HIST_FLUSH_ROWS = 248;        // per warp, < 256
+
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
 radix_histogram_kernel(const KeyT* __restrict__ keys, uint32_t n_max, const uint32_t* __restrict__ n_dev,
-                       int begin_bit, int end_bit, int p0, int np, int passes_total, uint32_t* __restrict__ hist) {
-    __shared__ uint32_t sh[8][HIST_PASSES][RADIX];
+                       int begin_bit, int end_bit, int passes_total, uint32_t* __restrict__ hist) {
+    extern __shared__ __align__(16) uint8_t s_cnt[];     // [8 warps][256 bins][32 lanes]
+    __shared__ uint32_t s_tot[RADIX];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < 8 * HIST_PASSES * RADIX; i += 256) (&sh[0][0][0])[i] = 0;
-    __syncthreads();
-    const int seg = blockIdx.y;
+    const int seg = blockIdx.y, pass = blockIdx.z;
+    const int shift = begin_bit + pass * RADIX_BITS;
+    const uint32_t mask = (1u << min(RADIX_BITS, end_bit - shift)) - 1u;
     keys += (size_t)seg * n_max;
-    hist += (size_t)seg * passes_total * RADIX;
     const uint32_t n = n_dev ? min(*n_dev, n_max) : n_max;
-    const uint32_t chunk = 256 * HIST_ITEMS;
-    for (uint32_t base = blockIdx.x * chunk; base < n; base += gridDim.x * chunk) {
-        const uint32_t e0 = base + warp * 32 * HIST_ITEMS + lane;
-        KeyT key[HIST_ITEMS];
+    s_tot[tid] = 0;
+    uint4* mine4 = reinterpret_cast<uint4*>(s_cnt + warp * (RADIX * 32));
+    for (int i = lane; i < RADIX * 32 / 16; i += 32) mine4[i] = make_uint4(0u, 0u, 0u, 0u);
+    __syncthreads();
+    uint8_t* mine = s_cnt + warp * (RADIX * 32) + lane;
+
+    auto flush = [&]() {    // warp-local: bins k*32 + lane, 32 byte counters each
+        __syncwarp();
 #pragma unroll
-        for (int i = 0; i < HIST_ITEMS; ++i) key[i] = (e0 + i * 32) < n ? keys[e0 + i * 32] : (KeyT)0;
+        for (int k = 0; k < RADIX / 32; ++k) {
+            const int bin = k * 32 + lane;
+            uint4* p = reinterpret_cast<uint4*>(s_cnt + warp * (RADIX * 32) + bin * 32);
+            const uint4 a = p[0], b = p[1];
+            uint32_t c = 0;
+            c = __dp4a(a.x, 0x01010101u, c); c = __dp4a(a.y, 0x01010101u, c);
+            c = __dp4a(a.z, 0x01010101u, c); c = __dp4a(a.w, 0x01010101u, c);
+            c = __dp4a(b.x, 0x01010101u, c); c = __dp4a(b.y, 0x01010101u, c);
+            c = __dp4a(b.z, 0x01010101u, c); c = __dp4a(b.w, 0x01010101u, c);
+            if (c) atomicAdd(&s_tot[bin], c);
+            p[0] = make_uint4(0u, 0u, 0u, 0u);
+            p[1] = make_uint4(0u, 0u, 0u, 0u);
+        }
+        __syncwarp();
+    };
+
+    const uint32_t rows = (n + 31u) / 32u;
+    constexpr int UNROLL = 4;
+    for (uint32_t r0 = blockIdx.x * HIST_ROWS_PER_BLOCK; r0 < rows; r0 += gridDim.x * HIST_ROWS_PER_BLOCK) {
+        const uint32_t r1 = min(r0 + HIST_ROWS_PER_BLOCK, rows);
+        int since_flush = 0;
+        for (uint32_t r = r0 + warp; r < r1; r += 8 * UNROLL) {
+            KeyT key[UNROLL];
+            bool ok[UNROLL];
 #pragma unroll
-        for (int i = 0; i < HIST_ITEMS; ++i) {
-            const bool valid = (e0 + i * 32) < n;
+            for (int u = 0; u < UNROLL; ++u) {
+                const uint32_t row = r + 8 * u;
+                const uint32_t e = row * 32u + lane;
+                ok[u] = row < r1 && e < n;
+                key[u] = ok[u] ? keys[e] : (KeyT)0;
+            }
 #pragma unroll
-            for (int p = 0; p < HIST_PASSES; ++p) {
-                if (p < np) {
-                    const int shift = begin_bit + (p0 + p) * RADIX_BITS;
-                    const int bits = min(RADIX_BITS, end_bit - shift);
-                    const uint32_t d = (uint32_t)(key[i] >> shift) & ((1u << bits) - 1u);
-                    uint32_t peers;
-                    warp_hist_add(sh[warp][p], d, valid, lane, peers);
+            for (int u = 0; u < UNROLL; ++u) {
+                if (ok[u]) {
+                    const uint32_t d = (uint32_t)(key[u] >> shift) & mask;
+                    mine[d * 32] = (uint8_t)(mine[d * 32] + 1);
                 }
             }
+            since_flush += UNROLL;
+            if (since_flush + UNROLL > HIST_FLUSH_ROWS) {
+                flush();
+                since_flush = 0;
+            }
         }
+        flush();
     }
     __syncthreads();
-    for (int i = tid; i < np * RADIX; i += 256) {
-        const int p = i / RADIX, d = i - p * RADIX;
-        uint32_t c = 0;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) c += sh[w][p][d];
-        if (c) atomicAdd(&hist[(p0 + p) * RADIX + d], c);
-    }
+    const uint32_t c = s_tot[tid];
+    if (c) atomicAdd(&hist[((size_t)seg * passes_total + pass) * RADIX + tid], c);
 }
 
 // exclusive scan of each (segment, pass)'s 256 bins, in place (one block of 256 threads each)
@@ -259,15 +294,19 @@ int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1,
     GSR_CUDA_TRY(cudaMemsetAsync(lookback, 0, (size_t)passes * segments * lb_seg * 4, s));
     GSR_CUDA_TRY(cudaMemsetAsync(tile_counters, 0, (size_t)passes * segments * 4, s));
     if (!hist_ready) {
-        int64_t hb = (n_max + 256 * HIST_ITEMS - 1) / (256 * HIST_ITEMS);
-        const int64_t cap = (148 * 8 + segments - 1) / segments;
-        const int hist_blocks = (int)(hb < cap ? hb : (cap > 1 ? cap : 1));
-        for (int p0 = 0; p0 < passes; p0 += HIST_PASSES) {
-            const int np = passes - p0 < HIST_PASSES ? passes - p0 : HIST_PASSES;
-            radix_histogram_kernel<KeyT><<<dim3(hist_blocks, segments), 256, 0, s>>>(
-                keys0, (uint32_t)n_max, n_dev, begin_bit, end_bit, p0, np, passes, hist);
-            GSR_LAUNCH_CHECK();
+        const int64_t rows = (n_max + 31) / 32;
+        const int64_t hb = (rows + HIST_ROWS_PER_BLOCK - 1) / HIST_ROWS_PER_BLOCK;
+        const int hist_blocks = (int)(hb < 4096 ? hb : 4096);
+        constexpr int hist_smem = 8 * RADIX * 32;
+        static bool attr_set = false;        // per instantiation (KeyT)
+        if (!attr_set) {
+            GSR_CUDA_TRY(cudaFuncSetAttribute(radix_histogram_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              hist_smem));
+            attr_set = true;
         }
+        radix_histogram_kernel<KeyT><<<dim3(hist_blocks, segments, passes), 256, hist_smem, s>>>(
+            keys0, (uint32_t)n_max, n_dev, begin_bit, end_bit, passes, hist);
+        GSR_LAUNCH_CHECK();
     }
     radix_scan_hist_kernel<<<passes * segments, RADIX, 0, s>>>(hist);
     GSR_LAUNCH_CHECK();
