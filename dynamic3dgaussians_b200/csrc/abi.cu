@@ -141,15 +141,16 @@ int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels,
     compute_layout(P, V, W, H, channels, sh_coeffs, 0, L);
     if (geom_bytes < L.geom_bytes) return GSR_ERR_WORKSPACE_TOO_SMALL;
 
-    // cameras -> device (small; staged through the driver for pageable memory)
+    // cameras -> device as kernel arguments (a few hundred bytes each): unlike a copy from pageable host memory this
+    // never makes the driver wait for the stream, and it can be captured into a CUDA graph
     {
-        CamDev tmp[64];
         CamDev* cd = at<CamDev>(geom_ws, L.cams);
-        for (int v0 = 0; v0 < V; v0 += 64) {
-            const int n = V - v0 < 64 ? V - v0 : 64;
-            for (int i = 0; i < n; ++i) fill_cam(cams_host[v0 + i], tmp[i]);
-            GSR_CUDA_TRY(cudaMemcpyAsync(cd + v0, tmp, sizeof(CamDev) * n, cudaMemcpyHostToDevice, s));
-            // tmp lives on this stack frame: the copy from pageable memory is staged before the call returns
+        for (int v0 = 0; v0 < V; v0 += CamPack::N) {
+            CamPack pack;
+            pack.n = V - v0 < CamPack::N ? V - v0 : CamPack::N;
+            for (int i = 0; i < pack.n; ++i) fill_cam(cams_host[v0 + i], pack.cam[i]);
+            rc = launch_store_cams(pack, cd + v0, s);
+            if (rc) return rc;
         }
     }
     uint32_t* counters = at<uint32_t>(geom_ws, L.counters);

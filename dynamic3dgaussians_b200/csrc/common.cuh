@@ -41,6 +41,13 @@ struct CamDev {
     int pad[3];
 };
 
+struct CamPack {            // cameras travel to the device as a kernel argument (<= 4 KB)
+    static constexpr int N = 16;
+    int n;
+    CamDev cam[N];
+};
+static_assert(sizeof(CamPack) <= 4000, "kernel argument space");
+
 // ------------------------------------------------------------------------------------------------------------
 // radix sort geometry
 // ------------------------------------------------------------------------------------------------------------
@@ -197,6 +204,7 @@ int launch_blend_forward(int V, int W, int H, int channels, const void* geom_ws,
 int launch_blend_backward(int V, int P, int W, int H, int channels, void* geom_ws, const void* binning_ws,
                           const void* image_ws, const Layout& L, const float* dL_dcolor, const float* dL_dextra,
                           const float* dL_ddepth, const float* dL_dalpha, cudaStream_t s);
+int launch_store_cams(const CamPack& pack, CamDev* dst, cudaStream_t s);
 int launch_feature_forward(int V, int P, int W, int H, const void* geom_ws, const void* binning_ws,
                            const void* image_ws, const Layout& L, const float* features, float* out_features,
                            cudaStream_t s);

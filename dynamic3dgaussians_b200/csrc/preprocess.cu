@@ -177,6 +177,19 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, fl
 
 }  // namespace
 
+__global__ void store_cams_kernel(const __grid_constant__ CamPack pack, CamDev* __restrict__ dst) {
+    constexpr int WORDS = sizeof(CamDev) / 4;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(pack.cam);
+    uint32_t* out = reinterpret_cast<uint32_t*>(dst);
+    for (int i = threadIdx.x; i < pack.n * WORDS; i += blockDim.x) out[i] = src[i];
+}
+
+int launch_store_cams(const CamPack& pack, CamDev* dst, cudaStream_t s) {
+    store_cams_kernel<<<1, 256, 0, s>>>(pack, dst);
+    GSR_LAUNCH_CHECK();
+    return GSR_OK;
+}
+
 int launch_preprocess(const CamDev* cams, int V, int P, int sh_coeffs, const float* means3D, const float* opacities,
                       const float* scales, const float* rotations, const float* cov3D_precomp, const float* sh,
                       void* ws, const Layout& L, int32_t* radii_out, cudaStream_t s) {

@@ -109,3 +109,44 @@ def sharded_step(settings, my_views: Sequence[int], params: dict, cotangents: di
         slab.flat.zero_()
     allreduce_grads(slab.flat, group)
     return out, slab
+
+
+class GraphedStep:
+    """`sharded_step` captured once into a CUDA graph and replayed: one launch per step instead of ~35 kernel launches,
+    ~15 allocations and the Python / ctypes work around them (about 0.4-1 ms of host time, which bounds the step once
+    a rank holds only 3-4 views).  Everything the step touches is static:
+
+      * `params` tensors are read in place: update them with in-place ops (optimizer.step does) before `replay()`;
+      * `cotangents` (already restricted to this rank's views) are read in place as well;
+      * `capacity` must be given (a graph cannot size its workspaces from a device-side count); `overflowed()` tells
+        after a replay whether the instance count exceeded it;
+      * outputs (`self.out`, the tuple of forward_views) and the gradient slab (`self.slab`) are overwritten by every
+        replay.  The all-reduce over `group` is part of the graph (NCCL collectives are capturable)."""
+
+    def __init__(self, settings, my_views: Sequence[int], params: dict, cotangents: dict, capacity: int, group=None,
+                 warmup: int = 2):
+        dev = params["means3D"].device
+        self.slab = GradSlab(params["means3D"].shape[0], dev)
+        self.out = None
+        args = (settings, list(my_views), params, cotangents)
+        kw = dict(group=group, capacity=int(capacity), slab=self.slab, local_cotangents=True)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):           # lazy initialisation (NCCL communicators, kernel attributes) happens here
+            for _ in range(max(1, warmup)):
+                sharded_step(*args, **kw)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.out, _ = sharded_step(*args, **kw)
+
+    def replay(self):
+        self.graph.replay()
+        return self.out, self.slab
+
+    def overflowed(self) -> bool:
+        if self.out is None:
+            return False
+        from . import rasterizer as RZ
+        return RZ.read_counters(self.out[5])[1]
