@@ -16,6 +16,7 @@ EXPORTED_SYMBOLS = [
     "gsr_forward_geometry", "gsr_forward_render", "gsr_read_counters", "gsr_backward", "gsr_mark_visible",
     "gsr_export_view_binning", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_knn_temp_bytes", "gsr_knn",
     "gsr_dyn_losses_temp_bytes", "gsr_dyn_losses",
+    "gsr_image_loss_state_bytes", "gsr_image_loss_forward", "gsr_image_loss_backward",
     "gsr_fp32_peak_probe", "gsr_probe_geometry", "gsr_stage_timing_enable", "gsr_stage_timing_count", "gsr_stage_name",
     "gsr_stage_timing_read",
 ]
@@ -85,6 +86,10 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.gsr_dyn_losses_temp_bytes.restype = sz
     lib.gsr_dyn_losses_temp_bytes.argtypes = [i64]
     lib.gsr_dyn_losses.argtypes = [i64, i32] + [vp] * 12 + [sz, vp]
+    lib.gsr_image_loss_state_bytes.restype = sz
+    lib.gsr_image_loss_state_bytes.argtypes = [i64, i32, i32]
+    lib.gsr_image_loss_forward.argtypes = [i64, i32, i32, vp, vp, C.c_float, C.c_float, vp, sz, vp, vp]
+    lib.gsr_image_loss_backward.argtypes = [i64, i32, i32, vp, vp, C.c_float, C.c_float, vp, sz, vp, vp, vp]
     lib.gsr_fp32_peak_probe.argtypes = [vp, i32, vp]
     lib.gsr_stage_timing_enable.argtypes = [i32]
     lib.gsr_stage_name.restype = C.c_char_p

@@ -269,6 +269,39 @@ int gsr_export_view_binning(int view, int V, int P, int W, int H, int channels, 
                               n_contrib_out, (cudaStream_t)stream);
 }
 
+// ---- fused L1 + SSIM image loss ----
+size_t gsr_image_loss_state_bytes(int64_t n_planes, int W, int H) {
+    if (n_planes <= 0 || W <= 0 || H <= 0) return 0;
+    return image_loss_state_bytes(n_planes, W, H);
+}
+
+static int check_loss_args(int64_t n_planes, int W, int H, const void* a, const void* b, const void* state,
+                           size_t state_bytes) {
+    if (n_planes <= 0 || n_planes > 65535 || W <= 0 || H <= 0 || W >= (1 << 20) || H >= (1 << 20))
+        return GSR_ERR_INVALID_ARGUMENT;
+    if (!a || !b || !state) return GSR_ERR_INVALID_ARGUMENT;
+    if (state_bytes < image_loss_state_bytes(n_planes, W, H)) return GSR_ERR_WORKSPACE_TOO_SMALL;
+    return GSR_OK;
+}
+
+int gsr_image_loss_forward(int64_t n_planes, int W, int H, const float* img, const float* target, float w_l1,
+                           float w_ssim, void* state, size_t state_bytes, float* loss_out, gsr_stream_t stream) {
+    int rc = check_loss_args(n_planes, W, H, img, target, state, state_bytes);
+    if (rc) return rc;
+    if (!loss_out) return GSR_ERR_INVALID_ARGUMENT;
+    return launch_image_loss_forward(n_planes, W, H, img, target, w_l1, w_ssim, state, loss_out, (cudaStream_t)stream);
+}
+
+int gsr_image_loss_backward(int64_t n_planes, int W, int H, const float* img, const float* target, float w_l1,
+                            float w_ssim, const void* state, size_t state_bytes, const float* grad_out, float* dL_dimg,
+                            gsr_stream_t stream) {
+    int rc = check_loss_args(n_planes, W, H, img, target, state, state_bytes);
+    if (rc) return rc;
+    if (!dL_dimg) return GSR_ERR_INVALID_ARGUMENT;
+    return launch_image_loss_backward(n_planes, W, H, img, target, w_l1, w_ssim, state, grad_out, dL_dimg,
+                                      (cudaStream_t)stream);
+}
+
 // ---- stand-alone sort (tests) ----
 static size_t sort_layout(int64_t n, int key_bytes, size_t off[7]) {
     size_t o = 0;

@@ -180,6 +180,21 @@ int gsr_knn(int64_t P, int K, const float* points, float* mean_dist2, int32_t* i
             void* tmp, size_t tmp_bytes, gsr_stream_t stream);
 
 /*
+ * Fused image loss of the training loop (SURVEY.md 8f "next" row 3): w_l1 * mean|x - y| + w_ssim * (1 - mean SSIM(x, y))
+ * and its gradient w.r.t. x.  Replaces the eager PyTorch code of REF/train.py:183 = 0.8 * l1_loss_v1 (REF/helpers.py)
+ * + 0.2 * (1 - calc_ssim) (REF/external.py:90-133: 11x11 Gaussian window, sigma 1.5, zero padding, mean over all
+ * channels and pixels).  img / target / dL_dimg: [n_planes][H][W] float32 (n_planes = images * channels);
+ * state: gsr_image_loss_state_bytes() bytes kept from forward to backward; loss_out [3] device floats: total, L1 mean,
+ * SSIM mean; grad_out: device scalar cotangent of the total (null = 1).
+ */
+size_t gsr_image_loss_state_bytes(int64_t n_planes, int W, int H);
+int gsr_image_loss_forward(int64_t n_planes, int W, int H, const float* img, const float* target, float w_l1,
+                           float w_ssim, void* state, size_t state_bytes, float* loss_out, gsr_stream_t stream);
+int gsr_image_loss_backward(int64_t n_planes, int W, int H, const float* img, const float* target, float w_l1,
+                            float w_ssim, const void* state, size_t state_bytes, const float* grad_out, float* dL_dimg,
+                            gsr_stream_t stream);
+
+/*
  * Fused local-rigidity / rotation-similarity / isometry losses over a fixed K-NN graph of F foreground Gaussians,
  * forward and (optionally) backward: replaces the eager PyTorch code of REF/train.py:253-273 (== REF/cvpr_dyn.py:304-330).
  *   pts [F][3], rot [F][4] (w,x,y,z; the normalised current rotations), prev_inv_rot [F][4] (REF/train.py:303-304),
