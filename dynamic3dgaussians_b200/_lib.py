@@ -16,10 +16,19 @@ EXPORTED_SYMBOLS = [
     "gsr_forward_geometry", "gsr_forward_render", "gsr_read_counters", "gsr_backward", "gsr_mark_visible",
     "gsr_export_view_binning", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_knn_temp_bytes", "gsr_knn",
     "gsr_dyn_losses_temp_bytes", "gsr_dyn_losses",
-    "gsr_image_loss_state_bytes", "gsr_image_loss_forward", "gsr_image_loss_backward",
+    "gsr_image_loss_state_bytes", "gsr_image_loss_forward", "gsr_image_loss_backward", "gsr_adam_step",
     "gsr_fp32_peak_probe", "gsr_probe_geometry", "gsr_stage_timing_enable", "gsr_stage_timing_count", "gsr_stage_name",
     "gsr_stage_timing_read",
 ]
+
+
+class GsrAdamTensor(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("step", C.c_void_p), ("n", C.c_int64), ("lr", C.c_float), ("pad_", C.c_int32)]
+
+
+ADAM_MAX_TENSORS = 16
+ADAM_SCRATCH_BYTES = 256
 
 
 class GsrCamera(C.Structure):
@@ -90,6 +99,7 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.gsr_image_loss_state_bytes.argtypes = [i64, i32, i32]
     lib.gsr_image_loss_forward.argtypes = [i64, i32, i32, vp, vp, C.c_float, C.c_float, vp, sz, vp, vp]
     lib.gsr_image_loss_backward.argtypes = [i64, i32, i32, vp, vp, C.c_float, C.c_float, vp, sz, vp, vp, vp]
+    lib.gsr_adam_step.argtypes = [i32, C.POINTER(GsrAdamTensor), C.c_double, C.c_double, C.c_double, vp, vp]
     lib.gsr_fp32_peak_probe.argtypes = [vp, i32, vp]
     lib.gsr_stage_timing_enable.argtypes = [i32]
     lib.gsr_stage_name.restype = C.c_char_p

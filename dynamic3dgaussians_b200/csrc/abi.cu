@@ -302,6 +302,20 @@ int gsr_image_loss_backward(int64_t n_planes, int W, int H, const float* img, co
                                       (cudaStream_t)stream);
 }
 
+// ---- fused Adam ----
+int gsr_adam_step(int n_tensors, const GsrAdamTensor* tensors_host, double beta1, double beta2, double eps,
+                  void* scratch, gsr_stream_t stream) {
+    if (n_tensors < 0 || n_tensors > GSR_ADAM_MAX_TENSORS || (n_tensors > 0 && !tensors_host) || !scratch)
+        return GSR_ERR_INVALID_ARGUMENT;
+    for (int i = 0; i < n_tensors; ++i) {
+        const GsrAdamTensor& t = tensors_host[i];
+        if (t.n < 0 || !t.step || (t.n > 0 && (!t.param || !t.grad || !t.exp_avg || !t.exp_avg_sq)))
+            return GSR_ERR_INVALID_ARGUMENT;
+    }
+    if (n_tensors == 0) return GSR_OK;
+    return launch_adam_step(n_tensors, tensors_host, beta1, beta2, eps, scratch, (cudaStream_t)stream);
+}
+
 // ---- stand-alone sort (tests) ----
 static size_t sort_layout(int64_t n, int key_bytes, size_t off[7]) {
     size_t o = 0;

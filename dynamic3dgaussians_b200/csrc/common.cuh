@@ -209,6 +209,8 @@ int launch_image_loss_forward(int64_t n_img, int W, int H, const float* img, con
                               void* state, float* loss_out, cudaStream_t s);
 int launch_image_loss_backward(int64_t n_img, int W, int H, const float* img, const float* tgt, float w_l1,
                                float w_ssim, const void* state, const float* grad_out, float* dL_dimg, cudaStream_t s);
+int launch_adam_step(int n_tensors, const GsrAdamTensor* tensors, double beta1, double beta2, double eps, void* scratch,
+                     cudaStream_t s);
 int launch_store_cams(const CamPack& pack, CamDev* dst, cudaStream_t s);
 int launch_feature_forward(int V, int P, int W, int H, const void* geom_ws, const void* binning_ws,
                            const void* image_ws, const Layout& L, const float* features, float* out_features,

@@ -59,12 +59,18 @@ def initialize_params(points: torch.Tensor, rgb: torch.Tensor, seg: torch.Tensor
     return params, variables
 
 
-def initialize_optimizer(params: Dict[str, torch.nn.Parameter], variables: dict, lrs: Optional[dict] = None):
-    """REF/train.py:119-135: one Adam group per tensor, eps 1e-15, means3D scaled by the scene radius."""
+def initialize_optimizer(params: Dict[str, torch.nn.Parameter], variables: dict, lrs: Optional[dict] = None,
+                         fused: bool = True):
+    """REF/train.py:119-135: one Adam group per tensor, eps 1e-15, means3D scaled by the scene radius.  fused=True
+    (default) is optim.FusedAdam -- one kernel for all groups, CUDA-graph capturable; fused=False is torch.optim.Adam
+    in capturable mode (the comparison arm of the tests)."""
     lrs = dict(LEARNING_RATES if lrs is None else lrs)
     lrs['means3D'] = lrs['means3D'] * variables['scene_radius']
     groups = [{'params': [v], 'name': k, 'lr': lrs[k]} for k, v in params.items()]
-    return torch.optim.Adam(groups, lr=0.0, eps=1e-15)
+    if fused:
+        from .optim import FusedAdam
+        return FusedAdam(groups, lr=0.0, eps=1e-15)
+    return torch.optim.Adam(groups, lr=0.0, eps=1e-15, capturable=True)
 
 
 def params2rendervar(params):
@@ -111,8 +117,9 @@ def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optiona
 
     loss = sum(weights[k] * v for k, v in losses.items())
     seen = radius > 0
-    variables['max_2D_radius'] = torch.where(seen, torch.maximum(radius.float(), variables['max_2D_radius']),
-                                             variables['max_2D_radius'])
+    # in place (REF/train.py:288-289), so that the statistics also accumulate when the step is replayed from a CUDA graph
+    variables['max_2D_radius'].copy_(torch.where(seen, torch.maximum(radius.float(), variables['max_2D_radius']),
+                                                 variables['max_2D_radius']))
     variables['seen'] = seen
     return loss, variables, losses
 
@@ -171,3 +178,63 @@ def train_timestep(params, variables, optimizer, dataset: Sequence[dict], num_it
             optimizer.zero_grad(set_to_none=True)
         history.append(loss.detach())
     return history
+
+
+class GraphedTrainer:
+    """One CUDA graph per training camera, each holding a WHOLE iteration -- render, losses, backward, statistics, Adam
+    step -- so that an iteration is a single launch (the eager loop spends ~2 ms of Python per iteration on ~1 ms of GPU
+    work).  The graphs share one memory pool (they never run concurrently).  Valid while the parameter tensors keep
+    their identity and size: build it after the densification phase (or rebuild it after every densify round) with an
+    optimizer created by initialize_optimizer() and a fixed per-view instance `capacity`."""
+
+    def __init__(self, params, variables, optimizer, dataset: Sequence[dict], is_initial_timestep: bool, capacity: int,
+                 weights: Optional[dict] = None, accumulate_stats: bool = True, warmup: int = 3):
+        dev = params['means3D'].device
+        self.params, self.variables, self.optimizer, self.dataset = params, variables, optimizer, list(dataset)
+        self.graphs: List[torch.cuda.CUDAGraph] = []
+        self.losses: List[torch.Tensor] = []
+        self.order: List[int] = []
+
+        def iteration(curr):
+            loss, _, _ = get_loss(params, curr, variables, is_initial_timestep, weights, capacity)
+            loss.backward()
+            with torch.no_grad():
+                if accumulate_stats and is_initial_timestep:
+                    _accumulate_inplace(variables)
+                optimizer.step()
+            return loss.detach()
+
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for i in range(max(1, warmup)):
+                optimizer.zero_grad(set_to_none=True)
+                iteration(self.dataset[i % len(self.dataset)])
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        pool = None
+        for curr in self.dataset:
+            optimizer.zero_grad(set_to_none=True)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, pool=pool):
+                loss = iteration(curr)
+            pool = g.pool() if pool is None else pool
+            self.graphs.append(g)
+            self.losses.append(loss)
+
+    def step(self, generator: Optional[torch.Generator] = None) -> torch.Tensor:
+        """One optimizer iteration on the next camera of a shuffled pass (get_batch); returns that graph's loss tensor
+        (overwritten by its next replay)."""
+        if not self.order:
+            self.order = torch.randperm(len(self.dataset), generator=generator).tolist()
+        i = self.order.pop()
+        self.graphs[i].replay()
+        return self.losses[i]
+
+
+def _accumulate_inplace(variables: dict):
+    """accumulate_mean2d_gradient (REF/external.py:136-140) with in-place updates, for graph replay."""
+    seen = variables['seen']
+    norm = torch.norm(variables['means2D'].grad[:, :2], dim=-1)
+    variables['means2D_gradient_accum'].add_(torch.where(seen, norm, torch.zeros_like(norm)))
+    variables['denom'].add_(seen.to(variables['denom'].dtype))

@@ -195,6 +195,28 @@ int gsr_image_loss_backward(int64_t n_planes, int W, int H, const float* img, co
                             gsr_stream_t stream);
 
 /*
+ * Fused Adam step over up to GSR_ADAM_MAX_TENSORS parameter tensors in one launch (the optimizer
+ * of the train.py-shaped loop; REF/train.py:119-135 builds one torch.optim.Adam group per tensor, lr per group,
+ * betas (0.9, 0.999), eps 1e-15).  Same update rule as torch.optim.Adam without weight decay / amsgrad.  All pointers
+ * are device pointers; `step` is a one-float device counter per tensor (incremented by the call); tensors with a zero
+ * learning rate still update their moments.  scratch: GSR_ADAM_SCRATCH_BYTES device bytes.
+ */
+#define GSR_ADAM_MAX_TENSORS 16
+#define GSR_ADAM_SCRATCH_BYTES 256
+typedef struct GsrAdamTensor {
+    float* param;
+    const float* grad;
+    float* exp_avg;
+    float* exp_avg_sq;
+    float* step;
+    int64_t n;
+    float lr;
+    int32_t pad_;
+} GsrAdamTensor;
+int gsr_adam_step(int n_tensors, const GsrAdamTensor* tensors_host, double beta1, double beta2, double eps,
+                  void* scratch, gsr_stream_t stream);
+
+/*
  * Fused local-rigidity / rotation-similarity / isometry losses over a fixed K-NN graph of F foreground Gaussians,
  * forward and (optionally) backward: replaces the eager PyTorch code of REF/train.py:253-273 (== REF/cvpr_dyn.py:304-330).
  *   pts [F][3], rot [F][4] (w,x,y,z; the normalised current rotations), prev_inv_rot [F][4] (REF/train.py:303-304),
