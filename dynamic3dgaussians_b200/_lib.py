@@ -47,7 +47,7 @@ class GsrWorkspaceSizes(C.Structure):
 
 _LAYOUT_SIZE_T = ["cams", "counters", "radii", "rects", "geomrec", "cov3D", "rgb", "col4", "ext4", "clamped",
                   "dkeys0", "dkeys1", "dvals0", "dvals1", "dhist", "dlookback", "dcounters", "block_sums", "grad_rec",
-                  "ikeys0", "ikeys1", "ivals0", "ivals1", "ihist", "ilookback", "st_ranges", "chunk_base", "chunk_key",
+                  "ikeys0", "ikeys1", "ivals0", "ivals1", "imasks", "ihist", "ilookback", "st_ranges", "chunk_base", "chunk_key",
                   "chunk_counts", "recA", "recB", "recC", "recD",
                   "ranges", "tile_start", "tile_order", "n_contrib", "final_T"]
 _LAYOUT_INT = ["tiles_x", "tiles_y", "stiles_x", "stiles_y", "tile_bits", "depth_passes", "tile_passes", "sorted_keys_in",

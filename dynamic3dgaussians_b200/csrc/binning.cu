@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(CHUNK)
 chunk_count_kernel(const uint32_t* __restrict__ counters, const uint32_t* __restrict__ chunk_key,
                    const uint32_t* __restrict__ chunk_base, const uint2* __restrict__ st_ranges, uint32_t S,
                    int stiles_x, const uint32_t* __restrict__ vals, const ushort4* __restrict__ rects,
-                   uint32_t* __restrict__ chunk_counts) {
+                   uint16_t* __restrict__ masks, uint32_t* __restrict__ chunk_counts) {
     __shared__ uint32_t s_cnt[ST_TILES][CHUNK / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     ChunkInfo c;
@@ -297,7 +297,10 @@ chunk_count_kernel(const uint32_t* __restrict__ counters, const uint32_t* __rest
     for (uint32_t cid = blockIdx.x; chunk_info(cid, counters, chunk_key, chunk_base, st_ranges, S, stiles_x, c);
          cid += gridDim.x) {
         uint32_t mask = 0;
-        if ((uint32_t)tid < c.count) mask = st_hit_mask(rects[vals[c.first + tid]], c.ox, c.oy);
+        if ((uint32_t)tid < c.count) {
+            mask = st_hit_mask(rects[vals[c.first + tid]], c.ox, c.oy);
+            masks[c.first + tid] = (uint16_t)mask;           // the scatter pass reads this instead of the rectangle
+        }
 #pragma unroll
         for (int t = 0; t < ST_TILES; ++t) {
             const uint32_t bal = __ballot_sync(FULL, (mask >> t) & 1u);
@@ -453,7 +456,7 @@ __global__ void __launch_bounds__(CHUNK)
 scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __restrict__ chunk_key,
                        const uint32_t* __restrict__ chunk_base, const uint2* __restrict__ st_ranges, uint32_t S,
                        int stiles_x, int tiles_x, int tiles_y, int P, uint32_t capacity,
-                       const uint32_t* __restrict__ vals, const ushort4* __restrict__ rects,
+                       const uint32_t* __restrict__ vals, const uint16_t* __restrict__ masks,
                        const uint32_t* __restrict__ chunk_offs, const uint32_t* __restrict__ tile_start,
                        const float4* __restrict__ geomrec, const float4* __restrict__ col4,
                        const float4* __restrict__ rgb_sh4, const float4* __restrict__ ext4,
@@ -463,23 +466,47 @@ scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __
     __shared__ uint32_t s_tbase[ST_TILES];            // list position of this chunk's first hit, per tile
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t lt = (1u << lane) - 1u;
-    ChunkInfo c;
-    for (uint32_t cid = blockIdx.x; chunk_info(cid, counters, chunk_key, chunk_base, st_ranges, S, stiles_x, c);
-         cid += gridDim.x) {
-        uint32_t mask = 0;
+    // software pipeline over the CTA's chunks (the kernel is bound by dependent-load latency: chunk table -> instance
+    // -> record): while chunk i's records are gathered and stored, the (instance, hit mask) pairs of chunk i+1 and the
+    // chunk-table entries of chunk i+2 are already in flight
+    const uint32_t nch = counters[CNT_NCHUNKS];
+    auto info = [&](uint32_t cid, ChunkInfo& o) -> bool {
+        if (cid >= nch) return false;
+        o.key = chunk_key[cid];
+        const uint2 r = st_ranges[o.key];
+        o.first = r.x + (cid - chunk_base[o.key]) * CHUNK;
+        o.count = min((uint32_t)CHUNK, r.y - o.first);
+        o.view = o.key / S;
+        const uint32_t sidx = o.key - o.view * S;
+        const uint32_t sy = sidx / (uint32_t)stiles_x;
+        o.ox = (sidx - sy * (uint32_t)stiles_x) * ST;
+        o.oy = sy * ST;
+        return true;
+    };
+    ChunkInfo c, cn, cnn;
+    bool have = info(blockIdx.x, c);
+    bool have_next = info(blockIdx.x + gridDim.x, cn);
+    uint32_t gi = 0, mask = 0;
+    if (have && (uint32_t)tid < c.count) {
+        gi = vals[c.first + tid];
+        mask = masks[c.first + tid];
+    }
+    for (uint32_t cid = blockIdx.x; have; cid += gridDim.x) {
         float4 rA, rB, rC, rD;
-        if ((uint32_t)tid < c.count) {
-            const uint32_t gi = vals[c.first + tid];
-            mask = st_hit_mask(rects[gi], c.ox, c.oy);
-            if (mask) {
-                const uint32_t g = gi - c.view * (uint32_t)P;
-                rA = geomrec[2 * (size_t)gi];
-                rB = geomrec[2 * (size_t)gi + 1];
-                rC = col4 ? col4[g] : rgb_sh4[gi];
-                rC.w = __uint_as_float(gi);
-                if (EXTRA) rD = ext4[g];
-            }
+        if (mask) {
+            const uint32_t g = gi - c.view * (uint32_t)P;
+            rA = geomrec[2 * (size_t)gi];
+            rB = geomrec[2 * (size_t)gi + 1];
+            rC = col4 ? col4[g] : rgb_sh4[gi];
+            rC.w = __uint_as_float(gi);
+            if (EXTRA) rD = ext4[g];
         }
+        uint32_t gi_next = 0, mask_next = 0;
+        if (have_next && (uint32_t)tid < cn.count) {
+            gi_next = vals[cn.first + tid];
+            mask_next = masks[cn.first + tid];
+        }
+        const bool have_nn = info(cid + 2 * gridDim.x, cnn);
         if (tid < ST_TILES) {
             const uint32_t gx = c.ox + (tid & 3), gy = c.oy + (tid >> 2);
             uint32_t b = 0;
@@ -519,6 +546,12 @@ scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __
             }
         }
         __syncthreads();                              // shared counters are reused by the next chunk
+        c = cn;
+        cn = cnn;
+        gi = gi_next;
+        mask = mask_next;
+        have = have_next;
+        have_next = have_nn;
     }
 }
 
@@ -619,7 +652,7 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     chunk_table_kernel<<<1, SCAN_BLOCK, 0, s>>>(VS, st_ranges, chunk_base, chunk_key, max_chunks, counters);
     GSR_LAUNCH_CHECK();
     chunk_count_kernel<<<chunk_grid, CHUNK, 0, s>>>(counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, svals,
-                                                   rects, chunk_counts);
+                                                   rects, at<uint16_t>(bws, L.imasks), chunk_counts);
     GSR_LAUNCH_CHECK();
     tile_offsets_kernel<<<(VS + 3) / 4, 128, 0, s>>>(VS, S, L.stiles_x, L.tiles_x, L.tiles_y, chunk_base, max_chunks,
                                                     chunk_counts, tile_start);
@@ -634,17 +667,25 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
                                                            at<float4>(gws, L.ext4));
         GSR_LAUNCH_CHECK();
     }
+    // persistent CTAs: exactly as many as are resident at once (a second, partial wave would run at low occupancy)
+    static int scatter_per_sm[2] = {0, 0};
+    if (scatter_per_sm[0] == 0) {
+        GSR_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&scatter_per_sm[0], scatter_records_kernel<false>, CHUNK, 0));
+        GSR_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&scatter_per_sm[1], scatter_records_kernel<true>, CHUNK, 0));
+    }
+    const uint32_t resident = 148u * (uint32_t)scatter_per_sm[channels > 3 ? 1 : 0];
+    const uint32_t scatter_grid = max_chunks < resident ? max_chunks : resident;
     const float4* col4 = colors_precomp ? at<float4>(gws, L.col4) : nullptr;
     const float4* rgb4 = sh_coeffs > 0 ? at<float4>(gws, L.rgb) : nullptr;
     if (channels > 3) {
-        scatter_records_kernel<true><<<chunk_grid, CHUNK, 0, s>>>(
-            counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals, rects,
-            chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, at<float4>(gws, L.ext4),
+        scatter_records_kernel<true><<<scatter_grid, CHUNK, 0, s>>>(
+            counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals,
+            at<uint16_t>(bws, L.imasks), chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, at<float4>(gws, L.ext4),
             at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC), at<float4>(bws, L.recD));
     } else {
-        scatter_records_kernel<false><<<chunk_grid, CHUNK, 0, s>>>(
-            counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals, rects,
-            chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, nullptr, at<float4>(bws, L.recA),
+        scatter_records_kernel<false><<<scatter_grid, CHUNK, 0, s>>>(
+            counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals,
+            at<uint16_t>(bws, L.imasks), chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, nullptr, at<float4>(bws, L.recA),
             at<float4>(bws, L.recB), at<float4>(bws, L.recC), nullptr);
     }
     GSR_LAUNCH_CHECK();

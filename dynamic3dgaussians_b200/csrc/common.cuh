@@ -132,6 +132,7 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     L.ikeys1 = take(cap * 4);
     L.ivals0 = take(cap * 4);
     L.ivals1 = take(cap * 4);
+    L.imasks = take(cap * 2);             // 16-bit tile hit mask of every sorted supertile instance
     L.ihist = take((size_t)MAX_PASSES * RADIX * 4);
     L.ilookback = take((size_t)MAX_PASSES * (sort_num_tiles((int64_t)cap, 4) + 1) * RADIX * 4);
     L.st_ranges = take(VS * 8);

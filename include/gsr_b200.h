@@ -72,7 +72,7 @@ typedef struct GsrLayout {
     size_t cams, counters, radii, rects, geomrec, cov3D, rgb, col4, ext4, clamped;
     size_t dkeys0, dkeys1, dvals0, dvals1, dhist, dlookback, dcounters, block_sums, grad_rec;
     /* binning workspace: supertile-instance sort arrays, chunk tables, per-instance records */
-    size_t ikeys0, ikeys1, ivals0, ivals1, ihist, ilookback, st_ranges, chunk_base, chunk_key, chunk_counts;
+    size_t ikeys0, ikeys1, ivals0, ivals1, imasks, ihist, ilookback, st_ranges, chunk_base, chunk_key, chunk_counts;
     size_t recA, recB, recC, recD;
     /* image workspace */
     size_t ranges, tile_start, tile_order, n_contrib, final_T;
