@@ -110,9 +110,12 @@ block_sums_scan_kernel(uint32_t nblocks, uint32_t* __restrict__ block_sums, uint
 }
 
 // Emits the (view*S + supertile, view*P + Gaussian) pairs of every visible (view, Gaussian) in depth order.
-// A CTA first scans its 2048 slots into shared memory, then walks its OUTPUT range with one thread per instance
-// (binary search of the owning slot), so stores are fully coalesced; the digit histograms of the following sort are
-// taken on the way (warp-private bins, radix_rank.cuh), which saves that sort's pass over the keys.
+// Every thread owns 8 consecutive slots of the depth-sorted list; the CTA scans the slots' instance counts, each
+// thread writes its own instances (walking its supertile rectangles, no search) into a shared-memory window at their
+// output positions, and the window is copied out with fully coalesced stores.  The digit histograms of the following
+// sort are taken on the way out (warp-private bins, radix_rank.cuh), which saves that sort's pass over the keys.
+constexpr int EMIT_WINDOW = 3072;        // staged outputs per round (a CTA of 2048 slots emits ~2900 at C2)
+
 __global__ void __launch_bounds__(SCAN_BLOCK)
 emit_st_instances_kernel(uint32_t VP, int P, int stiles_x, uint32_t S, const uint32_t* __restrict__ sorted_g,
                          const ushort4* __restrict__ rects, const uint32_t* __restrict__ block_sums, uint32_t capacity,
@@ -120,10 +123,8 @@ emit_st_instances_kernel(uint32_t VP, int P, int stiles_x, uint32_t S, const uin
                          int hist_passes, int key_bits, uint32_t* __restrict__ sort_hist) {
     __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
     __shared__ uint32_t s_hist[SCAN_BLOCK / 32][EMIT_HIST_PASSES][RADIX];
-    __shared__ uint32_t s_off[SCAN_TILE + 1];     // exclusive offset of every slot inside this CTA's output range
-    __shared__ uint32_t s_key0[SCAN_TILE];        // key of the slot's first supertile
-    __shared__ uint32_t s_gi[SCAN_TILE];          // view*P + Gaussian
-    __shared__ uint16_t s_w[SCAN_TILE];           // supertile-rect width
+    __shared__ uint32_t s_key[EMIT_WINDOW];
+    __shared__ uint32_t s_val[EMIT_WINDOW];
     const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
     uint32_t cnt[SCAN_ITEMS], gidx[SCAN_ITEMS], key0[SCAN_ITEMS], wid[SCAN_ITEMS];
     uint32_t sum = 0;
@@ -136,55 +137,58 @@ emit_st_instances_kernel(uint32_t VP, int P, int stiles_x, uint32_t S, const uin
         sum += cnt[k];
     }
     uint32_t total;
-    uint32_t off = block_exclusive_scan_256(sum, s_warp, total);
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; ++k) {
-        const int slot = threadIdx.x * SCAN_ITEMS + k;
-        s_off[slot] = off;
-        off += cnt[k];
-        s_key0[slot] = key0[k];
-        s_gi[slot] = gidx[k];
-        s_w[slot] = (uint16_t)wid[k];
-    }
-    if (threadIdx.x == 0) s_off[SCAN_TILE] = total;
+    const uint32_t off0 = block_exclusive_scan_256(sum, s_warp, total);
     if (hist_passes > 0)
         for (int i = threadIdx.x; i < (SCAN_BLOCK / 32) * EMIT_HIST_PASSES * RADIX; i += SCAN_BLOCK) (&s_hist[0][0][0])[i] = 0;
-    __syncthreads();
     const uint32_t out0 = block_sums[blockIdx.x];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     bool overflow = false;
-    for (uint32_t o0 = 0; o0 < total; o0 += SCAN_BLOCK) {     // warp-uniform trip count (the histogram uses ballots)
-        const uint32_t o = o0 + threadIdx.x;
-        bool stored = false;
-        uint32_t key = 0;
-        if (o < total) {
-            // last slot with s_off <= o (empty slots share their successor's offset and are skipped by construction)
-            uint32_t lo = 0, hi = SCAN_TILE;
+    for (uint32_t w0 = 0; w0 < total; w0 += EMIT_WINDOW) {
+        __syncthreads();                                  // the previous window has been copied out (and s_hist zeroed)
+        if (off0 < w0 + EMIT_WINDOW && off0 + sum > w0) {     // some of this thread's instances fall into the window
+            uint32_t o = off0;
 #pragma unroll
-            for (int step = 0; step < 11; ++step) {           // SCAN_TILE == 2^11
-                const uint32_t mid = (lo + hi) >> 1;
-                if (s_off[mid] <= o) lo = mid; else hi = mid;
-            }
-            const uint32_t l = o - s_off[lo];
-            const uint32_t w = s_w[lo];
-            const uint32_t ty = l / w;
-            key = s_key0[lo] + ty * (uint32_t)stiles_x + (l - ty * w);
-            const uint32_t dst = out0 + o;
-            if (dst < capacity) {
-                ikeys[dst] = key;
-                ivals[dst] = s_gi[lo];
-                stored = true;
-            } else {
-                overflow = true;
+            for (int k = 0; k < SCAN_ITEMS; ++k) {
+                uint32_t row = key0[k], x = 0;
+                for (uint32_t l = 0; l < cnt[k]; ++l) {
+                    const uint32_t rel = o - w0;           // wraps for o < w0: fails the test below
+                    if (rel < (uint32_t)EMIT_WINDOW) {
+                        s_key[rel] = row + x;
+                        s_val[rel] = gidx[k];
+                    }
+                    ++o;
+                    if (++x == wid[k]) { x = 0; row += (uint32_t)stiles_x; }
+                }
             }
         }
+        __syncthreads();
+        const uint32_t n = min((uint32_t)EMIT_WINDOW, total - w0);
+        for (uint32_t o0 = 0; o0 < n; o0 += SCAN_BLOCK) {     // warp-uniform trip count (the histogram uses ballots)
+            const uint32_t o = o0 + threadIdx.x;
+            bool stored = false;
+            uint32_t key = 0;
+            if (o < n) {
+                key = s_key[o];
+                const uint32_t dst = out0 + w0 + o;
+                if (dst < capacity) {
+                    ikeys[dst] = key;
+                    ivals[dst] = s_val[o];
+                    stored = true;
+                } else {
+                    overflow = true;
+                }
+            }
 #pragma unroll
-        for (int p = 0; p < EMIT_HIST_PASSES; ++p) {
-            if (p < hist_passes) {
-                const int shift = p * RADIX_BITS;
-                const int bits = min(RADIX_BITS, key_bits - shift);
-                uint32_t peers;
-                warp_hist_add(s_hist[warp][p], (key >> shift) & ((1u << bits) - 1u), stored, lane, peers);
+            for (int p = 0; p < EMIT_HIST_PASSES; ++p) {
+                if (p < hist_passes) {
+                    const int shift = p * RADIX_BITS;
+                    const int bits = min(RADIX_BITS, key_bits - shift);
+                    uint32_t peers;
+                    if (bits <= 4)
+                        warp_hist_add<4>(s_hist[warp][p], (key >> shift) & ((1u << bits) - 1u), stored, lane, peers);
+                    else
+                        warp_hist_add(s_hist[warp][p], (key >> shift) & ((1u << bits) - 1u), stored, lane, peers);
+                }
             }
         }
     }

@@ -100,7 +100,7 @@ __device__ void sh_backward(int deg, int M, const float* __restrict__ sh_g, floa
 }
 
 template <int NCH>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 preprocess_backward_kernel(const CamDev* __restrict__ cams, int V, int P, int sh_coeffs,
                            const float* __restrict__ means3D, const float* __restrict__ scales,
                            const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,

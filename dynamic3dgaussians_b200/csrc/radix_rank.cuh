@@ -9,10 +9,11 @@
 
 namespace gsr {
 
+template <int NBITS = RADIX_BITS>
 __device__ __forceinline__ uint32_t match_digit(uint32_t d, bool valid) {
     uint32_t peers = __ballot_sync(0xffffffffu, valid);
 #pragma unroll
-    for (int b = 0; b < RADIX_BITS; ++b) {
+    for (int b = 0; b < NBITS; ++b) {
         const bool bit = (d >> b) & 1u;
         const uint32_t bal = __ballot_sync(0xffffffffu, bit);
         peers &= bit ? bal : ~bal;
@@ -24,9 +25,11 @@ __device__ __forceinline__ uint32_t match_digit(uint32_t d, bool valid) {
 // every group of equal digits does a plain read-modify-write; groups have distinct digits, hence distinct addresses).
 // Shared-memory atomics would cost ~2 cycles per lane on this part (B300_MICROARCH.md), i.e. more than the whole pass.
 // Returns the histogram value BEFORE this row in the group's leader lane broadcast to the group (the rank base).
+// NBITS: live bits of the digit (the last pass of a sort is often narrower than 8 bits: fewer ballots).
+template <int NBITS = RADIX_BITS>
 __device__ __forceinline__ uint32_t warp_hist_add(uint32_t* __restrict__ hist_warp, uint32_t d, bool valid, int lane,
                                                   uint32_t& peers_out) {
-    const uint32_t peers = match_digit(d, valid);
+    const uint32_t peers = match_digit<NBITS>(d, valid);
     peers_out = peers;
     const int leader = __ffs(peers) - 1;
     uint32_t prev = 0;

@@ -180,13 +180,24 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
 
     // ---- stable in-warp ranking, one item row at a time ----
     const unsigned lt_mask = (1u << lane) - 1u;
+    if (digit_mask < 16u) {                        // a narrow (<= 4 bit) last digit needs half the ballots
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-        const bool valid = (e0 + i * 32) < valid_count;
-        const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
-        uint32_t peers;
-        const uint32_t prev = warp_hist_add(s_warp_hist[warp], d, valid, lane, peers);
-        rank[i] = prev + __popc(peers & lt_mask);
+        for (int i = 0; i < ITEMS; ++i) {
+            const bool valid = (e0 + i * 32) < valid_count;
+            const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
+            uint32_t peers;
+            const uint32_t prev = warp_hist_add<4>(s_warp_hist[warp], d, valid, lane, peers);
+            rank[i] = prev + __popc(peers & lt_mask);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const bool valid = (e0 + i * 32) < valid_count;
+            const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
+            uint32_t peers;
+            const uint32_t prev = warp_hist_add(s_warp_hist[warp], d, valid, lane, peers);
+            rank[i] = prev + __popc(peers & lt_mask);
+        }
     }
     __syncthreads();
 
