@@ -535,6 +535,16 @@ def main():
             "grad_zero": ("hbm", 48.0 * Vl * P), "preprocess_backward": ("hbm", (44.0 + 56.0) * P + 68.0 * Vl * P),
             "instance_count": ("hbm", 12.0 * Vl * P),
         }
+        # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed ncu --set full
+        # capture of this same command (profiles/; refreshed whenever the kernel changes) -- never measured under ncu here
+        traffic = None
+        try:
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic.json")) as f:
+                tj = json.load(f)
+            if world == 1 and dom in tj.get("bytes_per_launch", {}) and tj.get("views") == V and tj.get("gaussians") == P:
+                traffic = tj["bytes_per_launch"][dom]
+        except (OSError, ValueError):
+            pass
         roof = None
         if dom in work:
             kind, amount = work[dom]
@@ -542,12 +552,12 @@ def main():
             if kind == "fp32":
                 ach = amount / t / 1e12
                 roof = {"kernel": dom, "bound": "fp32", "achieved": round(ach, 3), "peak": round(fp32, 2),
-                        "unit": "TFLOP/s", "frac": round(ach / fp32, 4), "traffic": None,
+                        "unit": "TFLOP/s", "frac": round(ach / fp32, 4), "traffic": traffic,
                         "peak_source": "measured in this run (dependent-free FFMA loop); nominal 74.4"}
             else:
                 ach = amount / t / 1e9
                 roof = {"kernel": dom, "bound": "hbm", "achieved": round(ach, 1), "peak": hbm_gbs, "unit": "GB/s",
-                        "frac": round(ach / hbm_gbs, 4), "traffic": None, "peak_source": hbm_src}
+                        "frac": round(ach / hbm_gbs, 4), "traffic": traffic, "peak_source": hbm_src}
         line = {
             "metric": METRIC, "value": round(mpix, 2), "unit": "Mpix/s", "n_gpus": world, "steps": steps,
             "warmup": args.warmup, "ms_per_step": round(ms / steps, 3), "higher_is_better": True, "scaling": "strong",
