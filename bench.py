@@ -309,7 +309,8 @@ def run_ours(args, world, rank, local):
         ncon = st.image[L.n_contrib: L.n_contrib + st.V * st.W * st.H * 4].view(torch.int32)
         pairs = int(ncon.sum(dtype=torch.int64).item())
         R = st.num_rendered
-    res = dict(ms=ms, host_ms=t_host, stages=stages, pairs=pairs, R=R, R1=R1 if st is not None else 0, clocks=clocks, views_per_rank=[len(p) for p in parts], parts=parts,
+        vis = float((st.radii > 0).float().mean().item())
+    res = dict(ms=ms, host_ms=t_host, visible=vis if st is not None else 0.0, stages=stages, pairs=pairs, R=R, R1=R1 if st is not None else 0, clocks=clocks, views_per_rank=[len(p) for p in parts], parts=parts,
                launches=kernels_per_step(L, world > 1) * args.steps if st is not None else 0, state=st, dev=dev,
                rv=rv, sets=sets, sc=sc, lib=lib)
     return res
@@ -318,7 +319,8 @@ def run_ours(args, world, rank, local):
 def run_e2e(args, res, world, rank):
     """Same metric through the public autograd API with HOST inputs: every step copies the Gaussian parameter slab
     (pinned) and the uint8 target images (pinned) to the device, renders the rank's views, takes an L1 loss against the
-    targets, back-propagates, all-reduces the gradients and reads the loss and the gradient slab back to the host."""
+    targets, back-propagates, all-reduces the gradients and reads the loss and the gradient slab back to the host.
+    The copies run on their own streams (double-buffered inputs), overlapping the neighbouring steps' compute."""
     from dynamic3dgaussians_b200 import dist as D, rasterizer as RZ
     dev, sets, sc = res["dev"], res["sets"], res["sc"]
     parts = res["parts"]
@@ -326,39 +328,77 @@ def run_e2e(args, res, world, rank):
     my_sets = [sets[v] for v in mine]
     rv_host = sc.rendervar()
     P = rv_host["means3D"].shape[0]
-    slab_host = torch.cat([rv_host["means3D"], rv_host["colors_precomp"], rv_host["opacities"], rv_host["scales"],
-                           rv_host["rotations"]], dim=1).contiguous().pin_memory()
+    names = ("means3D", "colors_precomp", "opacities", "scales", "rotations")
+    par_host = [rv_host[k].contiguous().pin_memory() for k in names]               # 14 floats per Gaussian in all
     tgt_host = torch.randint(0, 256, (len(mine), 3, IMG_H, IMG_W), dtype=torch.uint8,
                              generator=torch.Generator().manual_seed(5)).pin_memory()
-    grad_host = torch.empty((P, D.GRAD_WIDTH), dtype=torch.float32).pin_memory()
+    grad_host = [torch.empty_like(t).pin_memory() for t in par_host]
     loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
-    h2d = slab_host.numel() * 4 + tgt_host.numel()
-    d2h = grad_host.numel() * 4 + 4
+    h2d = sum(t.numel() for t in par_host) * 4 + tgt_host.numel()
+    d2h = sum(t.numel() for t in grad_host) * 4 + 4
 
     states = []
     cap_e2e = int(res["R"] * 1.05) + 4096 if mine else None
+    # A three-stage pipeline like a training input pipeline: the copy engine uploads step i+1's inputs (H2D stream)
+    # while step i renders and back-propagates (compute stream) and step i-1's gradient slab and loss go back to the
+    # host (D2H stream).  Every step still copies ITS inputs in and ITS results out inside the timed region.
+    cur = torch.cuda.current_stream(dev)
+    h2d_s, d2h_s = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    bufs = [dict(par=[torch.empty(t.shape, dtype=torch.float32, device=dev) for t in par_host],
+                 tgt=torch.empty(tgt_host.shape, dtype=torch.uint8, device=dev),
+                 ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
+    for b in bufs:
+        b["free"].record(cur)
 
-    def step():
-        slab = slab_host.to(dev, non_blocking=True).requires_grad_(True)
-        tgt = tgt_host.to(dev, non_blocking=True)
-        m, c, o, s, r = slab[:, 0:3], slab[:, 3:6], slab[:, 6:7], slab[:, 7:10], slab[:, 10:14]
+    def prefetch(i):
+        b = bufs[i % 2]
+        with torch.cuda.stream(h2d_s):
+            h2d_s.wait_event(b["free"])
+            for d_, h_ in zip(b["par"], par_host):
+                d_.copy_(h_, non_blocking=True)
+            b["tgt"].copy_(tgt_host, non_blocking=True)
+            b["ready"].record(h2d_s)
+
+    def step(i):
+        b = bufs[i % 2]
+        cur.wait_event(b["ready"])
+        m, c, o, s, r = [t.detach().requires_grad_(True) for t in b["par"]]
+        tgt = b["tgt"]
         color, _, depth, alpha, radii = RZ.rasterize_views(my_sets, m, o, colors_precomp=c, scales=s, rotations=r,
                                                            capacity=cap_e2e, state_out=states)
         del states[:-1]
         loss = (color - tgt.float() * (1.0 / 255.0)).abs().mean()
         loss.backward()
-        D.allreduce_grads(slab.grad)
-        grad_host.copy_(slab.grad, non_blocking=True)
-        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+        grads = [t.grad for t in (m, c, o, s, r)]
+        for g_ in grads:
+            D.allreduce_grads(g_)
+        b["free"].record(cur)
+        done = torch.cuda.Event()
+        done.record(cur)
+        lossd = loss.detach().reshape(1)
+        with torch.cuda.stream(d2h_s):
+            d2h_s.wait_event(done)
+            for h_, g_ in zip(grad_host, grads):
+                h_.copy_(g_, non_blocking=True)
+            loss_host.copy_(lossd, non_blocking=True)
+        for g_ in grads:
+            g_.record_stream(d2h_s)
+        lossd.record_stream(d2h_s)
 
-    for _ in range(max(2, args.warmup // 2)):
-        step()
+    def run(k):
+        prefetch(0)
+        for i in range(k):
+            prefetch(i + 1)
+            step(i)
+        cur.wait_stream(d2h_s)
+        cur.wait_stream(h2d_s)
+
+    run(max(2, args.warmup // 2))
     barrier(world)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n = max(3, args.steps // 2)
     e0.record()
-    for _ in range(n):
-        step()
+    run(n)
     e1.record()
     barrier(world)
     ms = max_over_ranks(e0.elapsed_time(e1), world)
@@ -566,7 +606,7 @@ def main():
                        "views_per_rank": res["views_per_rank"], "parallelism": f"view-sharded dp{world}",
                        "launch": "eager" if args.no_graph else "one CUDA graph per step (forward + backward + all-reduce)",
                        "l2": "per-step working set (>1 GB of per-view state and instance records) exceeds the 126 MB L2",
-                       "num_rendered_rank0": R, "supertile_instances_rank0": res.get("R1", 0), "pairs_rank0": pairs},
+                       "num_rendered_rank0": R, "visible_fraction_rank0": round(res.get("visible", 0.0), 4), "supertile_instances_rank0": res.get("R1", 0), "pairs_rank0": pairs},
             "clocks": res["clocks"], "e2e": e2e, "gpu_launches": res["launches"],
             "roofline": roof,
             "stage_ms_rank0": {k: round(v, 4) for k, v in stages.items()},
