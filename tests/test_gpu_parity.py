@@ -326,3 +326,46 @@ def test_drop_in_module_semantic_feature_autograd():
     out = rast(means3D=rv["means3D"], means2D=means2D, opacities=rv["opacities"], colors_precomp=rv["colors_precomp"],
                scales=rv["scales"], rotations=rv["rotations"])
     assert out[2].numel() == 0
+
+
+def test_c5_stress_size_properties():
+    """BASELINE.json configs[4]: 2 M Gaussians at 1920x1080 (two of the eight views, to bound the test's time).  Far
+    beyond what the oracle can run, so the checks are size-independent properties: the tile ranges partition the
+    instance list, keys are sorted inside every tile, a batch equals its views rendered alone bit for bit, the
+    gradient is finite and linear in the cotangent."""
+    sc = scenes.make_scene_c2(2_000_000, seed=5, scale=2.0)
+    cams = scenes.cameras_c2(2, w=1920, h=1080, f=1400.0, radius=6.0)
+    sets = [settings_from_spec(c)[0] for c in cams]
+    rv = _rv(sc)
+    color, _, depth, alpha, radii, st = _fwd(sets, rv)
+    n, overflowed = RZ.read_counters(st)
+    assert not overflowed and n == st.num_rendered and n > 10_000_000
+    total = 0
+    for v in range(2):
+        keys, plist, ranges, ncon = export_view(st, v)
+        r = ranges.long()
+        lens = r[:, 1] - r[:, 0]
+        assert int(lens.min()) >= 0
+        nz = r[lens > 0]
+        assert int(nz[0, 0]) == 0 and torch.equal(nz[1:, 0], nz[:-1, 1])         # ranges tile [0, R_v) without gaps
+        assert keys.numel() == int(nz[-1, 1])
+        assert bool((keys[1:] >= keys[:-1]).all())                               # (tile, depth) order
+        tile_of = keys >> 32
+        assert torch.equal(tile_of[nz[:, 0]], torch.nonzero(lens > 0).squeeze(1))
+        assert int(ncon.max()) <= int(lens.max())
+        assert int(plist.min()) >= 0 and int(plist.max()) < 2_000_000
+        total += keys.numel()
+    assert total == n
+    c1, _, d1, a1, r1, st1 = _fwd([sets[1]], rv)
+    assert torch.equal(color[1], c1[0]) and torch.equal(depth[1], d1[0]) and torch.equal(radii[1], r1[0])
+    del st1, c1, d1, a1
+    gen = torch.Generator().manual_seed(6)
+    gc = torch.randn(2, 3, 1080, 1920, generator=gen).cuda()
+    g1 = RZ.backward_views(st, rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"], None,
+                           None, None, gc, None, None, None, want_means2D=False)
+    g2 = RZ.backward_views(st, rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"], None,
+                           None, None, 2.0 * gc, None, None, None, want_means2D=False)
+    for k in ("means3D", "colors", "opacity", "scales", "rotations"):
+        assert torch.isfinite(g1[k]).all(), k
+        assert rel_err(g2[k], 2.0 * g1[k]) <= 1e-5, k
+    assert float(g1["means3D"].abs().max()) > 0
