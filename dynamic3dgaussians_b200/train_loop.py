@@ -104,13 +104,15 @@ def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optiona
 
     if not is_initial_timestep:
         from .dyn_losses import rigidity_losses
-        is_fg = variables['is_fg']
-        fg_pts = rv['means3D'][is_fg]
-        fg_rot = rv['rotations'][is_fg]
+        # index lists instead of the reference's boolean masks (REF/train.py:254-257): static shapes, no host sync, so the
+        # iteration can be captured into a CUDA graph
+        fg_idx, bg_idx = variables['fg_idx'], variables['bg_idx']
+        fg_pts = rv['means3D'].index_select(0, fg_idx)
+        fg_rot = rv['rotations'].index_select(0, fg_idx)
         losses['rigid'], losses['rot'], losses['iso'] = rigidity_losses(fg_pts, fg_rot, variables['graph'])
         losses['floor'] = torch.clamp(fg_pts[:, 1], min=0).mean()
-        bg_pts = rv['means3D'][~is_fg]
-        bg_rot = rv['rotations'][~is_fg]
+        bg_pts = rv['means3D'].index_select(0, bg_idx)
+        bg_rot = rv['rotations'].index_select(0, bg_idx)
         losses['bg'] = (torch.abs(bg_pts - variables['init_bg_pts']).sum(-1)).mean() + \
                        (torch.abs(bg_rot - variables['init_bg_rot']).sum(-1)).mean()
         losses['soft_col_cons'] = (torch.abs(params['rgb_colors'] - variables['prev_col']).sum(-1)).mean()
@@ -146,6 +148,8 @@ def initialize_post_first_timestep(params, variables, optimizer, num_knn: int = 
     from .dyn_losses import build_neighbor_graph
     is_fg = (params['seg_colors'][:, 0] > 0.5).detach()
     variables['is_fg'] = is_fg
+    variables['fg_idx'] = torch.nonzero(is_fg).squeeze(1)
+    variables['bg_idx'] = torch.nonzero(~is_fg).squeeze(1)
     rot = torch.nn.functional.normalize(params['unnorm_rotations']).detach()
     variables['graph'] = build_neighbor_graph(params['means3D'][is_fg].detach(), rot[is_fg], num_knn)
     variables['init_bg_pts'] = params['means3D'][~is_fg].detach().clone()
