@@ -38,6 +38,7 @@ def parse():
     ap.add_argument("--views", type=int, default=N_VIEWS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the train-loop it/s sample")
+    ap.add_argument("--whole-views", action="store_true", help="N>1: shard whole views only (no tile-row bands)")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of one CUDA graph per step")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -244,13 +245,19 @@ def run_ours(args, world, rank, local):
     out, _ = step()
     torch.cuda.synchronize()
     if world > 1:
+        # tile-list lengths per (view, row of tiles) -> contiguous runs of equal cost: whole views where possible, bands
+        # of tile rows where a cut falls inside a view (27 views do not divide over 8 ranks)
         import torch.distributed as dist
-        costs = torch.zeros(V, device=dev, dtype=torch.float64)
+        ty = (IMG_H + 15) // 16
+        costs = torch.zeros(V, ty, device=dev, dtype=torch.float64)
         if mine:
-            rad = out[4]
-            costs[mine] = (rad > 0).sum(dim=1).double() + rad.clamp(min=0).double().pow(2).sum(dim=1) / 64.0
+            costs[mine] = RZ.tile_row_costs(out[5])
         dist.all_reduce(costs)
-        parts = D.partition_views(costs.tolist(), world)
+        if args.whole_views:
+            parts = D.partition_views(costs.sum(dim=1).tolist(), world)
+        else:
+            # per-view work that does not shrink with the band (preprocess, depth sort, instance count): ~12 % of a view
+            parts = D.partition_units(costs.tolist(), world, fixed_cost=0.12 * float(costs.sum()) / V)
         mine = parts[rank]
         local[0] = D.select_views(cot, mine)
     # one synchronising step with the final partition tells the instance count; from then on the binning workspace is
@@ -310,7 +317,7 @@ def run_ours(args, world, rank, local):
         pairs = int(ncon.sum(dtype=torch.int64).item())
         R = st.num_rendered
         vis = float((st.radii > 0).float().mean().item())
-    res = dict(ms=ms, host_ms=t_host, visible=vis if st is not None else 0.0, stages=stages, pairs=pairs, R=R, R1=R1 if st is not None else 0, clocks=clocks, views_per_rank=[len(p) for p in parts], parts=parts,
+    res = dict(ms=ms, host_ms=t_host, visible=vis if st is not None else 0.0, stages=stages, pairs=pairs, R=R, R1=R1 if st is not None else 0, clocks=clocks, views_per_rank=[round(sum(1.0 if isinstance(u, int) else (u[2] - u[1]) / float((IMG_H + 15) // 16) for u in p), 2) for p in parts], parts=parts,
                launches=kernels_per_step(L, world > 1) * args.steps if st is not None else 0, state=st, dev=dev,
                rv=rv, sets=sets, sc=sc, lib=lib)
     return res
@@ -325,7 +332,16 @@ def run_e2e(args, res, world, rank):
     dev, sets, sc = res["dev"], res["sets"], res["sc"]
     parts = res["parts"]
     mine = parts[rank]
-    my_sets = [sets[v] for v in mine]
+    my_views, my_bands = D.split_units(mine)
+    my_sets = [sets[v] for v in my_views]
+    # a band unit's loss covers its own rows only (the rest of that image belongs to another rank)
+    row_mask = None
+    if my_bands is not None:
+        row_mask = torch.zeros(len(mine), 1, IMG_H, 1, device=dev)
+        for i, b in enumerate(my_bands):
+            r0, r1 = (0, IMG_H) if b is None else (b[0] * 16, min(b[1] * 16, IMG_H))
+            row_mask[i, :, r0:r1] = 1.0
+        row_mask *= 1.0 / (3 * IMG_W * row_mask.sum())
     rv_host = sc.rendervar()
     P = rv_host["means3D"].shape[0]
     names = ("means3D", "colors_precomp", "opacities", "scales", "rotations")
@@ -365,9 +381,12 @@ def run_e2e(args, res, world, rank):
         m, c, o, s, r = [t.detach().requires_grad_(True) for t in b["par"]]
         tgt = b["tgt"]
         color, _, depth, alpha, radii = RZ.rasterize_views(my_sets, m, o, colors_precomp=c, scales=s, rotations=r,
-                                                           capacity=cap_e2e, state_out=states)
+                                                           capacity=cap_e2e, state_out=states, bands=my_bands)
         del states[:-1]
-        loss = (color - tgt.float() * (1.0 / 255.0)).abs().mean()
+        if row_mask is None:
+            loss = (color - tgt.float() * (1.0 / 255.0)).abs().mean()
+        else:
+            loss = ((color - tgt.float() * (1.0 / 255.0)).abs() * row_mask).sum()
         loss.backward()
         grads = [t.grad for t in (m, c, o, s, r)]
         for g_ in grads:
@@ -621,7 +640,7 @@ def main():
             "warmup": args.warmup, "ms_per_step": round(ms / steps, 3), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"C2: {P} Gaussians, {V} views {IMG_W}x{IMG_H}, fwd+bwd, colour+depth cotangents",
-                       "views_per_rank": res["views_per_rank"], "parallelism": f"view-sharded dp{world}",
+                       "views_per_rank": res["views_per_rank"], "parallelism": f"view-sharded dp{world}" + ("" if world == 1 or args.whole_views else " (cuts inside a view fall on tile-row bands)"),
                        "launch": "eager" if args.no_graph else "one CUDA graph per step (forward + backward + all-reduce)",
                        "l2": "per-step working set (>1 GB of per-view state and instance records) exceeds the 126 MB L2",
                        "num_rendered_rank0": R, "visible_fraction_rank0": round(res.get("visible", 0.0), 4), "supertile_instances_rank0": res.get("R1", 0), "pairs_rank0": pairs},

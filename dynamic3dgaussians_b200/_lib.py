@@ -37,7 +37,7 @@ class GsrCamera(C.Structure):
         ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("c_x", C.c_float), ("c_y", C.c_float),
         ("scale_modifier", C.c_float), ("sh_degree", C.c_int32), ("prefiltered", C.c_int32),
         ("bg", C.c_float * 8), ("viewmatrix", C.c_float * 16), ("projmatrix", C.c_float * 16),
-        ("campos", C.c_float * 3),
+        ("campos", C.c_float * 3), ("tile_row_begin", C.c_int32), ("tile_row_end", C.c_int32),
     ]
 
 

@@ -51,6 +51,11 @@ static void fill_cam(const GsrCamera& c, CamDev& d) {
     d.prefiltered = c.prefiltered;
     d.width = W;
     d.height = H;
+    const int tiles_y = (H + TILE_Y - 1) / TILE_Y;
+    const bool whole = c.tile_row_begin == 0 && c.tile_row_end == 0;
+    d.row_begin = whole ? 0 : (c.tile_row_begin < 0 ? 0 : c.tile_row_begin);
+    d.row_end = whole ? tiles_y : (c.tile_row_end > tiles_y ? tiles_y : c.tile_row_end);
+    if (d.row_end < d.row_begin) d.row_end = d.row_begin;
 }
 
 __global__ void fp32_peak_kernel(float* out, int iters) {
@@ -71,7 +76,7 @@ using namespace gsr;
 
 extern "C" {
 
-int gsr_abi_version(void) { return 2; }
+int gsr_abi_version(void) { return 3; }
 
 const char* gsr_strerror(int status) {
     switch (status) {

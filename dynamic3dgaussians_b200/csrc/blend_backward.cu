@@ -160,9 +160,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 if (g < nb) {
                     const float4 a = sA[buf][g];
                     const float4 b = sB[buf][g];
-                    const uint32_t m8 = blend_patch_mask(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
-                    const uint32_t t = m8 | (m8 >> 2);
-                    m4 = (t & 3u) | ((t >> 2) & 0xcu);
+                    m4 = blend_patch_mask4(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
                 }
 #pragma unroll
                 for (int w = 0; w < NW2; ++w) {

@@ -38,7 +38,8 @@ struct CamDev {
     int sh_degree;
     int prefiltered;
     int width, height;
-    int pad[3];
+    int row_begin, row_end;     // band of tile rows binned for this view (whole grid by default)
+    int pad[1];
 };
 
 struct CamPack {            // cameras travel to the device as a kernel argument (<= 4 KB)

@@ -139,6 +139,8 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
             const int r_i = (int)my_radius;
             uint2 mn, mx;
             tile_rect(pix, r_i, tiles_x, tiles_y, mn, mx);
+            mn.y = max(mn.y, (uint32_t)cam.row_begin);           // band of tile rows rendered by this call
+            mx.y = max(min(mx.y, (uint32_t)cam.row_end), mn.y);
             const uint32_t area = (mx.x - mn.x) * (mx.y - mn.y);
             if (area != 0) {
                 if (sh != nullptr) {

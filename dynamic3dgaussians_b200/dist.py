@@ -28,6 +28,53 @@ def partition_views(costs: Sequence[float], world: int) -> List[List[int]]:
     return [sorted(x) for x in out]
 
 
+def partition_units(row_costs: Sequence[Sequence[float]], world: int, fixed_cost: float = 0.0):
+    """Splits V views into `world` contiguous runs of (view, first tile row, last tile row + 1) units of near-equal
+    cost.  `row_costs[v][r]` is the cost of tile row r of view v (e.g. its instance count); `fixed_cost` is what a rank
+    pays per view it touches regardless of the band (preprocess + depth sort), in the same units.
+
+    Views stay whole wherever possible: the cost line (views laid end to end, heaviest first) is cut at tile-row
+    boundaries into `world` equal parts, so a rank holds some whole views plus at most two partial ones, and at most
+    world - 1 views are shared by two ranks.  This lifts the ceiling of whole-view sharding (27 views on 8 ranks: one
+    rank in three holds 4 views, 84 % at best).  Deterministic: every rank computes the same table."""
+    V = len(row_costs)
+    order = sorted(range(V), key=lambda v: (-float(sum(row_costs[v])), v))
+    rows = [(v, r, float(c)) for v in order for r, c in enumerate(row_costs[v])]
+    out: List[List[tuple]] = [[] for _ in range(world)]
+    # a cut inside a view makes the next rank pay that view's per-view work again: budget one split per cut
+    remaining = sum(c for _, _, c in rows) + fixed_cost * (V + world - 1)
+    i, n = 0, len(rows)
+    for rank in range(world):
+        if i >= n:
+            break
+        if rank == world - 1:
+            take = n - i
+        else:
+            target = remaining / (world - rank)
+            load, take, seen_view = 0.0, 0, None
+            while i + take < n:
+                v, _, c = rows[i + take]
+                extra = c + (fixed_cost if v != seen_view else 0.0)
+                # stop at the row boundary nearest to the target, but always take at least one row and leave at least
+                # one row for every rank that follows
+                if take > 0 and (load + extra - target > target - load or n - (i + take) <= world - 1 - rank):
+                    break
+                load += extra
+                seen_view = v
+                take += 1
+            remaining -= load
+            if not (0 < i + take < n and rows[i + take][0] == rows[i + take - 1][0]):
+                remaining -= fixed_cost                          # the cut fell on a view boundary after all
+        chunk = rows[i:i + take]
+        i += take
+        for v, r, _ in chunk:                                   # merge consecutive rows of a view into one unit
+            if out[rank] and out[rank][-1][0] == v and out[rank][-1][2] == r:
+                out[rank][-1] = (v, out[rank][-1][1], r + 1)
+            else:
+                out[rank].append((v, r, r + 1))
+    return out
+
+
 def pack_grads(g: dict, P: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """[P, 14] contiguous slab (means3D 3 | colours 3 | opacity 1 | scales 3 | rotations 4): one collective per step."""
     dev = g["means3D"].device
@@ -77,16 +124,31 @@ def allreduce_grads(slab: torch.Tensor, group=None, async_op: bool = False):
     return dist.all_reduce(slab, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
 
 
-def select_views(cotangents: dict, my_views: Sequence[int]) -> dict:
-    """The local views' slices of [V_total, C, H, W] cotangent tensors (contiguous copies; done once per partition)."""
-    idx = list(my_views)
+def split_units(my_views: Sequence) -> tuple:
+    """A rank's work list holds whole views (int v) and bands of tile rows ((v, first, last + 1), from
+    partition_units()).  Returns (view indices, bands or None when every entry is a whole view)."""
+    views, bands = [], []
+    for u in my_views:
+        if isinstance(u, (tuple, list)):
+            views.append(int(u[0]))
+            bands.append((int(u[1]), int(u[2])))
+        else:
+            views.append(int(u))
+            bands.append(None)
+    return views, (bands if any(b is not None for b in bands) else None)
+
+
+def select_views(cotangents: dict, my_views: Sequence) -> dict:
+    """The local views' slices of [V_total, C, H, W] cotangent tensors (contiguous copies; done once per partition).
+    A band unit takes its whole view's cotangents: pixels outside the band have empty tile lists and are never read."""
+    idx = split_units(my_views)[0]
     return {k: (None if t is None else t[idx].contiguous()) for k, t in cotangents.items()}
 
 
-def sharded_step(settings, my_views: Sequence[int], params: dict, cotangents: dict, group=None,
+def sharded_step(settings, my_views: Sequence, params: dict, cotangents: dict, group=None,
                  capacity: Optional[int] = None, slab: Optional[GradSlab] = None, local_cotangents: bool = False):
-    """forward + backward of this rank's views and the all-reduce.  params: means3D, opacities, colors_precomp, scales,
-    rotations (replicated).  cotangents: dict of [V_total, C, H, W] tensors or None for color / depth / alpha (or, with
+    """forward + backward of this rank's views and the all-reduce.  `my_views`: view indices and / or (view, first tile
+    row, last + 1) bands (see split_units).  params: means3D, opacities, colors_precomp, scales, rotations (replicated).  cotangents: dict of [V_total, C, H, W] tensors or None for color / depth / alpha (or, with
     local_cotangents=True, already restricted to this rank's views by select_views()).
     `capacity`: instance capacity of the binning workspace (None = read the count back, one host sync per step).
     `slab`: a reusable GradSlab the gradients are written into (allocated when omitted).
@@ -97,9 +159,10 @@ def sharded_step(settings, my_views: Sequence[int], params: dict, cotangents: di
     if slab is None:
         slab = GradSlab(P, params["means3D"].device)
     if my_views:
-        sets = [settings[v] for v in my_views]
+        views, bands = split_units(my_views)
+        sets = [settings[v] for v in views]
         out = RZ.forward_views(sets, params["means3D"], params["opacities"], params["colors_precomp"],
-                               params["scales"], params["rotations"], capacity=capacity)
+                               params["scales"], params["rotations"], capacity=capacity, bands=bands)
         cot = cotangents if local_cotangents else select_views(cotangents, my_views)
         RZ.backward_views(out[5], params["means3D"], params["opacities"], params["colors_precomp"],
                           params["scales"], params["rotations"], None, None, None, cot.get("color"),
@@ -123,7 +186,7 @@ class GraphedStep:
       * outputs (`self.out`, the tuple of forward_views) and the gradient slab (`self.slab`) are overwritten by every
         replay.  The all-reduce over `group` is part of the graph (NCCL collectives are capturable)."""
 
-    def __init__(self, settings, my_views: Sequence[int], params: dict, cotangents: dict, capacity: int, group=None,
+    def __init__(self, settings, my_views: Sequence, params: dict, cotangents: dict, capacity: int, group=None,
                  warmup: int = 2):
         dev = params["means3D"].device
         self.slab = GradSlab(params["means3D"].shape[0], dev)

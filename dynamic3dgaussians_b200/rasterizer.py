@@ -57,13 +57,19 @@ def _host_floats(t, n: int, what: str) -> List[float]:
 _CAM_CACHE: dict = {}
 
 
-def camera_struct(s: GaussianRasterizationSettings, bg_extra=None) -> _lib.GsrCamera:
-    """GsrCamera for one settings tuple.  Matrices are read back from the device once per settings object."""
-    key = (id(s), id(bg_extra))
+def camera_struct(s: GaussianRasterizationSettings, bg_extra=None, band=None) -> _lib.GsrCamera:
+    """GsrCamera for one settings tuple.  Matrices are read back from the device once per settings object.
+    `band` = (first tile row, one past the last) restricts the render to a band of 16-pixel rows (None = all)."""
+    band = None if band is None else (int(band[0]), int(band[1]))
+    key = (id(s), id(bg_extra), band)
     hit = _CAM_CACHE.get(key)
     if hit is not None and hit[0] is s:
         return hit[1]
     cam = _lib.GsrCamera()
+    if band is not None:
+        if not (0 <= band[0] < band[1]):
+            raise ValueError(f"band must be a non-empty range of tile rows, got {band}")
+        cam.tile_row_begin, cam.tile_row_end = band
     cam.image_width = int(s.image_width)
     cam.image_height = int(s.image_height)
     cam.tanfovx = float(s.tanfovx)
@@ -122,11 +128,13 @@ def workspace_layout(P, V, W, H, channels, sh_coeffs, capacity) -> _lib.GsrLayou
 
 def forward_views(settings: Sequence[GaussianRasterizationSettings], means3D, opacities, colors_precomp=None,
                   scales=None, rotations=None, cov3D_precomp=None, shs=None, extra_colors=None, bg_extra=None,
-                  capacity: Optional[int] = None, semantic_feature=None):
+                  capacity: Optional[int] = None, semantic_feature=None, bands=None):
     """Runs the forward for V views.  Returns (color [V,3,H,W], extra [V,3,H,W] | None, depth [V,1,H,W],
     alpha [V,1,H,W], radii [V,P] int32, RasterState).  With `semantic_feature` ([P,32] or the reference's [P,1,32],
     R/diff_gaussian_rasterization/__init__.py:215) the 32-channel feature map [V,32,H,W] is left in
-    RasterState.feature_map.  With capacity=None the instance count is read back from the
+    RasterState.feature_map.  `bands[v]` = (first, last + 1) tile rows to render for view v, or None for the whole
+    view: the rest of that image is background and takes no part in the backward (dist.partition_units shards single
+    views over GPUs this way).  With capacity=None the instance count is read back from the
     device once (the reference's one host sync, rasterizer_impl.cu:287); otherwise no sync happens and the caller
     checks `read_counters` later.
     """
@@ -164,7 +172,10 @@ def forward_views(settings: Sequence[GaussianRasterizationSettings], means3D, op
                              f"(R/cuda_rasterizer/config.h:17), got {tuple(semantic_feature.shape)}")
         semantic_feature = semantic_feature.reshape(P, NUM_SEMANTIC_CHANNELS)
 
-    cams = (_lib.GsrCamera * V)(*[camera_struct(s, bg_extra) for s in settings])
+    if bands is not None and len(bands) != V:
+        raise ValueError("bands must have one entry per view")
+    cams = (_lib.GsrCamera * V)(*[camera_struct(s, bg_extra, None if bands is None else bands[i])
+                                  for i, s in enumerate(settings)])
     sizes = _lib.GsrWorkspaceSizes()
     _lib.check(lib.gsr_workspace_sizes(P, V, W, H, channels, sh_coeffs, 0, C.byref(sizes)), "workspace_sizes")
     geom = torch.empty(sizes.geom_bytes, dtype=torch.uint8, device=dev)
@@ -207,6 +218,15 @@ def read_counters(st: RasterState):
     """(num_rendered, overflowed) -- synchronises the current stream."""
     c = st.geom[:8].view(torch.int32).cpu()
     return int(c[0]), bool(c[1])
+
+
+def tile_row_costs(st: RasterState) -> torch.Tensor:
+    """[V, tile rows] float64: summed tile-list lengths of every row of 16-pixel tiles (the blend work of that row);
+    what dist.partition_units() balances.  Reads the forward's tile ranges from the image workspace."""
+    L = workspace_layout(st.P, st.V, st.W, st.H, st.channels, st.sh_coeffs, st.capacity)
+    tx, ty = (st.W + 15) // 16, (st.H + 15) // 16
+    r = st.image[L.ranges: L.ranges + st.V * tx * ty * 8].view(torch.int32).view(st.V, ty, tx, 2)
+    return (r[..., 1] - r[..., 0]).double().sum(dim=2)
 
 
 def backward_views(st: RasterState, means3D, opacities, colors_precomp, scales, rotations, cov3D_precomp, shs,
@@ -288,10 +308,10 @@ class _RasterizeViews(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, extra_colors, opacities, scales, rotations, cov3Ds_precomp,
-                settings, label, bg_extra, capacity, state_out):
+                settings, label, bg_extra, capacity, state_out, bands=None):
         color, extra, depth, alpha, radii, st = forward_views(
             settings, means3D, opacities, _opt(colors_precomp), _opt(scales), _opt(rotations), _opt(cov3Ds_precomp),
-            _opt(sh), _opt(extra_colors), bg_extra, capacity=capacity)
+            _opt(sh), _opt(extra_colors), bg_extra, capacity=capacity, bands=bands)
         ctx.state = st
         if state_out is not None:
             state_out.append(st)
@@ -322,12 +342,13 @@ class _RasterizeViews(torch.autograd.Function):
             g_means2D = g_means2D.reshape(ctx.means2D_shape)
         g_op = g["opacity"].reshape(opacities.shape)
         return (g["means3D"], g_means2D, g["sh"], g["colors"], g["extra"], g_op, g["scales"], g["rotations"],
-                g["cov3D"], None, None, None, None, None)
+                g["cov3D"], None, None, None, None, None, None)
 
 
 def rasterize_views(settings: Sequence[GaussianRasterizationSettings], means3D, opacities, means2D=None, shs=None,
                     colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None, extra_colors=None,
-                    label=None, bg_extra=None, capacity: Optional[int] = None, state_out: Optional[list] = None):
+                    label=None, bg_extra=None, capacity: Optional[int] = None, state_out: Optional[list] = None,
+                    bands=None):
     """Renders all `settings` (V cameras of equal resolution) in one batch.
 
     Returns (color [V,3,H,W], extra [V,3,H,W] or None, depth [V,1,H,W], alpha [V,1,H,W], radii [V,P]).
@@ -337,6 +358,8 @@ def rasterize_views(settings: Sequence[GaussianRasterizationSettings], means3D, 
     `capacity` (instances the binning workspace is sized for) removes the reference's one host sync per call
     (rasterizer_impl.cu:287): pass e.g. 1.1x the previous step's count; append-only `state_out` receives the
     RasterState, whose `read_counters` tells afterwards whether the capacity was exceeded (surplus instances dropped).
+    `bands[v]` = (first, last + 1) tile rows of view v to render (see forward_views); pixels outside the band come back
+    as background and their cotangents are ignored.
     """
     if (shs is None) == (colors_precomp is None):
         raise Exception('Please provide excatly one of either SHs or precomputed colors!')
@@ -348,7 +371,7 @@ def rasterize_views(settings: Sequence[GaussianRasterizationSettings], means3D, 
         means3D, means2D, e if shs is None else shs, e if colors_precomp is None else colors_precomp,
         e if extra_colors is None else extra_colors, opacities, e if scales is None else scales,
         e if rotations is None else rotations, e if cov3D_precomp is None else cov3D_precomp, list(settings), label,
-        bg_extra, capacity, state_out)
+        bg_extra, capacity, state_out, bands)
     return color, (extra if extra.numel() else None), depth, alpha, radii
 
 

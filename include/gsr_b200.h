@@ -57,6 +57,12 @@ typedef struct GsrCamera {
     float viewmatrix[16];
     float projmatrix[16];
     float campos[3];
+    /* Optional band of TILE rows [tile_row_begin, tile_row_end) this call renders for the view (both 0 = the whole
+     * image).  Gaussians are binned only into tiles of the band; pixels outside it get the background and take no part
+     * in the backward.  Used to shard one view over several GPUs (dist.partition_units): the per-Gaussian gradients
+     * of the bands of a view add up to the view's gradient. */
+    int32_t tile_row_begin;
+    int32_t tile_row_end;
 } GsrCamera;
 
 /* Byte sizes of the three caller-owned workspaces (the reference's geomBuffer / binningBuffer / imgBuffer). */
@@ -108,7 +114,7 @@ int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels,
                          int32_t* radii, uint32_t* num_rendered_dev, gsr_stream_t stream);
 
 /*
- * Forward, stage 2 of 2: instance emission, tile sort, tile ranges, record gather and the fused tile blend
+ * Forward, stage 2 of 2: supertile instance emission and sort, per-tile offsets, record scatter and the fused tile blend
  * (replaces duplicateWithKeys / SortPairs / identifyTileRanges / FORWARD::render, rasterizer_impl.cu:295-343).
  * `capacity` is the number of instances the binning workspace was sized for; if the true count exceeds it the
  * surplus instances are dropped and the overflow flag (gsr_check_overflow) is raised.

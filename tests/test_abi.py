@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
     assert sorted(_lib.EXPORTED_SYMBOLS) == names
-    assert lib.gsr_abi_version() == 2
+    assert lib.gsr_abi_version() == 3
     assert lib.gsr_strerror(0) == b"ok" and lib.gsr_strerror(-2) == b"workspace too small"
 
 

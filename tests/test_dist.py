@@ -26,6 +26,42 @@ def test_partition_views_balances_counts_and_costs():
     assert D.partition_views(costs, 2) == parts                     # deterministic
 
 
+def test_partition_units_covers_every_tile_row_once_and_balances():
+    import random
+    rnd = random.Random(0)
+    V, rows = 27, 23
+    rc = [[rnd.random() * (2.0 - (r - 11) ** 2 * 0.005) for r in range(rows)] for _ in range(V)]
+    fixed = 0.1 * sum(map(sum, rc)) / V
+    for world in (1, 2, 3, 4, 8):
+        parts = D.partition_units(rc, world, fixed_cost=fixed)
+        assert len(parts) == world and parts == D.partition_units(rc, world, fixed_cost=fixed)       # deterministic
+        seen = {}
+        for p in parts:
+            for v, a, b in p:
+                assert 0 <= a < b <= rows
+                for r in range(a, b):
+                    seen[(v, r)] = seen.get((v, r), 0) + 1
+        assert len(seen) == V * rows and set(seen.values()) == {1}
+        loads = [sum(sum(rc[v][a:b]) + fixed for v, a, b in p) for p in parts]
+        assert max(loads) <= 1.05 * sum(loads) / world                  # whole views alone: 4 / 3.375 = 1.19 at world 8
+        shared = sum(1 for v in range(V) if sum(1 for p in parts for u in p if u[0] == v) > 1)
+        assert shared <= world - 1                                      # views stay whole wherever possible
+    # more ranks than rows, empty input, all-zero costs
+    parts = D.partition_units([[1.0] * 3] * 2, 8)
+    assert sorted(u for p in parts for u in p) == [(v, r, r + 1) for v in range(2) for r in range(3)]
+    assert D.partition_units([], 2) == [[], []]
+    z = D.partition_units([[0.0] * 4] * 3, 2)
+    assert sorted((v, r) for p in z for v, a, b in p for r in range(a, b)) == [(v, r) for v in range(3) for r in range(4)]
+
+
+def test_split_units_mixes_whole_views_and_bands():
+    assert D.split_units([3, 5]) == ([3, 5], None)
+    assert D.split_units([(3, 0, 7), 5, (6, 2, 4)]) == ([3, 5, 6], [(0, 7), None, (2, 4)])
+    cot = dict(color=torch.arange(8.0).reshape(8, 1, 1, 1), depth=None)
+    sel = D.select_views(cot, [(3, 0, 7), 5])
+    assert sel["depth"] is None and sel["color"].flatten().tolist() == [3.0, 5.0]
+
+
 def test_pack_unpack_roundtrip():
     P = 17
     g = dict(means3D=torch.randn(P, 3), colors=torch.randn(P, 3), opacity=torch.randn(P, 1), scales=torch.randn(P, 3),

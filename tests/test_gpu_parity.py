@@ -166,6 +166,57 @@ def test_batched_views_equal_single_views_and_fused_extra_colours():
         assert rel_err(gb[k], acc[k]) <= GRAD_TOL, k
 
 
+def test_tile_row_bands_partition_a_view():
+    """Band units (dist.partition_units): a view rendered as bands of tile rows gives, band by band, exactly the rows
+    of the whole-view images, and the bands' gradients add up to the whole view's (what the all-reduce sums)."""
+    from dynamic3dgaussians_b200 import dist as D
+    sc = scenes.make_scene_c2(30_000, seed=5)
+    cams = scenes.cameras_c2(3, w=320, h=180, f=233.0)                 # 12 tile rows, the last one ragged (180 = 11*16+4)
+    sets = [settings_from_spec(c)[0] for c in cams]
+    rv = _rv(sc)
+    gen = torch.Generator().manual_seed(4)
+    gc = torch.randn(3, 3, 180, 320, generator=gen).cuda()
+    gd = torch.randn(3, 1, 180, 320, generator=gen).cuda() * 0.1
+    cw, _, dw, aw, rw, stw = _fwd(sets, rv)
+    gw = RZ.backward_views(stw, rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"],
+                           None, None, None, gc, None, gd, None)
+    costs = RZ.tile_row_costs(stw)
+    assert costs.shape == (3, 12) and int(costs.sum().item()) == stw.num_rendered
+    parts = D.partition_units(costs.tolist(), 4, fixed_cost=0.1 * float(costs.sum()) / 3)
+    assert any(len(p) > 1 for p in parts) and sum(len(p) for p in parts) > 3        # at least one view is cut
+    acc = None
+    total = 0
+    vis = torch.zeros_like(rw)
+    for units in parts:
+        views, bands = D.split_units(units)
+        out = RZ.forward_views([sets[v] for v in views], rv["means3D"], rv["opacities"], rv["colors_precomp"],
+                               rv["scales"], rv["rotations"], bands=bands)
+        cb, _, db, ab, rb, stb = out
+        total += stb.num_rendered
+        for i, (v, r0, r1) in enumerate(units):
+            y0, y1 = r0 * 16, min(r1 * 16, 180)
+            assert torch.equal(cb[i, :, y0:y1], cw[v, :, y0:y1]) and torch.equal(db[i, :, y0:y1], dw[v, :, y0:y1])
+            assert torch.equal(ab[i, :, y0:y1], aw[v, :, y0:y1])
+            outside = torch.ones(180, dtype=torch.bool, device="cuda")
+            outside[y0:y1] = False
+            assert (ab[i, 0, outside] == 0).all() and (cb[i, :, outside] == 0).all()           # background only
+            assert ((rb[i] == 0) | (rb[i] == rw[v])).all()                     # radii: the view's, or 0 outside the band
+            vis[v] |= rb[i]
+        g = RZ.backward_views(stb, rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"],
+                              rv["rotations"], None, None, None, gc[views].contiguous(), None, gd[views].contiguous(),
+                              None)
+        part = {k: g[k] for k in ("means3D", "colors", "opacity", "scales", "rotations")}
+        acc = part if acc is None else {k: acc[k] + part[k] for k in acc}
+    assert total == stw.num_rendered and torch.equal(vis, rw)
+    for k in acc:
+        assert rel_err(acc[k], gw[k]) <= GRAD_TOL, k
+    # the sharded step takes the same unit lists
+    slab = D.GradSlab(rv["means3D"].shape[0], "cuda")
+    D.sharded_step(sets, parts[0] + parts[1] + parts[2] + parts[3], rv, dict(color=gc, depth=gd, alpha=None), slab=slab)
+    for k in acc:
+        assert rel_err(slab.views[k].reshape(gw[k].shape), gw[k]) <= GRAD_TOL, k
+
+
 def test_edge_cases_empty_culled_and_ragged():
     cs = scenes.camera_c1()
     st_, _ = settings_from_spec(cs, bg=(0.5, 0.25, 0.125))
