@@ -41,6 +41,10 @@ def parse():
     ap.add_argument("--whole-views", action="store_true", help="N>1: shard whole views only (no tile-row bands)")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of one CUDA graph per step")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--emulate-world", type=int, default=0,
+                    help="diagnostic, 1 GPU: run only the share rank --emulate-rank would get of an N-way partition "
+                         "(no collective), to profile the small per-rank step; the line is marked and is not a result")
+    ap.add_argument("--emulate-rank", type=int, default=0)
     return ap.parse_args()
 
 
@@ -244,7 +248,8 @@ def run_ours(args, world, rank, local):
     # first pass: per-view instance counts -> cost-aware partition (deterministic on every rank)
     out, _ = step()
     torch.cuda.synchronize()
-    if world > 1:
+    emu = args.emulate_world if world == 1 else 0
+    if world > 1 or emu:
         # tile-list lengths per (view, row of tiles) -> contiguous runs of equal cost: whole views where possible, bands
         # of tile rows where a cut falls inside a view (27 views do not divide over 8 ranks)
         import torch.distributed as dist
@@ -252,13 +257,14 @@ def run_ours(args, world, rank, local):
         costs = torch.zeros(V, ty, device=dev, dtype=torch.float64)
         if mine:
             costs[mine] = RZ.tile_row_costs(out[5])
-        dist.all_reduce(costs)
+        if world > 1:
+            dist.all_reduce(costs)
         if args.whole_views:
-            parts = D.partition_views(costs.sum(dim=1).tolist(), world)
+            parts = D.partition_views(costs.sum(dim=1).tolist(), emu or world)
         else:
             # per-view work that does not shrink with the band (preprocess, depth sort, instance count): ~12 % of a view
-            parts = D.partition_units(costs.tolist(), world, fixed_cost=0.12 * float(costs.sum()) / V)
-        mine = parts[rank]
+            parts = D.partition_units(costs.tolist(), emu or world, fixed_cost=0.12 * float(costs.sum()) / V)
+        mine = parts[args.emulate_rank if emu else rank]
         local[0] = D.select_views(cot, mine)
     # one synchronising step with the final partition tells the instance count; from then on the binning workspace is
     # sized for 1.05x that count and no step touches the host (overflow is checked after the timed region)
@@ -375,34 +381,74 @@ def run_e2e(args, res, world, rank):
             b["tgt"].copy_(tgt_host, non_blocking=True)
             b["ready"].record(h2d_s)
 
-    def step(i):
-        b = bufs[i % 2]
-        cur.wait_event(b["ready"])
-        m, c, o, s, r = [t.detach().requires_grad_(True) for t in b["par"]]
-        tgt = b["tgt"]
+    def compute(b):
+        m, c, o, s, r = b["leaves"]
         color, _, depth, alpha, radii = RZ.rasterize_views(my_sets, m, o, colors_precomp=c, scales=s, rotations=r,
                                                            capacity=cap_e2e, state_out=states, bands=my_bands)
         del states[:-1]
         if row_mask is None:
-            loss = (color - tgt.float() * (1.0 / 255.0)).abs().mean()
+            loss = (color - b["tgt"].float() * (1.0 / 255.0)).abs().mean()
         else:
-            loss = ((color - tgt.float() * (1.0 / 255.0)).abs() * row_mask).sum()
+            loss = ((color - b["tgt"].float() * (1.0 / 255.0)).abs() * row_mask).sum()
         loss.backward()
-        grads = [t.grad for t in (m, c, o, s, r)]
+        grads = [t.grad for t in b["leaves"]]
         for g_ in grads:
             D.allreduce_grads(g_)
+        return loss.detach().reshape(1), grads
+
+    for b in bufs:
+        b["leaves"] = [t.detach().requires_grad_(True) for t in b["par"]]      # same storage as the upload targets
+        b["drained"] = torch.cuda.Event()
+        b["drained"].record(cur)
+    if not args.no_graph:
+        # the compute of a step (render, loss, backward, all-reduce) is ONE graph per input buffer: at N>1 a rank's GPU
+        # work is ~1 ms and the ~2.5 ms of Python/autograd dispatch per eager step would bound the pipeline
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            for b in bufs:
+                for d_, h_ in zip(b["par"], par_host):
+                    d_.copy_(h_, non_blocking=True)
+                b["tgt"].copy_(tgt_host, non_blocking=True)
+            for _ in range(2):
+                for t in bufs[0]["leaves"]:
+                    t.grad = None
+                compute(bufs[0])
+        cur.wait_stream(side)
+        torch.cuda.synchronize(dev)
+        pool = None
+        for b in bufs:
+            for t in b["leaves"]:
+                t.grad = None
+            b["graph"] = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(b["graph"], pool=pool):
+                b["out"] = compute(b)
+            pool = b["graph"].pool() if pool is None else pool
+
+    def step(i):
+        b = bufs[i % 2]
+        cur.wait_event(b["ready"])
+        if "graph" in b:
+            cur.wait_event(b["drained"])           # this buffer's previous results have left for the host
+            b["graph"].replay()
+            lossd, grads = b["out"]
+        else:
+            for t in b["leaves"]:
+                t.grad = None
+            lossd, grads = compute(b)
         b["free"].record(cur)
         done = torch.cuda.Event()
         done.record(cur)
-        lossd = loss.detach().reshape(1)
         with torch.cuda.stream(d2h_s):
             d2h_s.wait_event(done)
             for h_, g_ in zip(grad_host, grads):
                 h_.copy_(g_, non_blocking=True)
             loss_host.copy_(lossd, non_blocking=True)
-        for g_ in grads:
-            g_.record_stream(d2h_s)
-        lossd.record_stream(d2h_s)
+            b["drained"].record(d2h_s)
+        if "graph" not in b:
+            for g_ in grads:
+                g_.record_stream(d2h_s)
+            lossd.record_stream(d2h_s)
 
     def run(k):
         prefetch(0)
@@ -587,7 +633,7 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the rasterizer has no CPU path")
     world, rank, local = dist_setup(args)
     res = run_ours(args, world, rank, local)
-    e2e = None if args.no_e2e else run_e2e(args, res, world, rank)
+    e2e = None if (args.no_e2e or args.emulate_world) else run_e2e(args, res, world, rank)
     if rank == 0:
         steps, ms = args.steps, res["ms"]
         V = args.views
@@ -646,6 +692,8 @@ def main():
                        "num_rendered_rank0": R, "visible_fraction_rank0": round(res.get("visible", 0.0), 4), "supertile_instances_rank0": res.get("R1", 0), "pairs_rank0": pairs},
             "clocks": res["clocks"], "e2e": e2e, "gpu_launches": res["launches"],
             "roofline": roof,
+            **({"diagnostic": f"NOT a result: only rank {args.emulate_rank}'s share of a {args.emulate_world}-way partition "
+                              "ran (value counts all views)"} if args.emulate_world else {}),
             "stage_ms_rank0": {k: round(v, 4) for k, v in stages.items()},
             "host_enqueue_ms_per_step_rank0": round(res["host_ms"], 3),
             "train_it_per_s_equiv": round(V * steps / (ms * 1e-3), 1),
