@@ -333,7 +333,12 @@ def run_e2e(args, res, world, rank):
     """Same metric through the public autograd API with HOST inputs: every step copies the Gaussian parameter slab
     (pinned) and the uint8 target images (pinned) to the device, renders the rank's views, takes an L1 loss against the
     targets, back-propagates, all-reduces the gradients and reads the loss and the gradient slab back to the host.
-    The copies run on their own streams (double-buffered inputs), overlapping the neighbouring steps' compute."""
+    The copies run on their own streams (double-buffered inputs), overlapping the neighbouring steps' compute.
+
+    At N > 1 the job still moves every input and result across PCIe ONCE per step: rank r uploads slice r of the
+    parameter slab and the ranks all-gather it over NVLink (8 processes uploading the same 16.8 MB and downloading the
+    same gradients measured 23 / 12 GB/s per rank, the host side of the box being shared), and rank r reads slice r of
+    the all-reduced gradient slab back."""
     from dynamic3dgaussians_b200 import dist as D, rasterizer as RZ
     dev, sets, sc = res["dev"], res["sets"], res["sc"]
     parts = res["parts"]
@@ -351,13 +356,25 @@ def run_e2e(args, res, world, rank):
     rv_host = sc.rendervar()
     P = rv_host["means3D"].shape[0]
     names = ("means3D", "colors_precomp", "opacities", "scales", "rotations")
-    par_host = [rv_host[k].contiguous().pin_memory() for k in names]               # 14 floats per Gaussian in all
+    # the five parameter tensors travel as ONE pinned slab (14 floats per Gaussian), and so do their gradients: one
+    # DMA each way per step and one all-reduce, instead of five of each
+    shapes = [tuple(rv_host[k].shape) for k in names]
+    sizes = [rv_host[k].numel() for k in names]
+    import torch.distributed as tdist
+    nw = world if (world > 1 and tdist.is_initialized()) else 1
+    drank = tdist.get_rank() if nw > 1 else 0
+    n_par = sum(sizes)
+    chunk = -(-n_par // nw)
+    lo, hi = drank * chunk, (drank + 1) * chunk
+    par_full = torch.zeros(chunk * nw)
+    par_full[:n_par] = torch.cat([rv_host[k].reshape(-1).float() for k in names])
+    par_host = par_full[lo:hi].clone().pin_memory()                # this rank's slice of the slab
     tgt_host = torch.randint(0, 256, (len(mine), 3, IMG_H, IMG_W), dtype=torch.uint8,
                              generator=torch.Generator().manual_seed(5)).pin_memory()
-    grad_host = [torch.empty_like(t).pin_memory() for t in par_host]
+    grad_host = torch.empty_like(par_host).pin_memory()
     loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
-    h2d = sum(t.numel() for t in par_host) * 4 + tgt_host.numel()
-    d2h = sum(t.numel() for t in grad_host) * 4 + 4
+    h2d = par_host.numel() * 4 + tgt_host.numel()
+    d2h = grad_host.numel() * 4 + 4
 
     states = []
     cap_e2e = int(res["R"] * 1.05) + 4096 if mine else None
@@ -366,7 +383,7 @@ def run_e2e(args, res, world, rank):
     # host (D2H stream).  Every step still copies ITS inputs in and ITS results out inside the timed region.
     cur = torch.cuda.current_stream(dev)
     h2d_s, d2h_s = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
-    bufs = [dict(par=[torch.empty(t.shape, dtype=torch.float32, device=dev) for t in par_host],
+    bufs = [dict(par=torch.zeros(chunk * nw, dtype=torch.float32, device=dev),
                  tgt=torch.empty(tgt_host.shape, dtype=torch.uint8, device=dev),
                  ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
     for b in bufs:
@@ -376,12 +393,13 @@ def run_e2e(args, res, world, rank):
         b = bufs[i % 2]
         with torch.cuda.stream(h2d_s):
             h2d_s.wait_event(b["free"])
-            for d_, h_ in zip(b["par"], par_host):
-                d_.copy_(h_, non_blocking=True)
+            b["par"][lo:hi].copy_(par_host, non_blocking=True)
             b["tgt"].copy_(tgt_host, non_blocking=True)
             b["ready"].record(h2d_s)
 
     def compute(b):
+        if nw > 1:
+            tdist.all_gather_into_tensor(b["par"], b["par"][lo:hi])         # in place: every rank now holds the slab
         m, c, o, s, r = b["leaves"]
         color, _, depth, alpha, radii = RZ.rasterize_views(my_sets, m, o, colors_precomp=c, scales=s, rotations=r,
                                                            capacity=cap_e2e, state_out=states, bands=my_bands)
@@ -391,13 +409,14 @@ def run_e2e(args, res, world, rank):
         else:
             loss = ((color - b["tgt"].float() * (1.0 / 255.0)).abs() * row_mask).sum()
         loss.backward()
-        grads = [t.grad for t in b["leaves"]]
-        for g_ in grads:
-            D.allreduce_grads(g_)
-        return loss.detach().reshape(1), grads
+        torch.cat([t.grad.reshape(-1) for t in b["leaves"]], out=b["grad"][:n_par])
+        D.allreduce_grads(b["grad"])
+        return loss.detach().reshape(1), b["grad"][lo:hi]
 
     for b in bufs:
-        b["leaves"] = [t.detach().requires_grad_(True) for t in b["par"]]      # same storage as the upload targets
+        # leaves share storage with the upload target
+        b["leaves"] = [t.view(sh).detach().requires_grad_(True) for t, sh in zip(b["par"][:n_par].split(sizes), shapes)]
+        b["grad"] = torch.zeros_like(b["par"])
         b["drained"] = torch.cuda.Event()
         b["drained"].record(cur)
     if not args.no_graph:
@@ -407,8 +426,7 @@ def run_e2e(args, res, world, rank):
         side.wait_stream(cur)
         with torch.cuda.stream(side):
             for b in bufs:
-                for d_, h_ in zip(b["par"], par_host):
-                    d_.copy_(h_, non_blocking=True)
+                b["par"][lo:hi].copy_(par_host, non_blocking=True)
                 b["tgt"].copy_(tgt_host, non_blocking=True)
             for _ in range(2):
                 for t in bufs[0]["leaves"]:
@@ -428,8 +446,8 @@ def run_e2e(args, res, world, rank):
     def step(i):
         b = bufs[i % 2]
         cur.wait_event(b["ready"])
+        cur.wait_event(b["drained"])               # this buffer's previous results have left for the host
         if "graph" in b:
-            cur.wait_event(b["drained"])           # this buffer's previous results have left for the host
             b["graph"].replay()
             lossd, grads = b["out"]
         else:
@@ -441,13 +459,10 @@ def run_e2e(args, res, world, rank):
         done.record(cur)
         with torch.cuda.stream(d2h_s):
             d2h_s.wait_event(done)
-            for h_, g_ in zip(grad_host, grads):
-                h_.copy_(g_, non_blocking=True)
+            grad_host.copy_(grads, non_blocking=True)
             loss_host.copy_(lossd, non_blocking=True)
             b["drained"].record(d2h_s)
         if "graph" not in b:
-            for g_ in grads:
-                g_.record_stream(d2h_s)
             lossd.record_stream(d2h_s)
 
     def run(k):
@@ -470,8 +485,46 @@ def run_e2e(args, res, world, rank):
     if states and cap_e2e is not None:
         assert not RZ.read_counters(states[-1])[1], "instance capacity exceeded inside the e2e region"
     mpix = args.views * IMG_W * IMG_H * n / (ms * 1e-3) / 1e6
+    loss_value = float(loss_host.item())
+    if nw > 1:                                     # bytes per step of the whole job (sum over the ranks)
+        t = torch.tensor([h2d, d2h], device=dev, dtype=torch.float64)
+        tdist.all_reduce(t)
+        h2d, d2h = int(t[0].item()), int(t[1].item())
+
+    # the three legs of the pipeline timed one at a time (diagnostic, outside the timed region; this rank's numbers)
+    def leg(fn, reps=5):
+        torch.cuda.synchronize(dev)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        return round(e0.elapsed_time(e1) / reps, 3)
+
+    def leg_h2d():
+        prefetch(0)
+        cur.wait_stream(h2d_s)
+
+    def leg_compute():
+        b = bufs[0]
+        if "graph" in b:
+            b["graph"].replay()
+        else:
+            for t in b["leaves"]:
+                t.grad = None
+            compute(b)
+
+    def leg_d2h():
+        with torch.cuda.stream(d2h_s):
+            d2h_s.wait_stream(cur)
+            grad_host.copy_(bufs[0]["grad"][lo:hi], non_blocking=True)
+        cur.wait_stream(d2h_s)
+
+    legs = {"h2d_ms": leg(leg_h2d), "compute_ms": leg(leg_compute), "d2h_ms": leg(leg_d2h)}
     return {"value": round(mpix, 2), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-            "steps": n, "ms_per_step": round(ms / n, 3), "loss": float(loss_host.item())}
+            "steps": n, "ms_per_step": round(ms / n, 3), "loss_rank0": loss_value, "legs_alone_rank0": legs,
+            "host_io": "bytes are job totals; parameter slab uploaded / gradient slab read back once per step "
+                       + (f"(1/{nw} per rank, all-gathered / all-reduced over NVLink)" if nw > 1 else "(one rank)")}
 
 
 def run_train_loop(args, res):
@@ -633,7 +686,7 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the rasterizer has no CPU path")
     world, rank, local = dist_setup(args)
     res = run_ours(args, world, rank, local)
-    e2e = None if (args.no_e2e or args.emulate_world) else run_e2e(args, res, world, rank)
+    e2e = None if args.no_e2e else run_e2e(args, res, world, args.emulate_rank if args.emulate_world and world == 1 else rank)
     if rank == 0:
         steps, ms = args.steps, res["ms"]
         V = args.views
