@@ -41,6 +41,9 @@ def parse():
     ap.add_argument("--whole-views", action="store_true", help="N>1: shard whole views only (no tile-row bands)")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of one CUDA graph per step")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c5"],
+                    help="c2 (default, the metric's configuration: 300k Gaussians, 27 views 640x360, strong scaling) or "
+                         "c5 (BASELINE.json configs[4]: 2M Gaussians, 8 views 1920x1080 PER GPU, weak scaling; extra line)")
     ap.add_argument("--emulate-world", type=int, default=0,
                     help="diagnostic, 1 GPU: run only the share rank --emulate-rank would get of an N-way partition "
                          "(no collective), to profile the small per-rank step; the line is marked and is not a result")
@@ -180,8 +183,13 @@ def barrier(world: int):
 def build_workload(args, device):
     from dynamic3dgaussians_b200 import scenes
     from dynamic3dgaussians_b200.camera import settings_from_spec
-    sc = scenes.make_scene_c2(args.gaussians)
-    cams = scenes.cameras_c2(args.views, w=IMG_W, h=IMG_H)
+    if args.workload == "c5":
+        # the same 8 cameras for every GPU, so that the per-GPU work is exactly fixed as N grows
+        sc = scenes.make_scene_c2(args.gaussians, seed=5, scale=2.0)
+        cams = scenes.cameras_c2(8, w=IMG_W, h=IMG_H, f=1400.0, radius=6.0) * (args.views // 8)
+    else:
+        sc = scenes.make_scene_c2(args.gaussians)
+        cams = scenes.cameras_c2(args.views, w=IMG_W, h=IMG_H)
     sets = [settings_from_spec(c, device=device) for c in cams]
     return sc, sets
 
@@ -675,7 +683,14 @@ def run_reference(args, world, rank):
 
 
 def main():
+    global IMG_W, IMG_H, METRIC
     args = parse()
+    if args.workload == "c5":
+        IMG_W, IMG_H = 1920, 1080
+        args.gaussians = 2_000_000
+        args.views = 8 * int(os.environ.get("WORLD_SIZE", "1"))
+        args.whole_views = args.no_train = args.no_cpu_baseline = True
+        METRIC = "fwd+bwd rasterized Mpix/s @2M Gaussians, 8x1920x1080 views per GPU"
     if args.impl == "reference":
         world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
         line = run_reference(args, world, rank)
@@ -736,9 +751,10 @@ def main():
                         "frac": round(ach / hbm_gbs, 4), "traffic": traffic, "peak_source": hbm_src}
         line = {
             "metric": METRIC, "value": round(mpix, 2), "unit": "Mpix/s", "n_gpus": world, "steps": steps,
-            "warmup": args.warmup, "ms_per_step": round(ms / steps, 3), "higher_is_better": True, "scaling": "strong",
+            "warmup": args.warmup, "ms_per_step": round(ms / steps, 3), "higher_is_better": True,
+            "scaling": "weak" if args.workload == "c5" else "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"C2: {P} Gaussians, {V} views {IMG_W}x{IMG_H}, fwd+bwd, colour+depth cotangents",
+            "config": {"workload": f"{args.workload.upper()}: {P} Gaussians, {V} views {IMG_W}x{IMG_H}, fwd+bwd, colour+depth cotangents",
                        "views_per_rank": res["views_per_rank"], "parallelism": f"view-sharded dp{world}" + ("" if world == 1 or args.whole_views else " (cuts inside a view fall on tile-row bands)"),
                        "launch": "eager" if args.no_graph else "one CUDA graph per step (forward + backward + all-reduce)",
                        "l2": "per-step working set (>1 GB of per-view state and instance records) exceeds the 126 MB L2",
