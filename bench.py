@@ -39,6 +39,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the train-loop it/s sample")
     ap.add_argument("--whole-views", action="store_true", help="N>1: shard whole views only (no tile-row bands)")
+    ap.add_argument("--rebalance", type=int, default=0, help="N>1: feedback rounds of the cost-aware partition (dist.rescale_row_costs); at C2 the tile-list model is already within the run-to-run noise of the ranks")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of one CUDA graph per step")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--workload", default="c2", choices=["c2", "c5"],
@@ -247,6 +248,7 @@ def run_ours(args, world, rank, local):
     mine = parts[rank]
 
     cap = [None]
+    rebalance_ms = []
     slab = D.GradSlab(P, dev)
     local = [D.select_views(cot, mine)]       # the loss side hands each rank the cotangents of its own views
 
@@ -274,6 +276,31 @@ def run_ours(args, world, rank, local):
             parts = D.partition_units(costs.tolist(), emu or world, fixed_cost=0.12 * float(costs.sum()) / V)
         mine = parts[args.emulate_rank if emu else rank]
         local[0] = D.select_views(cot, mine)
+        # feedback: every rank times its own share (graph replay, no collective), the row costs are rescaled by the
+        # measured / modelled ratio of the rank that ran them, and the line is cut again
+        for _ in range(0 if (args.whole_views or emu) else args.rebalance):
+            out, _ = step()
+            c0 = int(out[5].num_rendered * 1.05) + 4096 if out is not None else 0
+            g0 = D.GraphedStep(sets, mine, rv, local[0], capacity=c0, reduce=False)
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            g0.replay()
+            torch.cuda.synchronize()
+            ev0.record()
+            for _k in range(5):
+                g0.replay()
+            ev1.record()
+            torch.cuda.synchronize()
+            t = torch.zeros(world, device=dev, dtype=torch.float64)
+            t[rank] = ev0.elapsed_time(ev1) / 5
+            dist.all_reduce(t)
+            del g0
+            fixed = 0.12 * float(costs.sum()) / V
+            costs = torch.tensor(D.rescale_row_costs(costs.tolist(), parts, t.tolist(), fixed), device=dev,
+                                 dtype=torch.float64)
+            parts = D.partition_units(costs.tolist(), world, fixed_cost=fixed)
+            mine = parts[rank]
+            local[0] = D.select_views(cot, mine)
+            rebalance_ms.append([round(x, 3) for x in t.tolist()])
     # one synchronising step with the final partition tells the instance count; from then on the binning workspace is
     # sized for 1.05x that count and no step touches the host (overflow is checked after the timed region)
     out, _ = step()
@@ -331,7 +358,7 @@ def run_ours(args, world, rank, local):
         pairs = int(ncon.sum(dtype=torch.int64).item())
         R = st.num_rendered
         vis = float((st.radii > 0).float().mean().item())
-    res = dict(ms=ms, host_ms=t_host, visible=vis if st is not None else 0.0, stages=stages, pairs=pairs, R=R, R1=R1 if st is not None else 0, clocks=clocks, views_per_rank=[round(sum(1.0 if isinstance(u, int) else (u[2] - u[1]) / float((IMG_H + 15) // 16) for u in p), 2) for p in parts], parts=parts,
+    res = dict(ms=ms, host_ms=t_host, visible=vis if st is not None else 0.0, stages=stages, pairs=pairs, R=R, R1=R1 if st is not None else 0, clocks=clocks, views_per_rank=[round(sum(1.0 if isinstance(u, int) else (u[2] - u[1]) / float((IMG_H + 15) // 16) for u in p), 2) for p in parts], parts=parts, rebalance_ms=rebalance_ms,
                launches=kernels_per_step(L, world > 1) * args.steps if st is not None else 0, state=st, dev=dev,
                rv=rv, sets=sets, sc=sc, lib=lib)
     return res
@@ -755,7 +782,8 @@ def main():
             "scaling": "weak" if args.workload == "c5" else "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload.upper()}: {P} Gaussians, {V} views {IMG_W}x{IMG_H}, fwd+bwd, colour+depth cotangents",
-                       "views_per_rank": res["views_per_rank"], "parallelism": f"view-sharded dp{world}" + ("" if world == 1 or args.whole_views else " (cuts inside a view fall on tile-row bands)"),
+                       "views_per_rank": res["views_per_rank"],
+                       **({"rank_ms_before_each_rebalance": res["rebalance_ms"]} if res["rebalance_ms"] else {}), "parallelism": f"view-sharded dp{world}" + ("" if world == 1 or args.whole_views else " (cuts inside a view fall on tile-row bands)"),
                        "launch": "eager" if args.no_graph else "one CUDA graph per step (forward + backward + all-reduce)",
                        "l2": "per-step working set (>1 GB of per-view state and instance records) exceeds the 126 MB L2",
                        "num_rendered_rank0": R, "visible_fraction_rank0": round(res.get("visible", 0.0), 4), "supertile_instances_rank0": res.get("R1", 0), "pairs_rank0": pairs},

@@ -75,6 +75,36 @@ def partition_units(row_costs: Sequence[Sequence[float]], world: int, fixed_cost
     return out
 
 
+def rescale_row_costs(row_costs: Sequence[Sequence[float]], parts, rank_ms: Sequence[float], fixed_cost: float = 0.0):
+    """Feedback step of the cost-aware partition ("last step's per-view R or ms").  `parts` is the
+    partition the ranks just ran, `rank_ms[r]` what rank r measured for it.  Every tile row's cost is rescaled by the
+    measured-to-modelled ratio of the rank that ran it, normalised so that the total stays put; re-partitioning the
+    result moves work away from the ranks that were slow.  Two or three rounds settle (the model is the tile-list
+    length; what it misses -- long single lists, termination depth -- is local to the rows).  Returns new row_costs."""
+    new = [list(map(float, r)) for r in row_costs]
+    loads = []
+    for units in parts:
+        views, bands = split_units(units)
+        load = 0.0
+        for v, b in zip(views, bands or [None] * len(views)):
+            a, e = (0, len(new[v])) if b is None else b
+            load += sum(new[v][a:e]) + fixed_cost
+        loads.append(load)
+    tot_ms, tot_load = float(sum(rank_ms)), float(sum(loads))
+    if tot_ms <= 0.0 or tot_load <= 0.0:
+        return new
+    for r, units in enumerate(parts):
+        if loads[r] <= 0.0:
+            continue
+        k = (float(rank_ms[r]) / tot_ms) / (loads[r] / tot_load)
+        views, bands = split_units(units)
+        for v, b in zip(views, bands or [None] * len(views)):
+            a, e = (0, len(new[v])) if b is None else b
+            for i in range(a, e):
+                new[v][i] *= k
+    return new
+
+
 def pack_grads(g: dict, P: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """[P, 14] contiguous slab (means3D 3 | colours 3 | opacity 1 | scales 3 | rotations 4): one collective per step."""
     dev = g["means3D"].device
@@ -146,12 +176,14 @@ def select_views(cotangents: dict, my_views: Sequence) -> dict:
 
 
 def sharded_step(settings, my_views: Sequence, params: dict, cotangents: dict, group=None,
-                 capacity: Optional[int] = None, slab: Optional[GradSlab] = None, local_cotangents: bool = False):
+                 capacity: Optional[int] = None, slab: Optional[GradSlab] = None, local_cotangents: bool = False,
+                 reduce: bool = True):
     """forward + backward of this rank's views and the all-reduce.  `my_views`: view indices and / or (view, first tile
     row, last + 1) bands (see split_units).  params: means3D, opacities, colors_precomp, scales, rotations (replicated).  cotangents: dict of [V_total, C, H, W] tensors or None for color / depth / alpha (or, with
     local_cotangents=True, already restricted to this rank's views by select_views()).
     `capacity`: instance capacity of the binning workspace (None = read the count back, one host sync per step).
     `slab`: a reusable GradSlab the gradients are written into (allocated when omitted).
+    `reduce=False` leaves the all-reduce out (to time a rank's own work for rescale_row_costs).
     Returns (outputs of the local views, GradSlab summed over ALL views)."""
     from . import rasterizer as RZ
     P = params["means3D"].shape[0]
@@ -170,7 +202,8 @@ def sharded_step(settings, my_views: Sequence, params: dict, cotangents: dict, g
     else:
         out = None
         slab.flat.zero_()
-    allreduce_grads(slab.flat, group)
+    if reduce:
+        allreduce_grads(slab.flat, group)
     return out, slab
 
 
@@ -187,12 +220,12 @@ class GraphedStep:
         replay.  The all-reduce over `group` is part of the graph (NCCL collectives are capturable)."""
 
     def __init__(self, settings, my_views: Sequence, params: dict, cotangents: dict, capacity: int, group=None,
-                 warmup: int = 2):
+                 warmup: int = 2, reduce: bool = True):
         dev = params["means3D"].device
         self.slab = GradSlab(params["means3D"].shape[0], dev)
         self.out = None
         args = (settings, list(my_views), params, cotangents)
-        kw = dict(group=group, capacity=int(capacity), slab=self.slab, local_cotangents=True)
+        kw = dict(group=group, capacity=int(capacity), slab=self.slab, local_cotangents=True, reduce=reduce)
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):           # lazy initialisation (NCCL communicators, kernel attributes) happens here

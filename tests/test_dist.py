@@ -54,6 +54,32 @@ def test_partition_units_covers_every_tile_row_once_and_balances():
     assert sorted((v, r) for p in z for v, a, b in p for r in range(a, b)) == [(v, r) for v in range(3) for r in range(4)]
 
 
+def test_rescale_row_costs_feedback_converges_on_a_systematic_model_error():
+    import random
+    rnd = random.Random(1)
+    V, rows, world = 27, 23, 8
+    scale = [0.5 + 1.5 * rnd.random() for _ in range(V)]
+    model = [[scale[v] * (0.5 + rnd.random()) for _ in range(rows)] for v in range(V)]
+    true = [[model[v][r] ** 0.7 + 0.2 for r in range(rows)] for v in range(V)]        # what the ranks would measure
+    fixed = 0.1 * sum(map(sum, model)) / V
+
+    def run(parts):
+        return [sum(sum(true[v][a:b]) + 1.5 * fixed for v, a, b in p) for p in parts]
+
+    costs, worst = model, []
+    for _ in range(4):
+        parts = D.partition_units(costs, world, fixed_cost=fixed)
+        ms = run(parts)
+        worst.append(max(ms) / (sum(ms) / world))
+        costs = D.rescale_row_costs(costs, parts, ms, fixed)
+        assert abs(sum(map(sum, costs)) - sum(map(sum, model))) < 0.05 * sum(map(sum, model))   # total roughly kept
+    assert worst[0] > 1.2 and worst[2] < 1.05 and worst[3] < 1.05
+    # whole-view units (ints) are accepted too, and a degenerate measurement changes nothing
+    c2 = D.rescale_row_costs([[1.0, 1.0], [2.0, 2.0]], [[0], [1]], [1.0, 1.0])
+    assert c2[0][0] > 1.0 and c2[1][0] < 2.0
+    assert D.rescale_row_costs([[1.0]], [[0]], [0.0]) == [[1.0]]
+
+
 def test_split_units_mixes_whole_views_and_bands():
     assert D.split_units([3, 5]) == ([3, 5], None)
     assert D.split_units([(3, 0, 7), 5, (6, 2, 4)]) == ([3, 5, 6], [(0, 7), None, (2, 4)])
