@@ -15,6 +15,7 @@
 // * arithmetic per pair follows the reference binary exactly (see geom_math.cuh), so n_contrib and the images agree
 //   with the reference bit for bit.
 #include "geom_math.cuh"
+#include <stdlib.h>
 
 namespace gsr {
 
@@ -33,8 +34,31 @@ __device__ __forceinline__ float2 splat(float a) { return make_float2(a, a); }
 constexpr int NT2 = 128;
 constexpr int NW2 = NT2 / 32;
 
-template <int NCH>
-__global__ void __launch_bounds__(NT2, 8)
+// alpha of one Gaussian on a lane's pixel pair, and whether each pixel passes the skip tests of forward.cu:358-364
+// (power in range, alpha >= 1/255).  Depends on nothing the blend loop carries.
+struct PairAlpha {
+    float2 alpha;
+    bool ok0, ok1;
+};
+
+__device__ __forceinline__ PairAlpha pair_alpha(const float4 a, const float4 b, float npx, float2 npy) {
+    // blend_power (geom_math.cuh) on the pixel pair, component-wise the same roundings
+    const float dx = __fadd_rn(a.x, npx);
+    const float2 dy = __fadd2_rn(splat(a.y), npy);
+    const float dxca = __fmul_rn(dx, a.z), ndxcb = __fmul_rn(dx, -a.w);
+    const float2 t3 = __fmul2_rn(dy, __fmul2_rn(dy, splat(b.x)));
+    const float2 q2 = __ffma2_rn(splat(dx), splat(dxca), t3);
+    const float2 power = __ffma2_rn(q2, splat(-0.5f), __fmul2_rn(dy, splat(ndxcb)));
+    const float2 og = __fmul2_rn(splat(b.y), expf2_pinned(power));        // garbage where power is out of range: masked
+    PairAlpha r;
+    r.alpha = f2(fminf(0.99f, og.x), fminf(0.99f, og.y));
+    r.ok0 = !(power.x > 0.0f || power.x < b.w) && !(r.alpha.x < 1.0f / 255.0f);
+    r.ok1 = !(power.y > 0.0f || power.y < b.w) && !(r.alpha.y < 1.0f / 255.0f);
+    return r;
+}
+
+template <int NCH, int ILP>
+__global__ void __launch_bounds__(NT2, (NCH > 3 || ILP > 1) ? 6 : 8)
 blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                       const float4* __restrict__ recA, const float4* __restrict__ recB,
                       const float4* __restrict__ recC, const float4* __restrict__ recD,
@@ -103,7 +127,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         mbar_wait(&full[buf], (uint32_t)((r >> 1) & 1));
         const int nb = min(BATCH, n_total - r * BATCH);
         const uint32_t contrib_base = (uint32_t)r * BATCH;
-        {   // pre-pass: Gaussian `tid` x the four 8x8 patches -> one 128-bit work list per warp
+        {   // pre-pass: Gaussian `tid` x the four 8x8 patches -> one 256-bit work list per warp
 #pragma unroll
             for (int g0 = 0; g0 < BATCH; g0 += NT2) {
                 const int g = g0 + tid;
@@ -124,50 +148,103 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 #pragma unroll 1
         for (int q = 0; q < BATCH / 32; ++q) {
             uint32_t m = s_wmask[warp][q];
-            while (m != 0u && !(done0 && done1)) {
-                const int j = q * 32 + __ffs(m) - 1;
-                m &= m - 1u;
-                const float4 a = sA[buf][j];
-                const float4 b = sB[buf][j];
-                // blend_power (geom_math.cuh) on the pixel pair, component-wise the same roundings
-                const float dx = __fadd_rn(a.x, npx);
-                const float2 dy = __fadd2_rn(splat(a.y), npy);
-                const float dxca = __fmul_rn(dx, a.z), ndxcb = __fmul_rn(dx, -a.w);
-                const float2 t3 = __fmul2_rn(dy, __fmul2_rn(dy, splat(b.x)));
-                const float2 q2 = __ffma2_rn(splat(dx), splat(dxca), t3);
-                const float2 power = __ffma2_rn(q2, splat(-0.5f), __fmul2_rn(dy, splat(ndxcb)));
-                bool live0 = !done0 && !(power.x > 0.0f || power.x < b.w);
-                bool live1 = !done1 && !(power.y > 0.0f || power.y < b.w);
-                if (!(live0 || live1)) continue;
-                const float2 og = __fmul2_rn(splat(b.y), expf2_pinned(power));
-                float2 alpha = f2(fminf(0.99f, og.x), fminf(0.99f, og.y));
-                live0 = live0 && !(alpha.x < 1.0f / 255.0f);
-                live1 = live1 && !(alpha.y < 1.0f / 255.0f);
-                const float2 test_T = __fmul2_rn(T, __fadd2_rn(splat(1.0f), f2(-alpha.x, -alpha.y)));
-                const bool term0 = live0 && test_T.x < 0.0001f, term1 = live1 && test_T.y < 0.0001f;
-                done0 = done0 || term0;
-                done1 = done1 || term1;
-                const bool c0 = live0 && !term0, c1 = live1 && !term1;
-                if (!(c0 || c1)) continue;
-                alpha.x = c0 ? alpha.x : 0.0f;
-                alpha.y = c1 ? alpha.y : 0.0f;
-                const float4 c = sC[buf][j];
-                C[0] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.x)), C[0]);
-                C[1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.y)), C[1]);
-                C[2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.z)), C[2]);
-                if (EXTRA) {
-                    const float4 e = sD[buf][j];
-                    C[NCH - 3] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.x)), C[NCH - 3]);
-                    C[NCH - 2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.y)), C[NCH - 2]);
-                    C[NCH - 1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.z)), C[NCH - 1]);
+            if constexpr (ILP == 1) {
+                while (m != 0u && !(done0 && done1)) {
+                    const int j = q * 32 + __ffs(m) - 1;
+                    m &= m - 1u;
+                    const float4 a = sA[buf][j];
+                    const float4 b = sB[buf][j];
+                    // blend_power (geom_math.cuh) on the pixel pair, component-wise the same roundings
+                    const float dx = __fadd_rn(a.x, npx);
+                    const float2 dy = __fadd2_rn(splat(a.y), npy);
+                    const float dxca = __fmul_rn(dx, a.z), ndxcb = __fmul_rn(dx, -a.w);
+                    const float2 t3 = __fmul2_rn(dy, __fmul2_rn(dy, splat(b.x)));
+                    const float2 q2 = __ffma2_rn(splat(dx), splat(dxca), t3);
+                    const float2 power = __ffma2_rn(q2, splat(-0.5f), __fmul2_rn(dy, splat(ndxcb)));
+                    bool live0 = !done0 && !(power.x > 0.0f || power.x < b.w);
+                    bool live1 = !done1 && !(power.y > 0.0f || power.y < b.w);
+                    if (!(live0 || live1)) continue;
+                    const float2 og = __fmul2_rn(splat(b.y), expf2_pinned(power));
+                    float2 alpha = f2(fminf(0.99f, og.x), fminf(0.99f, og.y));
+                    live0 = live0 && !(alpha.x < 1.0f / 255.0f);
+                    live1 = live1 && !(alpha.y < 1.0f / 255.0f);
+                    const float2 test_T = __fmul2_rn(T, __fadd2_rn(splat(1.0f), f2(-alpha.x, -alpha.y)));
+                    const bool term0 = live0 && test_T.x < 0.0001f, term1 = live1 && test_T.y < 0.0001f;
+                    done0 = done0 || term0;
+                    done1 = done1 || term1;
+                    const bool c0 = live0 && !term0, c1 = live1 && !term1;
+                    if (!(c0 || c1)) continue;
+                    alpha.x = c0 ? alpha.x : 0.0f;
+                    alpha.y = c1 ? alpha.y : 0.0f;
+                    const float4 c = sC[buf][j];
+                    C[0] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.x)), C[0]);
+                    C[1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.y)), C[1]);
+                    C[2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.z)), C[2]);
+                    if (EXTRA) {
+                        const float4 e = sD[buf][j];
+                        C[NCH - 3] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.x)), C[NCH - 3]);
+                        C[NCH - 2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.y)), C[NCH - 2]);
+                        C[NCH - 1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.z)), C[NCH - 1]);
+                    }
+                    D = __ffma2_rn(T, __fmul2_rn(alpha, splat(b.z)), D);
+                    Wsum = __ffma2_rn(alpha, T, Wsum);
+                    T.x = c0 ? test_T.x : T.x;
+                    T.y = c1 ? test_T.y : T.y;
+                    const uint32_t pos1 = contrib_base + (uint32_t)j + 1u;
+                    lc0 = c0 ? pos1 : lc0;
+                    lc1 = c1 ? pos1 : lc1;
                 }
-                D = __ffma2_rn(T, __fmul2_rn(alpha, splat(b.z)), D);
-                Wsum = __ffma2_rn(alpha, T, Wsum);
-                T.x = c0 ? test_T.x : T.x;
-                T.y = c1 ? test_T.y : T.y;
-                const uint32_t pos1 = contrib_base + (uint32_t)j + 1u;
-                lc0 = c0 ? pos1 : lc0;
-                lc1 = c1 ? pos1 : lc1;
+            } else {
+                while (m != 0u && !(done0 && done1)) {
+                    // Two list entries per trip: their alphas are independent and are computed side by side (a lone heavy
+                    // tile -- one warp per scheduler at the tail of a small launch -- is bound by the latency of this
+                    // chain, not by issue), then blended one after the other in list order, exactly as before.
+                    const int ja = q * 32 + __ffs(m) - 1;
+                    m &= m - 1u;
+                    const bool two = m != 0u;
+                    const int jb = two ? q * 32 + __ffs(m) - 1 : ja;
+                    m &= m - 1u;                                   // no-op when m is already 0
+                    const float4 a0 = sA[buf][ja], b0 = sB[buf][ja];
+                    const float4 a1 = sA[buf][jb], b1 = sB[buf][jb];
+                    PairAlpha pa = pair_alpha(a0, b0, npx, npy);
+                    PairAlpha pb = pair_alpha(a1, b1, npx, npy);
+                    pb.ok0 = pb.ok0 && two;
+                    pb.ok1 = pb.ok1 && two;
+    #pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const PairAlpha& p = h == 0 ? pa : pb;
+                        const int j = h == 0 ? ja : jb;
+                        const float depth = h == 0 ? b0.z : b1.z;
+                        const bool live0 = !done0 && p.ok0, live1 = !done1 && p.ok1;
+                        float2 alpha = p.alpha;
+                        const float2 test_T = __fmul2_rn(T, __fadd2_rn(splat(1.0f), f2(-alpha.x, -alpha.y)));
+                        const bool term0 = live0 && test_T.x < 0.0001f, term1 = live1 && test_T.y < 0.0001f;
+                        done0 = done0 || term0;
+                        done1 = done1 || term1;
+                        const bool c0 = live0 && !term0, c1 = live1 && !term1;
+                        if (c0 || c1) {
+                            alpha.x = c0 ? alpha.x : 0.0f;
+                            alpha.y = c1 ? alpha.y : 0.0f;
+                            const float4 c = sC[buf][j];
+                            C[0] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.x)), C[0]);
+                            C[1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.y)), C[1]);
+                            C[2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.z)), C[2]);
+                            if (EXTRA) {
+                                const float4 e = sD[buf][j];
+                                C[NCH - 3] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.x)), C[NCH - 3]);
+                                C[NCH - 2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.y)), C[NCH - 2]);
+                                C[NCH - 1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.z)), C[NCH - 1]);
+                            }
+                            D = __ffma2_rn(T, __fmul2_rn(alpha, splat(depth)), D);
+                            Wsum = __ffma2_rn(alpha, T, Wsum);
+                            T.x = c0 ? test_T.x : T.x;
+                            T.y = c1 ? test_T.y : T.y;
+                            const uint32_t pos1 = contrib_base + (uint32_t)j + 1u;
+                            lc0 = c0 ? pos1 : lc0;
+                            lc1 = c1 ? pos1 : lc1;
+                        }
+                    }
+                }
             }
         }
         // everyone is finished with `buf`; stop fetching once the whole tile is saturated
@@ -205,6 +282,14 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 
 }  // namespace
 
+bool blend_ilp2(int blocks) {
+    const char* e = getenv("GSR_BLEND_ILP");
+    const int forced = e ? atoi(e) : 0;
+    if (forced == 1) return false;
+    if (forced == 2) return true;
+    return blocks <= BLEND_ILP2_MAX_BLOCKS;
+}
+
 int launch_blend_forward(int V, int W, int H, int channels, const void* gws, const void* bws, void* iws,
                          const Layout& L, float* out_color, float* out_extra, float* out_depth, float* out_alpha,
                          cudaStream_t s) {
@@ -219,14 +304,19 @@ int launch_blend_forward(int V, int W, int H, int channels, const void* gws, con
     const CamDev* cams = at<CamDev>(gws, L.cams);
     uint32_t* nc = at<uint32_t>(iws, L.n_contrib);
     float* fT = at<float>(iws, L.final_T);
-    if (channels == 3)
-        blend_forward_kernel<3><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H,
-                                                       L.tiles_x, T, out_color, out_extra, out_depth, out_alpha, nc, fT);
-    else if (channels == 6)
-        blend_forward_kernel<6><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H,
-                                                       L.tiles_x, T, out_color, out_extra, out_depth, out_alpha, nc, fT);
-    else
+    const bool ilp2 = blend_ilp2(blocks);        // see common.cuh: small launches end with lone heavy tiles
+#define GSR_FWD(NCH_, ILP_)                                                                                           \
+    blend_forward_kernel<NCH_, ILP_><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, \
+                                                            W, H, L.tiles_x, T, out_color, out_extra, out_depth,      \
+                                                            out_alpha, nc, fT)
+    if (channels == 3) {
+        if (ilp2) GSR_FWD(3, 2); else GSR_FWD(3, 1);
+    } else if (channels == 6) {
+        if (ilp2) GSR_FWD(6, 2); else GSR_FWD(6, 1);
+    } else {
         return GSR_ERR_UNSUPPORTED;
+    }
+#undef GSR_FWD
     GSR_LAUNCH_CHECK();
     return GSR_OK;
 }

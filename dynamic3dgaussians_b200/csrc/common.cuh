@@ -200,6 +200,14 @@ int launch_tile_scan(int V, int P, void* geom_ws, const Layout& L, cudaStream_t 
 int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
                    const float* colors_precomp, const float* extra_colors,
                    void* geom_ws, void* binning_ws, void* image_ws, const Layout& L, cudaStream_t s);
+// Forward blend: process two list entries per loop trip?  Launches of at most BLEND_ILP2_MAX_BLOCKS CTAs (a few views)
+// end with lone heavy tiles that are bound by the latency of the per-entry chain (-9 % on a 3.4-view launch, +3 % on
+// the issue-bound 27-view one, hence the switch).  GSR_BLEND_ILP=1|2 forces a variant (tuning and tests; the two
+// variants produce identical bits).  The backward gains nothing from the same change (its tail waits on the
+// per-batch barrier between a tile's four warps, not on the chain) and has one variant.
+constexpr int BLEND_ILP2_MAX_BLOCKS = 148 * 8 * 4;
+bool blend_ilp2(int blocks);
+
 int launch_blend_forward(int V, int W, int H, int channels, const void* geom_ws, const void* binning_ws,
                          void* image_ws, const Layout& L, float* out_color, float* out_extra, float* out_depth,
                          float* out_alpha, cudaStream_t s);

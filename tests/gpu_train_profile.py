@@ -18,7 +18,7 @@ def main():
     sets = [bench.make_settings(c, dev) for c in cams] if hasattr(bench, "make_settings") else None
     if sets is None:
         class A:  # noqa
-            gaussians, views = 300_000, 27
+            gaussians, views, workload = 300_000, 27, "c2"
         sc, sets = bench.build_workload(A, dev)
     rv = {k: v.to(dev).contiguous() for k, v in sc.rendervar().items()}
     seg = sc.seg_colors.to(dev)[:, 0].contiguous()

@@ -217,6 +217,39 @@ def test_tile_row_bands_partition_a_view():
         assert rel_err(slab.views[k].reshape(gw[k].shape), gw[k]) <= GRAD_TOL, k
 
 
+def test_blend_loop_variants_agree_bit_for_bit(monkeypatch):
+    """The forward blend kernel exists in a one-entry-per-trip and a two-entries-per-trip variant (picked by launch
+    size, common.cuh blend_ilp2).  Same arithmetic in the same order per pixel: images, n_contrib and final T must be
+    identical (and so the gradients, up to the atomics' reordering)."""
+    sc = scenes.make_scene_c2(30_000, seed=9)
+    cams = scenes.cameras_c2(2, w=320, h=180, f=233.0)
+    sets = [settings_from_spec(c)[0] for c in cams]
+    rv = _rv(sc)
+    seg = sc.seg_colors.cuda()
+    gen = torch.Generator().manual_seed(6)
+    gc = torch.randn(2, 3, 180, 320, generator=gen).cuda()
+    ge = torch.randn(2, 3, 180, 320, generator=gen).cuda()
+    gd = torch.randn(2, 1, 180, 320, generator=gen).cuda() * 0.1
+    res = {}
+    for ilp in ("1", "2"):
+        monkeypatch.setenv("GSR_BLEND_ILP", ilp)
+        for extra in (None, seg):
+            c, e, d, a, r, st = _fwd(sets, rv, extra_colors=extra)
+            ncon = [export_view(st, v)[3] for v in range(2)]
+            g = RZ.backward_views(st, rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"],
+                                  rv["rotations"], None, None, extra, gc, None if extra is None else ge, gd, None)
+            res[(ilp, extra is None)] = (c, e, d, a, ncon, g)
+    monkeypatch.delenv("GSR_BLEND_ILP")
+    for plain in (True, False):
+        c1, e1, d1, a1, n1, g1 = res[("1", plain)]
+        c2, e2, d2, a2, n2, g2 = res[("2", plain)]
+        assert torch.equal(c1, c2) and torch.equal(d1, d2) and torch.equal(a1, a2)
+        assert plain or torch.equal(e1, e2)
+        assert all(torch.equal(x, y) for x, y in zip(n1, n2))
+        for k in ("means3D", "colors", "opacity", "scales", "rotations", "means2D"):
+            assert rel_err(g2[k], g1[k]) <= GRAD_TOL, k
+
+
 def test_edge_cases_empty_culled_and_ragged():
     cs = scenes.camera_c1()
     st_, _ = settings_from_spec(cs, bg=(0.5, 0.25, 0.125))
