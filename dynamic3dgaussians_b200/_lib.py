@@ -18,7 +18,7 @@ EXPORTED_SYMBOLS = [
     "gsr_dyn_losses_temp_bytes", "gsr_dyn_losses",
     "gsr_image_loss_state_bytes", "gsr_image_loss_forward", "gsr_image_loss_backward", "gsr_adam_step",
     "gsr_fp32_peak_probe", "gsr_probe_geometry", "gsr_stage_timing_enable", "gsr_stage_timing_count", "gsr_stage_name",
-    "gsr_stage_timing_read",
+    "gsr_stage_timing_read", "gsr_debug_blend_trace",
 ]
 
 
@@ -106,6 +106,7 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.gsr_stage_name.argtypes = [i32]
     lib.gsr_stage_timing_read.argtypes = [vp, i32]
     lib.gsr_probe_geometry.argtypes = [C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.gsr_debug_blend_trace.argtypes = [vp, vp]
     for name in EXPORTED_SYMBOLS:
         fn = getattr(lib, name)
         if fn.restype is C.c_int and name not in ("gsr_abi_version",):

@@ -401,6 +401,12 @@ int gsr_stage_timing_read(float* ms_out, int n) {
     return GSR_OK;
 }
 
+int gsr_debug_blend_trace(uint64_t* fwd, uint64_t* bwd) {
+    int rc = gsr::set_blend_forward_trace((unsigned long long*)fwd);
+    if (rc != GSR_OK) return rc;
+    return gsr::set_blend_backward_trace((unsigned long long*)bwd);
+}
+
 int gsr_probe_geometry(int* blocks, int* threads) {
     if (blocks) *blocks = 148 * 8;
     if (threads) *threads = 256;

@@ -24,6 +24,10 @@ namespace gsr {
 
 namespace {
 
+__device__ unsigned long long* g_trace_bwd = nullptr;   // diagnostic: per-CTA (start ns, end ns, SM, tile)
+__device__ __forceinline__ unsigned long long trace_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ unsigned trace_smid() { unsigned r; asm volatile("mov.u32 %0, %smid;" : "=r"(r)); return r; }
+
 constexpr int BATCH = 128;
 constexpr int SUB = 32;
 constexpr unsigned FULL = 0xffffffffu;
@@ -36,6 +40,7 @@ constexpr unsigned FULL = 0xffffffffu;
 // dL/dalpha, which leaves T, the recurrence and every sum unchanged (no divergent region).
 __device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
 __device__ __forceinline__ float2 splat(float a) { return make_float2(a, a); }
+__device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 
 constexpr int NT2 = 128;
 constexpr int NW2 = NT2 / 32;
@@ -52,10 +57,11 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                        float* __restrict__ grad_rec) {
     constexpr bool EXTRA = NCH > 3;
     constexpr int K = GR_COL + NCH;
-    __shared__ __align__(128) float4 sA[2][BATCH];
-    __shared__ __align__(128) float4 sB[2][BATCH];
-    __shared__ __align__(128) float4 sC[2][BATCH];
-    __shared__ __align__(128) float4 sD[EXTRA ? 2 : 1][EXTRA ? BATCH : 1];
+    // one block per ring slot, so that the loop addresses all of an entry's records off ONE register (base + 16 j)
+    struct __align__(128) Stage {
+        float4 a[BATCH], b[BATCH], c[BATCH], d[EXTRA ? BATCH : 1];
+    };
+    __shared__ Stage stage[2];
     __shared__ __align__(8) uint64_t full[2];
     __shared__ uint32_t s_wmask[NW2][BATCH / SUB];
     __shared__ uint32_t s_max;
@@ -63,6 +69,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int vt = (int)tile_order[blockIdx.x];
+    unsigned long long* const trace = g_trace_bwd;
+    if (trace && threadIdx.x == 0) { trace[4 * blockIdx.x] = trace_now(); trace[4 * blockIdx.x + 2] = trace_smid(); trace[4 * blockIdx.x + 3] = (unsigned long long)vt; }
     const int view = vt / tiles_per_view;
     const int tile = vt - view * tiles_per_view;
     const int tile_yi = tile / tiles_x, tile_xi = tile - tile_yi * tiles_x;
@@ -91,7 +99,10 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     __syncthreads();
     const int n_proc = (int)min(s_max, range.y - range.x);
     const int rounds = (n_proc + BATCH - 1) / BATCH;
-    if (rounds == 0) return;
+    if (rounds == 0) {
+        if (trace && lane == 0) atomicMax(&trace[4 * blockIdx.x + 1], trace_now());
+        return;
+    }
 
     auto issue = [&](int r) {   // thread 0 only; round r walks chunk (rounds-1-r)
         const int buf = r & 1;
@@ -100,10 +111,10 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         const uint32_t bytes = (uint32_t)nb * 16u;
         const size_t src = (size_t)range.x + (size_t)c * BATCH;
         mbar_expect_tx(&full[buf], bytes * (EXTRA ? 4u : 3u));
-        tma_load_1d(sA[buf], recA + src, bytes, &full[buf]);
-        tma_load_1d(sB[buf], recB + src, bytes, &full[buf]);
-        tma_load_1d(sC[buf], recC + src, bytes, &full[buf]);
-        if (EXTRA) tma_load_1d(sD[buf], recD + src, bytes, &full[buf]);
+        tma_load_1d(stage[buf].a, recA + src, bytes, &full[buf]);
+        tma_load_1d(stage[buf].b, recB + src, bytes, &full[buf]);
+        tma_load_1d(stage[buf].c, recC + src, bytes, &full[buf]);
+        if (EXTRA) tma_load_1d(stage[buf].d, recD + src, bytes, &full[buf]);
     };
     if (tid == 0) {
         issue(0);
@@ -158,8 +169,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 const int g = g0 + tid;
                 uint32_t m4 = 0u;
                 if (g < nb) {
-                    const float4 a = sA[buf][g];
-                    const float4 b = sB[buf][g];
+                    const float4 a = stage[buf].a[g];
+                    const float4 b = stage[buf].b[g];
                     m4 = blend_patch_mask4(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
                 }
 #pragma unroll
@@ -182,8 +193,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 const int jl = 31 - __clz(m);
                 m &= ~(1u << jl);
                 const int j = lo + jl;
-                const float4 a = sA[buf][j];
-                const float4 b = sB[buf][j];
+                const float4 a = stage[buf].a[j];
+                const float4 b = stage[buf].b[j];
                 const uint32_t pos = (uint32_t)(c * BATCH + j);
                 // blend_power (geom_math.cuh) on the pixel pair; identical roundings per component
                 const float dx = __fadd_rn(a.x, npx);
@@ -203,9 +214,11 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 alpha.x = valid0 ? alpha.x : 0.0f;
                 alpha.y = valid1 ? alpha.y : 0.0f;
                 const float2 om = __fadd2_rn(splat(1.0f), f2(-alpha.x, -alpha.y));
-                T = f2(__fdividef(T.x, om.x), __fdividef(T.y, om.y));     // transmittance in front of this Gaussian
+                // transmittance in front of this Gaussian: T / (1 - alpha) as __fdividef computes it (MUFU.RCP, then a
+                // multiply) minus its rescaling path for denormal divisors, which 1 - alpha in [0.01, 1] never takes
+                T = __fmul2_rn(T, f2(rcp_approx(om.x), rcp_approx(om.y)));
                 const float2 w = __fmul2_rn(alpha, T);
-                const float4 col = sC[buf][j];
+                const float4 col = stage[buf].c[j];
                 float2 s = __ffma2_rn(splat(col.x), gC[0],
                            __ffma2_rn(splat(col.y), gC[1],
                            __ffma2_rn(splat(col.z), gC[2], __ffma2_rn(splat(b.z), gD, gA))));
@@ -213,7 +226,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 #pragma unroll
                 for (int k = 0; k < 3; ++k) v[GR_COL + k] = fmaf(w.y, gC[k].y, w.x * gC[k].x);
                 if (EXTRA) {
-                    const float4 e = sD[buf][j];
+                    const float4 e = stage[buf].d[j];
                     s = __ffma2_rn(splat(e.x), gC[NCH - 3],
                         __ffma2_rn(splat(e.y), gC[NCH - 2], __ffma2_rn(splat(e.z), gC[NCH - 1], s)));
 #pragma unroll
@@ -245,9 +258,15 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         __syncthreads();        // every warp is done with `buf`
         if (tid == 0 && r + 2 < rounds) issue(r + 2);
     }
+    if (trace && lane == 0) atomicMax(&trace[4 * blockIdx.x + 1], trace_now());
 }
 
 }  // namespace
+
+int set_blend_backward_trace(unsigned long long* p) {
+    GSR_CUDA_TRY(cudaMemcpyToSymbol(g_trace_bwd, &p, sizeof(p)));
+    return GSR_OK;
+}
 
 int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, const void* bws, const void* iws,
                           const Layout& L, const float* dL_dcolor, const float* dL_dextra, const float* dL_ddepth,

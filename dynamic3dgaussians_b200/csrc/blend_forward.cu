@@ -21,6 +21,10 @@ namespace gsr {
 
 namespace {
 
+__device__ unsigned long long* g_trace_fwd = nullptr;   // diagnostic: per-CTA (start ns, end ns, SM, tile)
+__device__ __forceinline__ unsigned long long trace_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ unsigned trace_smid() { unsigned r; asm volatile("mov.u32 %0, %smid;" : "=r"(r)); return r; }
+
 constexpr int BATCH = 256;
 
 // CTA = 128 threads = 4 warps; a warp owns an 8x8 patch, a lane the pixels (x, y) and (x, y + 4).  Record loads, loop
@@ -66,16 +70,19 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                       float* __restrict__ out_color, float* __restrict__ out_extra, float* __restrict__ out_depth,
                       float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib, float* __restrict__ final_T) {
     constexpr bool EXTRA = NCH > 3;
-    __shared__ __align__(128) float4 sA[2][BATCH];
-    __shared__ __align__(128) float4 sB[2][BATCH];
-    __shared__ __align__(128) float4 sC[2][BATCH];
-    __shared__ __align__(128) float4 sD[EXTRA ? 2 : 1][EXTRA ? BATCH : 1];
+    // one block per ring slot, so that the loop addresses all of an entry's records off ONE register (base + 16 j)
+    struct __align__(128) Stage {
+        float4 a[BATCH], b[BATCH], c[BATCH], d[EXTRA ? BATCH : 1];
+    };
+    __shared__ Stage stage[2];
     __shared__ __align__(8) uint64_t full[2];
     __shared__ uint32_t s_wmask[NW2][BATCH / 32];
     static_assert(BATCH % NT2 == 0, "pre-pass: BATCH / NT2 staged Gaussians per thread");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int vt = (int)tile_order[blockIdx.x];
+    unsigned long long* const trace = g_trace_fwd;
+    if (trace && threadIdx.x == 0) { trace[4 * blockIdx.x] = trace_now(); trace[4 * blockIdx.x + 2] = trace_smid(); trace[4 * blockIdx.x + 3] = (unsigned long long)vt; }
     const int view = vt / tiles_per_view;
     const int tile = vt - view * tiles_per_view;
     const int tile_yi = tile / tiles_x, tile_xi = tile - tile_yi * tiles_x;
@@ -103,10 +110,10 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         const uint32_t bytes = (uint32_t)nb * 16u;
         const size_t src = (size_t)range.x + (size_t)r * BATCH;
         mbar_expect_tx(&full[buf], bytes * (EXTRA ? 4u : 3u));
-        tma_load_1d(sA[buf], recA + src, bytes, &full[buf]);
-        tma_load_1d(sB[buf], recB + src, bytes, &full[buf]);
-        tma_load_1d(sC[buf], recC + src, bytes, &full[buf]);
-        if (EXTRA) tma_load_1d(sD[buf], recD + src, bytes, &full[buf]);
+        tma_load_1d(stage[buf].a, recA + src, bytes, &full[buf]);
+        tma_load_1d(stage[buf].b, recB + src, bytes, &full[buf]);
+        tma_load_1d(stage[buf].c, recC + src, bytes, &full[buf]);
+        if (EXTRA) tma_load_1d(stage[buf].d, recD + src, bytes, &full[buf]);
     };
     if (tid == 0) {
         if (rounds > 0) issue(0);
@@ -133,8 +140,8 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                 const int g = g0 + tid;
                 uint32_t m4 = 0u;
                 if (g < nb) {
-                    const float4 a = sA[buf][g];
-                    const float4 b = sB[buf][g];
+                    const float4 a = stage[buf].a[g];
+                    const float4 b = stage[buf].b[g];
                     m4 = blend_patch_mask4(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
                 }
 #pragma unroll
@@ -152,8 +159,8 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                 while (m != 0u && !(done0 && done1)) {
                     const int j = q * 32 + __ffs(m) - 1;
                     m &= m - 1u;
-                    const float4 a = sA[buf][j];
-                    const float4 b = sB[buf][j];
+                    const float4 a = stage[buf].a[j];
+                    const float4 b = stage[buf].b[j];
                     // blend_power (geom_math.cuh) on the pixel pair, component-wise the same roundings
                     const float dx = __fadd_rn(a.x, npx);
                     const float2 dy = __fadd2_rn(splat(a.y), npy);
@@ -176,12 +183,12 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                     if (!(c0 || c1)) continue;
                     alpha.x = c0 ? alpha.x : 0.0f;
                     alpha.y = c1 ? alpha.y : 0.0f;
-                    const float4 c = sC[buf][j];
+                    const float4 c = stage[buf].c[j];
                     C[0] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.x)), C[0]);
                     C[1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.y)), C[1]);
                     C[2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.z)), C[2]);
                     if (EXTRA) {
-                        const float4 e = sD[buf][j];
+                        const float4 e = stage[buf].d[j];
                         C[NCH - 3] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.x)), C[NCH - 3]);
                         C[NCH - 2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.y)), C[NCH - 2]);
                         C[NCH - 1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.z)), C[NCH - 1]);
@@ -196,53 +203,59 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                 }
             } else {
                 while (m != 0u && !(done0 && done1)) {
-                    // Two list entries per trip: their alphas are independent and are computed side by side (a lone heavy
-                    // tile -- one warp per scheduler at the tail of a small launch -- is bound by the latency of this
-                    // chain, not by issue), then blended one after the other in list order, exactly as before.
-                    const int ja = q * 32 + __ffs(m) - 1;
-                    m &= m - 1u;
-                    const bool two = m != 0u;
-                    const int jb = two ? q * 32 + __ffs(m) - 1 : ja;
-                    m &= m - 1u;                                   // no-op when m is already 0
-                    const float4 a0 = sA[buf][ja], b0 = sB[buf][ja];
-                    const float4 a1 = sA[buf][jb], b1 = sB[buf][jb];
-                    PairAlpha pa = pair_alpha(a0, b0, npx, npy);
-                    PairAlpha pb = pair_alpha(a1, b1, npx, npy);
-                    pb.ok0 = pb.ok0 && two;
-                    pb.ok1 = pb.ok1 && two;
-    #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const PairAlpha& p = h == 0 ? pa : pb;
-                        const int j = h == 0 ? ja : jb;
-                        const float depth = h == 0 ? b0.z : b1.z;
-                        const bool live0 = !done0 && p.ok0, live1 = !done1 && p.ok1;
-                        float2 alpha = p.alpha;
+                    // ILP list entries per trip.  A lone heavy tile -- one warp per scheduler at the tail of a small
+                    // launch -- is bound by the latency of the per-entry chain, not by issue: the alphas (and the
+                    // colour loads) of the trip's entries depend on nothing the loop carries and are computed side by
+                    // side; only the short T chain (multiply, compare, select) is walked entry by entry, in list order
+                    // and with the same operations as the one-entry loop, so the bits are the same.
+                    int jj[ILP];
+                    bool has[ILP];
+#pragma unroll
+                    for (int e = 0; e < ILP; ++e) {
+                        has[e] = m != 0u;
+                        jj[e] = has[e] ? q * 32 + __ffs(m) - 1 : jj[0];
+                        m &= m - 1u;                               // no-op once m is 0
+                    }
+                    PairAlpha pa[ILP];
+                    float4 col[ILP], ext[EXTRA ? ILP : 1];
+                    float dep[ILP];
+#pragma unroll
+                    for (int e = 0; e < ILP; ++e) {
+                        const float4 a = stage[buf].a[jj[e]], b = stage[buf].b[jj[e]];
+                        col[e] = stage[buf].c[jj[e]];
+                        if (EXTRA) ext[e] = stage[buf].d[jj[e]];
+                        dep[e] = b.z;
+                        pa[e] = pair_alpha(a, b, npx, npy);
+                        pa[e].ok0 = pa[e].ok0 && has[e];
+                        pa[e].ok1 = pa[e].ok1 && has[e];
+                    }
+#pragma unroll
+                    for (int e = 0; e < ILP; ++e) {
+                        const bool live0 = !done0 && pa[e].ok0, live1 = !done1 && pa[e].ok1;
+                        float2 alpha = pa[e].alpha;
                         const float2 test_T = __fmul2_rn(T, __fadd2_rn(splat(1.0f), f2(-alpha.x, -alpha.y)));
                         const bool term0 = live0 && test_T.x < 0.0001f, term1 = live1 && test_T.y < 0.0001f;
                         done0 = done0 || term0;
                         done1 = done1 || term1;
                         const bool c0 = live0 && !term0, c1 = live1 && !term1;
-                        if (c0 || c1) {
-                            alpha.x = c0 ? alpha.x : 0.0f;
-                            alpha.y = c1 ? alpha.y : 0.0f;
-                            const float4 c = sC[buf][j];
-                            C[0] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.x)), C[0]);
-                            C[1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.y)), C[1]);
-                            C[2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(c.z)), C[2]);
-                            if (EXTRA) {
-                                const float4 e = sD[buf][j];
-                                C[NCH - 3] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.x)), C[NCH - 3]);
-                                C[NCH - 2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.y)), C[NCH - 2]);
-                                C[NCH - 1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(e.z)), C[NCH - 1]);
-                            }
-                            D = __ffma2_rn(T, __fmul2_rn(alpha, splat(depth)), D);
-                            Wsum = __ffma2_rn(alpha, T, Wsum);
-                            T.x = c0 ? test_T.x : T.x;
-                            T.y = c1 ? test_T.y : T.y;
-                            const uint32_t pos1 = contrib_base + (uint32_t)j + 1u;
-                            lc0 = c0 ? pos1 : lc0;
-                            lc1 = c1 ? pos1 : lc1;
+                        // a pixel that does not blend this entry runs the same instructions with alpha = 0
+                        alpha.x = c0 ? alpha.x : 0.0f;
+                        alpha.y = c1 ? alpha.y : 0.0f;
+                        C[0] = __ffma2_rn(T, __fmul2_rn(alpha, splat(col[e].x)), C[0]);
+                        C[1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(col[e].y)), C[1]);
+                        C[2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(col[e].z)), C[2]);
+                        if (EXTRA) {
+                            C[NCH - 3] = __ffma2_rn(T, __fmul2_rn(alpha, splat(ext[EXTRA ? e : 0].x)), C[NCH - 3]);
+                            C[NCH - 2] = __ffma2_rn(T, __fmul2_rn(alpha, splat(ext[EXTRA ? e : 0].y)), C[NCH - 2]);
+                            C[NCH - 1] = __ffma2_rn(T, __fmul2_rn(alpha, splat(ext[EXTRA ? e : 0].z)), C[NCH - 1]);
                         }
+                        D = __ffma2_rn(T, __fmul2_rn(alpha, splat(dep[e])), D);
+                        Wsum = __ffma2_rn(alpha, T, Wsum);
+                        T.x = c0 ? test_T.x : T.x;
+                        T.y = c1 ? test_T.y : T.y;
+                        const uint32_t pos1 = contrib_base + (uint32_t)jj[e] + 1u;
+                        lc0 = c0 ? pos1 : lc0;
+                        lc1 = c1 ? pos1 : lc1;
                     }
                 }
             }
@@ -278,16 +291,21 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         out_depth[(size_t)view * HW + pix] = i == 0 ? D.x : D.y;
         out_alpha[(size_t)view * HW + pix] = i == 0 ? Wsum.x : Wsum.y;
     }
+    if (trace && lane == 0) atomicMax(&trace[4 * blockIdx.x + 1], trace_now());
 }
 
 }  // namespace
 
-bool blend_ilp2(int blocks) {
+int set_blend_forward_trace(unsigned long long* p) {
+    GSR_CUDA_TRY(cudaMemcpyToSymbol(g_trace_fwd, &p, sizeof(p)));
+    return GSR_OK;
+}
+
+int blend_ilp(int blocks) {
     const char* e = getenv("GSR_BLEND_ILP");
     const int forced = e ? atoi(e) : 0;
-    if (forced == 1) return false;
-    if (forced == 2) return true;
-    return blocks <= BLEND_ILP2_MAX_BLOCKS;
+    if (forced == 1 || forced == 2) return forced;
+    return blocks <= BLEND_ILP_MAX_BLOCKS ? BLEND_ILP_SMALL : 1;
 }
 
 int launch_blend_forward(int V, int W, int H, int channels, const void* gws, const void* bws, void* iws,
@@ -304,15 +322,15 @@ int launch_blend_forward(int V, int W, int H, int channels, const void* gws, con
     const CamDev* cams = at<CamDev>(gws, L.cams);
     uint32_t* nc = at<uint32_t>(iws, L.n_contrib);
     float* fT = at<float>(iws, L.final_T);
-    const bool ilp2 = blend_ilp2(blocks);        // see common.cuh: small launches end with lone heavy tiles
+    const int ilp = blend_ilp(blocks);           // see common.cuh: small launches end with lone heavy tiles
 #define GSR_FWD(NCH_, ILP_)                                                                                           \
     blend_forward_kernel<NCH_, ILP_><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, \
                                                             W, H, L.tiles_x, T, out_color, out_extra, out_depth,      \
                                                             out_alpha, nc, fT)
     if (channels == 3) {
-        if (ilp2) GSR_FWD(3, 2); else GSR_FWD(3, 1);
+        if (ilp > 1) GSR_FWD(3, BLEND_ILP_SMALL); else GSR_FWD(3, 1);
     } else if (channels == 6) {
-        if (ilp2) GSR_FWD(6, 2); else GSR_FWD(6, 1);
+        if (ilp > 1) GSR_FWD(6, BLEND_ILP_SMALL); else GSR_FWD(6, 1);
     } else {
         return GSR_ERR_UNSUPPORTED;
     }

@@ -200,13 +200,20 @@ int launch_tile_scan(int V, int P, void* geom_ws, const Layout& L, cudaStream_t 
 int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
                    const float* colors_precomp, const float* extra_colors,
                    void* geom_ws, void* binning_ws, void* image_ws, const Layout& L, cudaStream_t s);
-// Forward blend: process two list entries per loop trip?  Launches of at most BLEND_ILP2_MAX_BLOCKS CTAs (a few views)
-// end with lone heavy tiles that are bound by the latency of the per-entry chain (-9 % on a 3.4-view launch, +3 % on
-// the issue-bound 27-view one, hence the switch).  GSR_BLEND_ILP=1|2 forces a variant (tuning and tests; the two
-// variants produce identical bits).  The backward gains nothing from the same change (its tail waits on the
-// per-batch barrier between a tile's four warps, not on the chain) and has one variant.
-constexpr int BLEND_ILP2_MAX_BLOCKS = 148 * 8 * 4;
-bool blend_ilp2(int blocks);
+// Forward blend: BLEND_ILP_SMALL list entries per loop trip for launches of at most BLEND_ILP_MAX_BLOCKS CTAs (a few
+// views).  Such launches end with a handful of deep tiles running alone (tests/gpu_tile_trace.py: at one C2 view the
+// deepest tile lasts the whole kernel while the average SM is done at half of it).  A lone tile has one warp per
+// scheduler, so its time is that warp's instruction stream on one scheduler's pipes: two entries per trip with the
+// alphas computed side by side and a branch-free blend shorten the stream's stalls (-15 % on a one-view launch), more
+// entries per trip or fewer resident CTAs change nothing (measured), and the same change makes the backward slower
+// (more instructions on the same scheduler), so the backward has one variant.  The issue-bound 27-view launch is 3 %
+// faster with the one-entry loop, hence the switch.  GSR_BLEND_ILP=1|2 forces a variant (tuning and tests; the
+// variants produce identical bits).
+constexpr int BLEND_ILP_MAX_BLOCKS = 148 * 8 * 4;
+constexpr int BLEND_ILP_SMALL = 2;
+int blend_ilp(int blocks);
+int set_blend_forward_trace(unsigned long long* p);     // diagnostics (gsr_debug_blend_trace)
+int set_blend_backward_trace(unsigned long long* p);
 
 int launch_blend_forward(int V, int W, int H, int channels, const void* geom_ws, const void* binning_ws,
                          void* image_ws, const Layout& L, float* out_color, float* out_extra, float* out_depth,

@@ -249,6 +249,11 @@ int gsr_stage_timing_read(float* ms_out, int n);
 int gsr_fp32_peak_probe(float* out, int iters, gsr_stream_t stream);   /* flops = blocks*threads*iters*2*8 */
 int gsr_probe_geometry(int* blocks, int* threads);
 
+/* Diagnostic: when non-null, every CTA of the blend forward / backward kernels writes 4 x uint64 at index blockIdx.x:
+ * (first-thread start ns, last-warp end ns [atomicMax: zero the buffer first], SM id, view*T + tile).  Buffers must hold
+ * 4 * V * T uint64 each; pass null to switch the trace off.  Synchronises the device (cudaMemcpyToSymbol). */
+int gsr_debug_blend_trace(uint64_t* fwd, uint64_t* bwd);
+
 #ifdef __cplusplus
 }
 #endif
