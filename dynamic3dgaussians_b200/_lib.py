@@ -9,7 +9,8 @@ import os
 from typing import Optional
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libgsr_b200.so")
+# GSR_LIB_PATH: load another build of the same library (A/B runs of kernel variants; tests/gpu_ab.sh)
+LIB_PATH = os.environ.get("GSR_LIB_PATH") or os.path.join(HERE, "libgsr_b200.so")
 
 EXPORTED_SYMBOLS = [
     "gsr_abi_version", "gsr_strerror", "gsr_last_cuda_error", "gsr_workspace_sizes", "gsr_workspace_layout",

@@ -40,13 +40,20 @@ constexpr unsigned FULL = 0xffffffffu;
 // dL/dalpha, which leaves T, the recurrence and every sum unchanged (no divergent region).
 __device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
 __device__ __forceinline__ float2 splat(float a) { return make_float2(a, a); }
+// predicated RED (no branch around the atomic)
+__device__ __forceinline__ void red_add_if(bool p, float* addr, float v) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p red.global.add.f32 [%0], %1;\n\t}" ::"l"(addr), "f"(v), "r"((unsigned)p) : "memory");
+}
 __device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 
 constexpr int NT2 = 128;
 constexpr int NW2 = NT2 / 32;
 
 template <int NCH>
-__global__ void __launch_bounds__(NT2, 8)
+#ifndef GSR_BWD_MINB
+#define GSR_BWD_MINB 8
+#endif
+__global__ void __launch_bounds__(NT2, GSR_BWD_MINB)
 blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                        const float4* __restrict__ recA, const float4* __restrict__ recB,
                        const float4* __restrict__ recC, const float4* __restrict__ recD,
@@ -151,7 +158,6 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         if (dL_ddepth) gD = f2(in0 ? dL_ddepth[pix0] : 0.0f, in1 ? dL_ddepth[pix1] : 0.0f);
         if (dL_dalpha) gA = f2(in0 ? dL_dalpha[pix0] : 0.0f, in1 ? dL_dalpha[pix1] : 0.0f);
     }
-    float2 last_alpha = splat(0.0f), last_s = splat(0.0f);
 
     const int my_slot = PackedReduce<K>::slot(lane);
     const unsigned slot_peers = __match_any_sync(FULL, my_slot);
@@ -162,6 +168,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         const int buf = r & 1;
         const int c = rounds - 1 - r;
         const int nb = min(BATCH, n_proc - c * BATCH);
+        const int rel0 = (int)lc0 - c * BATCH, rel1 = (int)lc1 - c * BATCH;   // list position < n_contrib  <=>  j < rel
         mbar_wait(&full[buf], (uint32_t)((r >> 1) & 1));
         {   // pre-pass: per-warp work lists, Gaussian `tid` x the four 8x8 patches
 #pragma unroll
@@ -195,7 +202,6 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 const int j = lo + jl;
                 const float4 a = stage[buf].a[j];
                 const float4 b = stage[buf].b[j];
-                const uint32_t pos = (uint32_t)(c * BATCH + j);
                 // blend_power (geom_math.cuh) on the pixel pair; identical roundings per component
                 const float dx = __fadd_rn(a.x, npx);
                 const float2 dy = __fadd2_rn(splat(a.y), npy);
@@ -203,8 +209,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 const float2 t3 = __fmul2_rn(dy, __fmul2_rn(dy, splat(b.x)));
                 const float2 q = __ffma2_rn(splat(dx), splat(dxca), t3);
                 const float2 power = __ffma2_rn(q, splat(-0.5f), __fmul2_rn(dy, splat(ndxcb)));
-                const bool pre0 = (pos < lc0) && !(power.x > 0.0f) && !(power.x < b.w);
-                const bool pre1 = (pos < lc1) && !(power.y > 0.0f) && !(power.y < b.w);
+                const bool pre0 = (j < rel0) && !(power.x > 0.0f) && !(power.x < b.w);
+                const bool pre1 = (j < rel1) && !(power.y > 0.0f) && !(power.y < b.w);
                 if (!__any_sync(FULL, pre0 || pre1)) continue;      // warp-uniform
                 const float2 G = expf2_pinned(power);        // garbage where !pre: masked by the selects below
                 const float2 og = __fmul2_rn(splat(b.y), G);
@@ -233,11 +239,10 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                     for (int k = NCH - 3; k < NCH; ++k) v[GR_COL + k] = fmaf(w.y, gC[k].y, w.x * gC[k].x);
                 }
                 v[GR_DEPTH] = fmaf(w.y, gD.y, w.x * gD.x);
-                // colour-behind recurrence (see header); with alpha = 0 it only flushes the pending term
-                acc = __ffma2_rn(last_alpha, __fadd2_rn(last_s, f2(-acc.x, -acc.y)), acc);
-                last_s = s;
-                last_alpha = alpha;
-                float2 gq = __fmul2_rn(G, __fmul2_rn(__fadd2_rn(s, f2(-acc.x, -acc.y)), T));   // G * dL/dalpha
+                // colour-behind recurrence (see header); alpha = 0 leaves acc as it is
+                const float2 sd = __fadd2_rn(s, f2(-acc.x, -acc.y));          // s_j - acc_j
+                float2 gq = __fmul2_rn(G, __fmul2_rn(sd, T));                   // G * dL/dalpha
+                acc = __ffma2_rn(alpha, sd, acc);                               // what the next (nearer) entry has behind it
                 gq.x = valid0 ? gq.x : 0.0f;
                 gq.y = valid1 ? gq.y : 0.0f;
                 const float2 am = __fmul2_rn(splat(b.y), gq);
@@ -252,7 +257,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 PackedReduce<K>::run(v, lane);
                 // one reduction (RED) per (warp patch, Gaussian, value): the K sums sit in K different lanes and land in
                 // one 64-byte gradient record
-                if (writer) atomicAdd(grad_rec + (size_t)__float_as_uint(col.w) * grad_rec_stride(NCH) + my_slot, v[0]);
+                red_add_if(writer, grad_rec + (size_t)__float_as_uint(col.w) * grad_rec_stride(NCH) + my_slot, v[0]);
             }
         }
         __syncthreads();        // every warp is done with `buf`
