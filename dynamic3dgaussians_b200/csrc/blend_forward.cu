@@ -120,13 +120,16 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         if (rounds > 1) issue(1);
     }
 
-    float2 T = splat(1.0f);
+    // T > 0: the pixel's running transmittance.  T < 0: the pixel is finished (saturated, or outside the image) and |T|
+    // is its final transmittance -- the flag rides in the sign bit, so the loop carries no predicates: a finished pixel
+    // gives test_T < 0, which fails the "still above 0.0001" test below like a terminating Gaussian does, blends with
+    // alpha = 0 and keeps its T.
+    float2 T = f2(in0 ? 1.0f : -1.0f, in1 ? 1.0f : -1.0f);
     float2 C[NCH];
 #pragma unroll
     for (int k = 0; k < NCH; ++k) C[k] = splat(0.0f);
     float2 D = splat(0.0f), Wsum = splat(0.0f);
     uint32_t lc0 = 0, lc1 = 0;
-    bool done0 = !in0, done1 = !in1;
 
     const float tile_x0 = (float)(tile_xi * TILE_X), tile_y0 = (float)(tile_yi * TILE_Y);
     for (int r = 0; r < rounds; ++r) {
@@ -156,7 +159,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         for (int q = 0; q < BATCH / 32; ++q) {
             uint32_t m = s_wmask[warp][q];
             if constexpr (ILP == 1) {
-                while (m != 0u && !(done0 && done1)) {
+                while (m != 0u && !(T.x < 0.0f && T.y < 0.0f)) {
                     const int j = q * 32 + __ffs(m) - 1;
                     m &= m - 1u;
                     const float4 a = stage[buf].a[j];
@@ -168,18 +171,18 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                     const float2 t3 = __fmul2_rn(dy, __fmul2_rn(dy, splat(b.x)));
                     const float2 q2 = __ffma2_rn(splat(dx), splat(dxca), t3);
                     const float2 power = __ffma2_rn(q2, splat(-0.5f), __fmul2_rn(dy, splat(ndxcb)));
-                    bool live0 = !done0 && !(power.x > 0.0f || power.x < b.w);
-                    bool live1 = !done1 && !(power.y > 0.0f || power.y < b.w);
-                    if (!(live0 || live1)) continue;
+                    bool ok0 = !(power.x > 0.0f || power.x < b.w);
+                    bool ok1 = !(power.y > 0.0f || power.y < b.w);
+                    if (!(ok0 || ok1)) continue;
                     const float2 og = __fmul2_rn(splat(b.y), expf2_pinned(power));
                     float2 alpha = f2(fminf(0.99f, og.x), fminf(0.99f, og.y));
-                    live0 = live0 && !(alpha.x < 1.0f / 255.0f);
-                    live1 = live1 && !(alpha.y < 1.0f / 255.0f);
+                    ok0 = ok0 && !(alpha.x < 1.0f / 255.0f);
+                    ok1 = ok1 && !(alpha.y < 1.0f / 255.0f);
                     const float2 test_T = __fmul2_rn(T, __fadd2_rn(splat(1.0f), f2(-alpha.x, -alpha.y)));
-                    const bool term0 = live0 && test_T.x < 0.0001f, term1 = live1 && test_T.y < 0.0001f;
-                    done0 = done0 || term0;
-                    done1 = done1 || term1;
-                    const bool c0 = live0 && !term0, c1 = live1 && !term1;
+                    const bool c0 = ok0 && !(test_T.x < 0.0001f), c1 = ok1 && !(test_T.y < 0.0001f);
+                    // ok && !c: this Gaussian would saturate the pixel (or the pixel already is): finished from here on
+                    T.x = (ok0 && !c0) ? -fabsf(T.x) : T.x;
+                    T.y = (ok1 && !c1) ? -fabsf(T.y) : T.y;
                     if (!(c0 || c1)) continue;
                     alpha.x = c0 ? alpha.x : 0.0f;
                     alpha.y = c1 ? alpha.y : 0.0f;
@@ -202,7 +205,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                     lc1 = c1 ? pos1 : lc1;
                 }
             } else {
-                while (m != 0u && !(done0 && done1)) {
+                while (m != 0u && !(T.x < 0.0f && T.y < 0.0f)) {
                     // ILP list entries per trip.  A lone heavy tile -- one warp per scheduler at the tail of a small
                     // launch -- is bound by the latency of the per-entry chain, not by issue: the alphas (and the
                     // colour loads) of the trip's entries depend on nothing the loop carries and are computed side by
@@ -231,13 +234,11 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                     }
 #pragma unroll
                     for (int e = 0; e < ILP; ++e) {
-                        const bool live0 = !done0 && pa[e].ok0, live1 = !done1 && pa[e].ok1;
                         float2 alpha = pa[e].alpha;
                         const float2 test_T = __fmul2_rn(T, __fadd2_rn(splat(1.0f), f2(-alpha.x, -alpha.y)));
-                        const bool term0 = live0 && test_T.x < 0.0001f, term1 = live1 && test_T.y < 0.0001f;
-                        done0 = done0 || term0;
-                        done1 = done1 || term1;
-                        const bool c0 = live0 && !term0, c1 = live1 && !term1;
+                        const bool c0 = pa[e].ok0 && !(test_T.x < 0.0001f), c1 = pa[e].ok1 && !(test_T.y < 0.0001f);
+                        T.x = (pa[e].ok0 && !c0) ? -fabsf(T.x) : T.x;      // finished from here on (see the T comment)
+                        T.y = (pa[e].ok1 && !c1) ? -fabsf(T.y) : T.y;
                         // a pixel that does not blend this entry runs the same instructions with alpha = 0
                         alpha.x = c0 ? alpha.x : 0.0f;
                         alpha.y = c1 ? alpha.y : 0.0f;
@@ -261,7 +262,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
             }
         }
         // everyone is finished with `buf`; stop fetching once the whole tile is saturated
-        const int num_done = __syncthreads_count(done0 && done1);
+        const int num_done = __syncthreads_count(T.x < 0.0f && T.y < 0.0f);
         if (num_done == NT2) {
             // batch r+1 may still be in flight: the CTA must not retire under it
             if (tid == 0 && r + 1 < rounds) mbar_wait(&full[(r + 1) & 1], (uint32_t)(((r + 1) >> 1) & 1));
@@ -276,7 +277,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     for (int i = 0; i < 2; ++i) {
         if (!(i == 0 ? in0 : in1)) continue;
         const size_t pix = (size_t)(i == 0 ? py0 : py1) * W + px;
-        const float Ti = i == 0 ? T.x : T.y;
+        const float Ti = fabsf(i == 0 ? T.x : T.y);
         n_contrib[(size_t)view * HW + pix] = i == 0 ? lc0 : lc1;
         final_T[(size_t)view * HW + pix] = Ti;
 #pragma unroll
