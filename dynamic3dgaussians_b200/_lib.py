@@ -20,6 +20,8 @@ EXPORTED_SYMBOLS = [
     "gsr_image_loss_state_bytes", "gsr_image_loss_forward", "gsr_image_loss_backward", "gsr_adam_step",
     "gsr_fp32_peak_probe", "gsr_probe_geometry", "gsr_stage_timing_enable", "gsr_stage_timing_count", "gsr_stage_name",
     "gsr_stage_timing_read", "gsr_debug_blend_trace",
+    "gsr_activations_forward", "gsr_activations_backward", "gsr_cam_affine_forward", "gsr_cam_affine_backward",
+    "gsr_densify_stats",
 ]
 
 
@@ -108,6 +110,11 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.gsr_stage_timing_read.argtypes = [vp, i32]
     lib.gsr_probe_geometry.argtypes = [C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.gsr_debug_blend_trace.argtypes = [vp, vp]
+    lib.gsr_activations_forward.argtypes = [i64, vp, vp, vp, vp, vp, vp, vp]
+    lib.gsr_activations_backward.argtypes = [i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.gsr_cam_affine_forward.argtypes = [i64, vp, vp, vp, vp, vp]
+    lib.gsr_cam_affine_backward.argtypes = [i64, vp, vp, vp, vp, vp, vp, vp]
+    lib.gsr_densify_stats.argtypes = [i64, vp, vp, vp, vp, vp, vp, vp, vp]
     for name in EXPORTED_SYMBOLS:
         fn = getattr(lib, name)
         if fn.restype is C.c_int and name not in ("gsr_abi_version",):

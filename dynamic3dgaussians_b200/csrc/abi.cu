@@ -321,6 +321,46 @@ int gsr_adam_step(int n_tensors, const GsrAdamTensor* tensors_host, double beta1
     return launch_adam_step(n_tensors, tensors_host, beta1, beta2, eps, scratch, (cudaStream_t)stream);
 }
 
+// ---- training-loop glue ----
+int gsr_activations_forward(int64_t P, const float* unnorm_rotations, const float* logit_opacities,
+                            const float* log_scales, float* rotations, float* opacities, float* scales,
+                            gsr_stream_t stream) {
+    if (P < 0 || (P > 0 && (!unnorm_rotations || !logit_opacities || !log_scales || !rotations || !opacities || !scales)))
+        return GSR_ERR_INVALID_ARGUMENT;
+    return launch_activations_forward(P, unnorm_rotations, logit_opacities, log_scales, rotations, opacities, scales,
+                                      (cudaStream_t)stream);
+}
+
+int gsr_activations_backward(int64_t P, const float* unnorm_rotations, const float* opacities, const float* scales,
+                             const float* dL_drotations, const float* dL_dopacities, const float* dL_dscales,
+                             float* dL_dunnorm_rotations, float* dL_dlogit_opacities, float* dL_dlog_scales,
+                             gsr_stream_t stream) {
+    if (P < 0 || (P > 0 && (!unnorm_rotations || !opacities || !scales))) return GSR_ERR_INVALID_ARGUMENT;
+    return launch_activations_backward(P, unnorm_rotations, opacities, scales, dL_drotations, dL_dopacities, dL_dscales,
+                                       dL_dunnorm_rotations, dL_dlogit_opacities, dL_dlog_scales, (cudaStream_t)stream);
+}
+
+int gsr_cam_affine_forward(int64_t HW, const float* im, const float* cam_m3, const float* cam_c3, float* out,
+                           gsr_stream_t stream) {
+    if (HW < 0 || (HW > 0 && (!im || !cam_m3 || !cam_c3 || !out))) return GSR_ERR_INVALID_ARGUMENT;
+    return launch_cam_affine_forward(HW, im, cam_m3, cam_c3, out, (cudaStream_t)stream);
+}
+
+int gsr_cam_affine_backward(int64_t HW, const float* im, const float* cam_m3, const float* dL_dout, float* dL_dim,
+                            float* dL_dcam_m3, float* dL_dcam_c3, gsr_stream_t stream) {
+    if (HW < 0 || (HW > 0 && (!im || !cam_m3 || !dL_dout))) return GSR_ERR_INVALID_ARGUMENT;
+    return launch_cam_affine_backward(HW, im, cam_m3, dL_dout, dL_dim, dL_dcam_m3, dL_dcam_c3, (cudaStream_t)stream);
+}
+
+int gsr_densify_stats(int64_t P, const int32_t* radii, const uint8_t* seen_in, const float* means2D_grad,
+                      float* max_2D_radius, float* means2D_gradient_accum, float* denom, uint8_t* seen_out,
+                      gsr_stream_t stream) {
+    if (P < 0 || (P > 0 && ((!radii && !seen_in) || (means2D_gradient_accum && !means2D_grad))))
+        return GSR_ERR_INVALID_ARGUMENT;
+    return launch_densify_stats(P, radii, seen_in, means2D_grad, max_2D_radius, means2D_gradient_accum, denom, seen_out,
+                                (cudaStream_t)stream);
+}
+
 // ---- stand-alone sort (tests) ----
 static size_t sort_layout(int64_t n, int key_bytes, size_t off[7]) {
     size_t o = 0;

@@ -226,6 +226,17 @@ int launch_image_loss_forward(int64_t n_img, int W, int H, const float* img, con
                               void* state, float* loss_out, cudaStream_t s);
 int launch_image_loss_backward(int64_t n_img, int W, int H, const float* img, const float* tgt, float w_l1,
                                float w_ssim, const void* state, const float* grad_out, float* dL_dimg, cudaStream_t s);
+// train_glue.cu: the small per-iteration ops around the rasterizer in the training loop
+int launch_activations_forward(int64_t P, const float* unnorm_rot, const float* logit_op, const float* log_scales,
+                               float* rot, float* op, float* scales, cudaStream_t s);
+int launch_activations_backward(int64_t P, const float* unnorm_rot, const float* op, const float* scales,
+                                const float* d_rot, const float* d_op, const float* d_scales, float* d_unnorm_rot,
+                                float* d_logit, float* d_log_scales, cudaStream_t s);
+int launch_cam_affine_forward(int64_t HW, const float* im, const float* m3, const float* c3, float* out, cudaStream_t s);
+int launch_cam_affine_backward(int64_t HW, const float* im, const float* m3, const float* g, float* d_im, float* d_m3,
+                               float* d_c3, cudaStream_t s);
+int launch_densify_stats(int64_t P, const int32_t* radii, const uint8_t* seen_in, const float* grad2d,
+                         float* max_radius, float* accum, float* denom, uint8_t* seen_out, cudaStream_t s);
 int launch_adam_step(int n_tensors, const GsrAdamTensor* tensors, double beta1, double beta2, double eps, void* scratch,
                      cudaStream_t s);
 int launch_store_cams(const CamPack& pack, CamDev* dst, cudaStream_t s);

@@ -23,8 +23,14 @@ from typing import Dict, List, Optional, Sequence
 import torch
 
 from . import rasterizer as RZ
+from . import train_ops
 from .densify import accumulate_mean2d_gradient, densify, replace_param
 from .image_loss import l1_ssim_loss
+
+# The small ops around the rasterizer (activations, camera colour correction, densification statistics) run as one CUDA
+# kernel each (train_ops.py) instead of ~40 eager kernels per iteration; False keeps the eager torch ops (the comparison
+# arm of the tests).
+FUSED_GLUE = True
 
 # REF/train.py:120-129 as written has means3D 0.0000016 * scene_radius, rgb 0.000025, rotations 0.0 (the fork froze
 # most of them for its ego-camera experiments); the upstream values are the defaults here
@@ -73,31 +79,46 @@ def initialize_optimizer(params: Dict[str, torch.nn.Parameter], variables: dict,
     return torch.optim.Adam(groups, lr=0.0, eps=1e-15, capturable=True)
 
 
-def params2rendervar(params):
+def params2rendervar(params, fused: Optional[bool] = None):
     """REF/helpers.py:98-107."""
+    fused = FUSED_GLUE if fused is None else fused
+    if fused:
+        rotations, opacities, scales = train_ops.activations(params['unnorm_rotations'], params['logit_opacities'],
+                                                             params['log_scales'])
+        # the rasterizer never reads means2D (it is the handle the screen-space gradient comes back on): a fresh leaf
+        means2D = torch.zeros_like(params['means3D']).requires_grad_(True)
+    else:
+        rotations = torch.nn.functional.normalize(params['unnorm_rotations'])
+        opacities = torch.sigmoid(params['logit_opacities'])
+        scales = torch.exp(params['log_scales'])
+        means2D = torch.zeros_like(params['means3D'], requires_grad=True) + 0
     return {
         'means3D': params['means3D'],
         'colors_precomp': params['rgb_colors'],
-        'rotations': torch.nn.functional.normalize(params['unnorm_rotations']),
-        'opacities': torch.sigmoid(params['logit_opacities']),
-        'scales': torch.exp(params['log_scales']),
-        'means2D': torch.zeros_like(params['means3D'], requires_grad=True) + 0,
+        'rotations': rotations,
+        'opacities': opacities,
+        'scales': scales,
+        'means2D': means2D,
     }
 
 
 def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optional[dict] = None,
-             capacity: Optional[int] = None):
+             capacity: Optional[int] = None, fused: Optional[bool] = None):
     """REF/train.py:138-291.  curr_data: {'cam': GaussianRasterizationSettings, 'im': [3,H,W], 'seg': [3,H,W], 'id'}."""
     weights = LOSS_WEIGHTS if weights is None else weights
+    fused = FUSED_GLUE if fused is None else fused
     losses = {}
-    rv = params2rendervar(params)
+    rv = params2rendervar(params, fused)
     rv['means2D'].retain_grad()
     color, seg, depth, alpha, radii = RZ.rasterize_views(
         [curr_data['cam']], rv['means3D'], rv['opacities'], means2D=rv['means2D'], colors_precomp=rv['colors_precomp'],
         scales=rv['scales'], rotations=rv['rotations'], extra_colors=params['seg_colors'], capacity=capacity)
     im, seg, radius = color[0], seg[0], radii[0]
     cid = curr_data['id']
-    im = torch.exp(params['cam_m'][cid])[:, None, None] * im + params['cam_c'][cid][:, None, None]
+    if fused:
+        im = train_ops.cam_affine(im, params['cam_m'], params['cam_c'], cid)
+    else:
+        im = torch.exp(params['cam_m'][cid])[:, None, None] * im + params['cam_c'][cid][:, None, None]
     losses['im'] = l1_ssim_loss(im, curr_data['im'])
     variables['means2D'] = rv['means2D']                 # gradient only accumulated from this render for densification
     losses['seg'] = l1_ssim_loss(seg, curr_data['seg'])
@@ -117,11 +138,17 @@ def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optiona
                        (torch.abs(bg_rot - variables['init_bg_rot']).sum(-1)).mean()
         losses['soft_col_cons'] = (torch.abs(params['rgb_colors'] - variables['prev_col']).sum(-1)).mean()
 
-    loss = sum(weights[k] * v for k, v in losses.items())
-    seen = radius > 0
+    loss = None
+    for k, v in losses.items():
+        term = v if weights[k] == 1.0 else weights[k] * v
+        loss = term if loss is None else loss + term
     # in place (REF/train.py:288-289), so that the statistics also accumulate when the step is replayed from a CUDA graph
-    variables['max_2D_radius'].copy_(torch.where(seen, torch.maximum(radius.float(), variables['max_2D_radius']),
-                                                 variables['max_2D_radius']))
+    if fused:
+        seen = train_ops.update_max_radius(radius, variables['max_2D_radius'])
+    else:
+        seen = radius > 0
+        variables['max_2D_radius'].copy_(torch.where(seen, torch.maximum(radius.float(), variables['max_2D_radius']),
+                                                     variables['max_2D_radius']))
     variables['seen'] = seen
     return loss, variables, losses
 
@@ -236,9 +263,13 @@ class GraphedTrainer:
         return self.losses[i]
 
 
-def _accumulate_inplace(variables: dict):
+def _accumulate_inplace(variables: dict, fused: Optional[bool] = None):
     """accumulate_mean2d_gradient (REF/external.py:136-140) with in-place updates, for graph replay."""
     seen = variables['seen']
+    if FUSED_GLUE if fused is None else fused:
+        train_ops.accumulate_mean2d_gradient_(seen, variables['means2D'].grad, variables['means2D_gradient_accum'],
+                                              variables['denom'])
+        return
     norm = torch.norm(variables['means2D'].grad[:, :2], dim=-1)
     variables['means2D_gradient_accum'].add_(torch.where(seen, norm, torch.zeros_like(norm)))
     variables['denom'].add_(seen.to(variables['denom'].dtype))

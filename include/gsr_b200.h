@@ -223,6 +223,33 @@ int gsr_adam_step(int n_tensors, const GsrAdamTensor* tensors_host, double beta1
                   void* scratch, gsr_stream_t stream);
 
 /*
+ * The small per-iteration ops around the rasterizer in the train.py-shaped loop, one kernel each.
+ *   gsr_activations_*: params2rendervar, REF/helpers.py:98-107 -- rotations = F.normalize(unnorm_rotations) [P][4],
+ *     opacities = sigmoid(logit_opacities) [P], scales = exp(log_scales) [P][3]; the backward takes the cotangents of the
+ *     three outputs (any may be null = zero) and writes the gradients of the three raw parameters (any may be null).
+ *   gsr_cam_affine_*: the per-camera colour correction exp(cam_m[c])[:, None, None] * im + cam_c[c][:, None, None] of
+ *     REF/train.py:181; im / out [3][HW], cam_m3 / cam_c3 point at the camera's 3 floats.  The backward ADDS the two
+ *     per-channel reductions into dL_dcam_m3 / dL_dcam_c3 (caller zeroes them) and writes dL_dim (nullable).
+ *   gsr_densify_stats: REF/train.py:288-289 and accumulate_mean2d_gradient (REF/external.py:136-140).  seen = radii > 0
+ *     (or seen_in when radii is null); max_2D_radius = max(radii, max_2D_radius) where seen; means2D_gradient_accum +=
+ *     |means2D_grad.xy| where seen; denom += seen; every output is optional.
+ */
+int gsr_activations_forward(int64_t P, const float* unnorm_rotations, const float* logit_opacities,
+                            const float* log_scales, float* rotations, float* opacities, float* scales,
+                            gsr_stream_t stream);
+int gsr_activations_backward(int64_t P, const float* unnorm_rotations, const float* opacities, const float* scales,
+                             const float* dL_drotations, const float* dL_dopacities, const float* dL_dscales,
+                             float* dL_dunnorm_rotations, float* dL_dlogit_opacities, float* dL_dlog_scales,
+                             gsr_stream_t stream);
+int gsr_cam_affine_forward(int64_t HW, const float* im, const float* cam_m3, const float* cam_c3, float* out,
+                           gsr_stream_t stream);
+int gsr_cam_affine_backward(int64_t HW, const float* im, const float* cam_m3, const float* dL_dout, float* dL_dim,
+                            float* dL_dcam_m3, float* dL_dcam_c3, gsr_stream_t stream);
+int gsr_densify_stats(int64_t P, const int32_t* radii, const uint8_t* seen_in, const float* means2D_grad,
+                      float* max_2D_radius, float* means2D_gradient_accum, float* denom, uint8_t* seen_out,
+                      gsr_stream_t stream);
+
+/*
  * Fused local-rigidity / rotation-similarity / isometry losses over a fixed K-NN graph of F foreground Gaussians,
  * forward and (optionally) backward: replaces the eager PyTorch code of REF/train.py:253-273 (== REF/cvpr_dyn.py:304-330).
  *   pts [F][3], rot [F][4] (w,x,y,z; the normalised current rotations), prev_inv_rot [F][4] (REF/train.py:303-304),
