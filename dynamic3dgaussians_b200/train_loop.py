@@ -31,6 +31,18 @@ from .image_loss import l1_ssim_loss
 # kernel each (train_ops.py) instead of ~40 eager kernels per iteration; False keeps the eager torch ops (the comparison
 # arm of the tests).
 FUSED_GLUE = True
+# Work that does not depend on the render (the rigidity / background / colour-consistency terms of a dynamic timestep)
+# and the segmentation image loss run on a side stream next to the rasterizer / the colour image loss; autograd replays
+# the same fork in the backward, and a captured iteration keeps it as parallel graph branches.
+OVERLAP_LOSSES = True
+_SIDE_STREAMS: Dict[torch.device, torch.cuda.Stream] = {}
+
+
+def _side_stream(dev: torch.device) -> torch.cuda.Stream:
+    s = _SIDE_STREAMS.get(dev)
+    if s is None:
+        s = _SIDE_STREAMS[dev] = torch.cuda.Stream(device=dev)
+    return s
 
 # REF/train.py:120-129 as written has means3D 0.0000016 * scene_radius, rgb 0.000025, rotations 0.0 (the fork froze
 # most of them for its ego-camera experiments); the upstream values are the defaults here
@@ -103,17 +115,44 @@ def params2rendervar(params, fused: Optional[bool] = None):
 
 
 def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optional[dict] = None,
-             capacity: Optional[int] = None, fused: Optional[bool] = None):
+             capacity: Optional[int] = None, fused: Optional[bool] = None, overlap: Optional[bool] = None):
     """REF/train.py:138-291.  curr_data: {'cam': GaussianRasterizationSettings, 'im': [3,H,W], 'seg': [3,H,W], 'id'}."""
     weights = LOSS_WEIGHTS if weights is None else weights
     fused = FUSED_GLUE if fused is None else fused
     losses = {}
+    # eager iterations are bound by the host (~1 ms of Python per step): the fork's events only cost there
+    overlap = (OVERLAP_LOSSES and torch.cuda.is_current_stream_capturing()) if overlap is None else overlap
+    dev = params['means3D'].device
+    cur = torch.cuda.current_stream(dev)
+    side = _side_stream(dev) if overlap else cur
     rv = params2rendervar(params, fused)
     rv['means2D'].retain_grad()
+
+    if not is_initial_timestep:
+        from .dyn_losses import rigidity_losses
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            # index lists instead of the reference's boolean masks (REF/train.py:254-257): static shapes, no host sync,
+            # so the iteration can be captured into a CUDA graph
+            fg_idx, bg_idx = variables['fg_idx'], variables['bg_idx']
+            fg_pts = rv['means3D'].index_select(0, fg_idx)
+            fg_rot = rv['rotations'].index_select(0, fg_idx)
+            dyn = {}
+            dyn['rigid'], dyn['rot'], dyn['iso'] = rigidity_losses(fg_pts, fg_rot, variables['graph'])
+            dyn['floor'] = torch.clamp(fg_pts[:, 1], min=0).mean()
+            bg_pts = rv['means3D'].index_select(0, bg_idx)
+            bg_rot = rv['rotations'].index_select(0, bg_idx)
+            dyn['bg'] = (torch.abs(bg_pts - variables['init_bg_pts']).sum(-1)).mean() + \
+                        (torch.abs(bg_rot - variables['init_bg_rot']).sum(-1)).mean()
+            dyn['soft_col_cons'] = (torch.abs(params['rgb_colors'] - variables['prev_col']).sum(-1)).mean()
+
     color, seg, depth, alpha, radii = RZ.rasterize_views(
         [curr_data['cam']], rv['means3D'], rv['opacities'], means2D=rv['means2D'], colors_precomp=rv['colors_precomp'],
         scales=rv['scales'], rotations=rv['rotations'], extra_colors=params['seg_colors'], capacity=capacity)
     im, seg, radius = color[0], seg[0], radii[0]
+    side.wait_stream(cur)
+    with torch.cuda.stream(side):
+        loss_seg = l1_ssim_loss(seg, curr_data['seg'])
     cid = curr_data['id']
     if fused:
         im = train_ops.cam_affine(im, params['cam_m'], params['cam_c'], cid)
@@ -121,22 +160,10 @@ def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optiona
         im = torch.exp(params['cam_m'][cid])[:, None, None] * im + params['cam_c'][cid][:, None, None]
     losses['im'] = l1_ssim_loss(im, curr_data['im'])
     variables['means2D'] = rv['means2D']                 # gradient only accumulated from this render for densification
-    losses['seg'] = l1_ssim_loss(seg, curr_data['seg'])
-
+    losses['seg'] = loss_seg
     if not is_initial_timestep:
-        from .dyn_losses import rigidity_losses
-        # index lists instead of the reference's boolean masks (REF/train.py:254-257): static shapes, no host sync, so the
-        # iteration can be captured into a CUDA graph
-        fg_idx, bg_idx = variables['fg_idx'], variables['bg_idx']
-        fg_pts = rv['means3D'].index_select(0, fg_idx)
-        fg_rot = rv['rotations'].index_select(0, fg_idx)
-        losses['rigid'], losses['rot'], losses['iso'] = rigidity_losses(fg_pts, fg_rot, variables['graph'])
-        losses['floor'] = torch.clamp(fg_pts[:, 1], min=0).mean()
-        bg_pts = rv['means3D'].index_select(0, bg_idx)
-        bg_rot = rv['rotations'].index_select(0, bg_idx)
-        losses['bg'] = (torch.abs(bg_pts - variables['init_bg_pts']).sum(-1)).mean() + \
-                       (torch.abs(bg_rot - variables['init_bg_rot']).sum(-1)).mean()
-        losses['soft_col_cons'] = (torch.abs(params['rgb_colors'] - variables['prev_col']).sum(-1)).mean()
+        losses.update(dyn)
+    cur.wait_stream(side)
 
     loss = None
     for k, v in losses.items():
@@ -244,6 +271,9 @@ class GraphedTrainer:
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         pool = None
+        if hasattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch"):
+            # the side-stream branches hand gradients to AccumulateGrad nodes of the capture stream on purpose
+            torch.autograd.graph.set_warn_on_accumulate_grad_stream_mismatch(False)
         for curr in self.dataset:
             optimizer.zero_grad(set_to_none=True)
             g = torch.cuda.CUDAGraph()
