@@ -159,7 +159,8 @@ int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels,
         }
     }
     uint32_t* counters = at<uint32_t>(geom_ws, L.counters);
-    GSR_CUDA_TRY(cudaMemsetAsync(counters, 0, NUM_COUNTERS * sizeof(uint32_t), s));
+    // counters, the depth sort's histograms, look-back words and tile tickets: one memset
+    GSR_CUDA_TRY(cudaMemsetAsync(geom_ws, 0, L.geom_zero_bytes, s));
     {
         StageScope sc(ST_PREPROCESS, s);
         rc = launch_preprocess(at<CamDev>(geom_ws, L.cams), V, P, sh_coeffs, means3D, opacities, scales, rotations,
@@ -172,7 +173,7 @@ int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels,
         rc = radix_sort_pairs<uint32_t>(at<uint32_t>(geom_ws, L.dkeys0), at<uint32_t>(geom_ws, L.dkeys1),
                                         at<uint32_t>(geom_ws, L.dvals0), at<uint32_t>(geom_ws, L.dvals1), P, nullptr,
                                         0, 32, at<uint32_t>(geom_ws, L.dhist), at<uint32_t>(geom_ws, L.dlookback),
-                                        at<uint32_t>(geom_ws, L.dcounters), s, V, false);
+                                        at<uint32_t>(geom_ws, L.dcounters), s, V, false, true);
     }
     if (rc) return rc;
     {

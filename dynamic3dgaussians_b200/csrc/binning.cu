@@ -627,7 +627,8 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     const ushort4* rects = at<ushort4>(gws, L.rects);
     const bool fused_hist = L.tile_passes <= EMIT_HIST_PASSES;
     stage_begin(ST_EMIT, s);
-    if (fused_hist) GSR_CUDA_TRY(cudaMemsetAsync(at<uint32_t>(bws, L.ihist), 0, (size_t)L.tile_passes * RADIX * 4, s));
+    // instance sort histograms, tile tickets and look-back words, supertile ranges: one memset
+    GSR_CUDA_TRY(cudaMemsetAsync(bws, 0, L.binning_zero_bytes, s));
     emit_st_instances_kernel<<<nblocks, SCAN_BLOCK, 0, s>>>(
         VP, P, L.stiles_x, S, sorted_g, rects, at<uint32_t>(gws, L.block_sums), cap, at<uint32_t>(bws, L.ikeys0),
         at<uint32_t>(bws, L.ivals0), counters, fused_hist ? L.tile_passes : 0, L.tile_bits, at<uint32_t>(bws, L.ihist));
@@ -637,7 +638,8 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     int rc = radix_sort_pairs<uint32_t>(at<uint32_t>(bws, L.ikeys0), at<uint32_t>(bws, L.ikeys1),
                                         at<uint32_t>(bws, L.ivals0), at<uint32_t>(bws, L.ivals1), capacity,
                                         counters + CNT_ST_RENDERED, 0, L.tile_bits, at<uint32_t>(bws, L.ihist),
-                                        at<uint32_t>(bws, L.ilookback), counters + CNT_INST_TILE, s, 1, fused_hist);
+                                        at<uint32_t>(bws, L.ilookback), at<uint32_t>(bws, L.ihist) + MAX_PASSES * RADIX, s, 1,
+                                        fused_hist, true);
     stage_end(ST_TILE_SORT, s);
     if (rc != GSR_OK) return rc;
     const uint32_t* skeys = at<uint32_t>(bws, L.sorted_keys_in ? L.ikeys1 : L.ikeys0);
@@ -650,7 +652,6 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     const uint32_t max_chunks = (uint32_t)L.max_chunks;
     const uint32_t chunk_grid = max_chunks < 148u * 8u ? max_chunks : 148u * 8u;   // persistent CTAs, 8 per SM
     stage_begin(ST_RANGES, s);
-    GSR_CUDA_TRY(cudaMemsetAsync(st_ranges, 0, (size_t)VS * sizeof(uint2), s));
     st_ranges_kernel<<<min((cap + 255u) / 256u, 148u * 16u), 256, 0, s>>>(counters, cap, skeys, st_ranges);
     GSR_LAUNCH_CHECK();
     chunk_table_kernel<<<1, SCAN_BLOCK, 0, s>>>(VS, st_ranges, chunk_base, chunk_key, max_chunks, counters);

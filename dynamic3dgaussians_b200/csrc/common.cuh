@@ -78,6 +78,8 @@ inline int ceil_log2(uint32_t n) {  // smallest b with (1<<b) >= n, at least 1
 
 struct Layout : GsrLayout {
     size_t geom_bytes, binning_bytes, image_bytes;
+    // every array that must be zero when a forward starts sits at the head of its workspace: one memset per workspace
+    size_t geom_zero_bytes, binning_zero_bytes;
 };
 
 inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
@@ -105,6 +107,10 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes); return r; };
     // geom
     L.counters = take(NUM_COUNTERS * sizeof(uint32_t));   // always at offset 0 (gsr_read_counters relies on it)
+    L.dhist = take((size_t)V * MAX_PASSES * RADIX * 4);
+    L.dlookback = take((size_t)MAX_PASSES * V * (sort_num_tiles((int64_t)P, 4) + 1) * RADIX * 4);
+    L.dcounters = take((size_t)MAX_PASSES * V * 4);
+    L.geom_zero_bytes = o;                // counters + the depth sort's histograms / look-back words / tile tickets
     L.cams = take((size_t)V * sizeof(CamDev));
     L.radii = take(VP * 4);
     L.rects = take(VP * 8);               // ushort4 tile rectangle (min.x, min.y, max.x, max.y), all zero when culled
@@ -118,9 +124,6 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     L.dkeys1 = take(VP * 4);
     L.dvals0 = take(VP * 4);
     L.dvals1 = take(VP * 4);
-    L.dhist = take((size_t)V * MAX_PASSES * RADIX * 4);
-    L.dlookback = take((size_t)MAX_PASSES * V * (sort_num_tiles((int64_t)P, 4) + 1) * RADIX * 4);
-    L.dcounters = take((size_t)MAX_PASSES * V * 4);
     L.block_sums = take(((VP + SCAN_TILE - 1) / SCAN_TILE + 2) * 4);
     L.grad_rec = take(VP * grad_rec_stride(channels) * 4);
     L.geom_bytes = o;
@@ -129,14 +132,15 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     const size_t cap = (size_t)(capacity > 0 ? capacity : 0);
     const size_t max_chunks = cap / CHUNK + VS + 1;
     L.max_chunks = (int32_t)max_chunks;
+    L.ihist = take(((size_t)MAX_PASSES * RADIX + MAX_PASSES) * 4);      // + the instance sort's tile tickets
+    L.ilookback = take((size_t)L.tile_passes * (sort_num_tiles((int64_t)cap, 4) + 1) * RADIX * 4);
+    L.st_ranges = take(VS * 8);
+    L.binning_zero_bytes = o;             // instance sort histograms / look-back words, supertile ranges
     L.ikeys0 = take(cap * 4);             // supertile instances: at most one per (Gaussian, tile) instance
     L.ikeys1 = take(cap * 4);
     L.ivals0 = take(cap * 4);
     L.ivals1 = take(cap * 4);
     L.imasks = take(cap * 2);             // 16-bit tile hit mask of every sorted supertile instance
-    L.ihist = take((size_t)MAX_PASSES * RADIX * 4);
-    L.ilookback = take((size_t)MAX_PASSES * (sort_num_tiles((int64_t)cap, 4) + 1) * RADIX * 4);
-    L.st_ranges = take(VS * 8);
     L.chunk_base = take((VS + 1) * 4);
     L.chunk_key = take(max_chunks * 4);
     L.chunk_counts = take(max_chunks * ST_TILES * 4);
@@ -194,7 +198,8 @@ int launch_mark_visible(const float* view, int P, const float* means3D, uint8_t*
 template <typename KeyT>
 int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1, int64_t n_max,
                      const uint32_t* n_dev, int begin_bit, int end_bit, uint32_t* hist, uint32_t* lookback,
-                     uint32_t* tile_counters, cudaStream_t s, int segments = 1, bool hist_ready = false);
+                     uint32_t* tile_counters, cudaStream_t s, int segments = 1, bool hist_ready = false,
+                     bool scratch_zeroed = false);   // scratch_zeroed: hist / lookback / tile_counters are already 0
 
 int launch_tile_scan(int V, int P, void* geom_ws, const Layout& L, cudaStream_t s);
 int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,

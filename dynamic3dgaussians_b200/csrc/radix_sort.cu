@@ -290,7 +290,7 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
 template <typename KeyT>
 int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1, int64_t n_max,
                      const uint32_t* n_dev, int begin_bit, int end_bit, uint32_t* hist, uint32_t* lookback,
-                     uint32_t* tile_counters, cudaStream_t s, int segments, bool hist_ready) {
+                     uint32_t* tile_counters, cudaStream_t s, int segments, bool hist_ready, bool scratch_zeroed) {
     if (n_max <= 0 || end_bit <= begin_bit || segments <= 0) return GSR_OK;
     if (n_max >= (int64_t)VALUE_MASK) return GSR_ERR_UNSUPPORTED;
     if (segments > 1 && n_dev != nullptr) return GSR_ERR_INVALID_ARGUMENT;
@@ -301,9 +301,11 @@ int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1,
     const int tiles = (int)((n_max + TILE - 1) / TILE);
     const size_t hist_seg = (size_t)passes * RADIX;
     const size_t lb_seg = (size_t)tiles * RADIX;
-    if (!hist_ready) GSR_CUDA_TRY(cudaMemsetAsync(hist, 0, (size_t)segments * hist_seg * 4, s));
-    GSR_CUDA_TRY(cudaMemsetAsync(lookback, 0, (size_t)passes * segments * lb_seg * 4, s));
-    GSR_CUDA_TRY(cudaMemsetAsync(tile_counters, 0, (size_t)passes * segments * 4, s));
+    if (!scratch_zeroed) {
+        if (!hist_ready) GSR_CUDA_TRY(cudaMemsetAsync(hist, 0, (size_t)segments * hist_seg * 4, s));
+        GSR_CUDA_TRY(cudaMemsetAsync(lookback, 0, (size_t)passes * segments * lb_seg * 4, s));
+        GSR_CUDA_TRY(cudaMemsetAsync(tile_counters, 0, (size_t)passes * segments * 4, s));
+    }
     if (!hist_ready) {
         const int64_t rows = (n_max + 31) / 32;
         const int64_t hb = (rows + HIST_ROWS_PER_BLOCK - 1) / HIST_ROWS_PER_BLOCK;
@@ -338,8 +340,8 @@ int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1,
 }
 
 template int radix_sort_pairs<uint32_t>(uint32_t*, uint32_t*, uint32_t*, uint32_t*, int64_t, const uint32_t*, int, int,
-                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t, int, bool);
+                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t, int, bool, bool);
 template int radix_sort_pairs<uint64_t>(uint64_t*, uint64_t*, uint32_t*, uint32_t*, int64_t, const uint32_t*, int, int,
-                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t, int, bool);
+                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t, int, bool, bool);
 
 }  // namespace gsr

@@ -18,6 +18,7 @@ weights REF/train.py:284-285; open3d / wandb dependencies), so the loss weights 
 upstream Dynamic3DGaussians values the fork was derived from and can be overridden."""
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Optional, Sequence
 
 import torch
@@ -31,10 +32,11 @@ from .image_loss import l1_ssim_loss
 # kernel each (train_ops.py) instead of ~40 eager kernels per iteration; False keeps the eager torch ops (the comparison
 # arm of the tests).
 FUSED_GLUE = True
-# Work that does not depend on the render (the rigidity / background / colour-consistency terms of a dynamic timestep)
-# and the segmentation image loss run on a side stream next to the rasterizer / the colour image loss; autograd replays
-# the same fork in the backward, and a captured iteration keeps it as parallel graph branches.
-OVERLAP_LOSSES = True
+# The segmentation image loss runs on a side stream next to the colour correction and the colour image loss; autograd
+# replays the same fork in the backward, and a captured iteration keeps it as parallel graph branches (+2 % it/s).
+# Forking the render-independent terms of a dynamic timestep (rigidity / background / colour consistency) the same
+# way measured 2-3 % SLOWER than leaving them in line before the render, so they stay on the main stream.
+OVERLAP_LOSSES = os.environ.get("GSR_OVERLAP_LOSSES", "1") != "0"
 _SIDE_STREAMS: Dict[torch.device, torch.cuda.Stream] = {}
 
 
@@ -121,7 +123,7 @@ def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optiona
     fused = FUSED_GLUE if fused is None else fused
     losses = {}
     # eager iterations are bound by the host (~1 ms of Python per step): the fork's events only cost there
-    overlap = (OVERLAP_LOSSES and torch.cuda.is_current_stream_capturing()) if overlap is None else overlap
+    overlap = False if overlap is None else overlap       # GraphedTrainer asks for it (OVERLAP_LOSSES)
     dev = params['means3D'].device
     cur = torch.cuda.current_stream(dev)
     side = _side_stream(dev) if overlap else cur
@@ -130,8 +132,7 @@ def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optiona
 
     if not is_initial_timestep:
         from .dyn_losses import rigidity_losses
-        side.wait_stream(cur)
-        with torch.cuda.stream(side):
+        with torch.cuda.stream(cur):
             # index lists instead of the reference's boolean masks (REF/train.py:254-257): static shapes, no host sync,
             # so the iteration can be captured into a CUDA graph
             fg_idx, bg_idx = variables['fg_idx'], variables['bg_idx']
@@ -254,7 +255,8 @@ class GraphedTrainer:
         self.order: List[int] = []
 
         def iteration(curr):
-            loss, _, _ = get_loss(params, curr, variables, is_initial_timestep, weights, capacity)
+            loss, _, _ = get_loss(params, curr, variables, is_initial_timestep, weights, capacity,
+                                  overlap=OVERLAP_LOSSES)
             loss.backward()
             with torch.no_grad():
                 if accumulate_stats and is_initial_timestep:
