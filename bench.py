@@ -374,7 +374,7 @@ def run_e2e(args, res, world, rank):
     parameter slab and the ranks all-gather it over NVLink (8 processes uploading the same 16.8 MB and downloading the
     same gradients measured 23 / 12 GB/s per rank, the host side of the box being shared), and rank r reads slice r of
     the all-reduced gradient slab back."""
-    from dynamic3dgaussians_b200 import dist as D, rasterizer as RZ
+    from dynamic3dgaussians_b200 import dist as D, rasterizer as RZ, train_ops as TO
     dev, sets, sc = res["dev"], res["sets"], res["sc"]
     parts = res["parts"]
     mine = parts[rank]
@@ -388,6 +388,7 @@ def run_e2e(args, res, world, rank):
             r0, r1 = (0, IMG_H) if b is None else (b[0] * 16, min(b[1] * 16, IMG_H))
             row_mask[i, :, r0:r1] = 1.0
         row_mask *= 1.0 / (3 * IMG_W * row_mask.sum())
+    row_weight = None if row_mask is None else row_mask.reshape(len(mine), IMG_H).contiguous()
     rv_host = sc.rendervar()
     P = rv_host["means3D"].shape[0]
     names = ("means3D", "colors_precomp", "opacities", "scales", "rotations")
@@ -439,10 +440,9 @@ def run_e2e(args, res, world, rank):
         color, _, depth, alpha, radii = RZ.rasterize_views(my_sets, m, o, colors_precomp=c, scales=s, rotations=r,
                                                            capacity=cap_e2e, state_out=states, bands=my_bands)
         del states[:-1]
-        if row_mask is None:
-            loss = (color - b["tgt"].float() * (1.0 / 255.0)).abs().mean()
-        else:
-            loss = ((color - b["tgt"].float() * (1.0 / 255.0)).abs() * row_mask).sum()
+        # mean |color - target / 255| straight from the uint8 frames (one fused kernel each way; with bands, weighted by
+        # the rows this rank owns)
+        loss = TO.l1_loss_u8(color, b["tgt"], row_weight)
         loss.backward()
         torch.cat([t.grad.reshape(-1) for t in b["leaves"]], out=b["grad"][:n_par])
         D.allreduce_grads(b["grad"])

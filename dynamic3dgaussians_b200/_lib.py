@@ -21,7 +21,7 @@ EXPORTED_SYMBOLS = [
     "gsr_fp32_peak_probe", "gsr_probe_geometry", "gsr_stage_timing_enable", "gsr_stage_timing_count", "gsr_stage_name",
     "gsr_stage_timing_read", "gsr_debug_blend_trace",
     "gsr_activations_forward", "gsr_activations_backward", "gsr_cam_affine_forward", "gsr_cam_affine_backward",
-    "gsr_densify_stats",
+    "gsr_densify_stats", "gsr_l1_u8_loss_forward", "gsr_l1_u8_loss_backward",
 ]
 
 
@@ -115,6 +115,8 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.gsr_cam_affine_forward.argtypes = [i64, vp, vp, vp, vp, vp]
     lib.gsr_cam_affine_backward.argtypes = [i64, vp, vp, vp, vp, vp, vp, vp]
     lib.gsr_densify_stats.argtypes = [i64, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.gsr_l1_u8_loss_forward.argtypes = [i64, i32, i32, vp, vp, vp, C.c_float, vp, vp]
+    lib.gsr_l1_u8_loss_backward.argtypes = [i64, i32, i32, vp, vp, vp, C.c_float, vp, vp, vp]
     for name in EXPORTED_SYMBOLS:
         fn = getattr(lib, name)
         if fn.restype is C.c_int and name not in ("gsr_abi_version",):

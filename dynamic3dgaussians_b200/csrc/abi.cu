@@ -362,6 +362,22 @@ int gsr_densify_stats(int64_t P, const int32_t* radii, const uint8_t* seen_in, c
                                 (cudaStream_t)stream);
 }
 
+int gsr_l1_u8_loss_forward(int64_t n_views, int W, int H, const float* img, const uint8_t* target,
+                           const float* row_weight, float weight, float* loss_out, gsr_stream_t stream) {
+    if (n_views < 0 || W <= 0 || H <= 0 || !loss_out || (n_views > 0 && (!img || !target)))
+        return GSR_ERR_INVALID_ARGUMENT;
+    return launch_l1_u8_forward(n_views, W, H, img, target, row_weight, weight, loss_out, (cudaStream_t)stream);
+}
+
+int gsr_l1_u8_loss_backward(int64_t n_views, int W, int H, const float* img, const uint8_t* target,
+                            const float* row_weight, float weight, const float* grad_out, float* dL_dimg,
+                            gsr_stream_t stream) {
+    if (n_views < 0 || W <= 0 || H <= 0 || (n_views > 0 && (!img || !target || !dL_dimg)))
+        return GSR_ERR_INVALID_ARGUMENT;
+    return launch_l1_u8_backward(n_views, W, H, img, target, row_weight, weight, grad_out, dL_dimg,
+                                 (cudaStream_t)stream);
+}
+
 // ---- stand-alone sort (tests) ----
 static size_t sort_layout(int64_t n, int key_bytes, size_t off[7]) {
     size_t o = 0;

@@ -240,6 +240,10 @@ int launch_activations_backward(int64_t P, const float* unnorm_rot, const float*
 int launch_cam_affine_forward(int64_t HW, const float* im, const float* m3, const float* c3, float* out, cudaStream_t s);
 int launch_cam_affine_backward(int64_t HW, const float* im, const float* m3, const float* g, float* d_im, float* d_m3,
                                float* d_c3, cudaStream_t s);
+int launch_l1_u8_forward(int64_t n_views, int W, int H, const float* img, const uint8_t* tgt, const float* row_weight,
+                         float w_const, float* loss, cudaStream_t s);
+int launch_l1_u8_backward(int64_t n_views, int W, int H, const float* img, const uint8_t* tgt, const float* row_weight,
+                          float w_const, const float* g, float* d_img, cudaStream_t s);
 int launch_densify_stats(int64_t P, const int32_t* radii, const uint8_t* seen_in, const float* grad2d,
                          float* max_radius, float* accum, float* denom, uint8_t* seen_out, cudaStream_t s);
 int launch_adam_step(int n_tensors, const GsrAdamTensor* tensors, double beta1, double beta2, double eps, void* scratch,

@@ -131,6 +131,77 @@ densify_stats_kernel(int64_t P, const int32_t* __restrict__ radii, const uint8_t
     if (denom && seen) denom[i] += 1.0f;
 }
 
+// L1 image loss against 8-bit targets: sum_i w_i |x_i - t_i / 255| with w_i = row_weight[view][y] (or a constant), the
+// loss a training input pipeline feeds straight from uint8 frames (the reference converts its PNGs to float tensors on
+// the host, REF/train.py:33-43, and takes l1_loss_v1).  One pass for the value, one for the gradient; 4 pixels per
+// thread (W % 4 == 0) or 1.
+constexpr int L1_ITEMS = 4;
+// x - t / 255 with torch's two roundings (t * (1 / 255), then the subtraction): no FMA contraction, so that a pixel
+// that equals its target gives exactly 0 and sign(0) = 0
+__device__ __forceinline__ float diff255(float x, uint8_t t) { return __fsub_rn(x, __fmul_rn((float)t, 1.0f / 255.0f)); }
+template <bool VEC>
+__global__ void __launch_bounds__(GLUE_BLOCK)
+l1_u8_forward_kernel(int64_t n, int W, int H, const float* __restrict__ img, const uint8_t* __restrict__ tgt,
+                     const float* __restrict__ row_weight, float w_const, float* __restrict__ loss) {
+    __shared__ float s_part[GLUE_BLOCK / 32];
+    const int64_t HW = (int64_t)W * H;
+    float acc = 0.0f;
+    const int64_t i0 = ((int64_t)blockIdx.x * GLUE_BLOCK + threadIdx.x) * (VEC ? L1_ITEMS : 1);
+    if (i0 < n) {
+        float w = w_const;
+        if (row_weight) {
+            const int64_t plane = i0 / HW;
+            w = row_weight[(plane / 3) * H + (i0 - plane * HW) / W];
+        }
+        if (VEC) {
+            const float4 x = *reinterpret_cast<const float4*>(img + i0);
+            const uchar4 t = *reinterpret_cast<const uchar4*>(tgt + i0);
+            acc = fabsf(diff255(x.x, t.x)) + fabsf(diff255(x.y, t.y)) +
+                  fabsf(diff255(x.z, t.z)) + fabsf(diff255(x.w, t.w));
+        } else {
+            acc = fabsf(diff255(img[i0], tgt[i0]));
+        }
+        acc *= w;
+    }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.0f;
+#pragma unroll
+        for (int k = 0; k < GLUE_BLOCK / 32; ++k) t += s_part[k];
+        atomicAdd(loss, t);
+    }
+}
+
+__device__ __forceinline__ float sgn(float d) { return d > 0.0f ? 1.0f : (d < 0.0f ? -1.0f : 0.0f); }
+
+template <bool VEC>
+__global__ void __launch_bounds__(GLUE_BLOCK)
+l1_u8_backward_kernel(int64_t n, int W, int H, const float* __restrict__ img, const uint8_t* __restrict__ tgt,
+                      const float* __restrict__ row_weight, float w_const, const float* __restrict__ g,
+                      float* __restrict__ d_img) {
+    const int64_t HW = (int64_t)W * H;
+    const int64_t i0 = ((int64_t)blockIdx.x * GLUE_BLOCK + threadIdx.x) * (VEC ? L1_ITEMS : 1);
+    if (i0 >= n) return;
+    float w = w_const;
+    if (row_weight) {
+        const int64_t plane = i0 / HW;
+        w = row_weight[(plane / 3) * H + (i0 - plane * HW) / W];
+    }
+    w *= g ? g[0] : 1.0f;
+    if (VEC) {
+        const float4 x = *reinterpret_cast<const float4*>(img + i0);
+        const uchar4 t = *reinterpret_cast<const uchar4*>(tgt + i0);
+        *reinterpret_cast<float4*>(d_img + i0) =
+            make_float4(w * sgn(diff255(x.x, t.x)), w * sgn(diff255(x.y, t.y)),
+                        w * sgn(diff255(x.z, t.z)), w * sgn(diff255(x.w, t.w)));
+    } else {
+        d_img[i0] = w * sgn(diff255(img[i0], tgt[i0]));
+    }
+}
+
 }  // namespace
 
 int launch_activations_forward(int64_t P, const float* unnorm_rot, const float* logit_op, const float* log_scales,
@@ -177,6 +248,39 @@ int launch_densify_stats(int64_t P, const int32_t* radii, const uint8_t* seen_in
     if (P == 0) return GSR_OK;
     densify_stats_kernel<<<(unsigned)((P + GLUE_BLOCK - 1) / GLUE_BLOCK), GLUE_BLOCK, 0, s>>>(
         P, radii, seen_in, grad2d, max_radius, accum, denom, seen_out);
+    GSR_LAUNCH_CHECK();
+    return GSR_OK;
+}
+
+int launch_l1_u8_forward(int64_t n_views, int W, int H, const float* img, const uint8_t* tgt, const float* row_weight,
+                         float w_const, float* loss, cudaStream_t s) {
+    GSR_CUDA_TRY(cudaMemsetAsync(loss, 0, sizeof(float), s));
+    const int64_t n = n_views * 3 * (int64_t)W * H;
+    if (n == 0) return GSR_OK;
+    if (W % 4 == 0) {
+        const int64_t per = (int64_t)GLUE_BLOCK * L1_ITEMS;
+        l1_u8_forward_kernel<true><<<(unsigned)((n + per - 1) / per), GLUE_BLOCK, 0, s>>>(n, W, H, img, tgt, row_weight,
+                                                                                        w_const, loss);
+    } else {
+        l1_u8_forward_kernel<false><<<(unsigned)((n + GLUE_BLOCK - 1) / GLUE_BLOCK), GLUE_BLOCK, 0, s>>>(
+            n, W, H, img, tgt, row_weight, w_const, loss);
+    }
+    GSR_LAUNCH_CHECK();
+    return GSR_OK;
+}
+
+int launch_l1_u8_backward(int64_t n_views, int W, int H, const float* img, const uint8_t* tgt, const float* row_weight,
+                          float w_const, const float* g, float* d_img, cudaStream_t s) {
+    const int64_t n = n_views * 3 * (int64_t)W * H;
+    if (n == 0) return GSR_OK;
+    if (W % 4 == 0) {
+        const int64_t per = (int64_t)GLUE_BLOCK * L1_ITEMS;
+        l1_u8_backward_kernel<true><<<(unsigned)((n + per - 1) / per), GLUE_BLOCK, 0, s>>>(n, W, H, img, tgt, row_weight,
+                                                                                         w_const, g, d_img);
+    } else {
+        l1_u8_backward_kernel<false><<<(unsigned)((n + GLUE_BLOCK - 1) / GLUE_BLOCK), GLUE_BLOCK, 0, s>>>(
+            n, W, H, img, tgt, row_weight, w_const, g, d_img);
+    }
     GSR_LAUNCH_CHECK();
     return GSR_OK;
 }

@@ -136,3 +136,46 @@ def accumulate_mean2d_gradient_(seen: torch.Tensor, means2D_grad: torch.Tensor, 
         _lib.check(_lib.load().gsr_densify_stats(P, None, seen.contiguous().data_ptr(), g.data_ptr(), None,
                                                  _f32(accum, "accum").data_ptr(), _f32(denom, "denom").data_ptr(), None,
                                                  _stream(seen.device)), "densify_stats")
+
+
+class _L1U8(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, img, target, row_weight):
+        img = _f32(img, "img")
+        if not target.is_cuda or target.dtype != torch.uint8 or target.shape != img.shape:
+            raise ValueError("target must be a uint8 CUDA tensor of img's shape")
+        if img.dim() != 4 or img.shape[1] != 3:
+            raise ValueError("expected img [V,3,H,W]")
+        V, _, H, W = img.shape
+        target = target.contiguous()
+        if row_weight is not None:
+            row_weight = _f32(row_weight, "row_weight")
+            if row_weight.numel() != V * H:
+                raise ValueError("row_weight must be [V,H]")
+        weight = 1.0 / max(img.numel(), 1)
+        loss = torch.empty((), dtype=torch.float32, device=img.device)
+        with torch.cuda.device(img.device):
+            _lib.check(_lib.load().gsr_l1_u8_loss_forward(V, W, H, img.data_ptr(), target.data_ptr(), _ptr(row_weight),
+                                                          weight, loss.data_ptr(), _stream(img.device)), "l1_u8_forward")
+        ctx.save_for_backward(img, target, row_weight)
+        ctx.weight = weight
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        img, target, row_weight = ctx.saved_tensors
+        V, _, H, W = img.shape
+        g = _f32(g, "dL/dloss").reshape(1)
+        d_img = torch.empty_like(img)
+        with torch.cuda.device(img.device):
+            _lib.check(_lib.load().gsr_l1_u8_loss_backward(V, W, H, img.data_ptr(), target.data_ptr(), _ptr(row_weight),
+                                                           ctx.weight, g.data_ptr(), d_img.data_ptr(),
+                                                           _stream(img.device)), "l1_u8_backward")
+        return d_img, None, None
+
+
+def l1_loss_u8(img: torch.Tensor, target_u8: torch.Tensor, row_weight: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """mean |img - target / 255| over [V,3,H,W] against uint8 frames (l1_loss_v1, REF/helpers.py), or
+    sum row_weight[v, y] * |.| when per-(view, row) weights are given -- one kernel forward, one backward, no float copy
+    of the targets."""
+    return _L1U8.apply(img, target_u8, row_weight)

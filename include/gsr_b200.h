@@ -234,6 +234,17 @@ int gsr_adam_step(int n_tensors, const GsrAdamTensor* tensors_host, double beta1
  *     (or seen_in when radii is null); max_2D_radius = max(radii, max_2D_radius) where seen; means2D_gradient_accum +=
  *     |means2D_grad.xy| where seen; denom += seen; every output is optional.
  */
+/*
+ * L1 image loss against 8-bit target frames: loss = sum_i w_i |img_i - target_i / 255| over [n_views][3][H][W], with
+ * w_i = row_weight[view][y] ([n_views][H], e.g. the rows of a view a rank owns, pre-normalised) or the constant `weight`
+ * (1 / N for the mean, l1_loss_v1 of REF/helpers.py) when row_weight is null.  loss_out: one device float (written).
+ * Backward: dL_dimg = grad_out[0] (device scalar, null = 1) * w_i * sign(img_i - target_i / 255).
+ */
+int gsr_l1_u8_loss_forward(int64_t n_views, int W, int H, const float* img, const uint8_t* target,
+                           const float* row_weight, float weight, float* loss_out, gsr_stream_t stream);
+int gsr_l1_u8_loss_backward(int64_t n_views, int W, int H, const float* img, const uint8_t* target,
+                            const float* row_weight, float weight, const float* grad_out, float* dL_dimg,
+                            gsr_stream_t stream);
 int gsr_activations_forward(int64_t P, const float* unnorm_rotations, const float* logit_opacities,
                             const float* log_scales, float* rotations, float* opacities, float* scales,
                             gsr_stream_t stream);

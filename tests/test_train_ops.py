@@ -21,6 +21,8 @@ def test_no_cpu_path():
         TO.cam_affine(torch.zeros(3, 8, 8), torch.zeros(2, 3), torch.zeros(2, 3), 0)
     with pytest.raises(ValueError):
         TO.update_max_radius(torch.zeros(4, dtype=torch.int32), torch.zeros(4))
+    with pytest.raises(ValueError):
+        TO.l1_loss_u8(torch.zeros(1, 3, 8, 8), torch.zeros(1, 3, 8, 8, dtype=torch.uint8))
 
 
 @pytest.mark.gpu
@@ -127,3 +129,27 @@ def test_get_loss_fused_glue_matches_eager_glue():
             assert torch.equal(x, y)
         else:
             assert rel_err(x, y) <= 1e-4          # the rasterizer backward's atomics
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("W", [64, 61])          # 4 pixels per thread, and the scalar path
+def test_l1_loss_u8_matches_torch(W):
+    from dynamic3dgaussians_b200 import train_ops as TO
+    g = torch.Generator().manual_seed(6)
+    V, H = 3, 37
+    img = torch.rand(V, 3, H, W, generator=g).cuda()
+    tgt = torch.randint(0, 256, (V, 3, H, W), dtype=torch.uint8, generator=g).cuda()
+    img[0, 0, 0, :4] = tgt[0, 0, 0, :4].float() * (1.0 / 255.0)  # sign(0) = 0
+    rw = torch.rand(V, H, generator=g).cuda()
+    rw[1, 5:] = 0.0
+    rw /= rw.sum() * 3 * W
+    for weights in (None, rw):
+        a = img.clone().requires_grad_(True)
+        b = img.clone().requires_grad_(True)
+        la = TO.l1_loss_u8(a, tgt, weights)
+        d = (b - tgt.float() * (1.0 / 255.0)).abs()
+        lb = d.mean() if weights is None else (d * weights[:, None, :, None]).sum()
+        (2.5 * la).backward()
+        (2.5 * lb).backward()
+        assert abs(float(la.detach()) - float(lb.detach())) <= 2e-6 * abs(float(lb.detach()))
+        assert rel_err(a.grad, b.grad) <= 1e-6
