@@ -30,6 +30,7 @@ __device__ __forceinline__ unsigned trace_smid() { unsigned r; asm volatile("mov
 
 constexpr int BATCH = 128;
 constexpr int SUB = 32;
+constexpr int RING = 3;                  // staged batches in flight per CTA
 constexpr unsigned FULL = 0xffffffffu;
 
 // CTA = 128 threads = 4 warps; a warp owns an 8x8 pixel patch, a lane the two pixels (x, y) and (x, y + 4) of it, so
@@ -68,11 +69,14 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     struct __align__(128) Stage {
         float4 a[BATCH], b[BATCH], c[BATCH], d[EXTRA ? BATCH : 1];
     };
-    __shared__ Stage stage[2];
-    __shared__ __align__(8) uint64_t full[2];
-    __shared__ uint32_t s_wmask[NW2][BATCH / SUB];
+    // The four warps of the CTA walk the ring on their own: each builds the work list of its patch from the staged
+    // batch, and the last warp out of a ring slot (an atomic count) refills it.  No CTA barrier inside the walk --
+    // with a barrier per batch the warps of a tile waited for the one with the longest work list every 128 entries
+    // (ncu: barrier was the largest stall reason).
+    __shared__ Stage stage[RING];
+    __shared__ __align__(8) uint64_t full[RING];
+    __shared__ uint32_t s_done[RING];
     __shared__ uint32_t s_max;
-    static_assert(BATCH % NT2 == 0, "pre-pass: BATCH / NT2 staged Gaussians per thread");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int vt = (int)tile_order[blockIdx.x];
@@ -96,8 +100,11 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 
     if (tid == 0) {
         s_max = 0;
-        mbar_init(&full[0], 1);
-        mbar_init(&full[1], 1);
+#pragma unroll
+        for (int i = 0; i < RING; ++i) {
+            mbar_init(&full[i], 1);
+            s_done[i] = 0;
+        }
         mbar_fence_init();
     }
     __syncthreads();
@@ -111,8 +118,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         return;
     }
 
-    auto issue = [&](int r) {   // thread 0 only; round r walks chunk (rounds-1-r)
-        const int buf = r & 1;
+    auto issue = [&](int r) {   // one thread; round r walks chunk (rounds-1-r)
+        const int buf = r % RING;
         const int c = rounds - 1 - r;
         const int nb = min(BATCH, n_proc - c * BATCH);
         const uint32_t bytes = (uint32_t)nb * 16u;
@@ -124,8 +131,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         if (EXTRA) tma_load_1d(stage[buf].d, recD + src, bytes, &full[buf]);
     };
     if (tid == 0) {
-        issue(0);
-        if (rounds > 1) issue(1);
+        for (int r = 0; r < RING && r < rounds; ++r) issue(r);
     }
 
     // pixel cotangents (x: first pixel, y: second)
@@ -162,35 +168,31 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     const int my_slot = PackedReduce<K>::slot(lane);
     const unsigned slot_peers = __match_any_sync(FULL, my_slot);
     const bool writer = lane == (__ffs(slot_peers) - 1);
-    const float tile_x0 = (float)(tile_xi * TILE_X), tile_y0 = (float)(tile_yi * TILE_Y);
+    const float patch_x0 = (float)(tile_xi * TILE_X + (warp & 1) * 8), patch_y0 = (float)(tile_yi * TILE_Y + (warp >> 1) * 8);
 
     for (int r = 0; r < rounds; ++r) {
-        const int buf = r & 1;
+        const int buf = r % RING;
         const int c = rounds - 1 - r;
         const int nb = min(BATCH, n_proc - c * BATCH);
         const int rel0 = (int)lc0 - c * BATCH, rel1 = (int)lc1 - c * BATCH;   // list position < n_contrib  <=>  j < rel
-        mbar_wait(&full[buf], (uint32_t)((r >> 1) & 1));
-        {   // pre-pass: per-warp work lists, Gaussian `tid` x the four 8x8 patches
+        mbar_wait(&full[buf], (uint32_t)((r / RING) & 1));
+        // pre-pass: this warp's work list, 32 staged Gaussians per ballot against its 8x8 patch
+        uint32_t wm[BATCH / SUB];
 #pragma unroll
-            for (int g0 = 0; g0 < BATCH; g0 += NT2) {
-                const int g = g0 + tid;
-                uint32_t m4 = 0u;
-                if (g < nb) {
-                    const float4 a = stage[buf].a[g];
-                    const float4 b = stage[buf].b[g];
-                    m4 = blend_patch_mask4(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
-                }
-#pragma unroll
-                for (int w = 0; w < NW2; ++w) {
-                    const uint32_t bal = __ballot_sync(FULL, (m4 >> w) & 1u);
-                    if (lane == 0) s_wmask[w][g0 / 32 + warp] = bal;
-                }
+        for (int sb = 0; sb < BATCH / SUB; ++sb) {
+            const int g = sb * SUB + lane;
+            bool hit = false;
+            if (g < nb && (uint32_t)(c * BATCH + sb * SUB) < warp_last) {
+                const float4 a = stage[buf].a[g];
+                const float4 b = stage[buf].b[g];
+                hit = blend_patch_hit(a.x, a.y, a.z, a.w, b.x, b.w, patch_x0, patch_y0);
             }
+            wm[sb] = __ballot_sync(FULL, hit);
         }
-        __syncthreads();
-        for (int sub = (nb - 1) / SUB; sub >= 0; --sub) {
+#pragma unroll
+        for (int sub = BATCH / SUB - 1; sub >= 0; --sub) {
             const int lo = sub * SUB;
-            uint32_t m = s_wmask[warp][sub];
+            uint32_t m = wm[sub];
             {
                 const uint32_t base = (uint32_t)(c * BATCH + lo);
                 if (warp_last <= base) m = 0u;
@@ -260,8 +262,16 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 red_add_if(writer, grad_rec + (size_t)__float_as_uint(col.w) * grad_rec_stride(NCH) + my_slot, v[0]);
             }
         }
-        __syncthreads();        // every warp is done with `buf`
-        if (tid == 0 && r + 2 < rounds) issue(r + 2);
+        // done with this ring slot; the last of the four warps to say so refills it
+        __syncwarp();
+        if (lane == 0) {
+            __threadfence_block();
+            if (atomicAdd(&s_done[buf], 1u) == NW2 - 1) {
+                s_done[buf] = 0;
+                __threadfence_block();
+                if (r + RING < rounds) issue(r + RING);
+            }
+        }
     }
     if (trace && lane == 0) atomicMax(&trace[4 * blockIdx.x + 1], trace_now());
 }
