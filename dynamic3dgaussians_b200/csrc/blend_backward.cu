@@ -30,7 +30,10 @@ __device__ __forceinline__ unsigned trace_smid() { unsigned r; asm volatile("mov
 
 constexpr int BATCH = 128;
 constexpr int SUB = 32;
-constexpr int RING = 3;                  // staged batches in flight per CTA
+#ifndef GSR_BWD_RING
+#define GSR_BWD_RING 3
+#endif
+constexpr int RING = GSR_BWD_RING;                  // staged batches in flight per CTA
 constexpr unsigned FULL = 0xffffffffu;
 
 // CTA = 128 threads = 4 warps; a warp owns an 8x8 pixel patch, a lane the two pixels (x, y) and (x, y + 4) of it, so

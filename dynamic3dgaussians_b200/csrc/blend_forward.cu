@@ -25,7 +25,14 @@ __device__ unsigned long long* g_trace_fwd = nullptr;   // diagnostic: per-CTA (
 __device__ __forceinline__ unsigned long long trace_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 __device__ __forceinline__ unsigned trace_smid() { unsigned r; asm volatile("mov.u32 %0, %smid;" : "=r"(r)); return r; }
 
-constexpr int BATCH = 256;
+#ifndef GSR_FWD_BATCH
+#define GSR_FWD_BATCH 128
+#endif
+constexpr int BATCH = GSR_FWD_BATCH;
+#ifndef GSR_FWD_RING
+#define GSR_FWD_RING 3
+#endif
+constexpr int RING = GSR_FWD_RING;      // staged batches in flight per CTA
 
 // CTA = 128 threads = 4 warps; a warp owns an 8x8 patch, a lane the pixels (x, y) and (x, y + 4).  Record loads, loop
 // control and dx are shared by the pair and the pair's arithmetic is issued as packed fp32x2 instructions (FFMA2 /
@@ -74,10 +81,15 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     struct __align__(128) Stage {
         float4 a[BATCH], b[BATCH], c[BATCH], d[EXTRA ? BATCH : 1];
     };
-    __shared__ Stage stage[2];
-    __shared__ __align__(8) uint64_t full[2];
-    __shared__ uint32_t s_wmask[NW2][BATCH / 32];
-    static_assert(BATCH % NT2 == 0, "pre-pass: BATCH / NT2 staged Gaussians per thread");
+    // The four warps walk the ring on their own (no CTA barrier per batch: with one, the warps of a tile waited for the
+    // slowest of them every batch -- the largest stall reason in ncu): each builds the work list of its patch from the
+    // staged batch, the last warp out of a ring slot (an atomic count) refills it, and a warp whose 64 pixels are all
+    // finished only keeps that count going until every warp is (then nothing more is fetched).
+    __shared__ Stage stage[RING];
+    __shared__ __align__(8) uint64_t full[RING];
+    __shared__ uint32_t s_done[RING];
+    __shared__ int s_slot_round[RING];      // the last round issued into each slot (-1: none)
+    __shared__ uint32_t s_fin;              // warps with nothing left to blend
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int vt = (int)tile_order[blockIdx.x];
@@ -98,17 +110,23 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     const int rounds = (n_total + BATCH - 1) / BATCH;
 
     if (tid == 0) {
-        mbar_init(&full[0], 1);
-        mbar_init(&full[1], 1);
+#pragma unroll
+        for (int i = 0; i < RING; ++i) {
+            mbar_init(&full[i], 1);
+            s_done[i] = 0;
+            s_slot_round[i] = -1;
+        }
+        s_fin = 0;
         mbar_fence_init();
     }
     __syncthreads();
 
-    auto issue = [&](int r) {   // thread 0 only
-        const int buf = r & 1;
+    auto issue = [&](int r) {   // one thread
+        const int buf = r % RING;
         const int nb = min(BATCH, n_total - r * BATCH);
         const uint32_t bytes = (uint32_t)nb * 16u;
         const size_t src = (size_t)range.x + (size_t)r * BATCH;
+        s_slot_round[buf] = r;
         mbar_expect_tx(&full[buf], bytes * (EXTRA ? 4u : 3u));
         tma_load_1d(stage[buf].a, recA + src, bytes, &full[buf]);
         tma_load_1d(stage[buf].b, recB + src, bytes, &full[buf]);
@@ -116,8 +134,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         if (EXTRA) tma_load_1d(stage[buf].d, recD + src, bytes, &full[buf]);
     };
     if (tid == 0) {
-        if (rounds > 0) issue(0);
-        if (rounds > 1) issue(1);
+        for (int r = 0; r < RING && r < rounds; ++r) issue(r);
     }
 
     // T > 0: the pixel's running transmittance.  T < 0: the pixel is finished (saturated, or outside the image) and |T|
@@ -131,33 +148,42 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     float2 D = splat(0.0f), Wsum = splat(0.0f);
     uint32_t lc0 = 0, lc1 = 0;
 
-    const float tile_x0 = (float)(tile_xi * TILE_X), tile_y0 = (float)(tile_yi * TILE_Y);
+    const float patch_x0 = (float)(tile_xi * TILE_X + (warp & 1) * 8), patch_y0 = (float)(tile_yi * TILE_Y + (warp >> 1) * 8);
+    bool fin = false;                        // warp-uniform: all 64 pixels of this warp are finished
     for (int r = 0; r < rounds; ++r) {
-        const int buf = r & 1;
-        mbar_wait(&full[buf], (uint32_t)((r >> 1) & 1));
-        const int nb = min(BATCH, n_total - r * BATCH);
-        const uint32_t contrib_base = (uint32_t)r * BATCH;
-        {   // pre-pass: Gaussian `tid` x the four 8x8 patches -> one 256-bit work list per warp
-#pragma unroll
-            for (int g0 = 0; g0 < BATCH; g0 += NT2) {
-                const int g = g0 + tid;
-                uint32_t m4 = 0u;
-                if (g < nb) {
-                    const float4 a = stage[buf].a[g];
-                    const float4 b = stage[buf].b[g];
-                    m4 = blend_patch_mask4(a.x, a.y, a.z, a.w, b.x, b.w, tile_x0, tile_y0);
-                }
-#pragma unroll
-                for (int w = 0; w < NW2; ++w) {
-                    const uint32_t bal = __ballot_sync(0xffffffffu, (m4 >> w) & 1u);
-                    if (lane == 0) s_wmask[w][g0 / 32 + warp] = bal;
+        const int buf = r % RING;
+        const uint32_t parity = (uint32_t)((r / RING) & 1);
+        if (fin) {
+            // nothing left to blend here: only keep the slot count going for the warps that still do
+            int st = 0;
+            if (lane == 0) {
+                while (st == 0) {
+                    if (mbar_try_wait(&full[buf], parity)) st = 1;
+                    else if (*(volatile uint32_t*)&s_fin == NW2) st = 2;
                 }
             }
+            st = __shfl_sync(0xffffffffu, st, 0);
+            if (st == 2) break;              // every warp is finished: round r may never have been fetched
+        } else {
+        mbar_wait(&full[buf], parity);
+        const int nb = min(BATCH, n_total - r * BATCH);
+        const uint32_t contrib_base = (uint32_t)r * BATCH;
+        // pre-pass: this warp's work list, 32 staged Gaussians per ballot against its 8x8 patch
+        uint32_t wm[BATCH / 32];
+#pragma unroll
+        for (int sb = 0; sb < BATCH / 32; ++sb) {
+            const int g = sb * 32 + lane;
+            bool hit = false;
+            if (g < nb) {
+                const float4 a = stage[buf].a[g];
+                const float4 b = stage[buf].b[g];
+                hit = blend_patch_hit(a.x, a.y, a.z, a.w, b.x, b.w, patch_x0, patch_y0);
+            }
+            wm[sb] = __ballot_sync(0xffffffffu, hit);
         }
-        __syncthreads();
-#pragma unroll 1
+#pragma unroll
         for (int q = 0; q < BATCH / 32; ++q) {
-            uint32_t m = s_wmask[warp][q];
+            uint32_t m = wm[q];
             if constexpr (ILP == 1) {
                 while (m != 0u && !(T.x < 0.0f && T.y < 0.0f)) {
                     const int j = q * 32 + __ffs(m) - 1;
@@ -261,14 +287,19 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                 }
             }
         }
-        // everyone is finished with `buf`; stop fetching once the whole tile is saturated
-        const int num_done = __syncthreads_count(T.x < 0.0f && T.y < 0.0f);
-        if (num_done == NT2) {
-            // batch r+1 may still be in flight: the CTA must not retire under it
-            if (tid == 0 && r + 1 < rounds) mbar_wait(&full[(r + 1) & 1], (uint32_t)(((r + 1) >> 1) & 1));
-            break;
+        fin = __all_sync(0xffffffffu, T.x < 0.0f && T.y < 0.0f);
+        if (fin && lane == 0) atomicAdd(&s_fin, 1u);
         }
-        if (tid == 0 && r + 2 < rounds) issue(r + 2);
+        // done with this ring slot; the last of the four warps to say so refills it while anyone still blends
+        __syncwarp();
+        if (lane == 0) {
+            __threadfence_block();
+            if (atomicAdd(&s_done[buf], 1u) == NW2 - 1) {
+                s_done[buf] = 0;
+                __threadfence_block();
+                if (r + RING < rounds && *(volatile uint32_t*)&s_fin < NW2) issue(r + RING);
+            }
+        }
     }
 
     const CamDev& cam = cams[view];
@@ -291,6 +322,15 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         }
         out_depth[(size_t)view * HW + pix] = i == 0 ? D.x : D.y;
         out_alpha[(size_t)view * HW + pix] = i == 0 ? Wsum.x : Wsum.y;
+    }
+    // the CTA must not retire under a batch that was fetched and never consumed
+    __syncthreads();
+    if (tid == 0) {
+#pragma unroll
+        for (int i = 0; i < RING; ++i) {
+            const int q = s_slot_round[i];
+            if (q >= 0) mbar_wait(&full[i], (uint32_t)((q / RING) & 1));
+        }
     }
     if (trace && lane == 0) atomicMax(&trace[4 * blockIdx.x + 1], trace_now());
 }
