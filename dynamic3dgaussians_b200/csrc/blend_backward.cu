@@ -2,12 +2,13 @@
 // Replaces BACKWARD::render / renderCUDA (R/cuda_rasterizer/backward.cu:432-652).
 //
 // Differences in structure from the reference (the gradients computed are the same quantities):
-//  * per-instance records arrive through the same double-buffered TMA bulk copies as the forward, walked back to front;
-//    the walk starts at the tile's largest n_contrib instead of at the end of the list;
+//  * per-instance records arrive through the same ring of TMA bulk copies as the forward, walked back to front by
+//    every warp on its own (no CTA barrier per batch); the walk starts at the tile's largest n_contrib instead of at
+//    the end of the list;
 //  * the colour / depth / alpha "colour behind me" recurrences (backward.cu:578,591,600,617) and the background term
 //    (backward.cu:626-629) collapse into ONE scalar recurrence, because the pixel cotangent is fixed per thread:
 //        s_j   = <c_j, dL/dC> + depth_j * dL/dD + dL/dA          (extended colour dotted with the pixel cotangent)
-//        acc_j = alpha_{j+1} * s_{j+1} + (1 - alpha_{j+1}) * acc_{j+1},   acc_last = <bg, dL/dC>
+//        acc_j = acc_{j+1} + alpha_{j+1} * (s_{j+1} - acc_{j+1}),   acc_last = <bg, dL/dC>
 //        dL/dalpha_j = T_j * (s_j - acc_j)
 //    which removes ~3 registers and ~3 flops per blended channel per pair (the reference kernel needs 198 registers);
 //  * what is reduced over the pixels are raw moments of a = opacity * G * dL/dalpha about d = mean - pixel (S1 = sum a d,
@@ -15,8 +16,7 @@
 //    through the conic once per Gaussian;
 //  * the 7+C partial sums of a warp (an 8x8 pixel patch) are reduced with a packed butterfly (12 shuffles for 10 values
 //    instead of 50) and land in the per-(view, Gaussian) gradient record with ONE reduction per (patch, Gaussian,
-//    value): the reference issues one atomic per (pixel, Gaussian, value) (backward.cu:586-649).  The warps of a CTA
-//    only meet once per 128-instance batch.
+//    value): the reference issues one atomic per (pixel, Gaussian, value) (backward.cu:586-649).
 #include "geom_math.cuh"
 #include "packed_reduce.cuh"
 

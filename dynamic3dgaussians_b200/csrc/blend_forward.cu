@@ -2,16 +2,18 @@
 // Replaces FORWARD::render / renderCUDA (R/cuda_rasterizer/forward.cu:274-408).
 //
 // * one CTA per (view, tile); sorted per-instance records are contiguous, so each 128-instance batch is staged into
-//   shared memory by 3-4 TMA bulk copies (cp.async.bulk + mbarrier), double buffered: no per-pair global gathers
+//   shared memory by 3-4 TMA bulk copies (cp.async.bulk + mbarrier) through a 3-slot ring: no per-pair global gathers
 //   (the reference fetches colour/depth/semantics from global memory for every contributing pair, forward.cu:375-383);
 // * colour, fg/bg segmentation colours, depth and accumulated alpha are blended in ONE pass over the list
 //   (the reference renders colour and segmentation with two full rasterizer calls, REF/train.py:142,249);
-// * a warp covers an 8x8 pixel patch, two pixels per lane.  Per staged batch a pre-pass (one thread per Gaussian)
-//   intersects the Gaussian's opacity-aware extent (the ellipse outside of which alpha < 1/255) with the 4 patches and
-//   warp ballots turn that into a 128-bit work list per warp: a warp only iterates over Gaussians that can reach its patch (2-3x fewer
-//   iterations than walking the tile's whole list as the reference does), and each lane tests `power < threshold`
-//   before paying for the exp.  Both filters are conservative, so the set of blended pairs is unchanged;
-// * a lane leaves the loop as soon as both of its pixels are saturated and the CTA stops fetching when all 256 are;
+// * a warp covers an 8x8 pixel patch, two pixels per lane, and walks the ring on its own (no CTA barrier per batch).
+//   Per staged batch it intersects every Gaussian's opacity-aware extent (the ellipse outside of which alpha < 1/255)
+//   with its patch and four ballots turn that into a 128-bit work list: a warp only iterates over Gaussians that can
+//   reach its patch (2-3x fewer iterations than walking the tile's whole list as the reference does), and each lane
+//   tests `power < threshold` before paying for the exp.  Both filters are conservative, so the set of blended pairs
+//   is unchanged;
+// * a lane leaves the loop as soon as both of its pixels are saturated, a warp stops blending when its 64 pixels are,
+//   and the CTA stops fetching when all 256 are;
 // * arithmetic per pair follows the reference binary exactly (see geom_math.cuh), so n_contrib and the images agree
 //   with the reference bit for bit.
 #include "geom_math.cuh"
