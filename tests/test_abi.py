@@ -42,6 +42,9 @@ def test_workspace_protocol_host_side():
     assert L.counters == 0
     offs = [getattr(L, n) for n in _lib._LAYOUT_SIZE_T[:18]]
     assert all(o % 256 == 0 for o in offs)
+    # what a forward needs zeroed sits at the head of its workspace (one memset per workspace)
+    assert max(L.counters, L.dhist, L.dlookback, L.dcounters) < min(L.cams, L.radii, L.rects, L.geomrec, L.dkeys0, L.grad_rec)
+    assert max(L.ihist, L.ilookback, L.st_ranges) < min(L.ikeys0, L.ivals0, L.imasks, L.chunk_base, L.recA)
     # error codes, not exceptions, across the ABI
     assert lib.gsr_workspace_sizes(10, 1, 0, 10, 3, 0, 0, C.byref(s)) == -1
     assert lib.gsr_workspace_sizes(10, 1, 16, 16, 4, 0, 0, C.byref(s)) == -4
