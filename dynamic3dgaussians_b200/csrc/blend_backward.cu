@@ -173,6 +173,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     const bool writer = lane == (__ffs(slot_peers) - 1);
     const float patch_x0 = (float)(tile_xi * TILE_X + (warp & 1) * 8), patch_y0 = (float)(tile_yi * TILE_Y + (warp >> 1) * 8);
 
+#ifdef GSR_TRACE_COUNTS
+    unsigned long long n_list = 0, n_done = 0;      // work-list entries walked / entries some pixel of the patch blends
+#endif
     for (int r = 0; r < rounds; ++r) {
         const int buf = r % RING;
         const int c = rounds - 1 - r;
@@ -201,6 +204,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 if (warp_last <= base) m = 0u;
                 else if (warp_last - base < 32u) m &= (1u << (warp_last - base)) - 1u;
             }
+#ifdef GSR_TRACE_COUNTS
+            n_list += __popc(m);
+#endif
             while (m != 0u) {                                       // warp-uniform, back to front
                 const int jl = 31 - __clz(m);
                 m &= ~(1u << jl);
@@ -217,6 +223,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 const bool pre0 = (j < rel0) && !(power.x > 0.0f) && !(power.x < b.w);
                 const bool pre1 = (j < rel1) && !(power.y > 0.0f) && !(power.y < b.w);
                 if (!__any_sync(FULL, pre0 || pre1)) continue;      // warp-uniform
+#ifdef GSR_TRACE_COUNTS
+                ++n_done;
+#endif
                 const float2 G = expf2_pinned(power);        // garbage where !pre: masked by the selects below
                 const float2 og = __fmul2_rn(splat(b.y), G);
                 float2 alpha = f2(fminf(0.99f, og.x), fminf(0.99f, og.y));
@@ -276,6 +285,12 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             }
         }
     }
+#ifdef GSR_TRACE_COUNTS
+    if (trace && lane == 0) {       // diagnostic build: counts ride in the upper bits of the SM / tile fields
+        atomicAdd(&trace[4 * blockIdx.x + 2], n_list << 16);
+        atomicAdd(&trace[4 * blockIdx.x + 3], n_done << 32);
+    }
+#endif
     if (trace && lane == 0) atomicMax(&trace[4 * blockIdx.x + 1], trace_now());
 }
 

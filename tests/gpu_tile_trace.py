@@ -1,5 +1,8 @@
 """Per-CTA timeline of the blend kernels for one C2 view (diagnostic): which SM ran which tile, from when to when.
-python tests/gpu_tile_trace.py [view]"""
+python tests/gpu_tile_trace.py [view | -n_views]
+With a library built with -DGSR_TRACE_COUNTS (tests/build_variant.sh counts -DGSR_TRACE_COUNTS; GSR_LIB_PATH=...) the
+backward also reports how many work-list entries were walked and how many of them some pixel of the patch blended
+(C2, 27 views: 12.8 M walked, 78.9 % blended -- the bounding-box filter lets 21 % through to the 32-instruction skip path)."""
 import os
 import sys
 
@@ -64,6 +67,12 @@ def full(nv):
     _lib.check(lib.gsr_debug_blend_trace(None, None), "trace off")
     for name, tr in (("forward", tf), ("backward", tb)):
         tr = tr.cpu().long()
+        if name == "backward" and int((tr[:, 2] >> 16).sum()) > 0:     # a -DGSR_TRACE_COUNTS build
+            n_list, n_done = int((tr[:, 2] >> 16).sum()), int((tr[:, 3] >> 32).sum())
+            print(f"backward work lists: {n_list} entries walked, {n_done} blended by some pixel of the patch "
+                  f"({100.0 * n_done / max(n_list, 1):.1f} %)")
+            tr[:, 2] &= 0xffff
+            tr[:, 3] &= 0xffffffff
         t0 = int(tr[:, 0].min())
         start, end, sm = (tr[:, 0] - t0) / 1e3, (tr[:, 1] - t0) / 1e3, tr[:, 2]
         dur = end - start
