@@ -19,6 +19,7 @@
 //    value): the reference issues one atomic per (pixel, Gaussian, value) (backward.cu:586-649).
 #include "geom_math.cuh"
 #include "packed_reduce.cuh"
+#include <stdlib.h>
 
 namespace gsr {
 
@@ -294,6 +295,57 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     if (trace && lane == 0) atomicMax(&trace[4 * blockIdx.x + 1], trace_now());
 }
 
+// Launch order of a SMALL backward launch (a few views: 3-4 waves of CTAs): tiles by the depth the forward walked them
+// (their largest n_contrib -- exactly how far the backward walks), deepest first.  The list-length order of tile_scan
+// starts the deepest tiles in the second wave (long lists saturate early; the deepest walks belong to mid-length lists
+// of faint Gaussians), and the launch then ends on a handful of them running alone (tests/gpu_tile_trace.py -4).
+// One CTA: counting sort into 1024 buckets.
+constexpr int ORD_THREADS = 1024;
+__global__ void __launch_bounds__(ORD_THREADS)
+tile_order_by_cost_kernel(uint32_t VT, const uint32_t* __restrict__ cost, uint32_t* __restrict__ order) {
+    __shared__ uint32_t s_bucket[ORD_THREADS];
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_maxc;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_maxc = 0;
+    s_bucket[threadIdx.x] = 0;
+    __syncthreads();
+    uint32_t vmax = 0;
+    for (uint32_t i = threadIdx.x; i < VT; i += ORD_THREADS) vmax = max(vmax, cost[i]);
+    vmax = __reduce_max_sync(FULL, vmax);
+    if (lane == 0 && vmax > 0) atomicMax(&s_maxc, vmax);
+    __syncthreads();
+    const uint32_t q = s_maxc / (ORD_THREADS - 1) + 1;
+    for (uint32_t i = threadIdx.x; i < VT; i += ORD_THREADS)
+        atomicAdd(&s_bucket[(ORD_THREADS - 1) - min(cost[i] / q, (uint32_t)ORD_THREADS - 1)], 1u);   // bucket 0: deepest
+    __syncthreads();
+    {   // exclusive scan of the 1024 bucket counts
+        const uint32_t c = s_bucket[threadIdx.x];
+        uint32_t inc = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(FULL, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        uint32_t w = s_warp[lane], winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(FULL, winc, o);
+            if (lane >= o) winc += t;
+        }
+        const uint32_t base = __shfl_sync(FULL, winc - w, warp);
+        __syncthreads();
+        s_bucket[threadIdx.x] = base + inc - c;
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < VT; i += ORD_THREADS) {
+        const uint32_t pos = atomicAdd(&s_bucket[(ORD_THREADS - 1) - min(cost[i] / q, (uint32_t)ORD_THREADS - 1)], 1u);
+        order[pos] = i;
+    }
+}
+
 }  // namespace
 
 int set_blend_backward_trace(unsigned long long* p) {
@@ -321,12 +373,20 @@ int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, c
     const uint32_t* nc = at<uint32_t>(iws, L.n_contrib);
     const float* fT = at<float>(iws, L.final_T);
     float* rec = at<float>(gws, L.grad_rec);
+    const uint32_t* order = at<uint32_t>(iws, L.tile_order);
+    static const bool cost_order = [] { const char* e = getenv("GSR_BWD_COST_ORDER"); return !(e && e[0] == '0'); }();
+    if (cost_order && blend_ilp(blocks) > 1) {          // small launch: deepest tiles first (see tile_order_by_cost_kernel)
+        uint32_t* ord = const_cast<uint32_t*>(at<uint32_t>(iws, L.tile_order_bwd));
+        tile_order_by_cost_kernel<<<1, ORD_THREADS, 0, s>>>((uint32_t)blocks, at<uint32_t>(iws, L.tile_cost), ord);
+        GSR_LAUNCH_CHECK();
+        order = ord;
+    }
     if (channels == 3)
-        blend_backward_kernel<3><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H,
+        blend_backward_kernel<3><<<blocks, NT2, 0, s>>>(ranges, order, A, B, C, D, cams, W, H,
                                                         L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
                                                         dL_dalpha, rec);
     else if (channels == 6)
-        blend_backward_kernel<6><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, W, H,
+        blend_backward_kernel<6><<<blocks, NT2, 0, s>>>(ranges, order, A, B, C, D, cams, W, H,
                                                         L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
                                                         dL_dalpha, rec);
     else

@@ -77,7 +77,8 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                       const float4* __restrict__ recC, const float4* __restrict__ recD,
                       const CamDev* __restrict__ cams, int W, int H, int tiles_x, int tiles_per_view,
                       float* __restrict__ out_color, float* __restrict__ out_extra, float* __restrict__ out_depth,
-                      float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib, float* __restrict__ final_T) {
+                      float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib, float* __restrict__ final_T,
+                      uint32_t* __restrict__ tile_cost) {
     constexpr bool EXTRA = NCH > 3;
     // one block per ring slot, so that the loop addresses all of an entry's records off ONE register (base + 16 j)
     struct __align__(128) Stage {
@@ -92,6 +93,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     __shared__ uint32_t s_done[RING];
     __shared__ int s_slot_round[RING];      // the last round issued into each slot (-1: none)
     __shared__ uint32_t s_fin;              // warps with nothing left to blend
+    __shared__ uint32_t s_cost;             // the tile's largest n_contrib: how deep the backward will walk it
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int vt = (int)tile_order[blockIdx.x];
@@ -119,6 +121,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
             s_slot_round[i] = -1;
         }
         s_fin = 0;
+        s_cost = 0;
         mbar_fence_init();
     }
     __syncthreads();
@@ -304,6 +307,10 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         }
     }
 
+    {
+        const uint32_t wmax = __reduce_max_sync(0xffffffffu, max(lc0, lc1));
+        if (lane == 0 && wmax > 0) atomicMax(&s_cost, wmax);
+    }
     const CamDev& cam = cams[view];
     const size_t HW = (size_t)H * W;
 #pragma unroll
@@ -328,6 +335,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     // the CTA must not retire under a batch that was fetched and never consumed
     __syncthreads();
     if (tid == 0) {
+        tile_cost[vt] = s_cost;
 #pragma unroll
         for (int i = 0; i < RING; ++i) {
             const int q = s_slot_round[i];
@@ -369,7 +377,7 @@ int launch_blend_forward(int V, int W, int H, int channels, const void* gws, con
 #define GSR_FWD(NCH_, ILP_)                                                                                           \
     blend_forward_kernel<NCH_, ILP_><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, \
                                                             W, H, L.tiles_x, T, out_color, out_extra, out_depth,      \
-                                                            out_alpha, nc, fT)
+                                                            out_alpha, nc, fT, at<uint32_t>(iws, L.tile_cost))
     if (channels == 3) {
         if (ilp > 1) GSR_FWD(3, BLEND_ILP_SMALL); else GSR_FWD(3, 1);
     } else if (channels == 6) {

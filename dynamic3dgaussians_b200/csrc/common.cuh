@@ -80,6 +80,8 @@ struct Layout : GsrLayout {
     size_t geom_bytes, binning_bytes, image_bytes;
     // every array that must be zero when a forward starts sits at the head of its workspace: one memset per workspace
     size_t geom_zero_bytes, binning_zero_bytes;
+    // image workspace, internal: per-tile walked depth (the forward's largest n_contrib) and the backward's launch order
+    size_t tile_cost, tile_order_bwd;
 };
 
 inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
@@ -156,6 +158,8 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     L.tile_order = take(VT * 4);          // (view, tile) indices, longest list first: the blend kernels' launch order
     L.n_contrib = take((size_t)V * W * H * 4);
     L.final_T = take((size_t)V * W * H * 4);
+    L.tile_cost = take(VT * 4);
+    L.tile_order_bwd = take(VT * 4);
     L.image_bytes = o;
 }
 
