@@ -353,7 +353,7 @@ int set_blend_backward_trace(unsigned long long* p) {
     return GSR_OK;
 }
 
-int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, const void* bws, const void* iws,
+int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, const void* bws, void* iws,
                           const Layout& L, const float* dL_dcolor, const float* dL_dextra, const float* dL_ddepth,
                           const float* dL_dalpha, cudaStream_t s) {
     const int T = L.tiles_x * L.tiles_y;
@@ -376,7 +376,7 @@ int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, c
     const uint32_t* order = at<uint32_t>(iws, L.tile_order);
     static const bool cost_order = [] { const char* e = getenv("GSR_BWD_COST_ORDER"); return !(e && e[0] == '0'); }();
     if (cost_order && blend_ilp(blocks) > 1) {          // small launch: deepest tiles first (see tile_order_by_cost_kernel)
-        uint32_t* ord = const_cast<uint32_t*>(at<uint32_t>(iws, L.tile_order_bwd));
+        uint32_t* ord = at<uint32_t>(iws, L.tile_order_bwd);
         tile_order_by_cost_kernel<<<1, ORD_THREADS, 0, s>>>((uint32_t)blocks, at<uint32_t>(iws, L.tile_cost), ord);
         GSR_LAUNCH_CHECK();
         order = ord;

@@ -228,7 +228,7 @@ int launch_blend_forward(int V, int W, int H, int channels, const void* geom_ws,
                          void* image_ws, const Layout& L, float* out_color, float* out_extra, float* out_depth,
                          float* out_alpha, cudaStream_t s);
 int launch_blend_backward(int V, int P, int W, int H, int channels, void* geom_ws, const void* binning_ws,
-                          const void* image_ws, const Layout& L, const float* dL_dcolor, const float* dL_dextra,
+                          void* image_ws, const Layout& L, const float* dL_dcolor, const float* dL_dextra,
                           const float* dL_ddepth, const float* dL_dalpha, cudaStream_t s);
 size_t image_loss_state_bytes(int64_t n_img, int W, int H);
 int launch_image_loss_forward(int64_t n_img, int W, int H, const float* img, const float* tgt, float w_l1, float w_ssim,
