@@ -195,13 +195,15 @@ def build_workload(args, device):
     return sc, sets
 
 
-def kernels_per_step(L, with_allreduce: bool) -> int:
+def kernels_per_step(L, with_allreduce: bool, views: int = 0) -> int:
     """Launches of OUR kernels in one forward+backward (memsets/memcpys not counted)."""
     # preprocess | depth sort (hist, scan, passes) | count + scan | emit | supertile sort (scan, passes) |
     # st ranges, chunk table, chunk count, tile offsets, tile scan | pack colours, scatter records | blend
     fwd = 1 + (2 + L.depth_passes) + 2 + 1 + (1 + L.tile_passes) + 5 + 2 + 1
     bwd = 1 + 1
-    return fwd + bwd
+    # launches of a few views (<= 148 * 8 * 4 CTAs) order the backward's CTAs by walked depth: one more kernel
+    small = 0 < views * L.tiles_x * L.tiles_y <= 148 * 8 * 4
+    return fwd + bwd + (1 if small else 0)
 
 
 def fp32_peak_tflops(lib, device) -> float:
@@ -359,7 +361,7 @@ def run_ours(args, world, rank, local):
         R = st.num_rendered
         vis = float((st.radii > 0).float().mean().item())
     res = dict(ms=ms, host_ms=t_host, visible=vis if st is not None else 0.0, stages=stages, pairs=pairs, R=R, R1=R1 if st is not None else 0, clocks=clocks, views_per_rank=[round(sum(1.0 if isinstance(u, int) else (u[2] - u[1]) / float((IMG_H + 15) // 16) for u in p), 2) for p in parts], parts=parts, rebalance_ms=rebalance_ms,
-               launches=kernels_per_step(L, world > 1) * args.steps if st is not None else 0, state=st, dev=dev,
+               launches=kernels_per_step(L, world > 1, st.V) * args.steps if st is not None else 0, state=st, dev=dev,
                rv=rv, sets=sets, sc=sc, lib=lib)
     return res
 
