@@ -88,6 +88,10 @@ __device__ void sh_backward(int deg, int M, const float* __restrict__ sh_g, floa
             }
         }
     }
+    // coefficients above the active degree take no part in the colour (forward.cu:20-71): their gradient is zero (the
+    // reference's buffer is zero-filled, rasterize_points.cu:176); written once, with the Gaussian's first visible view
+    if (first)
+        for (int i = (deg + 1) * (deg + 1) * 3; i < M * 3; ++i) dL_dsh_g[i] = 0.0f;
     // d(dir)/d(mean): normalisation Jacobian (auxiliary.h:108-119)
     const float ddx = dRGBdx[0] * dRGB[0] + dRGBdx[1] * dRGB[1] + dRGBdx[2] * dRGB[2];
     const float ddy = dRGBdy[0] * dRGB[0] + dRGBdy[1] * dRGB[1] + dRGBdy[2] * dRGB[2];

@@ -1,18 +1,26 @@
 """TEST INFRASTRUCTURE ONLY.  Compiles the reference's own CUDA sources, where they lie under /root/reference, into
 oracle/_ref/ (git-ignored; travels to the GPU box with the snapshot):
 
-  libref_rasterizer.so  R/cuda_rasterizer/{forward,backward,rasterizer_impl}.cu + oracle/ref_shim.cu
-  libref_knn.so         K/simple_knn.cu + oracle/ref_knn_shim.cu
+  libref_rasterizer.so          R/cuda_rasterizer/{forward,backward,rasterizer_impl}.cu + oracle/ref_shim.cu
+  libref_knn.so                 K/simple_knn.cu + oracle/ref_knn_shim.cu
+  libref_rasterizer_patched.so  the same three rasterizer sources with the minimal repairs of SURVEY.md 2.4
+                                (PATCHES below) -- the second gradient witness: its backward is then a function of its
+                                inputs and can be compared with the product at sizes autograd-through-the-oracle cannot
+                                reach (300k Gaussians x 640x360).
 
-No reference source is copied or edited: the two `-include` flags only supply the <cstdint>/<cfloat> declarations the
-sources rely on transitively with older toolchains.  The reference's own build system (setup.py /
-CMake + torch extension) is not used.
+No reference source is copied into the repository or edited in place: the two `-include` flags only supply the
+<cstdint>/<cfloat> declarations the sources rely on transitively with older toolchains; the patched build
+reads the three sources, applies PATCHES to the text in a temporary directory outside the repository, compiles from
+there (the headers still come from /root/reference through -I) and removes the directory.  The reference's own build
+system (setup.py / CMake + torch extension) is not used.
 """
 from __future__ import annotations
 
 import os
+import shutil
 import subprocess
 import sys
+import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, "_ref")
@@ -21,14 +29,77 @@ R = os.path.join(REF, "submodules_fsgs", "diff-gaussian-rasterization-confidence
 K = os.path.join(REF, "submodules_fsgs", "simple-knn")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-shared", "-w", "-lineinfo"]
+RAS_SRCS = ("forward.cu", "backward.cu", "rasterizer_impl.cu")
+
+# (file, exact text that must occur ONCE, replacement).  SURVEY.md 2.4:
+#   Q1  forward never stores the accumulated alpha (`weight`, forward.cu:322,378) -> store it next to the depth
+#   Q3  the clamp-gradient switches test `txtz < lim_x_neg` while the clamp is max(-lim_x_neg, .) (backward.cu:185,191-192)
+#   Q4  the semantic-feature scratch of the backward is read but never written (rasterizer_impl.cu:408-409,
+#       backward.cu:598): zero it, so that with dL_dfeature = 0 the term it feeds is exactly 0 instead of garbage * 0
+#   Q2  (argument order of the Python wrapper, __init__.py:130-133) needs no source patch: oracle/ref_shim.cu calls
+#       Rasterizer::backward with the order the C++ declares.
+PATCHES = [
+    ("forward.cu", "\t\tout_depth[pix_id] = D;\n", "\t\tout_depth[pix_id] = D;\n\t\tout_alpha[pix_id] = weight;\n"),
+    ("backward.cu", "const float x_grad_mul = txtz < lim_x_neg || txtz > lim_x_pos ? 0 : 1;",
+     "const float x_grad_mul = txtz < -lim_x_neg || txtz > lim_x_pos ? 0 : 1;"),
+    ("backward.cu", "const float y_grad_mul = tytz < lim_y_neg || tytz > lim_y_pos ? 0 : 1;",
+     "const float y_grad_mul = tytz < -lim_y_neg || tytz > lim_y_pos ? 0 : 1;"),
+    # T_final: the backward recovers it as 1 - alpha_out (backward.cu:484).  alpha_out is a float32 running sum, so for a
+    # pixel with T_final ~ 1e-3 the difference has ~1e-3 RELATIVE error, and every T of that pixel's walk (T_final divided
+    # back up, backward.cu:564) inherits it: measured 1e-3 .. 2e-3 max-norm on every gradient (profiles/
+    # r02_grad_witness.txt).  The witness keeps that route (alphas >= 0) and adds a second one: a NEGATIVE entry -T hands
+    # the kernel the forward's final transmittance itself, which is what upstream 3DGS stores (ImageState::accum_alpha).
+    ("backward.cu", "const float T_final = inside ? (1 - alphas[pix_id]) : 0;",
+     "const float T_final = inside ? (alphas[pix_id] < 0.0f ? -alphas[pix_id] : (1 - alphas[pix_id])) : 0;"),
+    ("rasterizer_impl.cu",
+     "cudaMalloc((void**)&collected_semantic_feature, NUM_SEMANTIC_CHANNELS * BLOCK_SIZE * sizeof(float)); \n",
+     "cudaMalloc((void**)&collected_semantic_feature, NUM_SEMANTIC_CHANNELS * BLOCK_SIZE * sizeof(float)); \n"
+     "\tcudaMemset(collected_semantic_feature, 0, NUM_SEMANTIC_CHANNELS * BLOCK_SIZE * sizeof(float));\n"),
+]
 
 
 def available() -> bool:
     return os.path.isdir(os.path.join(R, "cuda_rasterizer"))
 
 
+def _nvcc_rasterizer(src_dir: str, out: str) -> None:
+    nvcc = os.environ.get("NVCC", "nvcc")
+    srcs = [os.path.join(src_dir, f) for f in RAS_SRCS]
+    # -I <cuda_rasterizer dir of the reference>: the sources include their siblings ("auxiliary.h", "forward.h", ...) by
+    # bare name; for the patched build those headers still come from the reference tree
+    cmd = [nvcc, *ARCH, *COMMON, "-include", "cstdint", "-I", R, "-I", os.path.join(R, "cuda_rasterizer"),
+           "-I", os.path.join(R, "third_party", "glm"), *srcs, os.path.join(HERE, "ref_shim.cu"), "-o", out]
+    subprocess.check_call(cmd)
+
+
+def build_patched(force: bool = False) -> bool:
+    out = os.path.join(OUT, "libref_rasterizer_patched.so")
+    if not available():
+        return os.path.exists(out)
+    if os.path.exists(out) and not force:
+        return True
+    os.makedirs(OUT, exist_ok=True)
+    tmp = tempfile.mkdtemp(prefix="gsr_ref_patched_")
+    try:
+        text = {}
+        for f in RAS_SRCS:
+            with open(os.path.join(R, "cuda_rasterizer", f), "r") as fh:
+                text[f] = fh.read()
+        for f, old, new in PATCHES:
+            if text[f].count(old) != 1:
+                raise RuntimeError(f"patch anchor not found exactly once in {f}: {old!r}")
+            text[f] = text[f].replace(old, new)
+        for f in RAS_SRCS:
+            with open(os.path.join(tmp, f), "w") as fh:
+                fh.write(text[f])
+        _nvcc_rasterizer(tmp, out)
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    return True
+
+
 def build(force: bool = False) -> bool:
-    """Returns True when both libraries exist afterwards."""
+    """Returns True when all libraries exist afterwards."""
     ras = os.path.join(OUT, "libref_rasterizer.so")
     knn = os.path.join(OUT, "libref_knn.so")
     if not available():
@@ -36,15 +107,12 @@ def build(force: bool = False) -> bool:
     os.makedirs(OUT, exist_ok=True)
     nvcc = os.environ.get("NVCC", "nvcc")
     if force or not os.path.exists(ras):
-        srcs = [os.path.join(R, "cuda_rasterizer", f) for f in ("forward.cu", "backward.cu", "rasterizer_impl.cu")]
-        cmd = [nvcc, *ARCH, *COMMON, "-include", "cstdint", "-I", R, "-I", os.path.join(R, "third_party", "glm"),
-               *srcs, os.path.join(HERE, "ref_shim.cu"), "-o", ras]
-        subprocess.check_call(cmd)
+        _nvcc_rasterizer(os.path.join(R, "cuda_rasterizer"), ras)
     if force or not os.path.exists(knn):
         cmd = [nvcc, *ARCH, *COMMON, "-include", "cfloat", "-I", K, os.path.join(K, "simple_knn.cu"),
                os.path.join(HERE, "ref_knn_shim.cu"), "-o", knn]
         subprocess.check_call(cmd)
-    return True
+    return build_patched(force)
 
 
 if __name__ == "__main__":

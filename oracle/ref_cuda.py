@@ -10,9 +10,10 @@ import torch
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 RAS = os.path.join(HERE, "_ref", "libref_rasterizer.so")
+RAS_PATCHED = os.path.join(HERE, "_ref", "libref_rasterizer_patched.so")   # SURVEY.md 2.4 repairs, see build_ref.PATCHES
 KNN = os.path.join(HERE, "_ref", "libref_knn.so")
 
-_ras = None
+_ras = {}
 _knn = None
 
 
@@ -20,17 +21,22 @@ def available() -> bool:
     return os.path.exists(RAS)
 
 
-def _load():
-    global _ras
-    if _ras is None:
-        _ras = C.CDLL(RAS)
+def patched_available() -> bool:
+    return os.path.exists(RAS_PATCHED)
+
+
+def _load(patched: bool = False):
+    lib = _ras.get(patched)
+    if lib is None:
+        lib = C.CDLL(RAS_PATCHED if patched else RAS)
         vp, i, f = C.c_void_p, C.c_int, C.c_float
-        _ras.ref_forward.argtypes = [i, i, i, vp, i, i, vp, vp, vp, vp, vp, vp, f, vp, vp, vp, vp, vp, f, f, f, f,
-                                     vp, vp, vp, vp, vp]
-        _ras.ref_backward.argtypes = [i, i, i, vp, i, i, vp, vp, vp, vp, vp, vp, f, vp, vp, vp, vp, vp, f, f, f, f, vp,
-                                      vp, vp, vp, vp] + [vp] * 11
-        _ras.ref_export_state.argtypes = [vp] * 8
-    return _ras
+        lib.ref_forward.argtypes = [i, i, i, vp, i, i, vp, vp, vp, vp, vp, vp, f, vp, vp, vp, vp, vp, f, f, f, f,
+                                    vp, vp, vp, vp, vp]
+        lib.ref_backward.argtypes = [i, i, i, vp, i, i, vp, vp, vp, vp, vp, vp, f, vp, vp, vp, vp, vp, f, f, f, f, vp,
+                                     vp, vp, vp, vp] + [vp] * 11
+        lib.ref_export_state.argtypes = [vp] * 8
+        _ras[patched] = lib
+    return lib
 
 
 def _p(t):
@@ -40,8 +46,9 @@ def _p(t):
 class RefRasterizer:
     """One view at a time, like the reference.  `cam` is any object with the GaussianRasterizationSettings fields."""
 
-    def __init__(self, cam):
+    def __init__(self, cam, patched: bool = False):
         self.cam = cam
+        self.patched = patched
         dev = "cuda"
         self.view = cam.viewmatrix.reshape(-1).float().to(dev).contiguous()
         self.proj = cam.projmatrix.reshape(-1).float().to(dev).contiguous()
@@ -53,8 +60,10 @@ class RefRasterizer:
         self.c_x = float(cam.c_x) if cam.c_x is not None else 0.5 * self.W
         self.c_y = float(cam.c_y) if cam.c_y is not None else 0.5 * self.H
 
-    def forward(self, means3D, opacities, colors, scales, rotations, semantic=None):
-        lib = _load()
+    def forward(self, means3D, opacities, colors, scales, rotations, semantic=None, shs=None, cov3D_precomp=None):
+        """Exactly one of (colors | shs [P,M,3]) and one of (scales + rotations | cov3D_precomp [P,6]), as
+        R/diff_gaussian_rasterization/__init__.py:214-218; D = cam.sh_degree, M = shs.shape[1] (rasterize_points.cu:85-89)."""
+        lib = _load(self.patched)
         P = means3D.shape[0]
         dev = means3D.device
         if semantic is None:
@@ -67,31 +76,37 @@ class RefRasterizer:
         alpha = torch.zeros(1, H, W, device=dev)
         radii = torch.zeros(P, dtype=torch.int32, device=dev)
         cam = self.cam
-        R = lib.ref_forward(P, 0, 0, _p(self.bg), W, H, _p(means3D), None, _p(colors), _p(semantic), _p(opacities),
-                            _p(scales), float(cam.scale_modifier), _p(rotations), None, _p(self.view), _p(self.proj),
+        D = int(cam.sh_degree) if shs is not None else 0
+        M = int(shs.shape[1]) if shs is not None else 0
+        self.DM = (D, M)
+        R = lib.ref_forward(P, D, M, _p(self.bg), W, H, _p(means3D), _p(shs), _p(colors), _p(semantic), _p(opacities),
+                            _p(scales), float(cam.scale_modifier), _p(rotations), _p(cov3D_precomp), _p(self.view), _p(self.proj),
                             _p(self.campos), self.c_x, self.c_y, float(cam.tanfovx), float(cam.tanfovy), _p(color),
                             _p(feat), _p(depth), _p(alpha), _p(radii))
         if R < 0:
             raise RuntimeError("reference forward failed")
         self.saved = (means3D, opacities, colors, scales, rotations, radii, alpha)
+        self.saved_opt = (shs, cov3D_precomp)
         return dict(color=color, feature=feat, depth=depth, alpha=alpha, radii=radii, num_rendered=R)
 
     def backward(self, dL_dcolor, dL_ddepth, dL_dalpha, alphas=None):
         """Calls Rasterizer::backward with the argument order the C++ expects (the Python swap bug Q2 is not
         reproduced here).  `alphas` defaults to what the forward returned (all zeros)."""
-        lib = _load()
+        lib = _load(self.patched)
         means3D, opacities, colors, scales, rotations, radii, alpha = self.saved
+        shs, cov3D_precomp = self.saved_opt
+        D, M = self.DM
         P = means3D.shape[0]
         dev = means3D.device
         H, W = self.H, self.W
         z = lambda *s: torch.zeros(*s, device=dev)
         g = dict(means2D=z(P, 3), conic=z(P, 4), opacity=z(P, 1), colors=z(P, 3), semantic=z(P, 32), depth=z(P, 1),
-                 means3D=z(P, 3), cov3D=z(P, 6), sh=z(P, 1, 3), scales=z(P, 3), rotations=z(P, 4))
+                 means3D=z(P, 3), cov3D=z(P, 6), sh=z(P, max(M, 1), 3), scales=z(P, 3), rotations=z(P, 4))
         dfeat = z(32, H, W)
         cam = self.cam
-        rc = lib.ref_backward(P, 0, 0, _p(self.bg), W, H, _p(means3D), None, _p(colors), _p(self.semantic),
+        rc = lib.ref_backward(P, D, M, _p(self.bg), W, H, _p(means3D), _p(shs), _p(colors), _p(self.semantic),
                               _p(alpha if alphas is None else alphas), _p(scales), float(cam.scale_modifier),
-                              _p(rotations), None, _p(self.view), _p(self.proj), _p(self.campos), self.c_x, self.c_y,
+                              _p(rotations), _p(cov3D_precomp), _p(self.view), _p(self.proj), _p(self.campos), self.c_x, self.c_y,
                               float(cam.tanfovx), float(cam.tanfovy), _p(radii), _p(dL_dcolor.contiguous()), _p(dfeat),
                               _p(dL_ddepth.contiguous()), _p(dL_dalpha.contiguous()), _p(g["means2D"]), _p(g["conic"]),
                               _p(g["opacity"]), _p(g["colors"]), _p(g["semantic"]), _p(g["depth"]), _p(g["means3D"]),
@@ -101,7 +116,7 @@ class RefRasterizer:
         return g
 
     def export_state(self, R):
-        lib = _load()
+        lib = _load(self.patched)
         dev = "cuda"
         P = self.saved[0].shape[0]
         tiles = ((self.W + 15) // 16) * ((self.H + 15) // 16)

@@ -32,6 +32,23 @@ def rel_err(a, b):
     return float((a - b).abs().max() / (b.abs().max() + 1e-30))
 
 
+def elem_violations(a, b, rtol=1e-4, floor=1e-6):
+    """Per-element gradient criterion |a - b| <= rtol |b| + floor max|b|  (BASELINE.json: "gradients within 1e-4
+    relative"; the floor keeps elements that are sums of cancelling terms from being judged against their own rounding
+    noise).  Returns (number of violating elements, number of elements)."""
+    a = a.detach().double().cpu().reshape(-1)
+    b = b.detach().double().cpu().reshape(-1)
+    bad = (a - b).abs() > rtol * b.abs() + floor * b.abs().max()
+    return int(bad.sum()), a.numel()
+
+
+def final_T(st):
+    """[V,H,W] final transmittance per pixel, as the forward left it in the image workspace."""
+    L = RZ.workspace_layout(st.P, st.V, st.W, st.H, st.channels, st.sh_coeffs, st.capacity)
+    n = st.V * st.H * st.W
+    return st.image[L.final_T: L.final_T + 4 * n].view(torch.float32).view(st.V, st.H, st.W).clone()
+
+
 def export_view(st, view=0):
     """(keys u64-as-int64, point_list, ranges [T,2], n_contrib [H,W]) of one view in the reference's format."""
     from dynamic3dgaussians_b200 import _lib

@@ -1,0 +1,288 @@
+"""GPU parity tests (pytest -m gpu) for the rasterizer branches and sizes round 1 left untested (VERDICT r01 missing #2, #3,
+weak #1, #2): the SH colour path (forward.cu:20-71, backward.cu:20-139), cov3D_precomp (forward.cu:217-225; dL_dcov3D
+returned, backward.cu:295-358 bypassed), scale_modifier != 1, the FULL headline config against the reference binary, and
+the gradients at headline size against the reference's own backward with the four minimal repairs of SURVEY.md 2.4
+(oracle/_ref/libref_rasterizer_patched.so, oracle/build_ref.py PATCHES).
+
+Tolerances are BASELINE.json's: forward artefacts identical to the reference binary; gradients <= 1e-4 relative -- checked
+in the max-norm (helpers.rel_err) AND per element with a floor: |a - b| <= 1e-4 |b| + 1e-6 max|b| (helpers.elem_close)."""
+import os
+import sys
+
+import pytest
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from helpers import O, RZ, elem_violations, export_view, final_T, rel_err, settings_from_spec  # noqa: E402
+from dynamic3dgaussians_b200 import scenes  # noqa: E402
+from oracle import ref_cuda  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+IMG_TOL = 1e-5
+GRAD_TOL = 1e-4
+
+
+def _rv(sc):
+    return {k: v.cuda() for k, v in sc.rendervar().items()}
+
+
+def _cpu_leaves(d):
+    return {k: v.detach().cpu().clone().requires_grad_(True) for k, v in d.items()}
+
+
+def _check_grad(name, mine, ref, tol=GRAD_TOL, elem_frac=0.0):
+    assert rel_err(mine, ref) <= tol, (name, rel_err(mine, ref))
+    bad, n = elem_violations(mine, ref)
+    assert bad <= elem_frac * n, (name, bad, n)
+
+
+def _sh_inputs(P, M, seed):
+    g = torch.Generator().manual_seed(seed)
+    shs = torch.randn(P, M, 3, generator=g) * 0.35
+    shs[:, 0] = torch.randn(P, 3, generator=g) * 1.5 - 0.8      # C0 * sh0 + 0.5 < 0 for about a quarter: clamped at 0
+    return shs                                                  # (forward.cu:63-70), which also masks the gradient
+
+
+@pytest.mark.parametrize("deg,M", [(0, 16), (1, 16), (2, 16), (3, 16), (2, 9), (0, 1)])
+def test_sh_colour_path(deg, M):
+    """shs= instead of colors_precomp: colours evaluated per (view, Gaussian) from the view direction.  Forward equals
+    the reference binary bit for bit; dL/dsh, the view-direction term of dL/dmeans3D and the `clamped` masking equal
+    autograd through the oracle."""
+    P = 6000
+    sc = scenes.make_scene_c1(P, seed=deg + 10)
+    cs = scenes.camera_c1()
+    st_, oc = settings_from_spec(cs, bg=(0.3, 0.1, 0.2))
+    st_ = st_._replace(sh_degree=deg)
+    oc = oc._replace(sh_degree=deg)
+    rv = _rv(sc)
+    shs = _sh_inputs(P, M, deg)
+    color, _, depth, alpha, radii, st = RZ.forward_views([st_], rv["means3D"], rv["opacities"], None, rv["scales"],
+                                                         rv["rotations"], shs=shs.cuda())
+    if ref_cuda.available():
+        rr = ref_cuda.RefRasterizer(st_)
+        ro = rr.forward(rv["means3D"], rv["opacities"], None, rv["scales"], rv["rotations"], shs=shs.cuda())
+        assert torch.equal(radii[0], ro["radii"])
+        assert torch.equal(color[0], ro["color"]) and torch.equal(depth[0], ro["depth"])
+    leaves = _cpu_leaves({k: rv[k] for k in ("means3D", "opacities", "scales", "rotations")})
+    shl = shs.clone().requires_grad_(True)
+    out = O.rasterize(oc, leaves["means3D"], leaves["opacities"], scales=leaves["scales"],
+                      rotations=leaves["rotations"], shs=shl, collect_fragile=True)
+    ok = ~out["fragile"]
+    assert torch.equal(radii[0].cpu(), out["pre"]["radii"])
+    assert float((color[0].cpu() - out["color"]).abs()[:, ok].max()) <= IMG_TOL
+    vis = out["pre"]["radii"] > 0
+    assert bool(out["pre"]["clamped"][vis].any()) and not bool(out["pre"]["clamped"][vis].all())
+    gen = torch.Generator().manual_seed(3)
+    okf = ok.float()
+    gc, gd = [torch.randn(c, cs.h, cs.w, generator=gen) * okf for c in (3, 1)]
+    ((out["color"] * gc).sum() + (out["depth"] * gd).sum()).backward()
+    g = RZ.backward_views(st, rv["means3D"], rv["opacities"], None, rv["scales"], rv["rotations"], None, shs.cuda(),
+                          None, gc.cuda()[None], None, gd.cuda()[None], None)
+    assert g["sh"].shape == (P, M, 3) and g["colors"] is None
+    _check_grad("sh", g["sh"], shl.grad)
+    _check_grad("means3D", g["means3D"], leaves["means3D"].grad)
+    _check_grad("opacity", g["opacity"], leaves["opacities"].grad)
+    _check_grad("scales", g["scales"], leaves["scales"].grad)
+    _check_grad("rotations", g["rotations"], leaves["rotations"].grad)
+    # coefficients above the active degree get exactly zero gradient (backward.cu:20-139 never touches them)
+    if (deg + 1) ** 2 < M:
+        assert float(g["sh"][:, (deg + 1) ** 2:].abs().max()) == 0.0
+
+
+def test_sh_batched_views_equal_single_views():
+    """SH colours differ per view (the view direction): a batch must equal its views rendered alone, and dL/dsh must be
+    the sum over the views."""
+    P = 20_000
+    sc = scenes.make_scene_c2(P, seed=8)
+    cams = scenes.cameras_c2(3, w=320, h=180, f=233.0)
+    sets = [settings_from_spec(c)[0]._replace(sh_degree=3) for c in cams]
+    rv = _rv(sc)
+    shs = _sh_inputs(P, 16, 5).cuda()
+    cb, _, db, _, rb, stb = RZ.forward_views(sets, rv["means3D"], rv["opacities"], None, rv["scales"], rv["rotations"],
+                                             shs=shs)
+    gen = torch.Generator().manual_seed(1)
+    gc = torch.randn(3, 3, 180, 320, generator=gen).cuda()
+    gb = RZ.backward_views(stb, rv["means3D"], rv["opacities"], None, rv["scales"], rv["rotations"], None, shs, None,
+                           gc, None, None, None)
+    acc = None
+    for v, s in enumerate(sets):
+        c1, _, d1, _, r1, s1 = RZ.forward_views([s], rv["means3D"], rv["opacities"], None, rv["scales"],
+                                                rv["rotations"], shs=shs)
+        assert torch.equal(cb[v], c1[0]) and torch.equal(db[v], d1[0]) and torch.equal(rb[v], r1[0])
+        g1 = RZ.backward_views(s1, rv["means3D"], rv["opacities"], None, rv["scales"], rv["rotations"], None, shs,
+                               None, gc[v:v + 1], None, None, None)
+        part = {k: g1[k] for k in ("sh", "means3D", "opacity")}
+        acc = part if acc is None else {k: acc[k] + part[k] for k in acc}
+    for k in acc:
+        assert rel_err(gb[k], acc[k]) <= GRAD_TOL, k
+
+
+def test_cov3d_precomp_path():
+    """cov3D_precomp instead of scales + rotations (forward.cu:217-225): forward identical to the reference binary,
+    dL/dcov3D (6 unique entries, off-diagonals carrying both symmetric halves) equal to autograd through the oracle."""
+    P = 8000
+    sc = scenes.make_scene_c1(P, seed=21)
+    cs = scenes.camera_c1()
+    st_, oc = settings_from_spec(cs, bg=(0.0, 0.2, 0.4))
+    rv = _rv(sc)
+    A = O._Arith(torch.float32)
+    cov = O.compute_cov3d(A, rv["scales"].cpu(), rv["rotations"].cpu(), A.c(1.0)).contiguous()
+    color, _, depth, alpha, radii, st = RZ.forward_views([st_], rv["means3D"], rv["opacities"], rv["colors_precomp"],
+                                                         None, None, cov3D_precomp=cov.cuda())
+    # the same Gaussians through scales + rotations give the same bits (cov3D is computed with the same roundings)
+    c2, _, d2, _, r2, _ = RZ.forward_views([st_], rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"],
+                                           rv["rotations"])
+    assert torch.equal(color, c2) and torch.equal(depth, d2) and torch.equal(radii, r2)
+    if ref_cuda.available():
+        rr = ref_cuda.RefRasterizer(st_)
+        ro = rr.forward(rv["means3D"], rv["opacities"], rv["colors_precomp"], None, None, cov3D_precomp=cov.cuda())
+        assert torch.equal(radii[0], ro["radii"]) and torch.equal(color[0], ro["color"])
+        assert torch.equal(depth[0], ro["depth"])
+    leaves = _cpu_leaves({k: rv[k] for k in ("means3D", "opacities", "colors_precomp")})
+    covl = cov.clone().requires_grad_(True)
+    out = O.rasterize(oc, leaves["means3D"], leaves["opacities"], colors_precomp=leaves["colors_precomp"],
+                      cov3D_precomp=covl, collect_fragile=True)
+    ok = ~out["fragile"]
+    gen = torch.Generator().manual_seed(4)
+    okf = ok.float()
+    gc, gd, ga = [torch.randn(c, cs.h, cs.w, generator=gen) * okf for c in (3, 1, 1)]
+    ((out["color"] * gc).sum() + (out["depth"] * gd).sum() + (out["alpha"] * ga).sum()).backward()
+    g = RZ.backward_views(st, rv["means3D"], rv["opacities"], rv["colors_precomp"], None, None, cov.cuda(), None, None,
+                          gc.cuda()[None], None, gd.cuda()[None], ga.cuda()[None])
+    assert g["scales"] is None and g["rotations"] is None and g["cov3D"].shape == (P, 6)
+    _check_grad("cov3D", g["cov3D"], covl.grad)
+    _check_grad("means3D", g["means3D"], leaves["means3D"].grad)
+    _check_grad("opacity", g["opacity"], leaves["opacities"].grad)
+    _check_grad("colors", g["colors"], leaves["colors_precomp"].grad)
+
+
+def test_scale_modifier():
+    """scale_modifier = 0.7 (forward.cu:134-136): forward identical to the reference binary, gradients vs the oracle."""
+    P = 8000
+    sc = scenes.make_scene_c1(P, seed=31)
+    cs = scenes.camera_c1()
+    st_, oc = settings_from_spec(cs)
+    st_ = st_._replace(scale_modifier=0.7)
+    oc = oc._replace(scale_modifier=0.7)
+    rv = _rv(sc)
+    color, _, depth, alpha, radii, st = RZ.forward_views([st_], rv["means3D"], rv["opacities"], rv["colors_precomp"],
+                                                         rv["scales"], rv["rotations"])
+    c1, _, _, _, r1, _ = RZ.forward_views([st_._replace(scale_modifier=1.0)], rv["means3D"], rv["opacities"],
+                                          rv["colors_precomp"], rv["scales"], rv["rotations"])
+    assert not torch.equal(radii, r1)
+    if ref_cuda.available():
+        rr = ref_cuda.RefRasterizer(st_)
+        ro = rr.forward(rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"])
+        assert torch.equal(radii[0], ro["radii"]) and torch.equal(color[0], ro["color"])
+    leaves = _cpu_leaves(rv)
+    out = O.rasterize(oc, leaves["means3D"], leaves["opacities"], colors_precomp=leaves["colors_precomp"],
+                      scales=leaves["scales"], rotations=leaves["rotations"], collect_fragile=True)
+    ok = ~out["fragile"]
+    assert torch.equal(radii[0].cpu(), out["pre"]["radii"])
+    gen = torch.Generator().manual_seed(5)
+    gc = torch.randn(3, cs.h, cs.w, generator=gen) * ok.float()
+    (out["color"] * gc).sum().backward()
+    g = RZ.backward_views(st, rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"], None,
+                          None, None, gc.cuda()[None], None, None, None)
+    _check_grad("scales", g["scales"], leaves["scales"].grad)
+    _check_grad("rotations", g["rotations"], leaves["rotations"].grad)
+    _check_grad("means3D", g["means3D"], leaves["means3D"].grad)
+
+
+@pytest.mark.skipif(not ref_cuda.available(), reason="oracle/_ref not built")
+def test_full_headline_config_bit_exact_vs_reference():
+    """BASELINE.json configs[1] at FULL size -- 300k Gaussians, all 27 views of 640x360, one batch: the large-launch
+    kernel variants (blend_forward_kernel<3,1>, list-length launch order) against the reference binary, view by view."""
+    sc = scenes.make_scene_c2(300_000)
+    cams = scenes.cameras_c2(27)
+    rv = _rv(sc)
+    sets = [settings_from_spec(c, bg=(0.05, 0.1, 0.15))[0] for c in cams]
+    color, _, depth, alpha, radii, st = RZ.forward_views(sets, rv["means3D"], rv["opacities"], rv["colors_precomp"],
+                                                         rv["scales"], rv["rotations"])
+    total = 0
+    for v, s in enumerate(sets):
+        rr = ref_cuda.RefRasterizer(s)
+        ro = rr.forward(rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"])
+        rs = rr.export_state(ro["num_rendered"])
+        keys, plist, ranges, ncon = export_view(st, v)
+        total += ro["num_rendered"]
+        assert torch.equal(radii[v], ro["radii"]), v
+        assert keys.numel() == ro["num_rendered"], v
+        assert torch.equal(keys, rs["keys"]) and torch.equal(plist, rs["point_list"]), v
+        assert torch.equal(ranges, rs["ranges"]) and torch.equal(ncon, rs["n_contrib"]), v
+        assert torch.equal(color[v], ro["color"]) and torch.equal(depth[v], ro["depth"]), v
+    assert total == st.num_rendered
+
+
+@pytest.mark.skipif(not ref_cuda.patched_available(), reason="oracle/_ref/libref_rasterizer_patched.so not built")
+@pytest.mark.parametrize("P,n_views", [(10_000, 1), (300_000, 3)])
+def test_gradients_vs_patched_reference_backward(P, n_views):
+    """Second gradient witness: the reference's own backward kernels with the minimal repairs of
+    oracle/build_ref.py PATCHES, at C1 and at HEADLINE size (300k Gaussians, 640x360), where autograd through the oracle
+    cannot run.  Colour, depth and alpha cotangents.  Two routes for T_final:
+      * handed over directly (alphas = -final_T): <= 1e-4 in the max-norm and per element;
+      * as the reference recovers it, 1 - alpha_out (backward.cu:484): float32 cancellation makes every T of a nearly
+        saturated pixel ~1e-3 relatively wrong -- the reference's own precision, bounded here at 5e-3.
+    Remaining documented difference of the reference formulas: 1 / (det^2 + 1e-7) in computeCov2DCUDA (backward.cu:215;
+    det >= 0.09 after the +0.3 low-pass => <= 1.3e-5 relative)."""
+    if P == 10_000:
+        sc, cams = scenes.make_scene_c1(P), [scenes.camera_c1()]
+    else:
+        sc, cams = scenes.make_scene_c2(P), scenes.cameras_c2(27)[4:4 + 3 * 9:9]      # one camera per elevation ring
+    rv = _rv(sc)
+    sets = [settings_from_spec(c, bg=(0.2, 0.3, 0.1))[0] for c in cams[:n_views]]
+    H, W = sets[0].image_height, sets[0].image_width
+    color, _, depth, alpha, radii, st = RZ.forward_views(sets, rv["means3D"], rv["opacities"], rv["colors_precomp"],
+                                                         rv["scales"], rv["rotations"])
+    fT = final_T(st)
+    gen = torch.Generator().manual_seed(11)
+    gc = torch.randn(n_views, 3, H, W, generator=gen).cuda()
+    gd = (torch.randn(n_views, 1, H, W, generator=gen) * 0.1).cuda()
+    ga = torch.randn(n_views, 1, H, W, generator=gen).cuda()
+    g = RZ.backward_views(st, rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"], None,
+                          None, None, gc, None, gd, ga)
+    names = ("means3D", "opacity", "colors", "scales", "rotations")
+    acc = {True: None, False: None}
+    for v, s in enumerate(sets):
+        rr = ref_cuda.RefRasterizer(s, patched=True)
+        ro = rr.forward(rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"])
+        assert torch.equal(ro["color"], color[v]) and torch.equal(ro["radii"], radii[v])
+        assert torch.equal(ro["alpha"], alpha[v])                    # Q1 repaired: the reference stores sum(alpha T) now
+        # colour = C + T bg is identical with a non-zero background, so the product's final T IS the reference's
+        assert float(((1.0 - fT[v]) - ro["alpha"][0]).abs().max()) <= 2e-5
+        for direct in (True, False):
+            rg = rr.backward(gc[v], gd[v], ga[v], alphas=(-fT[v]).contiguous() if direct else None)
+            if direct:
+                _check_grad(f"means2D[{v}]", g["means2D"][v], rg["means2D"], elem_frac=1e-3)
+            else:
+                assert rel_err(g["means2D"][v], rg["means2D"]) <= 5e-3
+            part = {k: rg[k] for k in names}
+            acc[direct] = part if acc[direct] is None else {k: acc[direct][k] + part[k] for k in names}
+    for k in names:
+        _check_grad(k, g[k], acc[True][k].reshape(g[k].shape), elem_frac=1e-3)
+        assert rel_err(g[k], acc[False][k].reshape(g[k].shape)) <= 5e-3, k
+
+
+def test_mark_visible_half_behind_the_camera():
+    """checkFrustum (rasterizer_impl.cu:54-66): present = (view * p).z > 0, on a cloud that straddles the camera plane."""
+    from diff_gaussian_rasterization import GaussianRasterizer as Renderer
+    cs = scenes.camera_c1()
+    cam, oc = settings_from_spec(cs)
+    g = torch.Generator().manual_seed(2)
+    pts = (torch.rand(50_000, 3, generator=g) * 2 - 1) * 6.0
+    pts[:16] = 0.0                                                          # on the optical axis, in front
+    w2c = torch.tensor(cs.w2c, dtype=torch.float64)
+    z = (pts.double() @ w2c[:3, :3].T + w2c[:3, 3])[:, 2]
+    safe = z.abs() > 1e-4                                                   # float32 vs float64 sign near the plane
+    vis = Renderer(raster_settings=cam).markVisible(pts.cuda()).cpu()
+    assert vis.dtype == torch.bool and vis.shape == (50_000,)
+    assert 0.2 < float(vis.float().mean()) < 0.8
+    assert torch.equal(vis[safe], (z > 0)[safe])
+    # and it agrees with the forward's cull: radii > 0 implies visible
+    sc = scenes.make_scene_c1(4000, seed=6)
+    rv = _rv(sc)
+    rv["means3D"] = rv["means3D"] * 4.0
+    _, _, _, _, radii, _ = RZ.forward_views([cam], rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"],
+                                            rv["rotations"])
+    vis = Renderer(raster_settings=cam).markVisible(rv["means3D"])
+    assert bool(vis[radii[0] > 0].all()) and not bool(vis.all())
