@@ -13,7 +13,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GSR_LIB_PATH") or os.path.join(HERE, "libgsr_b200.so")
 
 EXPORTED_SYMBOLS = [
-    "gsr_abi_version", "gsr_strerror", "gsr_last_cuda_error", "gsr_workspace_sizes", "gsr_workspace_layout",
+    "gsr_abi_version", "gsr_strerror", "gsr_last_cuda_error", "gsr_set_option", "gsr_get_option",
+    "gsr_workspace_sizes", "gsr_workspace_layout",
     "gsr_forward_geometry", "gsr_forward_render", "gsr_read_counters", "gsr_backward", "gsr_mark_visible",
     "gsr_export_view_binning", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_knn_temp_bytes", "gsr_knn",
     "gsr_dyn_losses_temp_bytes", "gsr_dyn_losses",
@@ -40,8 +41,12 @@ class GsrCamera(C.Structure):
         ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("c_x", C.c_float), ("c_y", C.c_float),
         ("scale_modifier", C.c_float), ("sh_degree", C.c_int32), ("prefiltered", C.c_int32),
         ("bg", C.c_float * 8), ("viewmatrix", C.c_float * 16), ("projmatrix", C.c_float * 16),
-        ("campos", C.c_float * 3), ("tile_row_begin", C.c_int32), ("tile_row_end", C.c_int32),
+        ("campos", C.c_float * 3), ("tile_row_begin", C.c_int32), ("tile_row_end", C.c_int32), ("debug", C.c_int32),
     ]
+
+
+FLAG_DEBUG = 1
+ABI_VERSION = 4
 
 
 class GsrWorkspaceSizes(C.Structure):
@@ -84,9 +89,9 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.gsr_workspace_layout.argtypes = [i32, i32, i32, i32, i32, i32, i64, C.POINTER(GsrLayout)]
     lib.gsr_forward_geometry.argtypes = [C.POINTER(GsrCamera), i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, sz,
                                          vp, vp, vp]
-    lib.gsr_forward_render.argtypes = [i32, i32, i32, i32, i32, i32, i64, vp, vp, vp, i32] + [vp] * 9
+    lib.gsr_forward_render.argtypes = [i32, i32, i32, i32, i32, i32, i64, vp, vp, vp, i32] + [vp] * 8 + [i32, vp]
     lib.gsr_read_counters.argtypes = [vp, vp, vp]
-    lib.gsr_backward.argtypes = [i32, i32, i32, i32, i32, i32, i64] + [vp] * 9 + [i32] + [vp] * 21
+    lib.gsr_backward.argtypes = [i32, i32, i32, i32, i32, i32, i64] + [vp] * 9 + [i32] + [vp] * 21 + [i32, vp]
     lib.gsr_mark_visible.argtypes = [C.POINTER(GsrCamera), i32, vp, vp, vp]
     lib.gsr_export_view_binning.argtypes = [i32, i32, i32, i32, i32, i32, i32, i64, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.gsr_sort_temp_bytes.restype = sz
@@ -103,7 +108,9 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.gsr_image_loss_forward.argtypes = [i64, i32, i32, vp, vp, C.c_float, C.c_float, vp, sz, vp, vp]
     lib.gsr_image_loss_backward.argtypes = [i64, i32, i32, vp, vp, C.c_float, C.c_float, vp, sz, vp, vp, vp]
     lib.gsr_adam_step.argtypes = [i32, C.POINTER(GsrAdamTensor), C.c_double, C.c_double, C.c_double, vp, vp]
-    lib.gsr_fp32_peak_probe.argtypes = [vp, i32, vp]
+    lib.gsr_fp32_peak_probe.argtypes = [vp, i32, i32, vp]
+    lib.gsr_set_option.argtypes = [C.c_char_p, i32]
+    lib.gsr_get_option.argtypes = [C.c_char_p, C.POINTER(C.c_int)]
     lib.gsr_stage_timing_enable.argtypes = [i32]
     lib.gsr_stage_name.restype = C.c_char_p
     lib.gsr_stage_name.argtypes = [i32]
@@ -118,11 +125,28 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.gsr_l1_u8_loss_forward.argtypes = [i64, i32, i32, vp, vp, vp, C.c_float, vp, vp]
     lib.gsr_l1_u8_loss_backward.argtypes = [i64, i32, i32, vp, vp, vp, C.c_float, vp, vp, vp]
     for name in EXPORTED_SYMBOLS:
-        fn = getattr(lib, name)
-        if fn.restype is C.c_int and name not in ("gsr_abi_version",):
-            pass
+        getattr(lib, name)                                   # every declared entry point must be exported
+    if lib.gsr_abi_version() != ABI_VERSION:
+        raise RuntimeError(f"{LIB_PATH} has ABI version {lib.gsr_abi_version()}, this package needs {ABI_VERSION}: "
+                           f"rebuild with `python -m dynamic3dgaussians_b200.build --force`")
     _lib = lib
+    # The library itself never reads the environment (gsr_set_option); the tuning variables the tools of round 1 used are
+    # forwarded once, here, by the host binding.
+    for env, key in (("GSR_BLEND_ILP", "blend_ilp"), ("GSR_BWD_COST_ORDER", "bwd_cost_order"), ("GSR_NVTX", "nvtx")):
+        v = os.environ.get(env)
+        if v not in (None, ""):
+            check(lib.gsr_set_option(key.encode(), int(v)), f"set_option({key})")
     return lib
+
+
+def set_option(key: str, value: int) -> None:
+    check(load().gsr_set_option(key.encode(), int(value)), f"set_option({key})")
+
+
+def get_option(key: str) -> int:
+    v = C.c_int(0)
+    check(load().gsr_get_option(key.encode(), C.byref(v)), f"get_option({key})")
+    return int(v.value)
 
 
 def check(status: int, what: str = "") -> None:

@@ -17,16 +17,53 @@ void set_cuda_error(cudaError_t e, const char* where) {
 static bool g_timing = false;
 static cudaEvent_t g_ev[ST_COUNT][2];
 static bool g_ev_made = false, g_ev_used[ST_COUNT];
+static Options g_options;
+static thread_local bool g_debug_sync = false;     // this thread's current call runs in debug mode
+static thread_local int g_debug_status = GSR_OK;
+
+Options& options() { return g_options; }
+
+static const char* const kStageNames[ST_COUNT] = {
+    "preprocess", "depth_sort", "instance_count", "emit_supertile_instances", "supertile_sort", "tile_offsets",
+    "scatter_records", "blend_forward", "grad_zero", "blend_backward", "preprocess_backward"};
+
+}  // namespace gsr
+
+#include <nvtx3/nvToolsExt.h>     // header-only; resolves the profiler's injection library lazily, a no-op without one
+
+namespace gsr {
 
 void stage_begin(int st, cudaStream_t s) {
+    if (g_options.nvtx) nvtxRangePushA(kStageNames[st]);
     if (!g_timing) return;
     cudaEventRecord(g_ev[st][0], s);
 }
 void stage_end(int st, cudaStream_t s) {
-    if (!g_timing) return;
-    cudaEventRecord(g_ev[st][1], s);
-    g_ev_used[st] = true;
+    if (g_timing) {
+        cudaEventRecord(g_ev[st][1], s);
+        g_ev_used[st] = true;
+    }
+    if (g_options.nvtx) nvtxRangePop();
+    if (g_debug_sync && g_debug_status == GSR_OK) {
+        // the reference's debug mode: synchronise after every stage so that a faulting kernel is named
+        // (CHECK_CUDA, R/cuda_rasterizer/auxiliary.h:172-179)
+        cudaError_t e = cudaStreamSynchronize(s);
+        if (e == cudaSuccess) e = cudaGetLastError();
+        if (e != cudaSuccess) {
+            char where[96];
+            snprintf(where, sizeof(where), "stage '%s' (debug sync)", kStageNames[st]);
+            set_cuda_error(e, where);
+            g_debug_status = GSR_ERR_CUDA;
+        }
+    }
 }
+
+DebugSyncScope::DebugSyncScope(bool on) {
+    g_debug_sync = on;
+    g_debug_status = GSR_OK;
+}
+DebugSyncScope::~DebugSyncScope() { g_debug_sync = false; }
+int DebugSyncScope::status() const { return g_debug_status; }
 
 static void fill_cam(const GsrCamera& c, CamDev& d) {
     memset(&d, 0, sizeof(d));
@@ -58,16 +95,42 @@ static void fill_cam(const GsrCamera& c, CamDev& d) {
     if (d.row_end < d.row_begin) d.row_end = d.row_begin;
 }
 
-__global__ void fp32_peak_kernel(float* out, int iters) {
-    // 8 independent FFMA chains per thread: enough ILP to saturate the FP32 pipes at full occupancy
-    float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f,
-          a6 = a0 + 6.f, a7 = a0 + 7.f;
+// FP32-pipe peak probes: 8 independent chains per thread, 16 steps per chain per trip (128 FFMA or 128 FFMA2 between
+// two loop branches, so the loop overhead is < 2 % of the issued instructions; the round-1 probe had 8 per trip and
+// read 14 % under nominal).  PACKED issues fp32x2 FFMA2 -- what the blend kernels issue.
+template <bool PACKED>
+__global__ void __launch_bounds__(256) fp32_peak_kernel(float* out, int iters) {
     const float m = 0.9999f, c = 1e-4f;
-    for (int i = 0; i < iters; ++i) {
-        a0 = __fmaf_rn(a0, m, c); a1 = __fmaf_rn(a1, m, c); a2 = __fmaf_rn(a2, m, c); a3 = __fmaf_rn(a3, m, c);
-        a4 = __fmaf_rn(a4, m, c); a5 = __fmaf_rn(a5, m, c); a6 = __fmaf_rn(a6, m, c); a7 = __fmaf_rn(a7, m, c);
+    if constexpr (!PACKED) {
+        float a[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = threadIdx.x * 1e-3f + (float)k;
+        for (int i = 0; i < iters; ++i) {
+#pragma unroll
+            for (int u = 0; u < 16; ++u)
+#pragma unroll
+                for (int k = 0; k < 8; ++k) a[k] = __fmaf_rn(a[k], m, c);
+        }
+        float sum = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) sum += a[k];
+        out[blockIdx.x * blockDim.x + threadIdx.x] = sum;
+    } else {
+        float2 a[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = make_float2(threadIdx.x * 1e-3f + (float)k, (float)k - threadIdx.x * 1e-3f);
+        const float2 m2 = make_float2(m, m), c2 = make_float2(c, c);
+        for (int i = 0; i < iters; ++i) {
+#pragma unroll
+            for (int u = 0; u < 16; ++u)
+#pragma unroll
+                for (int k = 0; k < 8; ++k) a[k] = __ffma2_rn(a[k], m2, c2);
+        }
+        float sum = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) sum += a[k].x + a[k].y;
+        out[blockIdx.x * blockDim.x + threadIdx.x] = sum;
     }
-    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
 }
 
 }  // namespace gsr
@@ -76,7 +139,7 @@ using namespace gsr;
 
 extern "C" {
 
-int gsr_abi_version(void) { return 3; }
+int gsr_abi_version(void) { return 4; }
 
 const char* gsr_strerror(int status) {
     switch (status) {
@@ -91,6 +154,29 @@ const char* gsr_strerror(int status) {
 }
 
 const char* gsr_last_cuda_error(void) { return g_cuda_err; }
+
+static int* option_slot(const char* key) {
+    if (!key) return nullptr;
+    if (!strcmp(key, "blend_ilp")) return &g_options.blend_ilp;
+    if (!strcmp(key, "bwd_cost_order")) return &g_options.bwd_cost_order;
+    if (!strcmp(key, "nvtx")) return &g_options.nvtx;
+    return nullptr;
+}
+
+int gsr_set_option(const char* key, int value) {
+    int* slot = option_slot(key);
+    if (!slot) return GSR_ERR_INVALID_ARGUMENT;
+    if (slot == &g_options.blend_ilp && (value < 0 || value > 2)) return GSR_ERR_INVALID_ARGUMENT;
+    *slot = value;
+    return GSR_OK;
+}
+
+int gsr_get_option(const char* key, int* value) {
+    const int* slot = option_slot(key);
+    if (!slot || !value) return GSR_ERR_INVALID_ARGUMENT;
+    *value = *slot;
+    return GSR_OK;
+}
 
 static int check_dims(int P, int V, int W, int H, int channels, int sh_coeffs, int64_t capacity) {
     if (P < 0 || V < 0 || W <= 0 || H <= 0 || capacity < 0 || sh_coeffs < 0 || sh_coeffs > 16)
@@ -145,6 +231,7 @@ int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels,
     Layout L;
     compute_layout(P, V, W, H, channels, sh_coeffs, 0, L);
     if (geom_bytes < L.geom_bytes) return GSR_ERR_WORKSPACE_TOO_SMALL;
+    DebugSyncScope dbg(cams_host[0].debug != 0);
 
     // cameras -> device as kernel arguments (a few hundred bytes each): unlike a copy from pageable host memory this
     // never makes the driver wait for the stream, and it can be captured into a CUDA graph
@@ -183,17 +270,18 @@ int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels,
     if (rc) return rc;
     if (num_rendered_dev)
         GSR_CUDA_TRY(cudaMemcpyAsync(num_rendered_dev, counters + CNT_RENDERED, 4, cudaMemcpyDeviceToDevice, s));
-    return GSR_OK;
+    return dbg.status();
 }
 
 int gsr_forward_render(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
                        const float* colors_precomp, const float* extra_colors, const float* features,
                        int num_features, void* geom_ws, void* binning_ws, void* image_ws, float* out_color,
-                       float* out_extra, float* out_depth, float* out_alpha, float* out_features,
+                       float* out_extra, float* out_depth, float* out_alpha, float* out_features, int flags,
                        gsr_stream_t stream) {
     cudaStream_t s = (cudaStream_t)stream;
     int rc = check_dims(P, V, W, H, channels, sh_coeffs, capacity);
     if (rc) return rc;
+    DebugSyncScope dbg((flags & GSR_FLAG_DEBUG) != 0);
     if (!geom_ws || !image_ws || !out_color || !out_depth || !out_alpha) return GSR_ERR_INVALID_ARGUMENT;
     if (capacity > 0 && !binning_ws) return GSR_ERR_INVALID_ARGUMENT;
     if (channels == 6 && (!extra_colors || !out_extra)) return GSR_ERR_INVALID_ARGUMENT;
@@ -209,13 +297,19 @@ int gsr_forward_render(int V, int P, int W, int H, int channels, int sh_coeffs, 
         rc = launch_blend_forward(V, W, H, channels, geom_ws, binning_ws, image_ws, L, out_color, out_extra, out_depth,
                                   out_alpha, s);
     }
-    if (rc || !features) return rc;
-    return launch_feature_forward(V, P, W, H, geom_ws, binning_ws, image_ws, L, features, out_features, s);
+    if (rc) return rc;
+    if (features) {
+        rc = launch_feature_forward(V, P, W, H, geom_ws, binning_ws, image_ws, L, features, out_features, s);
+        if (rc) return rc;
+        if (flags & GSR_FLAG_DEBUG) GSR_CUDA_TRY(cudaStreamSynchronize(s));
+    }
+    return dbg.status();
 }
 
 int gsr_read_counters(const void* geom_ws, uint32_t* counters_host, gsr_stream_t stream) {
     if (!geom_ws || !counters_host) return GSR_ERR_INVALID_ARGUMENT;
-    // the counter block sits at offset 0 of the geometry workspace for every problem size (compute_layout)
+    // the counter block sits at offset 0 of the geometry workspace for every problem size (compute_layout):
+    // [CNT_RENDERED, CNT_OVERFLOW, CNT_PREFILTER, supertile instances]
     GSR_CUDA_TRY(cudaMemcpyAsync(counters_host, geom_ws, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost,
                                  (cudaStream_t)stream));
     return GSR_OK;
@@ -227,11 +321,13 @@ int gsr_backward(int V, int P, int W, int H, int channels, int sh_coeffs, int64_
                  int num_features, const int32_t* radii, void* geom_ws, void* binning_ws, void* image_ws,
                  const float* dL_dcolor, const float* dL_dextra, const float* dL_ddepth, const float* dL_dalpha,
                  const float* dL_dfeatures_img, const float* label, float* dL_dmeans3D, float* dL_dmeans2D,
-                 float* dL_dcolors, float* dL_dextra_colors, float* dL_dopacity, float* dL_dscales,
-                 float* dL_drotations, float* dL_dcov3D, float* dL_dsh, float* dL_dfeatures, gsr_stream_t stream) {
+                 float* dL_dmeans2D_color_only, float* dL_dcolors, float* dL_dextra_colors, float* dL_dopacity,
+                 float* dL_dscales, float* dL_drotations, float* dL_dcov3D, float* dL_dsh, float* dL_dfeatures,
+                 int flags, gsr_stream_t stream) {
     cudaStream_t s = (cudaStream_t)stream;
     int rc = check_dims(P, V, W, H, channels, sh_coeffs, capacity);
     if (rc) return rc;
+    DebugSyncScope dbg((flags & GSR_FLAG_DEBUG) != 0);
     if (!geom_ws || !image_ws) return GSR_ERR_INVALID_ARGUMENT;
     if (capacity > 0 && !binning_ws) return GSR_ERR_INVALID_ARGUMENT;
     if (P > 0 && !means3D) return GSR_ERR_INVALID_ARGUMENT;
@@ -240,7 +336,7 @@ int gsr_backward(int V, int P, int W, int H, int channels, int sh_coeffs, int64_
     Layout L;
     compute_layout(P, V, W, H, channels, sh_coeffs, capacity, L);
     rc = launch_blend_backward(V, P, W, H, channels, geom_ws, binning_ws, image_ws, L, dL_dcolor, dL_dextra, dL_ddepth,
-                               dL_dalpha, s);
+                               dL_dalpha, dL_dmeans2D_color_only != nullptr && channels == 6, s);
     if (rc) return rc;
     if (features && dL_dfeatures) {
         if (dL_dfeatures_img)
@@ -251,11 +347,14 @@ int gsr_backward(int V, int P, int W, int H, int channels, int sh_coeffs, int64_
                      ? GSR_OK : GSR_ERR_CUDA;
         if (rc) return rc;
     }
-    StageScope sc(ST_PREPROCESS_BWD, s);
-    return launch_preprocess_backward(V, P, W, H, channels, sh_coeffs, means3D, opacities, scales, rotations,
-                                      cov3D_precomp, sh, radii, geom_ws, L, label, dL_dmeans3D, dL_dmeans2D,
-                                      dL_dcolors, dL_dextra_colors, dL_dopacity, dL_dscales, dL_drotations, dL_dcov3D,
-                                      dL_dsh, s);
+    {
+        StageScope sc(ST_PREPROCESS_BWD, s);
+        rc = launch_preprocess_backward(V, P, W, H, channels, sh_coeffs, means3D, opacities, scales, rotations,
+                                        cov3D_precomp, sh, radii, geom_ws, L, label, dL_dmeans3D, dL_dmeans2D,
+                                        dL_dmeans2D_color_only, dL_dcolors, dL_dextra_colors, dL_dopacity, dL_dscales,
+                                        dL_drotations, dL_dcov3D, dL_dsh, s);
+    }
+    return rc ? rc : dbg.status();
 }
 
 int gsr_mark_visible(const GsrCamera* cam_host, int P, const float* means3D, uint8_t* present, gsr_stream_t stream) {
@@ -440,12 +539,7 @@ int gsr_stage_timing_enable(int on) {
 
 int gsr_stage_timing_count(void) { return ST_COUNT; }
 
-const char* gsr_stage_name(int stage) {
-    static const char* names[ST_COUNT] = {"preprocess", "depth_sort", "instance_count", "emit_supertile_instances",
-                                          "supertile_sort", "tile_offsets", "scatter_records", "blend_forward", "grad_zero",
-                                          "blend_backward", "preprocess_backward"};
-    return stage >= 0 && stage < ST_COUNT ? names[stage] : "?";
-}
+const char* gsr_stage_name(int stage) { return stage >= 0 && stage < ST_COUNT ? kStageNames[stage] : "?"; }
 
 int gsr_stage_timing_read(float* ms_out, int n) {
     if (!ms_out || !g_ev_made) return GSR_ERR_INVALID_ARGUMENT;
@@ -470,9 +564,12 @@ int gsr_probe_geometry(int* blocks, int* threads) {
     return GSR_OK;
 }
 
-int gsr_fp32_peak_probe(float* out, int iters, gsr_stream_t stream) {
+int gsr_fp32_peak_probe(float* out, int iters, int packed, gsr_stream_t stream) {
     if (!out || iters <= 0) return GSR_ERR_INVALID_ARGUMENT;
-    fp32_peak_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(out, iters);
+    if (packed)
+        fp32_peak_kernel<true><<<148 * 8, 256, 0, (cudaStream_t)stream>>>(out, iters);
+    else
+        fp32_peak_kernel<false><<<148 * 8, 256, 0, (cudaStream_t)stream>>>(out, iters);
     GSR_LAUNCH_CHECK();
     return GSR_OK;
 }

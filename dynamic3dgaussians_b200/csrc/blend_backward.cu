@@ -19,7 +19,6 @@
 //    value): the reference issues one atomic per (pixel, Gaussian, value) (backward.cu:586-649).
 #include "geom_math.cuh"
 #include "packed_reduce.cuh"
-#include <stdlib.h>
 
 namespace gsr {
 
@@ -54,7 +53,11 @@ __device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.
 constexpr int NT2 = 128;
 constexpr int NW2 = NT2 / 32;
 
-template <int NCH>
+// M2C (only with the fused extra colours, NCH == 6): additionally reduce the screen-space mean moments of the COLOUR
+// render alone -- colour, depth and alpha cotangents, without the extra (segmentation) channels -- into record slots
+// GR_COL + NCH and + 1.  The reference takes its densification statistic from the colour render's dL/dmeans2D only
+// (REF/train.py:245, REF/external.py:136-140; REF/README.md:89 on why fusing the two renders changes t = 0 otherwise).
+template <int NCH, bool M2C>
 #ifndef GSR_BWD_MINB
 #define GSR_BWD_MINB 8
 #endif
@@ -68,7 +71,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                        const float* __restrict__ dL_ddepth, const float* __restrict__ dL_dalpha,
                        float* __restrict__ grad_rec) {
     constexpr bool EXTRA = NCH > 3;
-    constexpr int K = GR_COL + NCH;
+    static_assert(!M2C || EXTRA, "the colour-only moments only differ from the totals when extra colours are blended");
+    constexpr int K = GR_COL + NCH + (M2C ? 2 : 0);
+    static_assert(K <= grad_rec_stride(NCH), "gradient record too small");
     // one block per ring slot, so that the loop addresses all of an entry's records off ONE register (base + 16 j)
     struct __align__(128) Stage {
         float4 a[BATCH], b[BATCH], c[BATCH], d[EXTRA ? BATCH : 1];
@@ -145,6 +150,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     for (int k = 0; k < NCH; ++k) gC[k] = splat(0.0f);
     const CamDev& cam = cams[view];
     float2 acc = splat(0.0f);
+    float2 acc_c = splat(0.0f);                // M2C: the recurrence of the colour render alone
     {
         const size_t o0 = pix0 - (size_t)view * HW, o1 = pix1 - (size_t)view * HW;
         if (dL_dcolor) {
@@ -156,6 +162,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 acc.y += cam.bg[ch] * gC[ch].y;
             }
         }
+        acc_c = acc;
         if (EXTRA && dL_dextra) {
 #pragma unroll
             for (int ch = 0; ch < 3; ++ch) {
@@ -246,6 +253,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 float v[K];
 #pragma unroll
                 for (int k = 0; k < 3; ++k) v[GR_COL + k] = fmaf(w.y, gC[k].y, w.x * gC[k].x);
+                float2 s_c;
+                if (M2C) s_c = s;
                 if (EXTRA) {
                     const float4 e = stage[buf].d[j];
                     s = __ffma2_rn(splat(e.x), gC[NCH - 3],
@@ -269,6 +278,16 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 v[GR_CB] = v[GR_MY] * dx;
                 v[GR_CC] = fmaf(uy.y, dy.y, uy.x * dy.x);
                 v[GR_OP] = gq.x + gq.y;
+                if (M2C) {
+                    const float2 sd_c = __fadd2_rn(s_c, f2(-acc_c.x, -acc_c.y));
+                    float2 gq_c = __fmul2_rn(G, __fmul2_rn(sd_c, T));
+                    acc_c = __ffma2_rn(alpha, sd_c, acc_c);
+                    gq_c.x = valid0 ? gq_c.x : 0.0f;
+                    gq_c.y = valid1 ? gq_c.y : 0.0f;
+                    const float2 am_c = __fmul2_rn(splat(b.y), gq_c);
+                    v[GR_COL + NCH] = (am_c.x + am_c.y) * dx;
+                    v[GR_COL + NCH + 1] = fmaf(am_c.y, dy.y, am_c.x * dy.x);
+                }
                 PackedReduce<K>::run(v, lane);
                 // one reduction (RED) per (warp patch, Gaussian, value): the K sums sit in K different lanes and land in
                 // one 64-byte gradient record
@@ -355,7 +374,7 @@ int set_blend_backward_trace(unsigned long long* p) {
 
 int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, const void* bws, void* iws,
                           const Layout& L, const float* dL_dcolor, const float* dL_dextra, const float* dL_ddepth,
-                          const float* dL_dalpha, cudaStream_t s) {
+                          const float* dL_dalpha, bool color_only_means2D, cudaStream_t s) {
     const int T = L.tiles_x * L.tiles_y;
     const int blocks = V * T;
     {
@@ -374,21 +393,24 @@ int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, c
     const float* fT = at<float>(iws, L.final_T);
     float* rec = at<float>(gws, L.grad_rec);
     const uint32_t* order = at<uint32_t>(iws, L.tile_order);
-    static const bool cost_order = [] { const char* e = getenv("GSR_BWD_COST_ORDER"); return !(e && e[0] == '0'); }();
-    if (cost_order && blend_ilp(blocks) > 1) {          // small launch: deepest tiles first (see tile_order_by_cost_kernel)
+    if (options().bwd_cost_order && blend_ilp(blocks) > 1) {          // small launch: deepest tiles first (see tile_order_by_cost_kernel)
         uint32_t* ord = at<uint32_t>(iws, L.tile_order_bwd);
         tile_order_by_cost_kernel<<<1, ORD_THREADS, 0, s>>>((uint32_t)blocks, at<uint32_t>(iws, L.tile_cost), ord);
         GSR_LAUNCH_CHECK();
         order = ord;
     }
     if (channels == 3)
-        blend_backward_kernel<3><<<blocks, NT2, 0, s>>>(ranges, order, A, B, C, D, cams, W, H,
-                                                        L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
-                                                        dL_dalpha, rec);
+        blend_backward_kernel<3, false><<<blocks, NT2, 0, s>>>(ranges, order, A, B, C, D, cams, W, H,
+                                                               L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
+                                                               dL_dalpha, rec);
+    else if (channels == 6 && color_only_means2D)
+        blend_backward_kernel<6, true><<<blocks, NT2, 0, s>>>(ranges, order, A, B, C, D, cams, W, H,
+                                                              L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
+                                                              dL_dalpha, rec);
     else if (channels == 6)
-        blend_backward_kernel<6><<<blocks, NT2, 0, s>>>(ranges, order, A, B, C, D, cams, W, H,
-                                                        L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
-                                                        dL_dalpha, rec);
+        blend_backward_kernel<6, false><<<blocks, NT2, 0, s>>>(ranges, order, A, B, C, D, cams, W, H,
+                                                               L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
+                                                               dL_dalpha, rec);
     else
         return GSR_ERR_UNSUPPORTED;
     GSR_LAUNCH_CHECK();

@@ -17,7 +17,6 @@
 // * arithmetic per pair follows the reference binary exactly (see geom_math.cuh), so n_contrib and the images agree
 //   with the reference bit for bit.
 #include "geom_math.cuh"
-#include <stdlib.h>
 
 namespace gsr {
 
@@ -353,8 +352,7 @@ int set_blend_forward_trace(unsigned long long* p) {
 }
 
 int blend_ilp(int blocks) {
-    const char* e = getenv("GSR_BLEND_ILP");
-    const int forced = e ? atoi(e) : 0;
+    const int forced = options().blend_ilp;             // gsr_set_option("blend_ilp", 1 | 2): tuning and tests
     if (forced == 1 || forced == 2) return forced;
     return blocks <= BLEND_ILP_MAX_BLOCKS ? BLEND_ILP_SMALL : 1;
 }

@@ -14,14 +14,16 @@ constexpr int TILE_Y = 16;
 constexpr int TILE_PIX = TILE_X * TILE_Y;
 constexpr int GRAD_REC = 16;          // upper bound on the floats per (view, Gaussian) gradient record
 // floats per (view, Gaussian) gradient record written by the blend backward: 7 geometry / opacity / depth sums + one per
-// blended channel, rounded up to whole float4s (12 for colour only, 16 with the fused extra colours)
+// blended channel, rounded up to whole float4s (12 for colour only, 16 with the fused extra colours -- the spare slots
+// 13, 14 of the latter take the colour-only screen-space moments when those are asked for)
 constexpr int grad_rec_stride(int channels) { return (7 + channels + 3) / 4 * 4; }
 constexpr int NUM_COUNTERS = 64;
 
 // gradient-record slots
 enum : int { GR_MX = 0, GR_MY = 1, GR_CA = 2, GR_CB = 3, GR_CC = 4, GR_OP = 5, GR_DEPTH = 6, GR_COL = 7 };
 // counter slots
-enum : int { CNT_RENDERED = 0, CNT_OVERFLOW = 1, CNT_SCRATCH = 2, CNT_ST_RENDERED = 3, CNT_NCHUNKS = 4, CNT_INST_TILE = 24 };
+// CNT_PREFILTER: a Gaussian was culled although the caller promised a prefiltered set (auxiliary.h:160-167 traps there)
+enum : int { CNT_RENDERED = 0, CNT_OVERFLOW = 1, CNT_PREFILTER = 2, CNT_ST_RENDERED = 3, CNT_NCHUNKS = 4, CNT_INST_TILE = 24 };
 
 // Device-side camera: GsrCamera plus the per-view constants the reference derives on the host
 // (focal lengths, rasterizer_impl.cu:227-228) or in every thread (clamp limits, forward.cu:87-99).
@@ -170,11 +172,27 @@ __host__ __device__ inline const T* at(const void* base, size_t off) {
     return reinterpret_cast<const T*>(reinterpret_cast<const char*>(base) + off);
 }
 
+// Process-wide switches of the library (gsr_set_option); nothing on the launch path reads the environment.
+struct Options {
+    int blend_ilp = 0;        // forward blend loop: 0 = by launch size (blend_ilp()), 1 / 2 = force that variant
+    int bwd_cost_order = 1;   // small backward launches ordered by the depth the forward walked (tile_order_by_cost_kernel)
+    int nvtx = 0;             // an NVTX range around every stage (profilers)
+};
+Options& options();
+
 // optional per-stage device timing (bench.py's roofline numbers): events are recorded on the launching stream
 enum Stage : int { ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_TILE_SCAN, ST_EMIT, ST_TILE_SORT, ST_RANGES, ST_GATHER,
                    ST_BLEND_FWD, ST_GRAD_ZERO, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_COUNT };
 void stage_begin(int stage, cudaStream_t s);
 void stage_end(int stage, cudaStream_t s);
+// debug mode of one call (GsrCamera.debug / GSR_FLAG_DEBUG, the reference's `debug` flag: CHECK_CUDA after every launch,
+// auxiliary.h:172-179): stage_end() synchronises the stream and checks for errors; the first failing stage is recorded
+// with its name (gsr_last_cuda_error) and the entry point returns GSR_ERR_CUDA.
+struct DebugSyncScope {
+    explicit DebugSyncScope(bool on);
+    ~DebugSyncScope();
+    int status() const;       // GSR_OK or GSR_ERR_CUDA
+};
 struct StageScope {
     int st; cudaStream_t s;
     StageScope(int stage, cudaStream_t stream) : st(stage), s(stream) { stage_begin(st, s); }
@@ -196,7 +214,7 @@ void set_cuda_error(cudaError_t e, const char* where);
 int launch_preprocess(const CamDev* cams, int V, int P, int sh_coeffs,
                       const float* means3D, const float* opacities, const float* scales, const float* rotations,
                       const float* cov3D_precomp, const float* sh, void* geom_ws, const Layout& L,
-                      int32_t* radii_out, cudaStream_t s);
+                      int32_t* radii_out, cudaStream_t s);   // sets counters[CNT_PREFILTER] (see preprocess.cu)
 int launch_mark_visible(const float* view, int P, const float* means3D, uint8_t* present, cudaStream_t s);
 
 template <typename KeyT>
@@ -229,7 +247,7 @@ int launch_blend_forward(int V, int W, int H, int channels, const void* geom_ws,
                          float* out_alpha, cudaStream_t s);
 int launch_blend_backward(int V, int P, int W, int H, int channels, void* geom_ws, const void* binning_ws,
                           void* image_ws, const Layout& L, const float* dL_dcolor, const float* dL_dextra,
-                          const float* dL_ddepth, const float* dL_dalpha, cudaStream_t s);
+                          const float* dL_ddepth, const float* dL_dalpha, bool color_only_means2D, cudaStream_t s);
 size_t image_loss_state_bytes(int64_t n_img, int W, int H);
 int launch_image_loss_forward(int64_t n_img, int W, int H, const float* img, const float* tgt, float w_l1, float w_ssim,
                               void* state, float* loss_out, cudaStream_t s);
@@ -263,9 +281,9 @@ int launch_preprocess_backward(int V, int P, int W, int H, int channels, int sh_
                                const float* means3D, const float* opacities, const float* scales,
                                const float* rotations, const float* cov3D_precomp, const float* sh,
                                const int32_t* radii, const void* geom_ws, const Layout& L, const float* label,
-                               float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors, float* dL_dextra_colors,
-                               float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
-                               float* dL_dsh, cudaStream_t s);
+                               float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dmeans2D_color_only, float* dL_dcolors,
+                               float* dL_dextra_colors, float* dL_dopacity, float* dL_dscales, float* dL_drotations,
+                               float* dL_dcov3D, float* dL_dsh, cudaStream_t s);
 int launch_export_view(int view, int V, int P, int W, int H, const void* geom_ws, const void* binning_ws,
                        const void* image_ws, const Layout& L, uint64_t* keys_out, uint32_t* list_out,
                        uint32_t* ranges_out, uint32_t* n_contrib_out, cudaStream_t s);

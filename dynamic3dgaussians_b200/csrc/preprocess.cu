@@ -88,7 +88,8 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
                   int tiles_x, int tiles_y,
                   int32_t* __restrict__ radii, ushort4* __restrict__ rects, float4* __restrict__ geomrec,
                   float* __restrict__ rgb, uint8_t* __restrict__ clamped,
-                  uint32_t* __restrict__ dkeys, uint32_t* __restrict__ dvals, int32_t* __restrict__ radii_out) {
+                  uint32_t* __restrict__ dkeys, uint32_t* __restrict__ dvals, int32_t* __restrict__ radii_out,
+                  uint32_t* __restrict__ counters) {
     __shared__ CamDev cam;
     const int v = blockIdx.y;
     {
@@ -161,6 +162,11 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
             }
         }
     }
+    else if (cam.prefiltered) {
+        // in_frustum with prefiltered = true (auxiliary.h:160-167): the reference prints and traps; here the flag comes
+        // back through gsr_read_counters and the host raises
+        counters[CNT_PREFILTER] = 1u;
+    }
     radii[idx] = radius;
     if (radii_out) radii_out[idx] = radius;
     rects[idx] = rect;
@@ -200,7 +206,8 @@ int launch_preprocess(const CamDev* cams, int V, int P, int sh_coeffs, const flo
     preprocess_kernel<<<grid, 256, 0, s>>>(
         cams, P, sh_coeffs, means3D, opacities, scales, rotations, cov3D_precomp, sh, L.tiles_x, L.tiles_y,
         at<int32_t>(ws, L.radii), at<ushort4>(ws, L.rects), at<float4>(ws, L.geomrec), at<float>(ws, L.rgb),
-        at<uint8_t>(ws, L.clamped), at<uint32_t>(ws, L.dkeys0), at<uint32_t>(ws, L.dvals0), radii_out);
+        at<uint8_t>(ws, L.clamped), at<uint32_t>(ws, L.dkeys0), at<uint32_t>(ws, L.dvals0), radii_out,
+        at<uint32_t>(ws, L.counters));
     GSR_LAUNCH_CHECK();
     return GSR_OK;
 }

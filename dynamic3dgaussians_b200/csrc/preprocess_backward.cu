@@ -111,7 +111,7 @@ preprocess_backward_kernel(const CamDev* __restrict__ cams, int V, int P, int sh
                            const float* __restrict__ sh, const int32_t* __restrict__ radii,
                            const uint8_t* __restrict__ clamped, const float* __restrict__ grad_rec,
                            const float* __restrict__ label, float* __restrict__ dL_dmeans3D,
-                           float* __restrict__ dL_dmeans2D, float* __restrict__ dL_dcolors,
+                           float* __restrict__ dL_dmeans2D, float* __restrict__ dL_dm2c, float* __restrict__ dL_dcolors,
                            float* __restrict__ dL_dextra, float* __restrict__ dL_dopacity,
                            float* __restrict__ dL_dscales, float* __restrict__ dL_drotations,
                            float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh) {
@@ -147,6 +147,11 @@ preprocess_backward_kernel(const CamDev* __restrict__ cams, int V, int P, int sh
                 dL_dmeans2D[3 * idx] = 0.0f;
                 dL_dmeans2D[3 * idx + 1] = 0.0f;
                 dL_dmeans2D[3 * idx + 2] = 0.0f;
+            }
+            if (dL_dm2c) {
+                dL_dm2c[3 * idx] = 0.0f;
+                dL_dm2c[3 * idx + 1] = 0.0f;
+                dL_dm2c[3 * idx + 2] = 0.0f;
             }
             continue;
         }
@@ -234,6 +239,19 @@ preprocess_backward_kernel(const CamDev* __restrict__ cams, int V, int P, int sh
             dL_dmeans2D[3 * idx] = gx;
             dL_dmeans2D[3 * idx + 1] = gy;
             dL_dmeans2D[3 * idx + 2] = 0.0f;
+        }
+        if (dL_dm2c) {
+            // the colour render's share (REF/train.py:245): its own moments when extra colours were blended in the same
+            // pass (slots GR_COL + NCH, + 1 of the record, blend_backward_kernel<6, true>), the whole gradient otherwise
+            float cx = gx, cy = gy;
+            if (NCH > 3) {
+                const float mxc = rec[GR_COL + NCH], myc = rec[GR_COL + NCH + 1];
+                cx = -0.5f * (float)cam.width * (conA * mxc + conB * myc);
+                cy = -0.5f * (float)cam.height * (conC * myc + conB * mxc);
+            }
+            dL_dm2c[3 * idx] = cx;
+            dL_dm2c[3 * idx + 1] = cy;
+            dL_dm2c[3 * idx + 2] = 0.0f;
         }
 
         dopac += rec[GR_OP];
@@ -327,8 +345,9 @@ int launch_preprocess_backward(int V, int P, int W, int H, int channels, int sh_
                                const float* opacities, const float* scales, const float* rotations,
                                const float* cov3D_precomp, const float* sh, const int32_t* radii, const void* gws,
                                const Layout& L, const float* label, float* dL_dmeans3D, float* dL_dmeans2D,
-                               float* dL_dcolors, float* dL_dextra_colors, float* dL_dopacity, float* dL_dscales,
-                               float* dL_drotations, float* dL_dcov3D, float* dL_dsh, cudaStream_t s) {
+                               float* dL_dmeans2D_color_only, float* dL_dcolors, float* dL_dextra_colors,
+                               float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
+                               float* dL_dsh, cudaStream_t s) {
     if (P == 0 || V == 0) return GSR_OK;
     const CamDev* cams = at<CamDev>(gws, L.cams);
     const int32_t* rad = radii ? radii : at<int32_t>(gws, L.radii);
@@ -338,12 +357,12 @@ int launch_preprocess_backward(int V, int P, int W, int H, int channels, int sh_
     if (channels == 3) {
         preprocess_backward_kernel<3><<<blocks, 256, 0, s>>>(cams, V, P, sh_coeffs, means3D, scales, rotations,
                                                             cov3D_precomp, sh, rad, cl, rec, label, dL_dmeans3D,
-                                                            dL_dmeans2D, dL_dcolors, dL_dextra_colors, dL_dopacity,
+                                                            dL_dmeans2D, dL_dmeans2D_color_only, dL_dcolors, dL_dextra_colors, dL_dopacity,
                                                             dL_dscales, dL_drotations, dL_dcov3D, dL_dsh);
     } else if (channels == 6) {
         preprocess_backward_kernel<6><<<blocks, 256, 0, s>>>(cams, V, P, sh_coeffs, means3D, scales, rotations,
                                                             cov3D_precomp, sh, rad, cl, rec, label, dL_dmeans3D,
-                                                            dL_dmeans2D, dL_dcolors, dL_dextra_colors, dL_dopacity,
+                                                            dL_dmeans2D, dL_dmeans2D_color_only, dL_dcolors, dL_dextra_colors, dL_dopacity,
                                                             dL_dscales, dL_drotations, dL_dcov3D, dL_dsh);
     } else {
         return GSR_ERR_UNSUPPORTED;

@@ -57,13 +57,21 @@ def _host_floats(t, n: int, what: str) -> List[float]:
 _CAM_CACHE: dict = {}
 
 
+def _versions(s: GaussianRasterizationSettings, bg_extra):
+    """(data_ptr, in-place version) of every tensor a GsrCamera is built from: an in-place update of a pose / background
+    tensor (camera optimisation, random backgrounds) must be seen, as the reference reads the tensors on every call."""
+    return tuple((t.data_ptr(), t._version) if torch.is_tensor(t) else t
+                 for t in (s.viewmatrix, s.projmatrix, s.campos, s.bg, bg_extra))
+
+
 def camera_struct(s: GaussianRasterizationSettings, bg_extra=None, band=None) -> _lib.GsrCamera:
-    """GsrCamera for one settings tuple.  Matrices are read back from the device once per settings object.
+    """GsrCamera for one settings tuple.  The matrices live on the device; reading them back costs a sync, so the struct
+    is cached per settings object and rebuilt when any of its tensors (or `bg_extra`) was replaced or modified in place.
     `band` = (first tile row, one past the last) restricts the render to a band of 16-pixel rows (None = all)."""
     band = None if band is None else (int(band[0]), int(band[1]))
     key = (id(s), id(bg_extra), band)
     hit = _CAM_CACHE.get(key)
-    if hit is not None and hit[0] is s:
+    if hit is not None and hit[0] is s and hit[2] is bg_extra and hit[3] == _versions(s, bg_extra):
         return hit[1]
     cam = _lib.GsrCamera()
     if band is not None:
@@ -79,6 +87,7 @@ def camera_struct(s: GaussianRasterizationSettings, bg_extra=None, band=None) ->
     cam.scale_modifier = float(s.scale_modifier)
     cam.sh_degree = int(s.sh_degree)
     cam.prefiltered = int(bool(s.prefiltered))
+    cam.debug = int(bool(s.debug))
     bg = _host_floats(s.bg, 3, "bg") + _host_floats(bg_extra, 3, "bg_extra") + [0.0, 0.0]
     for i in range(8):
         cam.bg[i] = bg[i]
@@ -92,7 +101,7 @@ def camera_struct(s: GaussianRasterizationSettings, bg_extra=None, band=None) ->
         cam.campos[i] = cp[i]
     if len(_CAM_CACHE) > 4096:
         _CAM_CACHE.clear()
-    _CAM_CACHE[key] = (s, cam)
+    _CAM_CACHE[key] = (s, cam, bg_extra, _versions(s, bg_extra))      # holds s and bg_extra alive: ids stay unique
     return cam
 
 
@@ -117,7 +126,7 @@ def _stream_ptr(device) -> int:
 class RasterState:
     """Everything the backward needs from the forward (the reference keeps geomBuffer/binningBuffer/imgBuffer on ctx)."""
     __slots__ = ("V", "P", "W", "H", "channels", "sh_coeffs", "capacity", "num_rendered", "geom", "binning", "image",
-                 "radii", "layout", "feature_map")
+                 "radii", "layout", "feature_map", "flags")
 
 
 def workspace_layout(P, V, W, H, channels, sh_coeffs, capacity) -> _lib.GsrLayout:
@@ -182,6 +191,9 @@ def forward_views(settings: Sequence[GaussianRasterizationSettings], means3D, op
     image = torch.empty(sizes.image_bytes, dtype=torch.uint8, device=dev)
     radii = torch.empty((V, P), dtype=torch.int32, device=dev)
     stream = _stream_ptr(dev)
+    flags = _lib.FLAG_DEBUG if any(bool(s.debug) for s in settings) else 0
+    if flags:
+        cams[0].debug = 1
     with torch.cuda.device(dev):
         _lib.check(lib.gsr_forward_geometry(cams, V, P, channels, sh_coeffs, _lib.ptr(means3D), _lib.ptr(opacities),
                                             _lib.ptr(scales), _lib.ptr(rotations), _lib.ptr(cov3D_precomp),
@@ -189,7 +201,13 @@ def forward_views(settings: Sequence[GaussianRasterizationSettings], means3D, op
                                             stream), "forward_geometry")
         num_rendered = None
         if capacity is None:
-            num_rendered = int(geom[:4].view(torch.int32).item()) if P > 0 else 0     # the one host sync
+            num_rendered = 0
+            if P > 0:
+                c = geom[:12].view(torch.int32).tolist()                              # the one host sync
+                num_rendered = c[0]
+                if c[2]:
+                    # R/cuda_rasterizer/auxiliary.h:160-167: with prefiltered = True a culled point is an error
+                    raise RuntimeError("Point is filtered although prefiltered is set. This shouldn't happen!")
             capacity = num_rendered
         _lib.check(lib.gsr_workspace_sizes(P, V, W, H, channels, sh_coeffs, capacity, C.byref(sizes)), "workspace_sizes")
         binning = torch.empty(max(sizes.binning_bytes, 16), dtype=torch.uint8, device=dev)
@@ -204,13 +222,14 @@ def forward_views(settings: Sequence[GaussianRasterizationSettings], means3D, op
                                           _lib.ptr(extra_colors), _lib.ptr(semantic_feature), NUM_SEMANTIC_CHANNELS,
                                           geom.data_ptr(), binning.data_ptr(), image.data_ptr(), color.data_ptr(),
                                           _lib.ptr(extra), depth.data_ptr(), alpha.data_ptr(), _lib.ptr(feature_map),
-                                          stream), "forward_render")
+                                          flags, stream), "forward_render")
     st = RasterState()
     st.V, st.P, st.W, st.H, st.channels, st.sh_coeffs = V, P, W, H, channels, sh_coeffs
     st.capacity, st.num_rendered = int(capacity), num_rendered
     st.geom, st.binning, st.image, st.radii = geom, binning, image, radii
     st.layout = None
     st.feature_map = feature_map
+    st.flags = flags
     return color, extra, depth, alpha, radii, st
 
 
@@ -218,6 +237,15 @@ def read_counters(st: RasterState):
     """(num_rendered, overflowed) -- synchronises the current stream."""
     c = st.geom[:8].view(torch.int32).cpu()
     return int(c[0]), bool(c[1])
+
+
+def read_flags(st: RasterState) -> dict:
+    """All device-side counters / flags of a forward (gsr_read_counters) -- synchronises the current stream.  With an
+    explicit `capacity` the forward never looks at them itself: check `overflowed` (instances were dropped) and
+    `prefilter_violation` (a camera said prefiltered=True and a Gaussian was culled anyway; the reference traps there,
+    R/cuda_rasterizer/auxiliary.h:160-167) afterwards."""
+    c = st.geom[:16].view(torch.int32).tolist()
+    return dict(num_rendered=c[0], overflowed=bool(c[1]), prefilter_violation=bool(c[2]))
 
 
 def tile_row_costs(st: RasterState) -> torch.Tensor:
@@ -231,9 +259,11 @@ def tile_row_costs(st: RasterState) -> torch.Tensor:
 
 def backward_views(st: RasterState, means3D, opacities, colors_precomp, scales, rotations, cov3D_precomp, shs,
                    extra_colors, dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, label=None, want_means2D=True, out=None,
-                   semantic_feature=None, dL_dfeature=None):
+                   semantic_feature=None, dL_dfeature=None, want_means2D_color=False):
     """Returns dict of gradients summed over the views of the batch (means2D: [V,P,3]; features: [P,32] when
-    `semantic_feature` is given, with `dL_dfeature` [V,32,H,W] the cotangent of the feature map).  `out` may carry preallocated
+    `semantic_feature` is given, with `dL_dfeature` [V,32,H,W] the cotangent of the feature map; means2D_color [V,P,3]
+    with want_means2D_color: the colour render's share of means2D -- everything but the fused extra colours' cotangent --
+    which is what the reference's densification statistic is made of, REF/train.py:245).  `out` may carry preallocated
     contiguous float32 tensors for means3D / colors / opacity / scales / rotations (e.g. views into one all-reduce
     slab, dist.GradSlab); every gradient is written, never accumulated."""
     lib = _lib.load()
@@ -270,6 +300,7 @@ def backward_views(st: RasterState, means3D, opacities, colors_precomp, scales, 
     g = dict(
         means3D=buf("means3D", (P, 3)),
         means2D=torch.empty((V, P, 3), **f32) if want_means2D else None,
+        means2D_color=torch.empty((V, P, 3), **f32) if want_means2D_color else None,
         colors=buf("colors", (P, 3)) if colors_precomp is not None else None,
         extra=torch.empty((P, 3), **f32) if st.channels == 6 else None,
         opacity=buf("opacity", (P, 1)),
@@ -290,9 +321,9 @@ def backward_views(st: RasterState, means3D, opacities, colors_precomp, scales, 
                                     p(extra_colors), p(semantic_feature), NUM_SEMANTIC_CHANNELS, p(st.radii),
                                     st.geom.data_ptr(), st.binning.data_ptr(), st.image.data_ptr(), p(dL_dcolor),
                                     p(dL_dextra), p(dL_ddepth), p(dL_dalpha), p(dL_dfeature), p(label),
-                                    p(g["means3D"]), p(g["means2D"]), p(g["colors"]), p(g["extra"]), p(g["opacity"]),
-                                    p(g["scales"]), p(g["rotations"]), p(g["cov3D"]), p(g["sh"]), p(g["features"]),
-                                    _stream_ptr(dev)), "backward")
+                                    p(g["means3D"]), p(g["means2D"]), p(g["means2D_color"]), p(g["colors"]),
+                                    p(g["extra"]), p(g["opacity"]), p(g["scales"]), p(g["rotations"]), p(g["cov3D"]),
+                                    p(g["sh"]), p(g["features"]), getattr(st, "flags", 0), _stream_ptr(dev)), "backward")
     return g
 
 
@@ -308,7 +339,7 @@ class _RasterizeViews(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, extra_colors, opacities, scales, rotations, cov3Ds_precomp,
-                settings, label, bg_extra, capacity, state_out, bands=None):
+                settings, label, bg_extra, capacity, state_out, bands=None, means2D_color=None):
         color, extra, depth, alpha, radii, st = forward_views(
             settings, means3D, opacities, _opt(colors_precomp), _opt(scales), _opt(rotations), _opt(cov3Ds_precomp),
             _opt(sh), _opt(extra_colors), bg_extra, capacity=capacity, bands=bands)
@@ -317,6 +348,7 @@ class _RasterizeViews(torch.autograd.Function):
             state_out.append(st)
         ctx.has = [_opt(t) is not None for t in (sh, colors_precomp, extra_colors, scales, rotations, cov3Ds_precomp)]
         ctx.means2D_shape = None if means2D is None else tuple(means2D.shape)
+        ctx.means2D_color_shape = None if means2D_color is None else tuple(means2D_color.shape)
         ctx.label = label if torch.is_tensor(label) else None
         ctx.save_for_backward(means3D, sh, colors_precomp, extra_colors, opacities, scales, rotations, cov3Ds_precomp)
         ctx.mark_non_differentiable(radii)
@@ -333,22 +365,26 @@ class _RasterizeViews(torch.autograd.Function):
                            _cuda_f32(_opt(rotations), "rotations"), _cuda_f32(_opt(cov3Ds_precomp), "cov3D_precomp"),
                            _cuda_f32(_opt(sh), "shs"), _cuda_f32(_opt(extra_colors), "extra_colors"),
                            g_color, g_extra if st.channels == 6 else None, g_depth, g_alpha, label=ctx.label,
-                           want_means2D=ctx.means2D_shape is not None)
-        g_means2D = None
-        if ctx.means2D_shape is not None:
-            g_means2D = g["means2D"]
-            if len(ctx.means2D_shape) == 2:        # [P,3] dummy shared by all views: sum over views
-                g_means2D = g_means2D.sum(dim=0) if st.V > 1 else g_means2D[0]
-            g_means2D = g_means2D.reshape(ctx.means2D_shape)
+                           want_means2D=ctx.means2D_shape is not None,
+                           want_means2D_color=ctx.means2D_color_shape is not None)
+
+        def handle_grad(t, shape):
+            if shape is None:
+                return None
+            if len(shape) == 2:                    # [P,3] dummy shared by all views: sum over views
+                t = t.sum(dim=0) if st.V > 1 else t[0]
+            return t.reshape(shape)
+        g_means2D = handle_grad(g["means2D"], ctx.means2D_shape)
+        g_means2D_color = handle_grad(g["means2D_color"], ctx.means2D_color_shape)
         g_op = g["opacity"].reshape(opacities.shape)
         return (g["means3D"], g_means2D, g["sh"], g["colors"], g["extra"], g_op, g["scales"], g["rotations"],
-                g["cov3D"], None, None, None, None, None, None)
+                g["cov3D"], None, None, None, None, None, None, g_means2D_color)
 
 
 def rasterize_views(settings: Sequence[GaussianRasterizationSettings], means3D, opacities, means2D=None, shs=None,
                     colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None, extra_colors=None,
                     label=None, bg_extra=None, capacity: Optional[int] = None, state_out: Optional[list] = None,
-                    bands=None):
+                    bands=None, means2D_color=None):
     """Renders all `settings` (V cameras of equal resolution) in one batch.
 
     Returns (color [V,3,H,W], extra [V,3,H,W] or None, depth [V,1,H,W], alpha [V,1,H,W], radii [V,P]).
@@ -360,6 +396,10 @@ def rasterize_views(settings: Sequence[GaussianRasterizationSettings], means3D, 
     RasterState, whose `read_counters` tells afterwards whether the capacity was exceeded (surplus instances dropped).
     `bands[v]` = (first, last + 1) tile rows of view v to render (see forward_views); pixels outside the band come back
     as background and their cotangents are ignored.
+    `means2D_color` ([P,3] or [V,P,3], requires_grad) is a second gradient handle like `means2D`: its .grad receives the
+    screen-space gradient of the COLOUR render alone (colour, depth, alpha cotangents; not `extra_colors`'), which is what
+    the reference accumulates for densification -- it renders colour and segmentation separately and keeps the colour
+    call's means2D (REF/train.py:245: "Gradient only accum from colour render for densification").
     """
     if (shs is None) == (colors_precomp is None):
         raise Exception('Please provide excatly one of either SHs or precomputed colors!')
@@ -371,7 +411,7 @@ def rasterize_views(settings: Sequence[GaussianRasterizationSettings], means3D, 
         means3D, means2D, e if shs is None else shs, e if colors_precomp is None else colors_precomp,
         e if extra_colors is None else extra_colors, opacities, e if scales is None else scales,
         e if rotations is None else rotations, e if cov3D_precomp is None else cov3D_precomp, list(settings), label,
-        bg_extra, capacity, state_out, bands)
+        bg_extra, capacity, state_out, bands, means2D_color)
     return color, (extra if extra.numel() else None), depth, alpha, radii
 
 

@@ -99,7 +99,10 @@ def load_ply_splat(path: str) -> Dict[str, np.ndarray]:
         if line != b"ply":
             raise ValueError("not a PLY file")
         while True:
-            line = f.readline().decode("ascii").strip()
+            raw = f.readline()
+            if not raw:
+                raise ValueError("truncated PLY header: reached the end of the file before 'end_header'")
+            line = raw.decode("ascii", errors="replace").strip()
             if line.startswith("format") and "binary_little_endian" not in line:
                 raise ValueError("only binary little-endian PLY is supported")
             if line.startswith("element vertex"):
@@ -111,7 +114,11 @@ def load_ply_splat(path: str) -> Dict[str, np.ndarray]:
                 names.append(name)
             elif line == "end_header":
                 break
-        table = np.frombuffer(f.read(n * len(names) * 4), dtype='<f4').reshape(n, len(names))
+        buf = f.read(n * len(names) * 4)
+        if len(buf) != n * len(names) * 4:
+            raise ValueError(f"truncated PLY body: header promises {n} vertices x {len(names)} floats "
+                             f"({n * len(names) * 4} bytes), file holds {len(buf)}")
+        table = np.frombuffer(buf, dtype='<f4').reshape(n, len(names))
     col = {a: table[:, i] for i, a in enumerate(names)}
     g = lambda *ks: np.stack([col[k] for k in ks], axis=1)
     return {'means3D': g('x', 'y', 'z'), 'normals': g('nx', 'ny', 'nz'),

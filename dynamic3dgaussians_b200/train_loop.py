@@ -5,7 +5,9 @@ initialisation, one Adam group per parameter (REF/train.py:89-136,138-291,294-33
 the hot path replaced:
 
   * colour and fg/bg segmentation are rendered in ONE fused pass (`rasterize_views(extra_colors=seg_colors)`) instead of
-    two rasterizer calls (REF/train.py:142,249);
+    two rasterizer calls (REF/train.py:142,249); the densification statistic still comes from the COLOUR render's
+    screen-space gradient alone, as in the reference (REF/train.py:245, REF/README.md:89): the fused backward returns that
+    share separately (`means2D_color`, gsr_backward's dL_dmeans2D_color_only);
   * the image losses are the fused L1 + SSIM kernels (`image_loss.l1_ssim_loss`, REF/train.py:183);
   * the rigidity / rotation / isometry terms are the fused kNN-loss kernels (`dyn_losses.rigidity_losses`,
     REF/train.py:253-273) on a 20-NN graph built on the GPU (`knn.knn`, REF/train.py:316-326 uses Open3D on the CPU);
@@ -117,8 +119,11 @@ def params2rendervar(params, fused: Optional[bool] = None):
 
 
 def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optional[dict] = None,
-             capacity: Optional[int] = None, fused: Optional[bool] = None, overlap: Optional[bool] = None):
-    """REF/train.py:138-291.  curr_data: {'cam': GaussianRasterizationSettings, 'im': [3,H,W], 'seg': [3,H,W], 'id'}."""
+             capacity: Optional[int] = None, fused: Optional[bool] = None, overlap: Optional[bool] = None,
+             state_out: Optional[list] = None):
+    """REF/train.py:138-291.  curr_data: {'cam': GaussianRasterizationSettings, 'im': [3,H,W], 'seg': [3,H,W], 'id'}.
+    `state_out` (append-only list) receives the render's RasterState: with a fixed `capacity` nothing in the step looks
+    at the overflow flag, so whoever fixes the capacity checks it afterwards (rasterizer.read_flags)."""
     weights = LOSS_WEIGHTS if weights is None else weights
     fused = FUSED_GLUE if fused is None else fused
     losses = {}
@@ -128,7 +133,9 @@ def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optiona
     cur = torch.cuda.current_stream(dev)
     side = _side_stream(dev) if overlap else cur
     rv = params2rendervar(params, fused)
-    rv['means2D'].retain_grad()
+    # handle for the colour render's screen-space gradient (the fused pass also blends the segmentation colours, whose
+    # cotangent must not leak into the densification statistic: REF/train.py:245)
+    means2D_color = torch.zeros_like(params['means3D']).requires_grad_(True)
 
     if not is_initial_timestep:
         from .dyn_losses import rigidity_losses
@@ -148,8 +155,9 @@ def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optiona
             dyn['soft_col_cons'] = (torch.abs(params['rgb_colors'] - variables['prev_col']).sum(-1)).mean()
 
     color, seg, depth, alpha, radii = RZ.rasterize_views(
-        [curr_data['cam']], rv['means3D'], rv['opacities'], means2D=rv['means2D'], colors_precomp=rv['colors_precomp'],
-        scales=rv['scales'], rotations=rv['rotations'], extra_colors=params['seg_colors'], capacity=capacity)
+        [curr_data['cam']], rv['means3D'], rv['opacities'], means2D=None, colors_precomp=rv['colors_precomp'],
+        scales=rv['scales'], rotations=rv['rotations'], extra_colors=params['seg_colors'], capacity=capacity,
+        state_out=state_out, means2D_color=means2D_color)
     im, seg, radius = color[0], seg[0], radii[0]
     side.wait_stream(cur)
     with torch.cuda.stream(side):
@@ -160,7 +168,7 @@ def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optiona
     else:
         im = torch.exp(params['cam_m'][cid])[:, None, None] * im + params['cam_c'][cid][:, None, None]
     losses['im'] = l1_ssim_loss(im, curr_data['im'])
-    variables['means2D'] = rv['means2D']                 # gradient only accumulated from this render for densification
+    variables['means2D'] = means2D_color                 # "Gradient only accum from colour render for densification"
     losses['seg'] = loss_seg
     if not is_initial_timestep:
         losses.update(dyn)
@@ -244,7 +252,15 @@ class GraphedTrainer:
     step -- so that an iteration is a single launch (the eager loop spends ~2 ms of Python per iteration on ~1 ms of GPU
     work).  The graphs share one memory pool (they never run concurrently).  Valid while the parameter tensors keep
     their identity and size: build it after the densification phase (or rebuild it after every densify round) with an
-    optimizer created by initialize_optimizer() and a fixed per-view instance `capacity`."""
+    optimizer created by initialize_optimizer() and a fixed per-view instance `capacity`.
+
+    `capacity` is baked into every captured iteration: when the Gaussians move or grow so that a view produces more
+    (Gaussian, tile) instances than that, the binning drops the surplus (the render is then wrong, silently).  Size it
+    with headroom (bench.py uses 1.25x the largest view's count at build time) and call `overflowed()` every few hundred
+    steps and at the end of a timestep -- one 16-byte read per camera; on True rebuild the trainer with more capacity.
+    Building the trainer does not train: the warm-up iterations run on the live tensors, but the parameters, the Adam
+    state and the densification statistics are restored afterwards.  Learning rates are read when a graph is captured;
+    `step()` refuses to replay after a `param_group['lr']` changed (rebuild instead)."""
 
     def __init__(self, params, variables, optimizer, dataset: Sequence[dict], is_initial_timestep: bool, capacity: int,
                  weights: Optional[dict] = None, accumulate_stats: bool = True, warmup: int = 3):
@@ -252,11 +268,13 @@ class GraphedTrainer:
         self.params, self.variables, self.optimizer, self.dataset = params, variables, optimizer, list(dataset)
         self.graphs: List[torch.cuda.CUDAGraph] = []
         self.losses: List[torch.Tensor] = []
+        self.states: List[RZ.RasterState] = []
         self.order: List[int] = []
+        self.capacity = int(capacity)
 
-        def iteration(curr):
+        def iteration(curr, state_out=None):
             loss, _, _ = get_loss(params, curr, variables, is_initial_timestep, weights, capacity,
-                                  overlap=OVERLAP_LOSSES)
+                                  overlap=OVERLAP_LOSSES, state_out=state_out)
             loss.backward()
             with torch.no_grad():
                 if accumulate_stats and is_initial_timestep:
@@ -264,6 +282,12 @@ class GraphedTrainer:
                 optimizer.step()
             return loss.detach()
 
+        # the warm-up must leave no trace: snapshot what an iteration updates in place
+        stat_keys = [k for k in ('means2D_gradient_accum', 'denom', 'max_2D_radius') if torch.is_tensor(variables.get(k))]
+        snap_params = {k: v.detach().clone() for k, v in params.items()}
+        snap_stats = {k: variables[k].clone() for k in stat_keys}
+        snap_state = {k: {n: t.clone() for n, t in optimizer.state[v].items() if torch.is_tensor(t)}
+                      for k, v in params.items() if v in optimizer.state}
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
@@ -271,7 +295,22 @@ class GraphedTrainer:
                 optimizer.zero_grad(set_to_none=True)
                 iteration(self.dataset[i % len(self.dataset)])
         torch.cuda.current_stream(dev).wait_stream(side)
+        with torch.no_grad():
+            for k, v in params.items():
+                v.copy_(snap_params[k])
+                st = optimizer.state.get(v)
+                if st is None:
+                    continue
+                for n, t in st.items():
+                    if torch.is_tensor(t):
+                        if k in snap_state and n in snap_state[k]:
+                            t.copy_(snap_state[k][n])
+                        else:
+                            t.zero_()                 # state created by the warm-up itself (first ever step)
+            for k in stat_keys:
+                variables[k].copy_(snap_stats[k])
         torch.cuda.synchronize(dev)
+        self._lrs = [float(g['lr']) for g in optimizer.param_groups]
         pool = None
         if hasattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch"):
             # the side-stream branches hand gradients to AccumulateGrad nodes of the capture stream on purpose
@@ -279,20 +318,34 @@ class GraphedTrainer:
         for curr in self.dataset:
             optimizer.zero_grad(set_to_none=True)
             g = torch.cuda.CUDAGraph()
+            st_out: list = []
             with torch.cuda.graph(g, pool=pool):
-                loss = iteration(curr)
+                loss = iteration(curr, st_out)
             pool = g.pool() if pool is None else pool
             self.graphs.append(g)
             self.losses.append(loss)
+            self.states.append(st_out[0])
 
     def step(self, generator: Optional[torch.Generator] = None) -> torch.Tensor:
         """One optimizer iteration on the next camera of a shuffled pass (get_batch); returns that graph's loss tensor
         (overwritten by its next replay)."""
         if not self.order:
             self.order = torch.randperm(len(self.dataset), generator=generator).tolist()
+            if [float(g['lr']) for g in self.optimizer.param_groups] != self._lrs:      # once per pass over the cameras
+                raise RuntimeError("a learning rate changed after the iterations were captured (they are baked into the "
+                                   "graphs): rebuild the GraphedTrainer")
         i = self.order.pop()
         self.graphs[i].replay()
         return self.losses[i]
+
+    def overflowed(self) -> bool:
+        """True when any camera's most recent replay needed more instances than `capacity` (its render dropped the
+        surplus).  Synchronises; reads 16 bytes per camera."""
+        return any(RZ.read_flags(st)['overflowed'] for st in self.states)
+
+    def max_num_rendered(self) -> int:
+        """Largest per-view instance count of the most recent replays (how much of `capacity` is in use)."""
+        return max(RZ.read_flags(st)['num_rendered'] for st in self.states)
 
 
 def _accumulate_inplace(variables: dict, fused: Optional[bool] = None):

@@ -63,7 +63,15 @@ typedef struct GsrCamera {
      * of the bands of a view add up to the view's gradient. */
     int32_t tile_row_begin;
     int32_t tile_row_end;
+    /* The reference's `debug` setting (R/diff_gaussian_rasterization/__init__.py:189; CHECK_CUDA after every launch,
+     * R/cuda_rasterizer/auxiliary.h:172-179): gsr_forward_geometry synchronises `stream` after every stage and returns
+     * GSR_ERR_CUDA naming the first failing stage in gsr_last_cuda_error().  Read from cams_host[0].  The other entry
+     * points take the same switch as GSR_FLAG_DEBUG. */
+    int32_t debug;
 } GsrCamera;
+
+/* `flags` of gsr_forward_render / gsr_backward */
+#define GSR_FLAG_DEBUG 1   /* synchronise + check after every stage (see GsrCamera.debug); not inside a graph capture */
 
 /* Byte sizes of the three caller-owned workspaces (the reference's geomBuffer / binningBuffer / imgBuffer). */
 typedef struct GsrWorkspaceSizes {
@@ -90,9 +98,21 @@ typedef struct GsrLayout {
 /* Number of colour channels blended in the single pass: 3 (colour) or 6 (colour + fg/bg segmentation colours). */
 #define GSR_MAX_CHANNELS 6
 
-int gsr_abi_version(void);
+int gsr_abi_version(void);   /* 4 */
 const char* gsr_strerror(int status);
 const char* gsr_last_cuda_error(void);
+
+/*
+ * Process-wide switches.  The library never reads the environment; whoever embeds it sets these explicitly.
+ *   "blend_ilp"       0 (default): forward blend loop variant picked by launch size; 1 / 2: force one / two list entries
+ *                     per trip (identical bits; tuning and tests)
+ *   "bwd_cost_order"  1 (default): small backward launches order their CTAs by the depth the forward walked each tile
+ *   "nvtx"            1: an NVTX range around every stage (preprocess, depth_sort, ..., blend_backward), for profilers
+ * Unknown key or value out of range: GSR_ERR_INVALID_ARGUMENT.  Apart from these switches, the stage-timing events and the
+ * blend trace pointers below, the library keeps no state: everything lives in the caller's workspaces.
+ */
+int gsr_set_option(const char* key, int value);
+int gsr_get_option(const char* key, int* value);
 
 /* Workspace protocol: query sizes for (P, V, W, H, channels, instance capacity). */
 int gsr_workspace_sizes(int P, int V, int W, int H, int channels, int sh_coeffs, int64_t capacity,
@@ -130,11 +150,15 @@ int gsr_forward_render(int V, int P, int W, int H, int channels, int sh_coeffs, 
                        const float* features, int num_features,
                        void* geom_ws, void* binning_ws, void* image_ws,
                        float* out_color, float* out_extra, float* out_depth, float* out_alpha, float* out_features,
-                       gsr_stream_t stream);
+                       int flags, gsr_stream_t stream);
 
-/* Reads back (asynchronously, into host memory) the overflow flag and the instance count. Caller synchronises. */
-int gsr_read_counters(const void* geom_ws, uint32_t* counters_host /* [4]: num_rendered, overflow, 0, 0 */,
-                      gsr_stream_t stream);
+/* Reads back (asynchronously, into host memory) the instance count and the two device-side flags.  Caller synchronises.
+ *   [0] num_rendered   [1] overflow: the instance capacity was exceeded, surplus instances were dropped
+ *   [2] prefilter violation: a camera had prefiltered = 1 and a Gaussian was culled all the same -- the reference prints
+ *       "Point is filtered although prefiltered is set" and traps the kernel (R/cuda_rasterizer/auxiliary.h:160-167); here
+ *       the Gaussian is skipped, the flag is raised and the binding turns it into an exception
+ *   [3] supertile instances (internal) */
+int gsr_read_counters(const void* geom_ws, uint32_t* counters_host /* [4] */, gsr_stream_t stream);
 
 /*
  * Backward (replaces BACKWARD::render + BACKWARD::preprocess, R/cuda_rasterizer/backward.cu:432-652,144-429).
@@ -144,6 +168,10 @@ int gsr_read_counters(const void* geom_ws, uint32_t* counters_host /* [4]: num_r
  * applies in Python (R/diff_gaussian_rasterization/__init__.py:159-170); it is not applied to dL_dfeatures (:164).
  * features / dL_dfeatures_img [V][32][H][W] / dL_dfeatures [P][32]: the semantic-feature branch (backward.cu:594-611),
  * all three null when the forward had no features.
+ * dL_dmeans2D_color_only [V][P][3] (nullable): dL_dmeans2D of the COLOUR render alone -- the colour, depth and alpha
+ * cotangents without the extra (segmentation) channels that were blended in the same pass.  The reference renders colour
+ * and segmentation with two calls and feeds densification from the colour call's means2D gradient only (REF/train.py:245,
+ * REF/external.py:136-140); with channels == 3 it equals dL_dmeans2D.
  */
 int gsr_backward(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
                  const float* means3D, const float* opacities, const float* scales, const float* rotations,
@@ -152,9 +180,9 @@ int gsr_backward(int V, int P, int W, int H, int channels, int sh_coeffs, int64_
                  void* geom_ws, void* binning_ws, void* image_ws,
                  const float* dL_dcolor, const float* dL_dextra, const float* dL_ddepth, const float* dL_dalpha,
                  const float* dL_dfeatures_img, const float* label,
-                 float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors, float* dL_dextra_colors,
-                 float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D, float* dL_dsh,
-                 float* dL_dfeatures, gsr_stream_t stream);
+                 float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dmeans2D_color_only, float* dL_dcolors,
+                 float* dL_dextra_colors, float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
+                 float* dL_dsh, float* dL_dfeatures, int flags, gsr_stream_t stream);
 
 /* present[i] = (view * p_i).z > 0   (checkFrustum, rasterizer_impl.cu:54-66).  present is [P] bytes. */
 int gsr_mark_visible(const GsrCamera* cam_host, int P, const float* means3D, uint8_t* present, gsr_stream_t stream);
@@ -283,8 +311,10 @@ int gsr_stage_timing_count(void);
 const char* gsr_stage_name(int stage);
 int gsr_stage_timing_read(float* ms_out, int n);
 
-/* Utility kernels used by bench.py: dependent-free FFMA loop (measures the FP32-pipe peak) and an L2 flush. */
-int gsr_fp32_peak_probe(float* out, int iters, gsr_stream_t stream);   /* flops = blocks*threads*iters*2*8 */
+/* Utility kernel used by bench.py: dependent-free FMA loop that measures the FP32-pipe peak.  packed = 0: scalar FFMA,
+ * flops = blocks * threads * iters * 256 (8 chains x 16 steps x 2);  packed = 1: fp32x2 FFMA2 (what the blend kernels
+ * issue), flops = blocks * threads * iters * 512.  `out` holds blocks * threads floats. */
+int gsr_fp32_peak_probe(float* out, int iters, int packed, gsr_stream_t stream);
 int gsr_probe_geometry(int* blocks, int* threads);
 
 /* Diagnostic: when non-null, every CTA of the blend forward / backward kernels writes 4 x uint64 at index blockIdx.x:

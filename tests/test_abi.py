@@ -26,8 +26,12 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
     assert sorted(_lib.EXPORTED_SYMBOLS) == names
-    assert lib.gsr_abi_version() == 3
+    assert lib.gsr_abi_version() == 4
     assert lib.gsr_strerror(0) == b"ok" and lib.gsr_strerror(-2) == b"workspace too small"
+    # host-only switches (the library reads no environment variables): unknown keys / values are error codes
+    v = C.c_int(-1)
+    assert lib.gsr_get_option(b"bwd_cost_order", C.byref(v)) == 0 and v.value == 1
+    assert lib.gsr_set_option(b"nope", 1) == -1 and lib.gsr_set_option(b"blend_ilp", 3) == -1
 
 
 def test_workspace_protocol_host_side():
@@ -62,6 +66,12 @@ def test_settings_tuple_matches_reference_fields():
                                          campos=torch.zeros(3))
     cam = RZ.camera_struct(s)
     assert cam.c_x == 4.0 and cam.c_y == 2.0 and cam.image_width == 8       # default principal point = centre
+    assert cam.debug == 0 and cam.prefiltered == 0
+    assert RZ.camera_struct(s) is cam                                       # cached per settings object ...
+    s.bg[0] = 0.5                                                           # ... until a tensor changes in place
+    cam2 = RZ.camera_struct(s)
+    assert cam2 is not cam and cam2.bg[0] == 0.5
+    assert RZ.camera_struct(s._replace(debug=True, prefiltered=True)).debug == 1
 
 
 def test_reference_validation_errors_and_no_cpu_path():

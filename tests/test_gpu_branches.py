@@ -1,7 +1,7 @@
 """GPU parity tests (pytest -m gpu) for the rasterizer branches and sizes round 1 left untested (VERDICT r01 missing #2, #3,
 weak #1, #2): the SH colour path (forward.cu:20-71, backward.cu:20-139), cov3D_precomp (forward.cu:217-225; dL_dcov3D
 returned, backward.cu:295-358 bypassed), scale_modifier != 1, the FULL headline config against the reference binary, and
-the gradients at headline size against the reference's own backward with the four minimal repairs of SURVEY.md 2.4
+the gradients at headline size against the reference's own backward with the minimal repairs of SURVEY.md 2.4
 (oracle/_ref/libref_rasterizer_patched.so, oracle/build_ref.py PATCHES).
 
 Tolerances are BASELINE.json's: forward artefacts identical to the reference binary; gradients <= 1e-4 relative -- checked
@@ -253,13 +253,13 @@ def test_gradients_vs_patched_reference_backward(P, n_views):
         for direct in (True, False):
             rg = rr.backward(gc[v], gd[v], ga[v], alphas=(-fT[v]).contiguous() if direct else None)
             if direct:
-                _check_grad(f"means2D[{v}]", g["means2D"][v], rg["means2D"], elem_frac=1e-3)
+                _check_grad(f"means2D[{v}]", g["means2D"][v], rg["means2D"])
             else:
                 assert rel_err(g["means2D"][v], rg["means2D"]) <= 5e-3
             part = {k: rg[k] for k in names}
             acc[direct] = part if acc[direct] is None else {k: acc[direct][k] + part[k] for k in names}
     for k in names:
-        _check_grad(k, g[k], acc[True][k].reshape(g[k].shape), elem_frac=1e-3)
+        _check_grad(k, g[k], acc[True][k].reshape(g[k].shape))
         assert rel_err(g[k], acc[False][k].reshape(g[k].shape)) <= 5e-3, k
 
 

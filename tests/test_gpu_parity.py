@@ -217,7 +217,7 @@ def test_tile_row_bands_partition_a_view():
         assert rel_err(slab.views[k].reshape(gw[k].shape), gw[k]) <= GRAD_TOL, k
 
 
-def test_blend_loop_variants_agree_bit_for_bit(monkeypatch):
+def test_blend_loop_variants_agree_bit_for_bit():
     """The forward blend kernel exists in a one-entry-per-trip and a two-entries-per-trip variant (picked by launch
     size, common.cuh blend_ilp2).  Same arithmetic in the same order per pixel: images, n_contrib and final T must be
     identical (and so the gradients, up to the atomics' reordering)."""
@@ -232,14 +232,15 @@ def test_blend_loop_variants_agree_bit_for_bit(monkeypatch):
     gd = torch.randn(2, 1, 180, 320, generator=gen).cuda() * 0.1
     res = {}
     for ilp in ("1", "2"):
-        monkeypatch.setenv("GSR_BLEND_ILP", ilp)
+        _lib.set_option("blend_ilp", int(ilp))                       # gsr_set_option: the library reads no environment
+        assert _lib.get_option("blend_ilp") == int(ilp)
         for extra in (None, seg):
             c, e, d, a, r, st = _fwd(sets, rv, extra_colors=extra)
             ncon = [export_view(st, v)[3] for v in range(2)]
             g = RZ.backward_views(st, rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"],
                                   rv["rotations"], None, None, extra, gc, None if extra is None else ge, gd, None)
             res[(ilp, extra is None)] = (c, e, d, a, ncon, g)
-    monkeypatch.delenv("GSR_BLEND_ILP")
+    _lib.set_option("blend_ilp", 0)
     for plain in (True, False):
         c1, e1, d1, a1, n1, g1 = res[("1", plain)]
         c2, e2, d2, a2, n2, g2 = res[("2", plain)]

@@ -174,11 +174,9 @@ def test_timestep_initialisation_equals_reference(z):
                  'means2D_gradient_accum': torch.zeros(P, device="cuda"), 'denom': torch.zeros(P, device="cuda")}
     opt = TL.initialize_optimizer(params, variables)
     for v in params.values():
-        v.grad = torch.full_like(v, 0.01)
-    opt.step()
+        v.grad = torch.zeros_like(v)
+    opt.step()                                    # creates the Adam state; a zero gradient leaves the parameters alone
     opt.zero_grad(set_to_none=True)
-    for k in ("means3D", "unnorm_rotations"):                       # undo that step: the fixture's t0 state is the input
-        params[k].data.copy_(T(z[f"t0_{k}"]).cuda())
     variables = TL.initialize_post_first_timestep(params, variables, opt)
     lr = {g['name']: g['lr'] for g in opt.param_groups}
     ref_lr = dict(zip(z["opt_names"].tolist(), z["post_lrs"].tolist()))
