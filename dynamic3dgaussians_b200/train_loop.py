@@ -135,7 +135,8 @@ def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optiona
     rv = params2rendervar(params, fused)
     # handle for the colour render's screen-space gradient (the fused pass also blends the segmentation colours, whose
     # cotangent must not leak into the densification statistic: REF/train.py:245)
-    means2D_color = torch.zeros_like(params['means3D']).requires_grad_(True)
+    # -- only the initial timestep densifies, the later ones skip the extra reduction
+    means2D_color = torch.zeros_like(params['means3D']).requires_grad_(True) if is_initial_timestep else None
 
     if not is_initial_timestep:
         from .dyn_losses import rigidity_losses
@@ -168,7 +169,8 @@ def get_loss(params, curr_data, variables, is_initial_timestep, weights: Optiona
     else:
         im = torch.exp(params['cam_m'][cid])[:, None, None] * im + params['cam_c'][cid][:, None, None]
     losses['im'] = l1_ssim_loss(im, curr_data['im'])
-    variables['means2D'] = means2D_color                 # "Gradient only accum from colour render for densification"
+    if means2D_color is not None:
+        variables['means2D'] = means2D_color             # "Gradient only accum from colour render for densification"
     losses['seg'] = loss_seg
     if not is_initial_timestep:
         losses.update(dyn)

@@ -207,7 +207,14 @@ def generate() -> dict:
             v = variables[kk]
             out[f"post_{kk}"] = v.numpy().astype(np.int64) if v.dtype == torch.int64 else f32(v)
         out.update({f"t0_{kk}": f32(tp[kk]) for kk in ("means3D", "unnorm_rotations", "rgb_colors", "seg_colors")})
-        # the scene moves a little (what timestep 0's optimisation would have done since prev_pts was stored)
+        # t = 0 -> 1: the reference calls initialize_per_timestep right after initialize_post_first_timestep
+        # (REF/train.py:416-417,445-446), and `prev_pts = params['means3D'].detach()` (:331) aliases the parameter anyway:
+        # the first hand-over always sees zero velocity
+        tp, variables = T_["initialize_per_timestep"](tp, variables, opt)
+        out["step1_means3D"] = f32(tp['means3D'])
+        out["step1_unnorm_rotations"] = f32(tp['unnorm_rotations'])
+        out["step1_prev_offset"] = f32(variables["prev_offset"])
+        # timestep 1 is optimised: the (new) parameters move in place, prev_pts keeps the old tensor
         with torch.no_grad():
             tp['means3D'].add_(0.01 * torch.randn(P, 3, generator=g))
             tp['unnorm_rotations'].add_(0.02 * torch.randn(P, 4, generator=g))

@@ -228,7 +228,7 @@ def test_graphed_trainer_capacity_warmup_and_learning_rates():
     params, variables = TL.initialize_params(rv["means3D"].clone(), rv["colors_precomp"].clone(), seg, 3, 3.3)
     opt = TL.initialize_optimizer(params, variables)
     before = {k: v.detach().clone() for k, v in params.items()}
-    trainer = TL.GraphedTrainer(params, variables, opt, data, True, capacity=400_000)
+    trainer = TL.GraphedTrainer(params, variables, opt, data, True, capacity=6_000_000)
     # building the trainer (3 warm-up iterations + one capture per camera) must not train
     for k, v in params.items():
         assert torch.equal(v.detach(), before[k]), k
@@ -238,7 +238,7 @@ def test_graphed_trainer_capacity_warmup_and_learning_rates():
     for _ in range(6):
         trainer.step(g)
     torch.cuda.synchronize()
-    assert not trainer.overflowed() and 0 < trainer.max_num_rendered() <= 400_000
+    assert not trainer.overflowed() and 0 < trainer.max_num_rendered() <= 6_000_000
     assert float(variables['denom'].max()) >= 1.0 and float(opt.state[params['means3D']]['step']) == 6.0
     assert not torch.equal(params['means3D'].detach(), before['means3D'])
     # a capacity below what a view needs: the render drops instances -- and says so

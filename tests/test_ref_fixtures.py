@@ -188,6 +188,11 @@ def test_timestep_initialisation_equals_reference(z):
     assert close(gr.dist.cpu(), z["post_neighbor_dist"], 1e-5) and close(gr.weight.cpu(), z["post_neighbor_weight"], 1e-5)
     assert close(variables['init_bg_pts'].cpu(), z["post_init_bg_pts"]) and close(variables['init_bg_rot'].cpu(), z["post_init_bg_rot"])
     assert close(variables['prev_pts'].cpu(), z["post_prev_pts"]) and close(variables['prev_rot'].cpu(), z["post_prev_rot"])
+    # t = 0 -> 1 follows immediately (REF/train.py:416-417,445-446): zero velocity, normalised rotations
+    params, variables = TL.initialize_per_timestep(params, variables, opt)
+    assert close(params['means3D'].detach().cpu(), z["step1_means3D"])
+    assert close(params['unnorm_rotations'].detach().cpu(), z["step1_unnorm_rotations"])
+    # timestep 1's optimisation moves the parameters in place; t = 1 -> 2 then extrapolates with that velocity
     with torch.no_grad():
         for k in ("means3D", "unnorm_rotations"):
             params[k].copy_(T(z[f"t1in_{k}"]).cuda())
