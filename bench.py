@@ -42,9 +42,12 @@ def parse():
     ap.add_argument("--rebalance", type=int, default=0, help="N>1: feedback rounds of the cost-aware partition (dist.rescale_row_costs); at C2 the tile-list model is already within the run-to-run noise of the ranks")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of one CUDA graph per step")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--workload", default="c2", choices=["c2", "c5"],
-                    help="c2 (default, the metric's configuration: 300k Gaussians, 27 views 640x360, strong scaling) or "
-                         "c5 (BASELINE.json configs[4]: 2M Gaussians, 8 views 1920x1080 PER GPU, weak scaling; extra line)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the apples-to-apples / c4 / kNN / dyn-loss sub-lines")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c4", "c5"],
+                    help="c2 (default, the metric's configuration: 300k Gaussians, 27 views 640x360, strong scaling); "
+                         "c4 (BASELINE.json configs[3]: the same scene in 4-return mode -- colour, depth AND alpha "
+                         "cotangents, `label` gradient mask on the last 40 %% of the Gaussians -- sharded over the ranks); "
+                         "c5 (configs[4]: 2M Gaussians, 8 views 1920x1080 PER GPU, weak scaling)")
     ap.add_argument("--emulate-world", type=int, default=0,
                     help="diagnostic, 1 GPU: run only the share rank --emulate-rank would get of an N-way partition "
                          "(no collective), to profile the small per-rank step; the line is marked and is not a result")
@@ -251,6 +254,12 @@ def run_ours(args, world, rank, local):
     gen = torch.Generator().manual_seed(123)
     cot = dict(color=torch.randn(V, 3, IMG_H, IMG_W, generator=gen).to(dev),
                depth=torch.randn(V, 1, IMG_H, IMG_W, generator=gen).to(dev) * 0.1, alpha=None)
+    label = None
+    if args.workload == "c4":
+        # 4-return callers (REF/cvpr_dyn.py:284) put a loss on alpha too and mask gradients by `label`
+        cot["alpha"] = torch.randn(V, 1, IMG_H, IMG_W, generator=gen).to(dev)
+        label = torch.zeros(P, device=dev)
+        label[int(0.6 * P):] = 1.0
     parts = D.partition_views([1.0] * V, world)
     mine = parts[rank]
 
@@ -260,7 +269,7 @@ def run_ours(args, world, rank, local):
     local = [D.select_views(cot, mine)]       # the loss side hands each rank the cotangents of its own views
 
     def step():
-        return D.sharded_step(sets, mine, rv, local[0], capacity=cap[0], slab=slab, local_cotangents=True)
+        return D.sharded_step(sets, mine, rv, local[0], capacity=cap[0], slab=slab, local_cotangents=True, label=label)
 
     # first pass: per-view instance counts -> cost-aware partition (deterministic on every rank)
     out, _ = step()
@@ -288,7 +297,7 @@ def run_ours(args, world, rank, local):
         for _ in range(0 if (args.whole_views or emu) else args.rebalance):
             out, _ = step()
             c0 = int(out[5].num_rendered * 1.05) + 4096 if out is not None else 0
-            g0 = D.GraphedStep(sets, mine, rv, local[0], capacity=c0, reduce=False)
+            g0 = D.GraphedStep(sets, mine, rv, local[0], capacity=c0, reduce=False, label=label)
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             g0.replay()
             torch.cuda.synchronize()
@@ -317,7 +326,7 @@ def run_ours(args, world, rank, local):
     graphed = None
     if not args.no_graph:
         # the whole step (forward, backward, all-reduce) as ONE CUDA graph launch: same kernels, no host work per step
-        graphed = D.GraphedStep(sets, mine, rv, local[0], capacity=cap[0] if cap[0] is not None else 0)
+        graphed = D.GraphedStep(sets, mine, rv, local[0], capacity=cap[0] if cap[0] is not None else 0, label=label)
         eager_step = step
 
         def step():                                            # noqa: F811
@@ -367,7 +376,14 @@ def run_ours(args, world, rank, local):
         vis = float((st.radii > 0).float().mean().item())
     res = dict(ms=ms, host_ms=t_host, visible=vis if st is not None else 0.0, stages=stages, pairs=pairs, R=R, R1=R1 if st is not None else 0, clocks=clocks, views_per_rank=[round(sum(1.0 if isinstance(u, int) else (u[2] - u[1]) / float((IMG_H + 15) // 16) for u in p), 2) for p in parts], parts=parts, rebalance_ms=rebalance_ms,
                launches=kernels_per_step(L, world > 1, st.V) * args.steps if st is not None else 0, state=st, dev=dev,
-               rv=rv, sets=sets, sc=sc, lib=lib)
+               rv=rv, sets=sets, sc=sc, lib=lib, cot=cot)
+    # correctness signal that survives sharding: the all-reduced gradient slab of the LAST (eager, stage-timed) step is the
+    # same quantity for every N (same scene, same cotangents); the driver can compare these across N = 1, 2, 4, 8
+    f64 = slab.flat.double()
+    res["grad_check"] = {"l2": float(f64.norm().item()), "sum": float(f64.sum().item()),
+                         "abs_sum": float(f64.abs().sum().item()), "n": int(f64.numel()),
+                         "what": "float64 norms of the all-reduced [14 x P] gradient slab (means3D | colours | opacity | "
+                                 "scales | rotations); equal across N up to summation order (<= 1e-5 relative)"}
     return res
 
 
@@ -627,9 +643,143 @@ def run_train_loop(args, res):
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
+    # BASELINE.json configs[1] says "train.py loop WITH densification": a sample that crosses two densification rounds
+    # (iterations 450..649: rounds at 500 and 600, REF/external.py:248).  The point count changes, so this stretch runs
+    # eagerly with the instance count read back every step (the reference's own host sync) and re-grown workspaces.
+    dyn_loss_value = float(loss)
+    del trainer
+    params2, variables2 = TL.initialize_params(rv["means3D"].clone(), rv["colors_precomp"].clone(), seg, len(sets), 3.3)
+    opt2 = TL.initialize_optimizer(params2, variables2)
+    TL.train_timestep(params2, variables2, opt2, data, 20, True, generator=g, do_densify=False, capacity=None, start_iter=430)
+    torch.cuda.synchronize()
+    p_before = int(params2['means3D'].shape[0])
+    nd = 200
+    e0.record()
+    TL.train_timestep(params2, variables2, opt2, data, nd, True, generator=g, do_densify=True, capacity=None, start_iter=450)
+    e1.record()
+    torch.cuda.synchronize()
+    msd = e0.elapsed_time(e1)
+    out["with_densification"] = {"it_per_s": round(nd / (msd * 1e-3), 1), "ms_per_it": round(msd / nd, 3),
+                                 "iterations": "450..649 (densification rounds at 500 and 600)",
+                                 "gaussians_before": p_before, "gaussians_after": int(params2['means3D'].shape[0]),
+                                 "launch": "eager, instance count read back every step (workspaces follow the point count)"}
+    del params2, variables2, opt2
     out["dynamic_timestep"] = {"it_per_s": round(n / (ms * 1e-3), 1), "ms_per_it": round(ms / n, 3),
                                "fg_gaussians": int(variables["is_fg"].sum()), "knn": 20,
-                               "final_loss": round(float(loss), 5), "readme_reference_it_per_s": 50.0}
+                               "final_loss": round(dyn_loss_value, 5), "readme_reference_it_per_s": 50.0}
+    return out
+
+
+def _time_ms(fn, reps, warm=2):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def run_extras(args, res):
+    """Sub-lines of the N = 1 line (not the metric): the same step with the work the reference is FORCED to do, the C4
+    variant, and the kNN / dynamic-loss kernels next to the reference's own kernel / the eager code they replace."""
+    from dynamic3dgaussians_b200 import dist as D, rasterizer as RZ
+    dev, sets, rv, cot, sc = res["dev"], res["sets"], res["rv"], res["cot"], res["sc"]
+    P, V = rv["means3D"].shape[0], len(sets)
+    cap = int(res["R"] * 1.05) + 4096
+    out = {}
+    pix = V * IMG_W * IMG_H
+    args5 = (rv["means3D"], rv["opacities"], rv["colors_precomp"], rv["scales"], rv["rotations"])
+
+    # (1) apples to apples: the vendored reference always blends 32 semantic channels (forward.cu:381-383) and scatters
+    # their gradients (backward.cu:594-611); bench --impl reference feeds it zeros[P,32].  Here the repo arm does that
+    # work too: semantic_feature = zeros[P,32], feature-map cotangent zeros.
+    feat = torch.zeros(P, 32, device=dev)
+    gfeat = torch.zeros(V, 32, IMG_H, IMG_W, device=dev)
+
+    def with_features():
+        *_, st = RZ.forward_views(sets, *args5, capacity=cap, semantic_feature=feat)
+        RZ.backward_views(st, *args5, None, None, None, cot["color"], None, cot["depth"], None, want_means2D=False,
+                          semantic_feature=feat, dL_dfeature=gfeat)
+    ms = _time_ms(with_features, 5)
+    out["apples_to_apples"] = {
+        "ms_per_step": round(ms, 3), "value": round(pix / (ms * 1e-3) / 1e6, 2), "unit": "Mpix/s",
+        "what": "the headline step PLUS the 32-channel semantic feature map forward and backward (semantic_feature = "
+                "zeros[P,32], dL_dfeature_map = zeros): the algorithmic work of the reference arm, which cannot switch "
+                "the feature channels off (SURVEY.md Q6); eager launches, device-timed"}
+    del feat, gfeat
+
+    # (2) C4 at N = 1 (BASELINE.json configs[3]); `--workload c4 --gpus N` runs the same thing sharded
+    if args.workload == "c2":
+        gen = torch.Generator().manual_seed(321)
+        cot4 = dict(cot, alpha=torch.randn(V, 1, IMG_H, IMG_W, generator=gen).to(dev))
+        label = torch.zeros(P, device=dev)
+        label[int(0.6 * P):] = 1.0
+        g4 = D.GraphedStep(sets, list(range(V)), rv, cot4, capacity=cap, label=label)
+        ms = _time_ms(lambda: g4.replay(), 10)
+        assert not g4.overflowed()
+        masked = float(g4.slab.views["means3D"][: int(0.6 * P)].abs().max().item())
+        out["c4"] = {"ms_per_step": round(ms, 3), "value": round(pix / (ms * 1e-3) / 1e6, 2), "unit": "Mpix/s",
+                     "masked_gradient_abs_max": masked,
+                     "what": "4-return mode: colour + depth + alpha cotangents, label mask = 1 on the last 40 % of the "
+                             "Gaussians (gradients of the first 60 % exactly 0), one CUDA graph per step"}
+        del g4, cot4
+
+    # (3) kNN (distCUDA2, K = 3; the 20-NN rigidity graph) and the fused dynamic losses (BASELINE.md section 5)
+    from dynamic3dgaussians_b200 import dyn_losses as DL, knn as KN
+    pts = rv["means3D"]
+    k3 = _time_ms(lambda: KN.knn(pts, 3), 10)
+    k20 = _time_ms(lambda: KN.knn(pts, 20), 5)
+    knn = {"points": P, "knn3_ms": round(k3, 3), "knn20_ms": round(k20, 3), "knn3_mpts_per_s": round(P / k3 / 1e3, 1)}
+    try:
+        from oracle import ref_cuda
+        if os.path.exists(ref_cuda.KNN):
+            knn["ref_knn3_ms"] = round(_time_ms(lambda: ref_cuda.knn(pts), 3, warm=1), 3)
+            knn["ref"] = "the reference's simple_knn.cu compiled unmodified (oracle/_ref/libref_knn.so), same B200"
+    except Exception as e:                                   # the comparator is optional, the product number is not
+        knn["ref_error"] = str(e)[:200]
+    out["knn"] = knn
+    fg = sc.seg_colors[:, 0].to(dev) > 0.5
+    fpts = pts[fg].contiguous()
+    frot = rv["rotations"][fg].contiguous()
+    graph = DL.build_neighbor_graph(fpts, frot, 20)
+    gsd = torch.Generator().manual_seed(9)
+    p2 = (fpts + 0.01 * torch.randn(fpts.shape, generator=gsd).to(dev)).requires_grad_(True)
+    r2 = torch.nn.functional.normalize(frot + 0.01 * torch.randn(frot.shape, generator=gsd).to(dev)).requires_grad_(True)
+    w = torch.tensor([4.0, 4.0, 2.0], device=dev)
+
+    def fused():
+        p2.grad = r2.grad = None
+        (DL.rigidity_losses(p2, r2, graph) * w).sum().backward()
+
+    idx = graph.idx.long()
+
+    def eager():                                             # REF/train.py:253-273 in plain torch on the same GPU
+        p2.grad = r2.grad = None
+        q1, q2 = r2, graph.prev_inv_rot
+        w1, x1, y1, z1 = q1.T
+        w2, x2, y2, z2 = q2.T
+        rel = torch.stack([w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2, w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2,
+                           w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2, w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2]).T
+        q = rel / rel.norm(dim=1, keepdim=True)
+        r, x, y, z = q.unbind(1)
+        Rm = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y), 2 * (x * y + r * z),
+                          1 - 2 * (x * x + z * z), 2 * (y * z - r * x), 2 * (x * z - r * y), 2 * (y * z + r * x),
+                          1 - 2 * (x * x + y * y)], dim=1).reshape(-1, 3, 3)
+        off = p2[idx] - p2[:, None]
+        c = (Rm.transpose(2, 1)[:, None] @ off[:, :, :, None]).squeeze(-1)
+        l2 = lambda a, b, ww: torch.sqrt(((a - b) ** 2).sum(-1) * ww + 1e-20).mean()
+        L = torch.stack([l2(c, graph.prev_offset, graph.weight), l2(rel[idx], rel[:, None], graph.weight),
+                         torch.sqrt((torch.sqrt((off ** 2).sum(-1) + 1e-20) - graph.dist) ** 2 * graph.weight + 1e-20).mean()])
+        (L * w).sum().backward()
+    out["dyn_losses"] = {"fg_gaussians": int(fpts.shape[0]), "knn": 20, "fused_ms": round(_time_ms(fused, 20), 3),
+                         "eager_torch_ms": round(_time_ms(eager, 10), 3),
+                         "what": "rigidity + rotation + isometry losses, forward + backward; eager = the reference's "
+                                 "expressions (REF/train.py:253-273) as plain torch ops on the same B200; the "
+                                 "reference's README quotes ~20 ms / iteration (REF/README.md:90)"}
     return out
 
 
@@ -665,7 +815,9 @@ def run_reference(args, world, rank):
     if rank != 0:
         return None
     from oracle import ref_cuda
-    base = {"metric": METRIC, "unit": "Mpix/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+    # the reference has no multi-GPU path: under torchrun rank 0 alone runs it, on ONE GPU, and says so
+    base = {"metric": METRIC, "unit": "Mpix/s", "n_gpus": 1, "requested_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "impl": "reference",
             "config": {"workload": f"C2: {args.gaussians} Gaussians, {args.views} views {IMG_W}x{IMG_H}, fwd+bwd, "
@@ -694,10 +846,10 @@ def run_reference(args, world, rank):
             rr.backward(gc[v], gd[v], ga)
             R += ro["num_rendered"]
         return R
-    for _ in range(max(1, min(args.warmup, 3))):
+    for _ in range(max(1, args.warmup)):
         step()
     torch.cuda.synchronize()
-    n = max(1, min(args.steps, 10))
+    n = max(1, args.steps)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(n):
@@ -723,7 +875,7 @@ def main():
         IMG_W, IMG_H = 1920, 1080
         args.gaussians = 2_000_000
         args.views = 8 * int(os.environ.get("WORLD_SIZE", "1"))
-        args.whole_views = args.no_train = args.no_cpu_baseline = True
+        args.whole_views = args.no_train = args.no_cpu_baseline = args.no_extras = True
         METRIC = "fwd+bwd rasterized Mpix/s @2M Gaussians, 8x1920x1080 views per GPU"
     if args.impl == "reference":
         world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
@@ -788,12 +940,28 @@ def main():
                 ach = amount / t / 1e9
                 roof = {"kernel": dom, "bound": "hbm", "achieved": round(ach, 1), "peak": hbm_gbs, "unit": "GB/s",
                         "frac": round(ach / hbm_gbs, 4), "traffic_from_committed_ncu": traffic, "peak_source": hbm_src}
+        stage_roofline = {}
+        for k, v in stages.items():
+            if k in work and v > 0:
+                kind, amount = work[k]
+                if kind == "fp32":
+                    a = amount / (v * 1e-3) / 1e12
+                    stage_roofline[k] = {"bound": "fp32", "achieved": round(a, 2), "unit": "TFLOP/s",
+                                         "frac": round(a / fp32["best"], 3)}
+                else:
+                    a = amount / (v * 1e-3) / 1e9
+                    stage_roofline[k] = {"bound": "hbm", "achieved": round(a, 1), "unit": "GB/s",
+                                         "frac": round(a / hbm_gbs, 3)}
+        ideal_ms = sum((work[k][1] / (fp32["best"] * 1e12) if work[k][0] == "fp32" else work[k][1] / (hbm_gbs * 1e9)) * 1e3
+                       for k in stages if k in work)
         line = {
             "metric": METRIC, "value": round(mpix, 2), "unit": "Mpix/s", "n_gpus": world, "steps": steps,
             "warmup": args.warmup, "ms_per_step": round(ms / steps, 3), "higher_is_better": True,
             "scaling": "weak" if args.workload == "c5" else "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{args.workload.upper()}: {P} Gaussians, {V} views {IMG_W}x{IMG_H}, fwd+bwd, colour+depth cotangents",
+            "config": {"workload": f"{args.workload.upper()}: {P} Gaussians, {V} views {IMG_W}x{IMG_H}, fwd+bwd, "
+                                   + ("colour+depth+alpha cotangents, label mask on the last 40 %" if args.workload == "c4"
+                                      else "colour+depth cotangents"),
                        "views_per_rank": res["views_per_rank"],
                        **({"rank_ms_before_each_rebalance": res["rebalance_ms"]} if res["rebalance_ms"] else {}), "parallelism": f"view-sharded dp{world}" + ("" if world == 1 or args.whole_views else " (cuts inside a view fall on tile-row bands)"),
                        "launch": "eager" if args.no_graph else "one CUDA graph per step (forward + backward + all-reduce)",
@@ -804,9 +972,16 @@ def main():
             **({"diagnostic": f"NOT a result: only rank {args.emulate_rank}'s share of a {args.emulate_world}-way partition "
                               "ran (value counts all views)"} if args.emulate_world else {}),
             "stage_ms_rank0": {k: round(v, 4) for k, v in stages.items()},
+            "stage_roofline_rank0": stage_roofline,
+            "step_vs_ideal_machine": {"ideal_ms": round(ideal_ms, 3), "frac": round(ideal_ms / (ms / steps), 3),
+                                      "what": "sum over stages of (this build's algorithmic work / measured peak) "
+                                              "divided by the measured step"},
+            "grad_check": res.get("grad_check"),
             "host_enqueue_ms_per_step_rank0": round(res["host_ms"], 3),
             "train_it_per_s_equiv": round(V * steps / (ms * 1e-3), 1),
         }
+        if world == 1 and not args.no_extras and not args.emulate_world:
+            line["extras"] = run_extras(args, res)
         if world == 1 and not args.no_train:
             line["train"] = run_train_loop(args, res)
         if world == 1 and not args.no_cpu_baseline:

@@ -301,6 +301,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             if (atomicAdd(&s_done[buf], 1u) == NW2 - 1) {
                 s_done[buf] = 0;
                 __threadfence_block();
+                fence_proxy_async_smem();          // the warps' generic-proxy reads of the slot before the TMA refill
                 if (r + RING < rounds) issue(r + RING);
             }
         }

@@ -319,6 +319,12 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {}
 }
+// Orders this thread's (and, through the preceding block-scope synchronisation, the CTA's) generic-proxy accesses to
+// shared memory before later async-proxy operations: a ring slot that warps have READ with ordinary loads is handed back
+// to the TMA engine (cp.async.bulk WRITES it through the async proxy) only behind this fence (PTX memory model: accesses
+// through different proxies need a proxy fence; an mbarrier hand-over would carry it implicitly, the ring's "last warp
+// out" atomic counter does not).
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 // global -> shared bulk copy; bytes must be a multiple of 16, both addresses 16-byte aligned.
 __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
     asm volatile(

@@ -177,13 +177,15 @@ def select_views(cotangents: dict, my_views: Sequence) -> dict:
 
 def sharded_step(settings, my_views: Sequence, params: dict, cotangents: dict, group=None,
                  capacity: Optional[int] = None, slab: Optional[GradSlab] = None, local_cotangents: bool = False,
-                 reduce: bool = True):
+                 reduce: bool = True, label: Optional[torch.Tensor] = None):
     """forward + backward of this rank's views and the all-reduce.  `my_views`: view indices and / or (view, first tile
     row, last + 1) bands (see split_units).  params: means3D, opacities, colors_precomp, scales, rotations (replicated).  cotangents: dict of [V_total, C, H, W] tensors or None for color / depth / alpha (or, with
     local_cotangents=True, already restricted to this rank's views by select_views()).
     `capacity`: instance capacity of the binning workspace (None = read the count back, one host sync per step).
     `slab`: a reusable GradSlab the gradients are written into (allocated when omitted).
     `reduce=False` leaves the all-reduce out (to time a rank's own work for rescale_row_costs).
+    `label` ([P] float, optional): the per-Gaussian gradient mask of the 4-return callers
+    (R/diff_gaussian_rasterization/__init__.py:159-170), applied inside the backward kernel.
     Returns (outputs of the local views, GradSlab summed over ALL views)."""
     from . import rasterizer as RZ
     P = params["means3D"].shape[0]
@@ -198,7 +200,7 @@ def sharded_step(settings, my_views: Sequence, params: dict, cotangents: dict, g
         cot = cotangents if local_cotangents else select_views(cotangents, my_views)
         RZ.backward_views(out[5], params["means3D"], params["opacities"], params["colors_precomp"],
                           params["scales"], params["rotations"], None, None, None, cot.get("color"),
-                          None, cot.get("depth"), cot.get("alpha"), want_means2D=False, out=slab.views)
+                          None, cot.get("depth"), cot.get("alpha"), label=label, want_means2D=False, out=slab.views)
     else:
         out = None
         slab.flat.zero_()
@@ -220,12 +222,12 @@ class GraphedStep:
         replay.  The all-reduce over `group` is part of the graph (NCCL collectives are capturable)."""
 
     def __init__(self, settings, my_views: Sequence, params: dict, cotangents: dict, capacity: int, group=None,
-                 warmup: int = 2, reduce: bool = True):
+                 warmup: int = 2, reduce: bool = True, label: Optional[torch.Tensor] = None):
         dev = params["means3D"].device
         self.slab = GradSlab(params["means3D"].shape[0], dev)
         self.out = None
         args = (settings, list(my_views), params, cotangents)
-        kw = dict(group=group, capacity=int(capacity), slab=self.slab, local_cotangents=True, reduce=reduce)
+        kw = dict(group=group, capacity=int(capacity), slab=self.slab, local_cotangents=True, reduce=reduce, label=label)
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):           # lazy initialisation (NCCL communicators, kernel attributes) happens here

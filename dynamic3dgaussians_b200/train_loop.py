@@ -270,7 +270,10 @@ class GraphedTrainer:
         self.params, self.variables, self.optimizer, self.dataset = params, variables, optimizer, list(dataset)
         self.graphs: List[torch.cuda.CUDAGraph] = []
         self.losses: List[torch.Tensor] = []
-        self.states: List[RZ.RasterState] = []
+        # [camera][num_rendered, overflow, prefilter violation, -]: copied out of the render's workspace at the end of every
+        # captured iteration.  The workspaces themselves live in the graphs' SHARED memory pool, where another camera's
+        # replay reuses them, so they cannot be read back later.
+        self.counters = torch.zeros(len(self.dataset), 4, dtype=torch.int32, device=dev)
         self.order: List[int] = []
         self.capacity = int(capacity)
 
@@ -323,10 +326,10 @@ class GraphedTrainer:
             st_out: list = []
             with torch.cuda.graph(g, pool=pool):
                 loss = iteration(curr, st_out)
+                self.counters[len(self.graphs)].copy_(st_out[0].geom[:16].view(torch.int32))
             pool = g.pool() if pool is None else pool
             self.graphs.append(g)
             self.losses.append(loss)
-            self.states.append(st_out[0])
 
     def step(self, generator: Optional[torch.Generator] = None) -> torch.Tensor:
         """One optimizer iteration on the next camera of a shuffled pass (get_batch); returns that graph's loss tensor
@@ -343,11 +346,11 @@ class GraphedTrainer:
     def overflowed(self) -> bool:
         """True when any camera's most recent replay needed more instances than `capacity` (its render dropped the
         surplus).  Synchronises; reads 16 bytes per camera."""
-        return any(RZ.read_flags(st)['overflowed'] for st in self.states)
+        return bool(self.counters[:, 1].any().item())
 
     def max_num_rendered(self) -> int:
         """Largest per-view instance count of the most recent replays (how much of `capacity` is in use)."""
-        return max(RZ.read_flags(st)['num_rendered'] for st in self.states)
+        return int(self.counters[:, 0].max().item())
 
 
 def _accumulate_inplace(variables: dict, fused: Optional[bool] = None):
