@@ -65,6 +65,49 @@ DebugSyncScope::DebugSyncScope(bool on) {
 DebugSyncScope::~DebugSyncScope() { g_debug_sync = false; }
 int DebugSyncScope::status() const { return g_debug_status; }
 
+// ---- the library's side stream (see common.cuh) ----
+namespace {
+struct SideStream {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+};
+constexpr int MAX_DEVICES = 64;
+thread_local SideStream g_side[MAX_DEVICES];
+
+int side_for_current_device(SideStream** out) {
+    int dev = 0;
+    GSR_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEVICES) return GSR_ERR_UNSUPPORTED;
+    SideStream& ss = g_side[dev];
+    if (!ss.stream) {
+        GSR_CUDA_TRY(cudaStreamCreateWithFlags(&ss.stream, cudaStreamNonBlocking));
+        GSR_CUDA_TRY(cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming));
+        GSR_CUDA_TRY(cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming));
+    }
+    *out = &ss;
+    return GSR_OK;
+}
+}  // namespace
+
+int side_fork(cudaStream_t main, cudaStream_t* side) {
+    SideStream* ss;
+    int rc = side_for_current_device(&ss);
+    if (rc) return rc;
+    GSR_CUDA_TRY(cudaEventRecord(ss->fork, main));
+    GSR_CUDA_TRY(cudaStreamWaitEvent(ss->stream, ss->fork, 0));
+    *side = ss->stream;
+    return GSR_OK;
+}
+
+int side_join(cudaStream_t main) {
+    SideStream* ss;
+    int rc = side_for_current_device(&ss);
+    if (rc) return rc;
+    GSR_CUDA_TRY(cudaEventRecord(ss->join, ss->stream));
+    GSR_CUDA_TRY(cudaStreamWaitEvent(main, ss->join, 0));
+    return GSR_OK;
+}
+
 static void fill_cam(const GsrCamera& c, CamDev& d) {
     memset(&d, 0, sizeof(d));
     memcpy(d.view, c.viewmatrix, sizeof(d.view));
@@ -183,8 +226,12 @@ static int check_dims(int P, int V, int W, int H, int channels, int sh_coeffs, i
         return GSR_ERR_INVALID_ARGUMENT;
     if (channels != 3 && channels != 6) return GSR_ERR_UNSUPPORTED;
     if ((int64_t)V * P >= (1ll << 30) || capacity >= (1ll << 30)) return GSR_ERR_UNSUPPORTED;
-    const int64_t VT = (int64_t)V * ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
-    if (VT >= (1ll << 28) || W >= (1 << 20) || H >= (1 << 20)) return GSR_ERR_UNSUPPORTED;   // tile rects are ushort4
+    const int64_t tx = (W + TILE_X - 1) / TILE_X, ty = (H + TILE_Y - 1) / TILE_Y;
+    const int64_t VT = (int64_t)V * tx * ty;
+    if (VT >= (1ll << 28) || tx > 1024 || ty > 1024) return GSR_ERR_UNSUPPORTED;   // supertile coordinates are bytes (16384 px)
+    // the instance key keeps view * supertiles + supertile in 16 bits (its upper half carries the tile hit mask): a batch
+    // may hold at most 65536 supertiles (64x64 px) over all its views -- e.g. 128 views of 1920x1080; split larger ones
+    if ((int64_t)V * ((tx + ST - 1) / ST) * ((ty + ST - 1) / ST) > (1ll << 16)) return GSR_ERR_UNSUPPORTED;
     return GSR_OK;
 }
 
@@ -257,17 +304,15 @@ int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels,
     {
         // every view's Gaussians by depth: V segments of P (depth bits, Gaussian index) pairs, 4 passes of 32-bit keys
         StageScope sc(ST_DEPTH_SORT, s);
+        // Gaussians that touch no tile carry the sentinel key ~0: the first pass drops them and leaves vis_count[v] per view
         rc = radix_sort_pairs<uint32_t>(at<uint32_t>(geom_ws, L.dkeys0), at<uint32_t>(geom_ws, L.dkeys1),
                                         at<uint32_t>(geom_ws, L.dvals0), at<uint32_t>(geom_ws, L.dvals1), P, nullptr,
                                         0, 32, at<uint32_t>(geom_ws, L.dhist), at<uint32_t>(geom_ws, L.dlookback),
-                                        at<uint32_t>(geom_ws, L.dcounters), s, V, false, true);
+                                        at<uint32_t>(geom_ws, L.dcounters), s, V, false, true,
+                                        at<uint32_t>(geom_ws, L.vis_count));
     }
     if (rc) return rc;
-    {
-        StageScope sc(ST_TILE_SCAN, s);
-        rc = launch_tile_scan(V, P, geom_ws, L, s);
-    }
-    if (rc) return rc;
+    // (the instance count -- the reference's num_rendered -- is summed by the preprocess kernel itself)
     if (num_rendered_dev)
         GSR_CUDA_TRY(cudaMemcpyAsync(num_rendered_dev, counters + CNT_RENDERED, 4, cudaMemcpyDeviceToDevice, s));
     return dbg.status();

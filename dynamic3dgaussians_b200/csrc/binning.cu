@@ -57,203 +57,17 @@ __device__ __forceinline__ uint32_t st_rect(ushort4 r, uint32_t& sx0, uint32_t& 
     return sw * ((r.w - 1u) / ST - sy0 + 1u);
 }
 
-// slot i of the depth-sorted list: view = i / P, Gaussian = sorted_g[i]
+// slot i of the depth-sorted list: view = i / P, Gaussian = sorted_g[i]; a view's list holds its vis_count[view] visible
+// Gaussians (the rest of its P slots is unused)
 __device__ __forceinline__ ushort4 slot_rect(uint32_t i, uint32_t VP, int P, const uint32_t* __restrict__ sorted_g,
-                                             const ushort4* __restrict__ rects, uint32_t& gidx) {
-    if (i >= VP) { gidx = 0; return make_ushort4(0, 0, 0, 0); }
+                                             const ushort4* __restrict__ rects, const uint32_t* __restrict__ vis_count,
+                                             uint32_t& gidx) {
+    gidx = 0;
+    if (i >= VP) return make_ushort4(0, 0, 0, 0);
     const uint32_t view = i / (uint32_t)P;
+    if (i - view * (uint32_t)P >= vis_count[view]) return make_ushort4(0, 0, 0, 0);
     gidx = view * (uint32_t)P + sorted_g[i];
     return rects[gidx];
-}
-
-// per block of 2048 slots: number of supertile instances (for the emit offsets); the tile-instance total
-// (the reference's num_rendered) is accumulated on the side
-__global__ void __launch_bounds__(SCAN_BLOCK)
-st_count_reduce_kernel(uint32_t VP, int P, const uint32_t* __restrict__ sorted_g, const ushort4* __restrict__ rects,
-                       uint32_t* __restrict__ block_sums, uint32_t* __restrict__ counters) {
-    __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
-    const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
-    uint32_t sum = 0, tiles = 0, gidx;
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; ++k) {
-        const ushort4 r = slot_rect(base + k, VP, P, sorted_g, rects, gidx);
-        uint32_t a, b, c;
-        sum += st_rect(r, a, b, c);
-        tiles += (uint32_t)(r.z - r.x) * (uint32_t)(r.w - r.y);
-    }
-    uint32_t total, total_tiles;
-    block_exclusive_scan_256(sum, s_warp, total);
-    block_exclusive_scan_256(tiles, s_warp, total_tiles);
-    if (threadIdx.x == 0) {
-        block_sums[blockIdx.x] = total;
-        if (total_tiles) atomicAdd(&counters[CNT_RENDERED], total_tiles);
-    }
-}
-
-// single block: exclusive scan of the per-block sums in place; total -> counters[CNT_ST_RENDERED]
-__global__ void __launch_bounds__(SCAN_BLOCK)
-block_sums_scan_kernel(uint32_t nblocks, uint32_t* __restrict__ block_sums, uint32_t* __restrict__ counters) {
-    __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
-    uint32_t carry = 0;
-    for (uint32_t start = 0; start < nblocks; start += SCAN_BLOCK) {
-        const uint32_t i = start + threadIdx.x;
-        const uint32_t v = i < nblocks ? block_sums[i] : 0u;
-        uint32_t total;
-        const uint32_t ex = block_exclusive_scan_256(v, s_warp, total);
-        if (i < nblocks) block_sums[i] = carry + ex;
-        carry += total;
-    }
-    if (threadIdx.x == 0) {
-        counters[CNT_ST_RENDERED] = carry;
-        counters[CNT_OVERFLOW] = 0;
-    }
-}
-
-// Emits the (view*S + supertile, view*P + Gaussian) pairs of every visible (view, Gaussian) in depth order.
-// Every thread owns 8 consecutive slots of the depth-sorted list; the CTA scans the slots' instance counts, each
-// thread writes its own instances (walking its supertile rectangles, no search) into a shared-memory window at their
-// output positions, and the window is copied out with fully coalesced stores.  The digit histograms of the following
-// sort are taken on the way out (warp-private bins, radix_rank.cuh), which saves that sort's pass over the keys.
-constexpr int EMIT_WINDOW = 3072;        // staged outputs per round (a CTA of 2048 slots emits ~2900 at C2)
-
-__global__ void __launch_bounds__(SCAN_BLOCK)
-emit_st_instances_kernel(uint32_t VP, int P, int stiles_x, uint32_t S, const uint32_t* __restrict__ sorted_g,
-                         const ushort4* __restrict__ rects, const uint32_t* __restrict__ block_sums, uint32_t capacity,
-                         uint32_t* __restrict__ ikeys, uint32_t* __restrict__ ivals, uint32_t* __restrict__ counters,
-                         int hist_passes, int key_bits, uint32_t* __restrict__ sort_hist) {
-    __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
-    __shared__ uint32_t s_hist[SCAN_BLOCK / 32][EMIT_HIST_PASSES][RADIX];
-    __shared__ uint32_t s_key[EMIT_WINDOW];
-    __shared__ uint32_t s_val[EMIT_WINDOW];
-    const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
-    uint32_t cnt[SCAN_ITEMS], gidx[SCAN_ITEMS], key0[SCAN_ITEMS], wid[SCAN_ITEMS];
-    uint32_t sum = 0;
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; ++k) {
-        const ushort4 r = slot_rect(base + k, VP, P, sorted_g, rects, gidx[k]);
-        uint32_t sx0, sy0;
-        cnt[k] = st_rect(r, sx0, sy0, wid[k]);
-        key0[k] = (gidx[k] / (uint32_t)P) * S + sy0 * (uint32_t)stiles_x + sx0;
-        sum += cnt[k];
-    }
-    uint32_t total;
-    const uint32_t off0 = block_exclusive_scan_256(sum, s_warp, total);
-    if (hist_passes > 0)
-        for (int i = threadIdx.x; i < (SCAN_BLOCK / 32) * EMIT_HIST_PASSES * RADIX; i += SCAN_BLOCK) (&s_hist[0][0][0])[i] = 0;
-    const uint32_t out0 = block_sums[blockIdx.x];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    bool overflow = false;
-    for (uint32_t w0 = 0; w0 < total; w0 += EMIT_WINDOW) {
-        __syncthreads();                                  // the previous window has been copied out (and s_hist zeroed)
-        if (off0 < w0 + EMIT_WINDOW && off0 + sum > w0) {     // some of this thread's instances fall into the window
-            uint32_t o = off0;
-#pragma unroll
-            for (int k = 0; k < SCAN_ITEMS; ++k) {
-                uint32_t row = key0[k], x = 0;
-                for (uint32_t l = 0; l < cnt[k]; ++l) {
-                    const uint32_t rel = o - w0;           // wraps for o < w0: fails the test below
-                    if (rel < (uint32_t)EMIT_WINDOW) {
-                        s_key[rel] = row + x;
-                        s_val[rel] = gidx[k];
-                    }
-                    ++o;
-                    if (++x == wid[k]) { x = 0; row += (uint32_t)stiles_x; }
-                }
-            }
-        }
-        __syncthreads();
-        const uint32_t n = min((uint32_t)EMIT_WINDOW, total - w0);
-        for (uint32_t o0 = 0; o0 < n; o0 += SCAN_BLOCK) {     // warp-uniform trip count (the histogram uses ballots)
-            const uint32_t o = o0 + threadIdx.x;
-            bool stored = false;
-            uint32_t key = 0;
-            if (o < n) {
-                key = s_key[o];
-                const uint32_t dst = out0 + w0 + o;
-                if (dst < capacity) {
-                    ikeys[dst] = key;
-                    ivals[dst] = s_val[o];
-                    stored = true;
-                } else {
-                    overflow = true;
-                }
-            }
-#pragma unroll
-            for (int p = 0; p < EMIT_HIST_PASSES; ++p) {
-                if (p < hist_passes) {
-                    const int shift = p * RADIX_BITS;
-                    const int bits = min(RADIX_BITS, key_bits - shift);
-                    uint32_t peers;
-                    if (bits <= 4)
-                        warp_hist_add<4>(s_hist[warp][p], (key >> shift) & ((1u << bits) - 1u), stored, lane, peers);
-                    else
-                        warp_hist_add(s_hist[warp][p], (key >> shift) & ((1u << bits) - 1u), stored, lane, peers);
-                }
-            }
-        }
-    }
-    if (overflow) counters[CNT_OVERFLOW] = 1;
-    if (hist_passes > 0) {
-        __syncthreads();
-        for (int i = threadIdx.x; i < hist_passes * RADIX; i += SCAN_BLOCK) {
-            const int p = i / RADIX, d = i - p * RADIX;
-            uint32_t c = 0;
-#pragma unroll
-            for (int w = 0; w < SCAN_BLOCK / 32; ++w) c += s_hist[w][p][d];
-            if (c) atomicAdd(&sort_hist[i], c);
-        }
-    }
-}
-
-// boundary detection on the sorted supertile keys (the reference's identifyTileRanges, rasterizer_impl.cu:116-138, one
-// level up): st_ranges[key] = [first, last+1) ; st_ranges is zeroed before
-__global__ void __launch_bounds__(256)
-st_ranges_kernel(const uint32_t* __restrict__ counters, uint32_t capacity, const uint32_t* __restrict__ keys,
-                 uint2* __restrict__ st_ranges) {
-    const uint32_t n = min(counters[CNT_ST_RENDERED], capacity);
-    // grid-stride: the count lives on the device, so the grid is sized for the SMs rather than for the capacity
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t cur = keys[i];
-        if (i == 0) {
-            st_ranges[cur].x = 0;
-        } else {
-            const uint32_t prev = keys[i - 1];
-            if (cur != prev) {
-                st_ranges[prev].y = i;
-                st_ranges[cur].x = i;
-            }
-        }
-        if (i == n - 1) st_ranges[cur].y = n;
-    }
-}
-
-// single block: chunk_base[k] = exclusive scan of ceil(len_k / CHUNK) over the V*S supertile keys, chunk_base[VS] and
-// counters[CNT_NCHUNKS] = number of chunks; chunk_key[c] = owning key of chunk c
-__global__ void __launch_bounds__(SCAN_BLOCK)
-chunk_table_kernel(uint32_t VS, const uint2* __restrict__ st_ranges, uint32_t* __restrict__ chunk_base,
-                   uint32_t* __restrict__ chunk_key, uint32_t max_chunks, uint32_t* __restrict__ counters) {
-    __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
-    uint32_t carry = 0;
-    for (uint32_t start = 0; start < VS; start += SCAN_BLOCK) {
-        const uint32_t k = start + threadIdx.x;
-        uint32_t nch = 0;
-        if (k < VS) {
-            const uint2 r = st_ranges[k];
-            nch = (r.y - r.x + CHUNK - 1) / CHUNK;
-        }
-        uint32_t total;
-        const uint32_t cb = carry + block_exclusive_scan_256(nch, s_warp, total);
-        if (k < VS) {
-            chunk_base[k] = cb;
-            for (uint32_t j = 0; j < nch; ++j)
-                if (cb + j < max_chunks) chunk_key[cb + j] = k;
-        }
-        carry += total;
-    }
-    if (threadIdx.x == 0) {
-        chunk_base[VS] = carry;
-        counters[CNT_NCHUNKS] = min(carry, max_chunks);
-    }
 }
 
 // 16-bit hit mask of a tile rectangle inside the supertile whose first tile is (ox, oy): bit ty*4+tx
@@ -267,89 +81,49 @@ __device__ __forceinline__ uint32_t st_hit_mask(ushort4 r, uint32_t ox, uint32_t
     return xb * ys;
 }
 
-struct ChunkInfo {
-    uint32_t key, first, count;      // supertile key, first sorted instance, instances in this chunk
-    uint32_t view, ox, oy;           // view and first tile of the supertile
-};
+__device__ __forceinline__ uint32_t ld_vol(const uint32_t* p) { return *reinterpret_cast<const volatile uint32_t*>(p); }
+__device__ __forceinline__ void st_vol(uint32_t* p, uint32_t v) { *reinterpret_cast<volatile uint32_t*>(p) = v; }
 
-__device__ __forceinline__ bool chunk_info(uint32_t cid, const uint32_t* __restrict__ counters,
-                                           const uint32_t* __restrict__ chunk_key, const uint32_t* __restrict__ chunk_base,
-                                           const uint2* __restrict__ st_ranges, uint32_t S, int stiles_x, ChunkInfo& c) {
-    if (cid >= counters[CNT_NCHUNKS]) return false;
-    c.key = chunk_key[cid];
-    const uint2 r = st_ranges[c.key];
-    c.first = r.x + (cid - chunk_base[c.key]) * CHUNK;
-    c.count = min((uint32_t)CHUNK, r.y - c.first);
-    c.view = c.key / S;
-    const uint32_t s = c.key - c.view * S;
-    const uint32_t sy = s / (uint32_t)stiles_x;
-    c.ox = (s - sy * (uint32_t)stiles_x) * ST;
-    c.oy = sy * ST;
-    return true;
-}
+// decoupled look-back word of the emit kernel: 2 flag bits + 30-bit count
+constexpr uint32_t LB_AGG = 1u << 30, LB_INC = 1u << 31, LB_VALUE = (1u << 30) - 1u;
+constexpr int ST_KEY_BITS = 16;          // the instance key's low half is view*S + supertile, its high half the tile hit mask
 
-// per chunk: how many of its instances hit each of the supertile's 16 tiles
-__global__ void __launch_bounds__(CHUNK)
-chunk_count_kernel(const uint32_t* __restrict__ counters, const uint32_t* __restrict__ chunk_key,
-                   const uint32_t* __restrict__ chunk_base, const uint2* __restrict__ st_ranges, uint32_t S,
-                   int stiles_x, const uint32_t* __restrict__ vals, const ushort4* __restrict__ rects,
-                   uint16_t* __restrict__ masks, uint32_t* __restrict__ chunk_counts) {
-    __shared__ uint32_t s_cnt[ST_TILES][CHUNK / 32];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    ChunkInfo c;
-    // persistent CTAs: the chunk count is only known on the device, so the grid is sized for the SMs, not the chunks
-    for (uint32_t cid = blockIdx.x; chunk_info(cid, counters, chunk_key, chunk_base, st_ranges, S, stiles_x, c);
-         cid += gridDim.x) {
-        uint32_t mask = 0;
-        if ((uint32_t)tid < c.count) {
-            mask = st_hit_mask(rects[vals[c.first + tid]], c.ox, c.oy);
-            masks[c.first + tid] = (uint16_t)mask;           // the scatter pass reads this instead of the rectangle
-        }
+// Emits the (key, view*P + Gaussian) pairs of every visible (view, Gaussian) in depth order, ONE pass over the
+// depth-sorted slots (no separate counting pass: the CTAs take their slot block from a ticket and get their output offset
+// by decoupled look-back over the blocks before them).
+//   key = hit mask << 16 | (view*S + supertile): the 16 tiles of the supertile the Gaussian's rectangle covers ride in the
+//   upper half of the sort key (the sort only looks at the low `key_bits`), so no later pass has to fetch the rectangle
+//   again (the round-1 chunk_count kernel gathered 32-byte sectors for 8 useful bytes per instance: 117 us at C2).
+// Every thread owns 8 consecutive slots of the depth-sorted list; each thread writes its own instances (walking its
+// supertile rectangles, no search) into a shared-memory window at their output positions, and the window is copied out
+// with fully coalesced stores.  On the way out the CTA counts: the digit histograms of the following sort (warp-private
+// bins, radix_rank.cuh) and the instances per supertile key (shared-memory bins over the one or two views a CTA's slots
+// belong to) -- the latter give st_ranges / the chunk table without a pass over the sorted keys.
+#ifndef GSR_EMIT_LOOKBACK
+#define GSR_EMIT_LOOKBACK 0              // 1: the emit CTAs find their output offset by decoupled look-back (one pass over the
+#endif                                   // slots; measured SLOWER at C2: 311 us against 147 + 58 us for count + emit)
+constexpr int EMIT_ITEMS = 4;            // depth-sorted slots per thread
+constexpr int EMIT_TILE = SCAN_BLOCK * EMIT_ITEMS;
+static_assert(EMIT_TILE == 1024, "compute_layout sizes the look-back words for blocks of 1024 slots");
+constexpr int EMIT_WINDOW = 2048;        // staged outputs per round (a CTA of 1024 slots emits ~1450 at C2)
+
+// per block of EMIT_TILE slots: number of supertile instances (for the emit offsets)
+__global__ void __launch_bounds__(SCAN_BLOCK)
+st_count_reduce_kernel(uint32_t VP, int P, const uint32_t* __restrict__ sorted_g, const ushort4* __restrict__ rects,
+                       const uint32_t* __restrict__ vis_count, uint32_t* __restrict__ block_sums) {
+    __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
+    const uint32_t base = blockIdx.x * EMIT_TILE + threadIdx.x * EMIT_ITEMS;
+    uint32_t sum = 0, gidx;
 #pragma unroll
-        for (int t = 0; t < ST_TILES; ++t) {
-            const uint32_t bal = __ballot_sync(FULL, (mask >> t) & 1u);
-            if (lane == 0) s_cnt[t][warp] = __popc(bal);
-        }
-        __syncthreads();
-        if (tid < ST_TILES) {
-            uint32_t n = 0;
-#pragma unroll
-            for (int w = 0; w < CHUNK / 32; ++w) n += s_cnt[tid][w];
-            chunk_counts[(size_t)cid * ST_TILES + tid] = n;
-        }
-        __syncthreads();
+    for (int k = 0; k < EMIT_ITEMS; ++k) {
+        const ushort4 r = slot_rect(base + k, VP, P, sorted_g, rects, vis_count, gidx);
+        uint32_t a, b, c;
+        sum += st_rect(r, a, b, c);
     }
+    uint32_t total;
+    block_exclusive_scan_256(sum, s_warp, total);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
 }
-
-// one warp per supertile key: per tile, exclusive prefix of the chunk counts over the key's chunks (in place), and the
-// tile's total -> tile_start[view*T + tile] (scanned by tile_scan_kernel)
-__global__ void __launch_bounds__(128)
-tile_offsets_kernel(uint32_t VS, uint32_t S, int stiles_x, int tiles_x, int tiles_y,
-                    const uint32_t* __restrict__ chunk_base, uint32_t max_chunks, uint32_t* __restrict__ chunk_counts,
-                    uint32_t* __restrict__ tile_start) {
-    const uint32_t k = blockIdx.x * 4 + (threadIdx.x >> 5);
-    const int t = threadIdx.x & 31;
-    if (k >= VS || t >= ST_TILES) return;
-    const uint32_t c0 = min(chunk_base[k], max_chunks), c1 = min(chunk_base[k + 1], max_chunks);
-    uint32_t run = 0;
-    for (uint32_t c = c0; c < c1; ++c) {
-        const uint32_t n = chunk_counts[(size_t)c * ST_TILES + t];
-        chunk_counts[(size_t)c * ST_TILES + t] = run;
-        run += n;
-    }
-    const uint32_t view = k / S, s = k - view * S;
-    const uint32_t sy = s / (uint32_t)stiles_x, sx = s - sy * (uint32_t)stiles_x;
-    const uint32_t gx = sx * ST + (t & 3), gy = sy * ST + (t >> 2);
-    if (gx < (uint32_t)tiles_x && gy < (uint32_t)tiles_y)
-        tile_start[(size_t)view * tiles_x * tiles_y + gy * (uint32_t)tiles_x + gx] = run;
-}
-
-// single block: exclusive scan of the per-tile counts in place (tile_start), ranges clamped to the capacity; then a
-// counting sort of the (view, tile) indices by list length, longest first -> tile_order.  The blend kernels launch
-// their CTAs in that order, so the longest sequential chains start first and the short tiles fill in behind them
-// (the hardware dispatches CTAs in blockIdx order).
-constexpr int ORDER_BUCKETS = 1024;
-constexpr int TSCAN_THREADS = 1024;          // one CTA on the critical path: as many loads in flight as one CTA can have
 
 __device__ __forceinline__ uint32_t block_exclusive_scan_1024(uint32_t v, uint32_t* s_warp /*[32]*/, uint32_t& total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -373,23 +147,333 @@ __device__ __forceinline__ uint32_t block_exclusive_scan_1024(uint32_t v, uint32
     return base + inc - v;
 }
 
+// single block of 1024 threads, 4 sums per thread and step: exclusive scan of the per-block sums in place;
+// total -> counters[CNT_ST_RENDERED]
+__global__ void __launch_bounds__(1024)
+block_sums_scan_kernel(uint32_t nblocks, uint32_t* __restrict__ block_sums, uint32_t* __restrict__ counters) {
+    __shared__ uint32_t s_warp[32];
+    uint32_t carry = 0;
+    for (uint32_t start = 0; start < nblocks; start += 4096) {
+        const uint32_t i0 = start + threadIdx.x * 4;
+        uint32_t v[4], sum = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { v[k] = i0 + k < nblocks ? block_sums[i0 + k] : 0u; sum += v[k]; }
+        uint32_t total;
+        uint32_t ex = carry + block_exclusive_scan_1024(sum, s_warp, total);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (i0 + k < nblocks) block_sums[i0 + k] = ex;
+            ex += v[k];
+        }
+        carry += total;
+    }
+    if (threadIdx.x == 0) counters[CNT_ST_RENDERED] = carry;
+}
+
+__global__ void __launch_bounds__(SCAN_BLOCK, 4)
+emit_st_instances_kernel(uint32_t VP, int P, int stiles_x, uint32_t S, const uint32_t* __restrict__ sorted_g,
+                         const ushort4* __restrict__ rects, const uint32_t* __restrict__ vis_count, uint32_t capacity,
+                         uint32_t nblocks,
+                         uint32_t* __restrict__ ikeys, uint32_t* __restrict__ ivals, uint32_t* __restrict__ counters,
+                         int hist_passes, int key_bits, uint32_t* __restrict__ sort_hist,
+                         uint32_t* __restrict__ lookback, uint32_t* __restrict__ ticket,
+                         uint32_t* __restrict__ key_hist, uint32_t khist_bins /* 0: global atomics */) {
+    extern __shared__ uint32_t s_khist[];                 // [khist_bins]: instances per key, keys kbase .. kbase + bins
+    __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
+    __shared__ uint32_t s_hist[SCAN_BLOCK / 32][EMIT_HIST_PASSES][RADIX];
+    __shared__ uint32_t s_key[EMIT_WINDOW];              // key | supertile x << 16 | supertile y << 24
+    __shared__ uint16_t s_slot[EMIT_WINDOW];             // which of the block's slots the instance belongs to
+    __shared__ uint32_t s_gidx[EMIT_TILE];               // per slot: view*P + Gaussian and the tile rectangle
+    __shared__ ushort4 s_rect[EMIT_TILE];
+    __shared__ uint32_t s_blk, s_out0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#if GSR_EMIT_LOOKBACK
+    if (threadIdx.x == 0) s_blk = atomicAdd(ticket, 1u);  // blocks are numbered in the order they start: a block only
+    __syncthreads();                                      // waits for blocks that already run
+    const uint32_t blk = s_blk;
+#else
+    const uint32_t blk = blockIdx.x;
+#endif
+    const uint32_t slot0 = blk * EMIT_TILE;
+    const uint32_t base = slot0 + threadIdx.x * EMIT_ITEMS;
+    // per slot: the tile rectangle, view*P + Gaussian and the key of its first supertile; counts and widths are re-derived
+    // from the rectangle where they are needed (registers decide how many CTAs hide the dependent loads)
+    uint32_t gidx[EMIT_ITEMS], key0[EMIT_ITEMS];
+    ushort4 rc[EMIT_ITEMS];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int k = 0; k < EMIT_ITEMS; ++k) {
+        rc[k] = slot_rect(base + k, VP, P, sorted_g, rects, vis_count, gidx[k]);
+        uint32_t sx0, sy0, w;
+        sum += st_rect(rc[k], sx0, sy0, w);
+        key0[k] = (gidx[k] / (uint32_t)P) * S + sy0 * (uint32_t)stiles_x + sx0;
+        s_gidx[threadIdx.x * EMIT_ITEMS + k] = gidx[k];
+        s_rect[threadIdx.x * EMIT_ITEMS + k] = rc[k];
+    }
+    uint32_t total;
+    const uint32_t off0 = block_exclusive_scan_256(sum, s_warp, total);
+#if !GSR_EMIT_LOOKBACK
+    if (threadIdx.x == 0) s_out0 = lookback[blk];         // exclusive scan of the per-block counts (block_sums_scan_kernel)
+#else
+    // ---- this block's first output position: decoupled look-back over the earlier blocks (warp 0, 32 words a step) ----
+    if (warp == 0) {
+        uint32_t excl = 0;
+        if (blk == 0) {
+            if (lane == 0) st_vol(&lookback[0], total | LB_INC);
+        } else {
+            if (lane == 0) st_vol(&lookback[blk], total | LB_AGG);
+            int64_t t = (int64_t)blk - 1;
+            while (true) {
+                const int64_t idx = t - lane;
+                uint32_t v = LB_INC;                                  // before block 0: inclusive prefix 0
+                if (idx >= 0) {
+                    while (((v = ld_vol(&lookback[idx])) >> 30) == 0u) __nanosleep(40);
+                }
+                const uint32_t inc = __ballot_sync(FULL, (v & LB_INC) != 0u);
+                const int first = inc ? __ffs(inc) - 1 : 32;          // nearest block with an inclusive prefix
+                uint32_t c = lane <= first ? (v & LB_VALUE) : 0u;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(FULL, c, o);
+                excl += c;
+                if (inc) break;
+                t -= 32;
+            }
+            if (lane == 0) st_vol(&lookback[blk], ((excl + total) & LB_VALUE) | LB_INC);
+        }
+        if (lane == 0) {
+            s_out0 = excl;
+            if (blk == nblocks - 1) counters[CNT_ST_RENDERED] = excl + total;
+        }
+    }
+#endif
+    if (hist_passes > 0)
+        for (int i = threadIdx.x; i < (SCAN_BLOCK / 32) * EMIT_HIST_PASSES * RADIX; i += SCAN_BLOCK) (&s_hist[0][0][0])[i] = 0;
+    // supertile keys this block can emit: those of the views its slots belong to
+    const uint32_t kbase = (slot0 / (uint32_t)P) * S;
+    for (uint32_t i = threadIdx.x; i < khist_bins; i += SCAN_BLOCK) s_khist[i] = 0;
+    __syncthreads();
+    const uint32_t out0 = s_out0;
+    bool overflow = false;
+    for (uint32_t w0 = 0; w0 < total; w0 += EMIT_WINDOW) {
+        if (w0) __syncthreads();                          // the previous window has been copied out
+        if (off0 < w0 + EMIT_WINDOW && off0 + sum > w0) {     // some of this thread's instances fall into the window
+            uint32_t o = off0;
+#pragma unroll
+            for (int k = 0; k < EMIT_ITEMS; ++k) {
+                uint32_t sx0, sy0, wid;
+                const uint32_t cnt = st_rect(rc[k], sx0, sy0, wid);
+                uint32_t row = key0[k], x = 0, sy = sy0;
+                for (uint32_t l = 0; l < cnt; ++l) {
+                    const uint32_t rel = o - w0;           // wraps for o < w0: fails the test below
+                    if (rel < (uint32_t)EMIT_WINDOW) {       // the serial walk only notes WHERE; the copy-out does the rest
+                        s_key[rel] = (row + x) | ((sx0 + x) << 16) | (sy << 24);
+                        s_slot[rel] = (uint16_t)(threadIdx.x * EMIT_ITEMS + k);
+                    }
+                    ++o;
+                    if (++x == wid) { x = 0; row += (uint32_t)stiles_x; ++sy; }
+                }
+            }
+        }
+        __syncthreads();
+        const uint32_t n = min((uint32_t)EMIT_WINDOW, total - w0);
+        for (uint32_t o0 = 0; o0 < n; o0 += SCAN_BLOCK) {     // warp-uniform trip count (the histogram uses ballots)
+            const uint32_t o = o0 + threadIdx.x;
+            bool stored = false;
+            uint32_t key = 0;
+            if (o < n) {
+                const uint32_t packed = s_key[o];
+                const uint32_t slot = s_slot[o];
+                const uint32_t kk = packed & ((1u << ST_KEY_BITS) - 1u);
+                key = (st_hit_mask(s_rect[slot], ((packed >> 16) & 0xffu) * ST, (packed >> 24) * ST) << ST_KEY_BITS) | kk;
+                const uint32_t dst = out0 + w0 + o;
+                if (dst < capacity) {
+                    ikeys[dst] = key;
+                    ivals[dst] = s_gidx[slot];
+                    stored = true;
+                    if (khist_bins) atomicAdd(&s_khist[kk - kbase], 1u);
+                    else atomicAdd(&key_hist[kk], 1u);
+                } else {
+                    overflow = true;
+                }
+            }
+#pragma unroll
+            for (int p = 0; p < EMIT_HIST_PASSES; ++p) {
+                if (p < hist_passes) {
+                    const int shift = p * RADIX_BITS;
+                    const int bits = min(RADIX_BITS, key_bits - shift);
+                    uint32_t peers;
+                    if (bits <= 4)
+                        warp_hist_add<4>(s_hist[warp][p], (key >> shift) & ((1u << bits) - 1u), stored, lane, peers);
+                    else
+                        warp_hist_add(s_hist[warp][p], (key >> shift) & ((1u << bits) - 1u), stored, lane, peers);
+                }
+            }
+        }
+    }
+    if (overflow) counters[CNT_OVERFLOW] = 1;
+    __syncthreads();
+    if (hist_passes > 0) {
+        for (int i = threadIdx.x; i < hist_passes * RADIX; i += SCAN_BLOCK) {
+            const int p = i / RADIX, d = i - p * RADIX;
+            uint32_t c = 0;
+#pragma unroll
+            for (int w = 0; w < SCAN_BLOCK / 32; ++w) c += s_hist[w][p][d];
+            if (c) atomicAdd(&sort_hist[i], c);
+        }
+    }
+    for (uint32_t i = threadIdx.x; i < khist_bins; i += SCAN_BLOCK) {
+        const uint32_t c = s_khist[i];
+        if (c) atomicAdd(&key_hist[kbase + i], c);
+    }
+}
+
+// single block, off the critical path (it runs next to the instance sort, launch_binning): from the per-key instance counts
+// the emit kernel took,
+//   st_ranges[k]  = [first, last + 1) of key k in the SORTED instance list (the reference's identifyTileRanges,
+//                   rasterizer_impl.cu:116-138, one level up -- but without reading the sorted keys),
+//   chunk_base[k] = exclusive scan of ceil(len_k / CHUNK), chunk_base[VS] and counters[CNT_NCHUNKS] = number of chunks,
+//   chunk_key[c]  = owning key of chunk c.
+constexpr int CT_THREADS = 1024;
+
+__global__ void __launch_bounds__(CT_THREADS)
+chunk_table_kernel(uint32_t VS, const uint32_t* __restrict__ key_hist, uint2* __restrict__ st_ranges,
+                   uint32_t* __restrict__ chunk_base, uint32_t* __restrict__ chunk_key, uint32_t max_chunks,
+                   uint32_t* __restrict__ counters) {
+    __shared__ uint32_t s_warp[32];
+    uint32_t carry_i = 0, carry_c = 0;
+    for (uint32_t start = 0; start < VS; start += CT_THREADS) {
+        const uint32_t k = start + threadIdx.x;
+        const uint32_t n = k < VS ? key_hist[k] : 0u;     // stored instances only: their sum never exceeds the capacity
+        uint32_t tot_i, tot_c;
+        const uint32_t first = carry_i + block_exclusive_scan_1024(n, s_warp, tot_i);
+        const uint32_t nch = (n + CHUNK - 1) / CHUNK;
+        const uint32_t cb = carry_c + block_exclusive_scan_1024(nch, s_warp, tot_c);
+        if (k < VS) {
+            st_ranges[k] = make_uint2(first, first + n);
+            chunk_base[k] = cb;
+            for (uint32_t j = 0; j < nch; ++j)
+                if (cb + j < max_chunks) chunk_key[cb + j] = k;
+        }
+        carry_i += tot_i;
+        carry_c += tot_c;
+    }
+    if (threadIdx.x == 0) {
+        chunk_base[VS] = carry_c;
+        counters[CNT_NCHUNKS] = min(carry_c, max_chunks);
+    }
+}
+
+struct ChunkInfo {
+    uint32_t key, first, count;      // supertile key, first sorted instance, instances in this chunk
+    uint32_t view, ox, oy;           // view and first tile of the supertile
+};
+
+__device__ __forceinline__ bool chunk_info(uint32_t cid, const uint32_t* __restrict__ counters,
+                                           const uint32_t* __restrict__ chunk_key, const uint32_t* __restrict__ chunk_base,
+                                           const uint2* __restrict__ st_ranges, uint32_t S, int stiles_x, ChunkInfo& c) {
+    if (cid >= counters[CNT_NCHUNKS]) return false;
+    c.key = chunk_key[cid];
+    const uint2 r = st_ranges[c.key];
+    c.first = r.x + (cid - chunk_base[c.key]) * CHUNK;
+    c.count = min((uint32_t)CHUNK, r.y - c.first);
+    c.view = c.key / S;
+    const uint32_t s = c.key - c.view * S;
+    const uint32_t sy = s / (uint32_t)stiles_x;
+    c.ox = (s - sy * (uint32_t)stiles_x) * ST;
+    c.oy = sy * ST;
+    return true;
+}
+
+// per chunk: how many of its instances hit each of the supertile's 16 tiles (hit masks: upper half of the sorted keys).
+// One WARP per chunk: 8 rows of 32 keys, 16 ballots a row, lane t < 16 keeps tile t's count in a register -- no shared
+// memory, no CTA barrier, and eight chunks per CTA in flight (the CTA-per-chunk version was bound by the latency of its
+// chunk-table look-ups: 77 us at C2).
+__global__ void __launch_bounds__(256)
+chunk_count_kernel(const uint32_t* __restrict__ counters, const uint32_t* __restrict__ chunk_key,
+                   const uint32_t* __restrict__ chunk_base, const uint2* __restrict__ st_ranges,
+                   const uint32_t* __restrict__ skeys, uint32_t* __restrict__ chunk_counts) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t wpb = blockDim.x >> 5;
+    const uint32_t nch = counters[CNT_NCHUNKS];
+    // persistent warps: the chunk count is only known on the device, so the grid is sized for the SMs, not the chunks
+    for (uint32_t cid = blockIdx.x * wpb + (threadIdx.x >> 5); cid < nch; cid += gridDim.x * wpb) {
+        const uint32_t key = chunk_key[cid];
+        const uint2 r = st_ranges[key];
+        const uint32_t first = r.x + (cid - chunk_base[key]) * CHUNK;
+        const uint32_t count = min((uint32_t)CHUNK, r.y - first);
+        uint32_t m[CHUNK / 32];
+#pragma unroll
+        for (int row = 0; row < CHUNK / 32; ++row) {
+            const uint32_t i = row * 32 + lane;
+            m[row] = i < count ? skeys[first + i] >> ST_KEY_BITS : 0u;
+        }
+        uint32_t n = 0;
+#pragma unroll
+        for (int row = 0; row < CHUNK / 32; ++row) {
+#pragma unroll
+            for (int t = 0; t < ST_TILES; ++t) {
+                const uint32_t bal = __ballot_sync(FULL, (m[row] >> t) & 1u);
+                if (lane == t) n += __popc(bal);
+            }
+        }
+        if (lane < ST_TILES) chunk_counts[(size_t)cid * ST_TILES + lane] = n;
+    }
+}
+
+// One CTA per supertile key, one WARP per tile of the supertile: exclusive prefix of the tile's chunk counts over the key's
+// chunks (in place, 32 chunks per step with a shuffle scan), and the tile's total -> tile_start[view*T + tile] (scanned by
+// tile_scan_kernel).  (Round 1 walked the chunks serially with one lane per tile: 55 us at C2, set by the longest
+// supertile list.)
+__global__ void __launch_bounds__(ST_TILES * 32)
+tile_offsets_kernel(uint32_t VS, uint32_t S, int stiles_x, int tiles_x, int tiles_y,
+                    const uint32_t* __restrict__ chunk_base, uint32_t max_chunks, uint32_t* __restrict__ chunk_counts,
+                    uint32_t* __restrict__ tile_start) {
+    const uint32_t k = blockIdx.x;
+    const int t = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t c0 = min(chunk_base[k], max_chunks), c1 = min(chunk_base[k + 1], max_chunks);
+    uint32_t run = 0;
+    for (uint32_t cb = c0; cb < c1; cb += 32) {
+        const uint32_t c = cb + lane;
+        const uint32_t n = c < c1 ? chunk_counts[(size_t)c * ST_TILES + t] : 0u;
+        uint32_t inc = n;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(FULL, inc, o);
+            if (lane >= o) inc += v;
+        }
+        if (c < c1) chunk_counts[(size_t)c * ST_TILES + t] = run + inc - n;
+        run += __shfl_sync(FULL, inc, 31);
+    }
+    if (lane == 0) {
+        const uint32_t view = k / S, s = k - view * S;
+        const uint32_t sy = s / (uint32_t)stiles_x, sx = s - sy * (uint32_t)stiles_x;
+        const uint32_t gx = sx * ST + (t & 3), gy = sy * ST + (t >> 2);
+        if (gx < (uint32_t)tiles_x && gy < (uint32_t)tiles_y)
+            tile_start[(size_t)view * tiles_x * tiles_y + gy * (uint32_t)tiles_x + gx] = run;
+    }
+}
+
+// single block: exclusive scan of the per-tile counts in place (tile_start), ranges clamped to the capacity
+constexpr int ORDER_BUCKETS = 1024;
+constexpr int TSCAN_THREADS = 1024;          // one CTA on the critical path: as many loads in flight as one CTA can have
+
 __global__ void __launch_bounds__(TSCAN_THREADS)
 tile_scan_kernel(uint32_t VT, uint32_t capacity, uint32_t* __restrict__ tile_start, uint2* __restrict__ ranges,
-                 uint32_t* __restrict__ tile_order, uint32_t* __restrict__ counters) {
+                 uint32_t* __restrict__ counters) {
     __shared__ uint32_t s_warp[32];
-    __shared__ uint32_t s_bucket[ORDER_BUCKETS];
-    __shared__ uint32_t s_maxlen;
-    static_assert(ORDER_BUCKETS == TSCAN_THREADS, "one bucket per thread in the bucket scan");
-    if (threadIdx.x == 0) s_maxlen = 0;
-    s_bucket[threadIdx.x] = 0;
-    __syncthreads();
-    uint32_t carry = 0, vmax = 0;
+    uint32_t carry = 0;
     constexpr int IT = 8;
+    uint32_t nxt[IT];                                    // the next step's counts are in flight while this one is scanned
+#pragma unroll
+    for (int k = 0; k < IT; ++k) nxt[k] = threadIdx.x * IT + k < VT ? tile_start[threadIdx.x * IT + k] : 0u;
     for (uint32_t start = 0; start < VT; start += TSCAN_THREADS * IT) {
         const uint32_t i0 = start + threadIdx.x * IT;
         uint32_t v[IT], sum = 0;
 #pragma unroll
-        for (int k = 0; k < IT; ++k) { v[k] = i0 + k < VT ? tile_start[i0 + k] : 0u; sum += v[k]; vmax = max(vmax, v[k]); }
+        for (int k = 0; k < IT; ++k) { v[k] = nxt[k]; sum += v[k]; }
+        const uint32_t i1 = i0 + TSCAN_THREADS * IT;
+#pragma unroll
+        for (int k = 0; k < IT; ++k) nxt[k] = i1 + k < VT ? tile_start[i1 + k] : 0u;
         uint32_t total;
         uint32_t ex = carry + block_exclusive_scan_1024(sum, s_warp, total);
 #pragma unroll
@@ -405,6 +489,26 @@ tile_scan_kernel(uint32_t VT, uint32_t capacity, uint32_t* __restrict__ tile_sta
     if (threadIdx.x == 0) {
         tile_start[VT] = carry;
         if (carry > capacity) counters[CNT_OVERFLOW] = 1;
+    }
+}
+
+// single block, off the critical path (it runs next to the record scatter; only the blend kernels need it): counting sort of
+// the (view, tile) indices by list length, longest first -> tile_order.  The blend kernels launch their CTAs in that
+// order, so the longest sequential chains start first and the short tiles fill in behind them (the hardware dispatches
+// CTAs in blockIdx order).
+__global__ void __launch_bounds__(TSCAN_THREADS)
+tile_order_kernel(uint32_t VT, const uint2* __restrict__ ranges, uint32_t* __restrict__ tile_order) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_bucket[ORDER_BUCKETS];
+    __shared__ uint32_t s_maxlen;
+    static_assert(ORDER_BUCKETS == TSCAN_THREADS, "one bucket per thread in the bucket scan");
+    if (threadIdx.x == 0) s_maxlen = 0;
+    s_bucket[threadIdx.x] = 0;
+    __syncthreads();
+    uint32_t vmax = 0;
+    for (uint32_t i = threadIdx.x; i < VT; i += TSCAN_THREADS) {
+        const uint2 r = ranges[i];
+        vmax = max(vmax, r.y - r.x);
     }
     vmax = __reduce_max_sync(FULL, vmax);
     if ((threadIdx.x & 31) == 0 && vmax > 0) atomicMax(&s_maxlen, vmax);
@@ -460,7 +564,7 @@ __global__ void __launch_bounds__(CHUNK)
 scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __restrict__ chunk_key,
                        const uint32_t* __restrict__ chunk_base, const uint2* __restrict__ st_ranges, uint32_t S,
                        int stiles_x, int tiles_x, int tiles_y, int P, uint32_t capacity,
-                       const uint32_t* __restrict__ vals, const uint16_t* __restrict__ masks,
+                       const uint32_t* __restrict__ vals, const uint32_t* __restrict__ skeys,
                        const uint32_t* __restrict__ chunk_offs, const uint32_t* __restrict__ tile_start,
                        const float4* __restrict__ geomrec, const float4* __restrict__ col4,
                        const float4* __restrict__ rgb_sh4, const float4* __restrict__ ext4,
@@ -493,7 +597,7 @@ scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __
     uint32_t gi = 0, mask = 0;
     if (have && (uint32_t)tid < c.count) {
         gi = vals[c.first + tid];
-        mask = masks[c.first + tid];
+        mask = skeys[c.first + tid] >> ST_KEY_BITS;
     }
     for (uint32_t cid = blockIdx.x; have; cid += gridDim.x) {
         float4 rA, rB, rC, rD;
@@ -508,7 +612,7 @@ scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __
         uint32_t gi_next = 0, mask_next = 0;
         if (have_next && (uint32_t)tid < cn.count) {
             gi_next = vals[cn.first + tid];
-            mask_next = masks[cn.first + tid];
+            mask_next = skeys[cn.first + tid] >> ST_KEY_BITS;
         }
         const bool have_nn = info(cid + 2 * gridDim.x, cnn);
         if (tid < ST_TILES) {
@@ -591,20 +695,6 @@ export_view_kernel(int view, int P, uint32_t T, const uint2* __restrict__ ranges
 
 }  // namespace
 
-int launch_tile_scan(int V, int P, void* ws, const Layout& L, cudaStream_t s) {
-    const uint32_t VP = (uint32_t)((size_t)V * P);
-    if (VP == 0) return GSR_OK;
-    const uint32_t nblocks = (VP + SCAN_TILE - 1) / SCAN_TILE;
-    const uint32_t* sorted_g = at<uint32_t>(ws, L.sorted_vals_in ? L.dvals1 : L.dvals0);
-    st_count_reduce_kernel<<<nblocks, SCAN_BLOCK, 0, s>>>(VP, P, sorted_g, at<ushort4>(ws, L.rects),
-                                                         at<uint32_t>(ws, L.block_sums), at<uint32_t>(ws, L.counters));
-    GSR_LAUNCH_CHECK();
-    block_sums_scan_kernel<<<1, SCAN_BLOCK, 0, s>>>(nblocks, at<uint32_t>(ws, L.block_sums),
-                                                    at<uint32_t>(ws, L.counters));
-    GSR_LAUNCH_CHECK();
-    return GSR_OK;
-}
-
 int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
                    const float* colors_precomp, const float* extra_colors, void* gws, void* bws, void* iws,
                    const Layout& L, cudaStream_t s) {
@@ -612,89 +702,129 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     const uint32_t T = (uint32_t)L.tiles_x * (uint32_t)L.tiles_y;
     const uint32_t S = (uint32_t)L.stiles_x * (uint32_t)L.stiles_y;
     const uint32_t VT = (uint32_t)V * T, VS = (uint32_t)V * S;
+    uint32_t* counters = at<uint32_t>(gws, L.counters);
     if (VP == 0 || capacity <= 0) {     // every tile list empty: zero counts through the same scan (ranges, launch order)
         if (VT == 0) return GSR_OK;
         GSR_CUDA_TRY(cudaMemsetAsync(at<uint32_t>(iws, L.tile_start), 0, ((size_t)VT + 1) * sizeof(uint32_t), s));
         tile_scan_kernel<<<1, TSCAN_THREADS, 0, s>>>(VT, 0u, at<uint32_t>(iws, L.tile_start), at<uint2>(iws, L.ranges),
-                                                  at<uint32_t>(iws, L.tile_order), at<uint32_t>(gws, L.counters));
+                                                  counters);
+        GSR_LAUNCH_CHECK();
+        tile_order_kernel<<<1, TSCAN_THREADS, 0, s>>>(VT, at<uint2>(iws, L.ranges), at<uint32_t>(iws, L.tile_order));
         GSR_LAUNCH_CHECK();
         return GSR_OK;
     }
+    if (L.tile_bits > ST_KEY_BITS) return GSR_ERR_UNSUPPORTED;      // check_dims refuses such batches before
     const uint32_t cap = (uint32_t)capacity;
-    uint32_t* counters = at<uint32_t>(gws, L.counters);
-    const uint32_t nblocks = (VP + SCAN_TILE - 1) / SCAN_TILE;
+    const uint32_t nblocks = (VP + EMIT_TILE - 1) / EMIT_TILE;
     const uint32_t* sorted_g = at<uint32_t>(gws, L.sorted_vals_in ? L.dvals1 : L.dvals0);
     const ushort4* rects = at<ushort4>(gws, L.rects);
     const bool fused_hist = L.tile_passes <= EMIT_HIST_PASSES;
-    stage_begin(ST_EMIT, s);
-    // instance sort histograms, tile tickets and look-back words, supertile ranges: one memset
-    GSR_CUDA_TRY(cudaMemsetAsync(bws, 0, L.binning_zero_bytes, s));
-    emit_st_instances_kernel<<<nblocks, SCAN_BLOCK, 0, s>>>(
-        VP, P, L.stiles_x, S, sorted_g, rects, at<uint32_t>(gws, L.block_sums), cap, at<uint32_t>(bws, L.ikeys0),
-        at<uint32_t>(bws, L.ivals0), counters, fused_hist ? L.tile_passes : 0, L.tile_bits, at<uint32_t>(bws, L.ihist));
-    GSR_LAUNCH_CHECK();
-    stage_end(ST_EMIT, s);
-    stage_begin(ST_TILE_SORT, s);
-    int rc = radix_sort_pairs<uint32_t>(at<uint32_t>(bws, L.ikeys0), at<uint32_t>(bws, L.ikeys1),
-                                        at<uint32_t>(bws, L.ivals0), at<uint32_t>(bws, L.ivals1), capacity,
-                                        counters + CNT_ST_RENDERED, 0, L.tile_bits, at<uint32_t>(bws, L.ihist),
-                                        at<uint32_t>(bws, L.ilookback), at<uint32_t>(bws, L.ihist) + MAX_PASSES * RADIX, s, 1,
-                                        fused_hist, true);
-    stage_end(ST_TILE_SORT, s);
-    if (rc != GSR_OK) return rc;
-    const uint32_t* skeys = at<uint32_t>(bws, L.sorted_keys_in ? L.ikeys1 : L.ikeys0);
-    const uint32_t* svals = at<uint32_t>(bws, L.sorted_keys_in ? L.ivals1 : L.ivals0);
+    uint32_t* key_hist = at<uint32_t>(bws, L.key_hist);
     uint2* st_ranges = at<uint2>(bws, L.st_ranges);
     uint32_t* chunk_base = at<uint32_t>(bws, L.chunk_base);
     uint32_t* chunk_key = at<uint32_t>(bws, L.chunk_key);
     uint32_t* chunk_counts = at<uint32_t>(bws, L.chunk_counts);
     uint32_t* tile_start = at<uint32_t>(iws, L.tile_start);
     const uint32_t max_chunks = (uint32_t)L.max_chunks;
-    const uint32_t chunk_grid = max_chunks < 148u * 8u ? max_chunks : 148u * 8u;   // persistent CTAs, 8 per SM
-    stage_begin(ST_RANGES, s);
-    st_ranges_kernel<<<min((cap + 255u) / 256u, 148u * 16u), 256, 0, s>>>(counters, cap, skeys, st_ranges);
-    GSR_LAUNCH_CHECK();
-    chunk_table_kernel<<<1, SCAN_BLOCK, 0, s>>>(VS, st_ranges, chunk_base, chunk_key, max_chunks, counters);
-    GSR_LAUNCH_CHECK();
-    chunk_count_kernel<<<chunk_grid, CHUNK, 0, s>>>(counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, svals,
-                                                   rects, at<uint16_t>(bws, L.imasks), chunk_counts);
-    GSR_LAUNCH_CHECK();
-    tile_offsets_kernel<<<(VS + 3) / 4, 128, 0, s>>>(VS, S, L.stiles_x, L.tiles_x, L.tiles_y, chunk_base, max_chunks,
-                                                    chunk_counts, tile_start);
-    GSR_LAUNCH_CHECK();
-    tile_scan_kernel<<<1, TSCAN_THREADS, 0, s>>>(VT, cap, tile_start, at<uint2>(iws, L.ranges),
-                                              at<uint32_t>(iws, L.tile_order), counters);
-    GSR_LAUNCH_CHECK();
-    stage_end(ST_RANGES, s);
-    StageScope sc(ST_GATHER, s);
-    if (colors_precomp || extra_colors) {
-        pack_colors_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, colors_precomp, extra_colors, at<float4>(gws, L.col4),
-                                                           at<float4>(gws, L.ext4));
+    cudaStream_t side = nullptr;
+    stage_begin(ST_EMIT, s);
+    // instance sort histograms, tile tickets and look-back words, the emit kernel's ticket / look-back words / key counts:
+    // one memset
+    GSR_CUDA_TRY(cudaMemsetAsync(bws, 0, L.binning_zero_bytes, s));
+    {
+        // key counts in shared memory: the keys of the (at most EMIT_TILE / P + 2) views a block's slots belong to
+        const uint32_t nv = (uint32_t)V < (uint32_t)(EMIT_TILE / P + 2) ? (uint32_t)V : (uint32_t)(EMIT_TILE / P + 2);
+        uint32_t bins = nv * S;
+        constexpr uint32_t MAX_BINS = 24 * 1024;                     // 96 KB next to the kernel's 40 KB of static smem
+        if (bins > MAX_BINS) bins = 0;                               // (tiny P with thousands of supertiles: global atomics)
+        static bool attr_set = false;
+        if (!attr_set) {
+            GSR_CUDA_TRY(cudaFuncSetAttribute(emit_st_instances_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              MAX_BINS * 4));
+            attr_set = true;
+        }
+#if GSR_EMIT_LOOKBACK
+        uint32_t* offs = at<uint32_t>(bws, L.emit_lookback);
+#else
+        uint32_t* offs = at<uint32_t>(gws, L.block_sums);
+        st_count_reduce_kernel<<<nblocks, SCAN_BLOCK, 0, s>>>(VP, P, sorted_g, rects, at<uint32_t>(gws, L.vis_count), offs);
+        GSR_LAUNCH_CHECK();
+        block_sums_scan_kernel<<<1, 1024, 0, s>>>(nblocks, offs, counters);
+        GSR_LAUNCH_CHECK();
+#endif
+        emit_st_instances_kernel<<<nblocks, SCAN_BLOCK, bins * 4, s>>>(
+            VP, P, L.stiles_x, S, sorted_g, rects, at<uint32_t>(gws, L.vis_count), cap, nblocks,
+            at<uint32_t>(bws, L.ikeys0), at<uint32_t>(bws, L.ivals0),
+            counters, fused_hist ? L.tile_passes : 0, L.tile_bits, at<uint32_t>(bws, L.ihist),
+            offs, at<uint32_t>(bws, L.emit_ticket), key_hist, bins);
         GSR_LAUNCH_CHECK();
     }
-    // persistent CTAs: exactly as many as are resident at once (a second, partial wave would run at low occupancy)
-    static int scatter_per_sm[2] = {0, 0};
-    if (scatter_per_sm[0] == 0) {
-        GSR_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&scatter_per_sm[0], scatter_records_kernel<false>, CHUNK, 0));
-        GSR_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&scatter_per_sm[1], scatter_records_kernel<true>, CHUNK, 0));
-    }
-    const uint32_t resident = 148u * (uint32_t)scatter_per_sm[channels > 3 ? 1 : 0];
-    const uint32_t scatter_grid = max_chunks < resident ? max_chunks : resident;
-    const float4* col4 = colors_precomp ? at<float4>(gws, L.col4) : nullptr;
-    const float4* rgb4 = sh_coeffs > 0 ? at<float4>(gws, L.rgb) : nullptr;
-    if (channels > 3) {
-        scatter_records_kernel<true><<<scatter_grid, CHUNK, 0, s>>>(
-            counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals,
-            at<uint16_t>(bws, L.imasks), chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, at<float4>(gws, L.ext4),
-            at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC), at<float4>(bws, L.recD));
-    } else {
-        scatter_records_kernel<false><<<scatter_grid, CHUNK, 0, s>>>(
-            counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals,
-            at<uint16_t>(bws, L.imasks), chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, nullptr, at<float4>(bws, L.recA),
-            at<float4>(bws, L.recB), at<float4>(bws, L.recC), nullptr);
-    }
+    stage_end(ST_EMIT, s);
+    // the chunk table only needs the key counts: it runs on the side stream while the instances are sorted
+    int rc = side_fork(s, &side);
+    if (rc != GSR_OK) return rc;
+    chunk_table_kernel<<<1, CT_THREADS, 0, side>>>(VS, key_hist, st_ranges, chunk_base, chunk_key, max_chunks, counters);
     GSR_LAUNCH_CHECK();
-    return GSR_OK;
+    stage_begin(ST_TILE_SORT, s);
+    rc = radix_sort_pairs<uint32_t>(at<uint32_t>(bws, L.ikeys0), at<uint32_t>(bws, L.ikeys1),
+                                    at<uint32_t>(bws, L.ivals0), at<uint32_t>(bws, L.ivals1), capacity,
+                                    counters + CNT_ST_RENDERED, 0, L.tile_bits, at<uint32_t>(bws, L.ihist),
+                                    at<uint32_t>(bws, L.ilookback), at<uint32_t>(bws, L.ihist) + MAX_PASSES * RADIX, s, 1,
+                                    fused_hist, true);
+    stage_end(ST_TILE_SORT, s);
+    if (rc != GSR_OK) return rc;
+    rc = side_join(s);
+    if (rc != GSR_OK) return rc;
+    const uint32_t* skeys = at<uint32_t>(bws, L.sorted_keys_in ? L.ikeys1 : L.ikeys0);
+    const uint32_t* svals = at<uint32_t>(bws, L.sorted_keys_in ? L.ivals1 : L.ivals0);
+    const uint32_t chunk_grid = max_chunks < 148u * 8u ? max_chunks : 148u * 8u;   // persistent CTAs, 8 per SM
+    stage_begin(ST_RANGES, s);
+    chunk_count_kernel<<<chunk_grid, 256, 0, s>>>(counters, chunk_key, chunk_base, st_ranges, skeys, chunk_counts);
+    GSR_LAUNCH_CHECK();
+    tile_offsets_kernel<<<VS, ST_TILES * 32, 0, s>>>(VS, S, L.stiles_x, L.tiles_x, L.tiles_y, chunk_base, max_chunks,
+                                                    chunk_counts, tile_start);
+    GSR_LAUNCH_CHECK();
+    tile_scan_kernel<<<1, TSCAN_THREADS, 0, s>>>(VT, cap, tile_start, at<uint2>(iws, L.ranges), counters);
+    GSR_LAUNCH_CHECK();
+    stage_end(ST_RANGES, s);
+    // the launch order of the blend kernels is not needed before the records are in place: side stream again
+    rc = side_fork(s, &side);
+    if (rc != GSR_OK) return rc;
+    tile_order_kernel<<<1, TSCAN_THREADS, 0, side>>>(VT, at<uint2>(iws, L.ranges), at<uint32_t>(iws, L.tile_order));
+    GSR_LAUNCH_CHECK();
+    {
+        StageScope sc(ST_GATHER, s);
+        if (colors_precomp || extra_colors) {
+            pack_colors_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, colors_precomp, extra_colors, at<float4>(gws, L.col4),
+                                                               at<float4>(gws, L.ext4));
+            GSR_LAUNCH_CHECK();
+        }
+        // persistent CTAs: exactly as many as are resident at once (a second, partial wave would run at low occupancy)
+        static int scatter_per_sm[2] = {0, 0};
+        if (scatter_per_sm[0] == 0) {
+            GSR_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&scatter_per_sm[0], scatter_records_kernel<false>, CHUNK, 0));
+            GSR_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&scatter_per_sm[1], scatter_records_kernel<true>, CHUNK, 0));
+        }
+        // ... minus one SM's worth: the tile_order CTA on the side stream takes an SM, and persistent CTAs queued behind
+        // it would finish a whole tile_order late
+        const uint32_t resident = 147u * (uint32_t)scatter_per_sm[channels > 3 ? 1 : 0];
+        const uint32_t scatter_grid = max_chunks < resident ? max_chunks : resident;
+        const float4* col4 = colors_precomp ? at<float4>(gws, L.col4) : nullptr;
+        const float4* rgb4 = sh_coeffs > 0 ? at<float4>(gws, L.rgb) : nullptr;
+        if (channels > 3) {
+            scatter_records_kernel<true><<<scatter_grid, CHUNK, 0, s>>>(
+                counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals, skeys,
+                chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, at<float4>(gws, L.ext4),
+                at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC), at<float4>(bws, L.recD));
+        } else {
+            scatter_records_kernel<false><<<scatter_grid, CHUNK, 0, s>>>(
+                counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals, skeys,
+                chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, nullptr, at<float4>(bws, L.recA),
+                at<float4>(bws, L.recB), at<float4>(bws, L.recC), nullptr);
+        }
+        GSR_LAUNCH_CHECK();
+    }
+    return side_join(s);
 }
 
 int launch_export_view(int view, int V, int P, int W, int H, const void* gws, const void* bws, const void* iws,

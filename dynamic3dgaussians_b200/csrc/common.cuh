@@ -84,6 +84,10 @@ struct Layout : GsrLayout {
     size_t geom_zero_bytes, binning_zero_bytes;
     // image workspace, internal: per-tile walked depth (the forward's largest n_contrib) and the backward's launch order
     size_t tile_cost, tile_order_bwd;
+    // binning workspace, internal (zeroed): instances per supertile key, the emit kernel's look-back words and ticket
+    size_t key_hist, emit_lookback, emit_ticket;
+    // geometry workspace, internal: per view, the number of Gaussians the depth sort kept (those that touch a tile)
+    size_t vis_count;
 };
 
 inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
@@ -115,6 +119,7 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     L.dlookback = take((size_t)MAX_PASSES * V * (sort_num_tiles((int64_t)P, 4) + 1) * RADIX * 4);
     L.dcounters = take((size_t)MAX_PASSES * V * 4);
     L.geom_zero_bytes = o;                // counters + the depth sort's histograms / look-back words / tile tickets
+    L.vis_count = take((size_t)V * 4);    // Gaussians per view that touch a tile: what the depth sort keeps (written by it)
     L.cams = take((size_t)V * sizeof(CamDev));
     L.radii = take(VP * 4);
     L.rects = take(VP * 8);               // ushort4 tile rectangle (min.x, min.y, max.x, max.y), all zero when culled
@@ -128,7 +133,7 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     L.dkeys1 = take(VP * 4);
     L.dvals0 = take(VP * 4);
     L.dvals1 = take(VP * 4);
-    L.block_sums = take(((VP + SCAN_TILE - 1) / SCAN_TILE + 2) * 4);
+    L.block_sums = take((VP / 1024 + 3) * 4);      // per block of 1024 depth-sorted slots (binning.cu EMIT_TILE)
     L.grad_rec = take(VP * grad_rec_stride(channels) * 4);
     L.geom_bytes = o;
     // binning
@@ -138,13 +143,16 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     L.max_chunks = (int32_t)max_chunks;
     L.ihist = take(((size_t)MAX_PASSES * RADIX + MAX_PASSES) * 4);      // + the instance sort's tile tickets
     L.ilookback = take((size_t)L.tile_passes * (sort_num_tiles((int64_t)cap, 4) + 1) * RADIX * 4);
+    L.key_hist = take(VS * 4);
+    L.emit_lookback = take((VP / 1024 + 2) * 4);       // one word per block of EMIT_TILE (= 1024) depth-sorted slots
+    L.emit_ticket = take(4);
+    L.binning_zero_bytes = o;             // instance sort histograms / look-back words, emit look-back, key counts
     L.st_ranges = take(VS * 8);
-    L.binning_zero_bytes = o;             // instance sort histograms / look-back words, supertile ranges
     L.ikeys0 = take(cap * 4);             // supertile instances: at most one per (Gaussian, tile) instance
     L.ikeys1 = take(cap * 4);
     L.ivals0 = take(cap * 4);
     L.ivals1 = take(cap * 4);
-    L.imasks = take(cap * 2);             // 16-bit tile hit mask of every sorted supertile instance
+    L.imasks = take(0);                   // (ABI v3 kept the tile hit masks here; they ride in the keys' upper half now)
     L.chunk_base = take((VS + 1) * 4);
     L.chunk_key = take(max_chunks * 4);
     L.chunk_counts = take(max_chunks * ST_TILES * 4);
@@ -221,9 +229,18 @@ template <typename KeyT>
 int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1, int64_t n_max,
                      const uint32_t* n_dev, int begin_bit, int end_bit, uint32_t* hist, uint32_t* lookback,
                      uint32_t* tile_counters, cudaStream_t s, int segments = 1, bool hist_ready = false,
-                     bool scratch_zeroed = false);   // scratch_zeroed: hist / lookback / tile_counters are already 0
+                     bool scratch_zeroed = false,    // scratch_zeroed: hist / lookback / tile_counters are already 0
+                     uint32_t* n_kept_dev = nullptr);
+// n_kept_dev (one word per segment, written): keys equal to ~0 are SENTINELS -- counted out by the histogram, dropped by
+// the first pass, and the later passes only move the n_kept_dev[segment] keys that remain (the rasterizer marks culled
+// Gaussians this way: they cost one read instead of four read-write round trips).  Needs hist_ready = false, n_dev = null.
 
-int launch_tile_scan(int V, int P, void* geom_ws, const Layout& L, cudaStream_t s);
+// fork / join of the library's own side stream (per host thread and device): side_fork makes the side stream wait for
+// everything enqueued on `main` so far and hands it out; side_join makes `main` wait for everything enqueued on the side
+// stream.  Works inside a stream capture (the side stream joins the capture).  The streams / events are created on first
+// use -- outside any capture, since every graph user warms up first.
+int side_fork(cudaStream_t main, cudaStream_t* side);
+int side_join(cudaStream_t main);
 int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
                    const float* colors_precomp, const float* extra_colors,
                    void* geom_ws, void* binning_ws, void* image_ws, const Layout& L, cudaStream_t s);

@@ -91,6 +91,7 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
                   uint32_t* __restrict__ dkeys, uint32_t* __restrict__ dvals, int32_t* __restrict__ radii_out,
                   uint32_t* __restrict__ counters) {
     __shared__ CamDev cam;
+    __shared__ uint32_t s_tiles[8];
     const int v = blockIdx.y;
     {
         const uint32_t* src = reinterpret_cast<const uint32_t*>(cams + v);
@@ -99,15 +100,15 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
     }
     __syncthreads();
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= P) return;
-    const size_t idx = (size_t)v * P + g;
+    const bool live = g < P;
+    const size_t idx = (size_t)v * P + (live ? g : 0);
 
     int radius = 0;
     ushort4 rect = make_ushort4(0, 0, 0, 0);
     uint32_t depth_key = 0xffffffffu;      // culled Gaussians sort behind every visible one of their view
 
-    const float x = means3D[3 * g], y = means3D[3 * g + 1], z = means3D[3 * g + 2];
-    const float depth = xform_row(cam.view, 2, x, y, z);          // p_view.z, auxiliary.h:156
+    const float x = live ? means3D[3 * g] : 0.0f, y = live ? means3D[3 * g + 1] : 0.0f, z = live ? means3D[3 * g + 2] : 0.0f;
+    const float depth = live ? xform_row(cam.view, 2, x, y, z) : 0.0f;          // p_view.z, auxiliary.h:156
     if (depth > 0.0f) {                                           // near cull: z <= 0 (auxiliary.h:158)
         const float hx = xform_row(cam.proj, 0, x, y, z);
         const float hy = xform_row(cam.proj, 1, x, y, z);
@@ -162,16 +163,30 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
             }
         }
     }
-    else if (cam.prefiltered) {
+    else if (live && cam.prefiltered) {
         // in_frustum with prefiltered = true (auxiliary.h:160-167): the reference prints and traps; here the flag comes
         // back through gsr_read_counters and the host raises
         counters[CNT_PREFILTER] = 1u;
     }
-    radii[idx] = radius;
-    if (radii_out) radii_out[idx] = radius;
-    rects[idx] = rect;
-    dkeys[idx] = depth_key;                // sorted per view (segmented sort), so the key is the depth alone
-    dvals[idx] = (uint32_t)g;
+    if (live) {
+        radii[idx] = radius;
+        if (radii_out) radii_out[idx] = radius;
+        rects[idx] = rect;
+        dkeys[idx] = depth_key;            // sorted per view (segmented sort), so the key is the depth alone; the sort's
+        dvals[idx] = (uint32_t)g;          // first pass drops the culled ones (key 0xffffffff)
+    }
+    // the batch's (Gaussian, tile) instance count -- what the reference returns as num_rendered (rasterizer_impl.cu:285-287):
+    // one atomic per CTA
+    uint32_t tiles = (uint32_t)(rect.z - rect.x) * (uint32_t)(rect.w - rect.y);
+    tiles = __reduce_add_sync(0xffffffffu, tiles);
+    if ((threadIdx.x & 31) == 0) s_tiles[threadIdx.x >> 5] = tiles;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += s_tiles[w];
+        if (t) atomicAdd(&counters[CNT_RENDERED], t);
+    }
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, float v2, float v6, float v10, float v14,

@@ -10,8 +10,8 @@
 // HBM traffic per pass: read (key,value) once, write once.  The look-back state is one 32-bit word per
 // (tile, digit): 2 flag bits + 30-bit count, so a single volatile load carries flag and value together.
 //
-// SEGMENTED mode (segments > 1): `segments` independent arrays of n_max elements each, laid out back to back, are
-// sorted by one set of launches (grid.y = segment).  The rasterizer sorts every view's Gaussians by depth this way
+// SEGMENTED mode (segments > 1): `segments` independent arrays of up to n_max elements each, laid out n_max apart, are
+// sorted by one set of launches (grid.y = segment); n_dev, when given, holds one device-side element count per segment.  The rasterizer sorts every view's Gaussians by depth this way
 // with 32-bit keys (4 passes) instead of one (view << 32 | depth) 64-bit sort (5 passes of 12-byte pairs).
 #include "radix_rank.cuh"
 
@@ -39,7 +39,7 @@ constexpr int HIST_FLUSH_ROWS = 248;        // per warp, < 256
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
 radix_histogram_kernel(const KeyT* __restrict__ keys, uint32_t n_max, const uint32_t* __restrict__ n_dev,
-                       int begin_bit, int end_bit, int passes_total, uint32_t* __restrict__ hist) {
+                       int begin_bit, int end_bit, int passes_total, uint32_t* __restrict__ hist, bool drop_sentinel) {
     extern __shared__ __align__(16) uint8_t s_cnt[];     // [8 warps][256 bins][32 lanes]
     __shared__ uint32_t s_tot[RADIX];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -47,7 +47,7 @@ radix_histogram_kernel(const KeyT* __restrict__ keys, uint32_t n_max, const uint
     const int shift = begin_bit + pass * RADIX_BITS;
     const uint32_t mask = (1u << min(RADIX_BITS, end_bit - shift)) - 1u;
     keys += (size_t)seg * n_max;
-    const uint32_t n = n_dev ? min(*n_dev, n_max) : n_max;
+    const uint32_t n = n_dev ? min(n_dev[seg], n_max) : n_max;      // one device-side count per segment
     s_tot[tid] = 0;
     uint4* mine4 = reinterpret_cast<uint4*>(s_cnt + warp * (RADIX * 32));
     for (int i = lane; i < RADIX * 32 / 16; i += 32) mine4[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -87,6 +87,7 @@ radix_histogram_kernel(const KeyT* __restrict__ keys, uint32_t n_max, const uint
                 const uint32_t e = row * 32u + lane;
                 ok[u] = row < r1 && e < n;
                 key[u] = ok[u] ? keys[e] : (KeyT)0;
+                if (drop_sentinel) ok[u] = ok[u] && key[u] != ~(KeyT)0;
             }
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u) {
@@ -109,7 +110,9 @@ radix_histogram_kernel(const KeyT* __restrict__ keys, uint32_t n_max, const uint
 }
 
 // exclusive scan of each (segment, pass)'s 256 bins, in place (one block of 256 threads each)
-__global__ void __launch_bounds__(RADIX) radix_scan_hist_kernel(uint32_t* __restrict__ hist) {
+// n_kept (nullable): n_kept[segment] <- number of keys counted in the segment's first-pass histogram (see radix_sort_pairs)
+__global__ void __launch_bounds__(RADIX) radix_scan_hist_kernel(uint32_t* __restrict__ hist, uint32_t* __restrict__ n_kept,
+                                                                int passes) {
     __shared__ uint32_t warp_tot[RADIX / 32];
     uint32_t* h = hist + blockIdx.x * RADIX;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -125,6 +128,7 @@ __global__ void __launch_bounds__(RADIX) radix_scan_hist_kernel(uint32_t* __rest
     uint32_t base = 0;
     for (int w = 0; w < warp; ++w) base += warp_tot[w];
     h[tid] = base + inc - v;
+    if (n_kept && tid == RADIX - 1 && (int)(blockIdx.x % passes) == 0) n_kept[blockIdx.x / passes] = base + inc;
 }
 
 template <typename KeyT>
@@ -133,7 +137,7 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
                      const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                      uint32_t n_max, const uint32_t* __restrict__ n_dev, int shift, uint32_t digit_mask,
                      const uint32_t* __restrict__ hist_excl, size_t hist_seg_stride, uint32_t* __restrict__ lookback,
-                     size_t lookback_seg_stride, uint32_t* __restrict__ tile_counter) {
+                     size_t lookback_seg_stride, uint32_t* __restrict__ tile_counter, bool drop_sentinel) {
     constexpr int ITEMS = SortCfg<KeyT>::ITEMS;
     constexpr int TILE = SORT_THREADS * ITEMS;
     constexpr int WARPS = SORT_THREADS / 32;
@@ -141,7 +145,7 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     __shared__ uint32_t s_block_excl[RADIX];
     __shared__ uint32_t s_glob_base[RADIX];
     __shared__ uint32_t s_warp_tot[WARPS];
-    __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_tile, s_kept;
     extern __shared__ __align__(16) unsigned char s_dyn[];
     KeyT* s_keys = reinterpret_cast<KeyT*>(s_dyn);
     uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_dyn + sizeof(KeyT) * TILE);
@@ -161,7 +165,7 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     for (int w = 0; w < WARPS; ++w) s_warp_hist[w][tid] = 0;
     __syncthreads();
     const uint32_t tile = s_tile;
-    const uint32_t n = n_dev ? min(*n_dev, n_max) : n_max;
+    const uint32_t n = n_dev ? min(n_dev[seg], n_max) : n_max;
     const uint64_t base64 = (uint64_t)tile * TILE;
     if (base64 >= n) return;                       // uniform: whole block leaves
     const uint32_t base = (uint32_t)base64;
@@ -172,10 +176,16 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     KeyT key[ITEMS];
     uint32_t rank[ITEMS];
     const uint32_t e0 = warp * 32 * ITEMS + lane;
+    // `live` bit i: item i takes part.  Sentinel keys (~0) are dropped by the pass that is told to (the first one): they
+    // get no rank and are not written, so the tile's output is shorter than its input and the later passes run on the
+    // kept keys only.
+    uint32_t live = 0;
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) {
         const uint32_t e = e0 + i * 32;
-        key[i] = e < valid_count ? keys_in[base + e] : (KeyT)0;
+        const bool in = e < valid_count;
+        key[i] = in ? keys_in[base + e] : (KeyT)0;
+        if (in && !(drop_sentinel && key[i] == ~(KeyT)0)) live |= 1u << i;
     }
 
     // ---- stable in-warp ranking, one item row at a time ----
@@ -183,7 +193,7 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     if (digit_mask < 16u) {                        // a narrow (<= 4 bit) last digit needs half the ballots
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
-            const bool valid = (e0 + i * 32) < valid_count;
+            const bool valid = (live >> i) & 1u;
             const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
             uint32_t peers;
             const uint32_t prev = warp_hist_add<4>(s_warp_hist[warp], d, valid, lane, peers);
@@ -192,7 +202,7 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     } else {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
-            const bool valid = (e0 + i * 32) < valid_count;
+            const bool valid = (live >> i) & 1u;
             const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
             uint32_t peers;
             const uint32_t prev = warp_hist_add(s_warp_hist[warp], d, valid, lane, peers);
@@ -228,6 +238,7 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
         for (int w = 0; w < warp; ++w) wbase += s_warp_tot[w];
         const uint32_t excl = wbase + inc - count;
         s_block_excl[d] = excl;
+        if (d == RADIX - 1) s_kept = excl + count;       // keys of this tile that take part (all but dropped sentinels)
 
         uint32_t prefix = 0;
         if (tile > 0) {
@@ -250,13 +261,14 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     for (int i = 0; i < ITEMS; ++i) {
         const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
         rank[i] += s_block_excl[d] + s_warp_hist[warp][d];      // rank[] becomes the tile-local sorted position
-        if ((e0 + i * 32) < valid_count) s_keys[rank[i]] = key[i];
+        if ((live >> i) & 1u) s_keys[rank[i]] = key[i];
     }
     __syncthreads();
+    const uint32_t kept = s_kept;
 #pragma unroll
     for (int k = 0; k < ITEMS; ++k) {
         const uint32_t sidx = tid + k * SORT_THREADS;
-        if (sidx < valid_count) {
+        if (sidx < kept) {
             const KeyT kk = s_keys[sidx];
             const uint32_t d = (uint32_t)(kk >> shift) & digit_mask;
             keys_out[s_glob_base[d] + sidx] = kk;
@@ -272,13 +284,13 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
         }
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i)
-            if ((e0 + i * 32) < valid_count) s_vals[rank[i]] = val[i];
+            if ((live >> i) & 1u) s_vals[rank[i]] = val[i];
     }
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < ITEMS; ++k) {
         const uint32_t sidx = tid + k * SORT_THREADS;
-        if (sidx < valid_count) {
+        if (sidx < kept) {
             const uint32_t d = (uint32_t)(s_keys[sidx] >> shift) & digit_mask;
             vals_out[s_glob_base[d] + sidx] = s_vals[sidx];
         }
@@ -290,10 +302,11 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
 template <typename KeyT>
 int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1, int64_t n_max,
                      const uint32_t* n_dev, int begin_bit, int end_bit, uint32_t* hist, uint32_t* lookback,
-                     uint32_t* tile_counters, cudaStream_t s, int segments, bool hist_ready, bool scratch_zeroed) {
+                     uint32_t* tile_counters, cudaStream_t s, int segments, bool hist_ready, bool scratch_zeroed,
+                     uint32_t* n_kept_dev) {
     if (n_max <= 0 || end_bit <= begin_bit || segments <= 0) return GSR_OK;
+    if (n_kept_dev && (hist_ready || n_dev)) return GSR_ERR_INVALID_ARGUMENT;
     if (n_max >= (int64_t)VALUE_MASK) return GSR_ERR_UNSUPPORTED;
-    if (segments > 1 && n_dev != nullptr) return GSR_ERR_INVALID_ARGUMENT;
     if (segments > 65535) return GSR_ERR_UNSUPPORTED;
     const int passes = (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS;
     if (passes > MAX_PASSES) return GSR_ERR_INVALID_ARGUMENT;
@@ -318,10 +331,10 @@ int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1,
             attr_set = true;
         }
         radix_histogram_kernel<KeyT><<<dim3(hist_blocks, segments, passes), 256, hist_smem, s>>>(
-            keys0, (uint32_t)n_max, n_dev, begin_bit, end_bit, passes, hist);
+            keys0, (uint32_t)n_max, n_dev, begin_bit, end_bit, passes, hist, n_kept_dev != nullptr);
         GSR_LAUNCH_CHECK();
     }
-    radix_scan_hist_kernel<<<passes * segments, RADIX, 0, s>>>(hist);
+    radix_scan_hist_kernel<<<passes * segments, RADIX, 0, s>>>(hist, n_kept_dev, passes);
     GSR_LAUNCH_CHECK();
     const size_t dyn = (size_t)TILE * (sizeof(KeyT) + 4);
     for (int p = 0; p < passes; ++p) {
@@ -331,17 +344,20 @@ int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1,
         KeyT* kout = (p & 1) ? keys0 : keys1;
         const uint32_t* vin = (p & 1) ? vals1 : vals0;
         uint32_t* vout = (p & 1) ? vals0 : vals1;
+        // with sentinel dropping the first pass reads all n_max keys and writes the kept ones; the others move those only
+        const uint32_t* n_pass = (n_kept_dev && p > 0) ? n_kept_dev : n_dev;
         onesweep_pass_kernel<KeyT><<<dim3(tiles, segments), SORT_THREADS, dyn, s>>>(
-            kin, kout, vin, vout, (uint32_t)n_max, n_dev, shift, (1u << bits) - 1u, hist + p * RADIX, hist_seg,
-            lookback + (size_t)p * segments * lb_seg, lb_seg, tile_counters + (size_t)p * segments);
+            kin, kout, vin, vout, (uint32_t)n_max, n_pass, shift, (1u << bits) - 1u, hist + p * RADIX, hist_seg,
+            lookback + (size_t)p * segments * lb_seg, lb_seg, tile_counters + (size_t)p * segments,
+            n_kept_dev != nullptr && p == 0);
         GSR_LAUNCH_CHECK();
     }
     return GSR_OK;
 }
 
 template int radix_sort_pairs<uint32_t>(uint32_t*, uint32_t*, uint32_t*, uint32_t*, int64_t, const uint32_t*, int, int,
-                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t, int, bool, bool);
+                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t, int, bool, bool, uint32_t*);
 template int radix_sort_pairs<uint64_t>(uint64_t*, uint64_t*, uint32_t*, uint32_t*, int64_t, const uint32_t*, int, int,
-                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t, int, bool, bool);
+                                        uint32_t*, uint32_t*, uint32_t*, cudaStream_t, int, bool, bool, uint32_t*);
 
 }  // namespace gsr
