@@ -229,9 +229,10 @@ static int check_dims(int P, int V, int W, int H, int channels, int sh_coeffs, i
     const int64_t tx = (W + TILE_X - 1) / TILE_X, ty = (H + TILE_Y - 1) / TILE_Y;
     const int64_t VT = (int64_t)V * tx * ty;
     if (VT >= (1ll << 28) || tx > 1024 || ty > 1024) return GSR_ERR_UNSUPPORTED;   // supertile coordinates are bytes (16384 px)
-    // the instance key keeps view * supertiles + supertile in 16 bits (its upper half carries the tile hit mask): a batch
-    // may hold at most 65536 supertiles (64x64 px) over all its views -- e.g. 128 views of 1920x1080; split larger ones
-    if ((int64_t)V * ((tx + ST - 1) / ST) * ((ty + ST - 1) / ST) > (1ll << 16)) return GSR_ERR_UNSUPPORTED;
+    // the instance key keeps supertile << view_bits | view in 16 bits (its upper half carries the tile hit mask):
+    // ceil(log2 views) + ceil(log2 supertiles per view) <= 16 -- e.g. 128 views of 1920x1080; split larger batches
+    if (ceil_log2((uint32_t)(V > 0 ? V : 1)) + ceil_log2((uint32_t)(((tx + ST - 1) / ST) * ((ty + ST - 1) / ST))) > 16)
+        return GSR_ERR_UNSUPPORTED;
     return GSR_OK;
 }
 

@@ -24,7 +24,6 @@ namespace gsr {
 namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
-constexpr int EMIT_HIST_PASSES = 2;      // instance sorts of up to 16 key bits get their histograms from the emit kernel
 
 __device__ __forceinline__ uint32_t block_exclusive_scan_256(uint32_t v, uint32_t* s_warp /*[8]*/, uint32_t& total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -171,22 +170,22 @@ block_sums_scan_kernel(uint32_t nblocks, uint32_t* __restrict__ block_sums, uint
 }
 
 __global__ void __launch_bounds__(SCAN_BLOCK, 4)
-emit_st_instances_kernel(uint32_t VP, int P, int stiles_x, uint32_t S, const uint32_t* __restrict__ sorted_g,
+emit_st_instances_kernel(uint32_t VP, int P, int stiles_x, uint32_t S, int view_bits,
+                         const uint32_t* __restrict__ sorted_g,
                          const ushort4* __restrict__ rects, const uint32_t* __restrict__ vis_count, uint32_t capacity,
                          uint32_t nblocks,
                          uint32_t* __restrict__ ikeys, uint32_t* __restrict__ ivals, uint32_t* __restrict__ counters,
-                         int hist_passes, int key_bits, uint32_t* __restrict__ sort_hist,
                          uint32_t* __restrict__ lookback, uint32_t* __restrict__ ticket,
-                         uint32_t* __restrict__ key_hist, uint32_t khist_bins /* 0: global atomics */) {
-    extern __shared__ uint32_t s_khist[];                 // [khist_bins]: instances per key, keys kbase .. kbase + bins
+                         uint32_t* __restrict__ key_hist, uint32_t khist_views /* 0: global atomics */) {
+    extern __shared__ uint32_t s_khist[];                 // [S][khist_views]: instances per key of the block's views
     __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
-    __shared__ uint32_t s_hist[SCAN_BLOCK / 32][EMIT_HIST_PASSES][RADIX];
     __shared__ uint32_t s_key[EMIT_WINDOW];              // key | supertile x << 16 | supertile y << 24
     __shared__ uint16_t s_slot[EMIT_WINDOW];             // which of the block's slots the instance belongs to
     __shared__ uint32_t s_gidx[EMIT_TILE];               // per slot: view*P + Gaussian and the tile rectangle
     __shared__ ushort4 s_rect[EMIT_TILE];
     __shared__ uint32_t s_blk, s_out0;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    (void)lane; (void)warp;
 #if GSR_EMIT_LOOKBACK
     if (threadIdx.x == 0) s_blk = atomicAdd(ticket, 1u);  // blocks are numbered in the order they start: a block only
     __syncthreads();                                      // waits for blocks that already run
@@ -206,7 +205,7 @@ emit_st_instances_kernel(uint32_t VP, int P, int stiles_x, uint32_t S, const uin
         rc[k] = slot_rect(base + k, VP, P, sorted_g, rects, vis_count, gidx[k]);
         uint32_t sx0, sy0, w;
         sum += st_rect(rc[k], sx0, sy0, w);
-        key0[k] = (gidx[k] / (uint32_t)P) * S + sy0 * (uint32_t)stiles_x + sx0;
+        key0[k] = ((sy0 * (uint32_t)stiles_x + sx0) << view_bits) | (gidx[k] / (uint32_t)P);
         s_gidx[threadIdx.x * EMIT_ITEMS + k] = gidx[k];
         s_rect[threadIdx.x * EMIT_ITEMS + k] = rc[k];
     }
@@ -246,10 +245,10 @@ emit_st_instances_kernel(uint32_t VP, int P, int stiles_x, uint32_t S, const uin
         }
     }
 #endif
-    if (hist_passes > 0)
-        for (int i = threadIdx.x; i < (SCAN_BLOCK / 32) * EMIT_HIST_PASSES * RADIX; i += SCAN_BLOCK) (&s_hist[0][0][0])[i] = 0;
-    // supertile keys this block can emit: those of the views its slots belong to
-    const uint32_t kbase = (slot0 / (uint32_t)P) * S;
+    // supertile keys this block can emit: those of the (khist_views) views its slots belong to
+    const uint32_t view_first = slot0 / (uint32_t)P;
+    const uint32_t vmask = (1u << view_bits) - 1u;
+    const uint32_t khist_bins = S * khist_views;
     for (uint32_t i = threadIdx.x; i < khist_bins; i += SCAN_BLOCK) s_khist[i] = 0;
     __syncthreads();
     const uint32_t out0 = s_out0;
@@ -266,123 +265,113 @@ emit_st_instances_kernel(uint32_t VP, int P, int stiles_x, uint32_t S, const uin
                 for (uint32_t l = 0; l < cnt; ++l) {
                     const uint32_t rel = o - w0;           // wraps for o < w0: fails the test below
                     if (rel < (uint32_t)EMIT_WINDOW) {       // the serial walk only notes WHERE; the copy-out does the rest
-                        s_key[rel] = (row + x) | ((sx0 + x) << 16) | (sy << 24);
+                        s_key[rel] = (row + (x << view_bits)) | ((sx0 + x) << 16) | (sy << 24);
                         s_slot[rel] = (uint16_t)(threadIdx.x * EMIT_ITEMS + k);
                     }
                     ++o;
-                    if (++x == wid) { x = 0; row += (uint32_t)stiles_x; ++sy; }
+                    if (++x == wid) { x = 0; row += (uint32_t)stiles_x << view_bits; ++sy; }
                 }
             }
         }
         __syncthreads();
         const uint32_t n = min((uint32_t)EMIT_WINDOW, total - w0);
-        for (uint32_t o0 = 0; o0 < n; o0 += SCAN_BLOCK) {     // warp-uniform trip count (the histogram uses ballots)
+        for (uint32_t o0 = 0; o0 < n; o0 += SCAN_BLOCK) {
             const uint32_t o = o0 + threadIdx.x;
-            bool stored = false;
-            uint32_t key = 0;
             if (o < n) {
                 const uint32_t packed = s_key[o];
                 const uint32_t slot = s_slot[o];
                 const uint32_t kk = packed & ((1u << ST_KEY_BITS) - 1u);
-                key = (st_hit_mask(s_rect[slot], ((packed >> 16) & 0xffu) * ST, (packed >> 24) * ST) << ST_KEY_BITS) | kk;
+                const uint32_t key =
+                    (st_hit_mask(s_rect[slot], ((packed >> 16) & 0xffu) * ST, (packed >> 24) * ST) << ST_KEY_BITS) | kk;
                 const uint32_t dst = out0 + w0 + o;
                 if (dst < capacity) {
                     ikeys[dst] = key;
                     ivals[dst] = s_gidx[slot];
-                    stored = true;
-                    if (khist_bins) atomicAdd(&s_khist[kk - kbase], 1u);
+                    // instances per key: everything the sort and the chunk table need to know about the key distribution
+                    if (khist_views) atomicAdd(&s_khist[(kk >> view_bits) * khist_views + ((kk & vmask) - view_first)], 1u);
                     else atomicAdd(&key_hist[kk], 1u);
                 } else {
                     overflow = true;
-                }
-            }
-#pragma unroll
-            for (int p = 0; p < EMIT_HIST_PASSES; ++p) {
-                if (p < hist_passes) {
-                    const int shift = p * RADIX_BITS;
-                    const int bits = min(RADIX_BITS, key_bits - shift);
-                    uint32_t peers;
-                    if (bits <= 4)
-                        warp_hist_add<4>(s_hist[warp][p], (key >> shift) & ((1u << bits) - 1u), stored, lane, peers);
-                    else
-                        warp_hist_add(s_hist[warp][p], (key >> shift) & ((1u << bits) - 1u), stored, lane, peers);
                 }
             }
         }
     }
     if (overflow) counters[CNT_OVERFLOW] = 1;
     __syncthreads();
-    if (hist_passes > 0) {
-        for (int i = threadIdx.x; i < hist_passes * RADIX; i += SCAN_BLOCK) {
-            const int p = i / RADIX, d = i - p * RADIX;
-            uint32_t c = 0;
-#pragma unroll
-            for (int w = 0; w < SCAN_BLOCK / 32; ++w) c += s_hist[w][p][d];
-            if (c) atomicAdd(&sort_hist[i], c);
-        }
-    }
     for (uint32_t i = threadIdx.x; i < khist_bins; i += SCAN_BLOCK) {
         const uint32_t c = s_khist[i];
-        if (c) atomicAdd(&key_hist[kbase + i], c);
+        const uint32_t st = i / khist_views, vl = i - st * khist_views;
+        if (c) atomicAdd(&key_hist[(st << view_bits) | (view_first + vl)], c);
     }
+}
+
+// single block: the digit histograms of the instance sort from the per-key counts (the sort digit is a bit field of the
+// key's supertile part), so that no pass over the instances is needed for them
+__global__ void __launch_bounds__(1024)
+sort_hist_from_keys_kernel(uint32_t num_keys, int view_bits, int passes, const uint32_t* __restrict__ key_hist,
+                           uint32_t* __restrict__ sort_hist) {
+    __shared__ uint32_t s_h[MAX_PASSES][RADIX];
+    for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) (&s_h[0][0])[i] = 0;
+    __syncthreads();
+    for (uint32_t k = threadIdx.x; k < num_keys; k += blockDim.x) {
+        const uint32_t c = key_hist[k];
+        if (!c) continue;
+        const uint32_t st = k >> view_bits;
+        for (int p = 0; p < passes; ++p) atomicAdd(&s_h[p][(st >> (p * RADIX_BITS)) & (RADIX - 1)], c);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) sort_hist[i] = (&s_h[0][0])[i];
 }
 
 // single block, off the critical path (it runs next to the instance sort, launch_binning): from the per-key instance counts
 // the emit kernel took,
 //   st_ranges[k]  = [first, last + 1) of key k in the SORTED instance list (the reference's identifyTileRanges,
 //                   rasterizer_impl.cu:116-138, one level up -- but without reading the sorted keys),
-//   chunk_base[k] = exclusive scan of ceil(len_k / CHUNK), chunk_base[VS] and counters[CNT_NCHUNKS] = number of chunks,
+//   chunk_base[k] = id of key k's first chunk (ceil(len_k / CHUNK) chunks each), counters[CNT_NCHUNKS] = number of chunks,
 //   chunk_key[c]  = owning key of chunk c.
 constexpr int CT_THREADS = 1024;
 
 __global__ void __launch_bounds__(CT_THREADS)
-chunk_table_kernel(uint32_t VS, const uint32_t* __restrict__ key_hist, uint2* __restrict__ st_ranges,
-                   uint32_t* __restrict__ chunk_base, uint32_t* __restrict__ chunk_key, uint32_t max_chunks,
-                   uint32_t* __restrict__ counters) {
+chunk_table_kernel(uint32_t num_keys, uint32_t S, int view_bits, const uint32_t* __restrict__ key_hist,
+                   uint2* __restrict__ st_ranges, uint32_t* __restrict__ chunk_base, uint32_t* __restrict__ chunk_key,
+                   uint32_t max_chunks, uint32_t* __restrict__ counters) {
     __shared__ uint32_t s_warp[32];
-    uint32_t carry_i = 0, carry_c = 0;
-    for (uint32_t start = 0; start < VS; start += CT_THREADS) {
+    // (1) the sorted list is in key order (supertile-major): ranges by a scan over the keys
+    uint32_t carry = 0;
+    for (uint32_t start = 0; start < num_keys; start += CT_THREADS) {
         const uint32_t k = start + threadIdx.x;
-        const uint32_t n = k < VS ? key_hist[k] : 0u;     // stored instances only: their sum never exceeds the capacity
-        uint32_t tot_i, tot_c;
-        const uint32_t first = carry_i + block_exclusive_scan_1024(n, s_warp, tot_i);
+        const uint32_t n = k < num_keys ? key_hist[k] : 0u;   // stored instances only: their sum never exceeds the capacity
+        uint32_t tot;
+        const uint32_t first = carry + block_exclusive_scan_1024(n, s_warp, tot);
+        if (k < num_keys) st_ranges[k] = make_uint2(first, first + n);
+        carry += tot;
+    }
+    // (2) chunks are NUMBERED view-major (view, supertile): the kernels that walk the chunks in id order then stay inside
+    // one view's per-Gaussian arrays for a long stretch (supertile-major numbering cycled through all views' 9.6 MB
+    // geometry records every few chunks and cost the record scatter 20 % more DRAM traffic)
+    carry = 0;
+    for (uint32_t start = 0; start < num_keys; start += CT_THREADS) {
+        const uint32_t j = start + threadIdx.x;
+        const uint32_t view = j / S, st = j - view * S;
+        const uint32_t k = (st << view_bits) | view;
+        const uint32_t n = j < num_keys ? key_hist[k] : 0u;
         const uint32_t nch = (n + CHUNK - 1) / CHUNK;
-        const uint32_t cb = carry_c + block_exclusive_scan_1024(nch, s_warp, tot_c);
-        if (k < VS) {
-            st_ranges[k] = make_uint2(first, first + n);
+        uint32_t tot;
+        const uint32_t cb = carry + block_exclusive_scan_1024(nch, s_warp, tot);
+        if (j < num_keys) {
             chunk_base[k] = cb;
-            for (uint32_t j = 0; j < nch; ++j)
-                if (cb + j < max_chunks) chunk_key[cb + j] = k;
+            for (uint32_t c = 0; c < nch; ++c)
+                if (cb + c < max_chunks) chunk_key[cb + c] = k;
         }
-        carry_i += tot_i;
-        carry_c += tot_c;
+        carry += tot;
     }
-    if (threadIdx.x == 0) {
-        chunk_base[VS] = carry_c;
-        counters[CNT_NCHUNKS] = min(carry_c, max_chunks);
-    }
+    if (threadIdx.x == 0) counters[CNT_NCHUNKS] = min(carry, max_chunks);
 }
 
 struct ChunkInfo {
     uint32_t key, first, count;      // supertile key, first sorted instance, instances in this chunk
     uint32_t view, ox, oy;           // view and first tile of the supertile
 };
-
-__device__ __forceinline__ bool chunk_info(uint32_t cid, const uint32_t* __restrict__ counters,
-                                           const uint32_t* __restrict__ chunk_key, const uint32_t* __restrict__ chunk_base,
-                                           const uint2* __restrict__ st_ranges, uint32_t S, int stiles_x, ChunkInfo& c) {
-    if (cid >= counters[CNT_NCHUNKS]) return false;
-    c.key = chunk_key[cid];
-    const uint2 r = st_ranges[c.key];
-    c.first = r.x + (cid - chunk_base[c.key]) * CHUNK;
-    c.count = min((uint32_t)CHUNK, r.y - c.first);
-    c.view = c.key / S;
-    const uint32_t s = c.key - c.view * S;
-    const uint32_t sy = s / (uint32_t)stiles_x;
-    c.ox = (s - sy * (uint32_t)stiles_x) * ST;
-    c.oy = sy * ST;
-    return true;
-}
 
 // per chunk: how many of its instances hit each of the supertile's 16 tiles (hit masks: upper half of the sorted keys).
 // One WARP per chunk: 8 rows of 32 keys, 16 ballots a row, lane t < 16 keeps tile t's count in a register -- no shared
@@ -407,15 +396,19 @@ chunk_count_kernel(const uint32_t* __restrict__ counters, const uint32_t* __rest
             const uint32_t i = row * 32 + lane;
             m[row] = i < count ? skeys[first + i] >> ST_KEY_BITS : 0u;
         }
-        uint32_t n = 0;
+        // warp-uniform counters (ballot -> popc -> add never leave the uniform datapath: the per-lane ALU only forms the
+        // predicates; with `if (lane == t) n += ...` the kernel was ALU-bound, 86 % pipe utilisation)
+        uint32_t cnt[ST_TILES];
+#pragma unroll
+        for (int t = 0; t < ST_TILES; ++t) cnt[t] = 0;
 #pragma unroll
         for (int row = 0; row < CHUNK / 32; ++row) {
 #pragma unroll
-            for (int t = 0; t < ST_TILES; ++t) {
-                const uint32_t bal = __ballot_sync(FULL, (m[row] >> t) & 1u);
-                if (lane == t) n += __popc(bal);
-            }
+            for (int t = 0; t < ST_TILES; ++t) cnt[t] += __popc(__ballot_sync(FULL, (m[row] >> t) & 1u));
         }
+        uint32_t n = 0;
+#pragma unroll
+        for (int t = 0; t < ST_TILES; ++t) n = lane == t ? cnt[t] : n;
         if (lane < ST_TILES) chunk_counts[(size_t)cid * ST_TILES + lane] = n;
     }
 }
@@ -425,12 +418,16 @@ chunk_count_kernel(const uint32_t* __restrict__ counters, const uint32_t* __rest
 // tile_scan_kernel).  (Round 1 walked the chunks serially with one lane per tile: 55 us at C2, set by the longest
 // supertile list.)
 __global__ void __launch_bounds__(ST_TILES * 32)
-tile_offsets_kernel(uint32_t VS, uint32_t S, int stiles_x, int tiles_x, int tiles_y,
-                    const uint32_t* __restrict__ chunk_base, uint32_t max_chunks, uint32_t* __restrict__ chunk_counts,
-                    uint32_t* __restrict__ tile_start) {
+tile_offsets_kernel(int V, int view_bits, int stiles_x, int tiles_x, int tiles_y,
+                    const uint32_t* __restrict__ chunk_base, const uint2* __restrict__ st_ranges, uint32_t max_chunks,
+                    uint32_t* __restrict__ chunk_counts, uint32_t* __restrict__ tile_start) {
     const uint32_t k = blockIdx.x;
+    const uint32_t view = k & ((1u << view_bits) - 1u), s = k >> view_bits;
+    if (view >= (uint32_t)V) return;                     // key slots of views the batch does not have
     const int t = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t c0 = min(chunk_base[k], max_chunks), c1 = min(chunk_base[k + 1], max_chunks);
+    const uint2 kr = st_ranges[k];
+    const uint32_t c0 = min(chunk_base[k], max_chunks);
+    const uint32_t c1 = min(chunk_base[k] + (kr.y - kr.x + CHUNK - 1) / CHUNK, max_chunks);
     uint32_t run = 0;
     for (uint32_t cb = c0; cb < c1; cb += 32) {
         const uint32_t c = cb + lane;
@@ -445,7 +442,6 @@ tile_offsets_kernel(uint32_t VS, uint32_t S, int stiles_x, int tiles_x, int tile
         run += __shfl_sync(FULL, inc, 31);
     }
     if (lane == 0) {
-        const uint32_t view = k / S, s = k - view * S;
         const uint32_t sy = s / (uint32_t)stiles_x, sx = s - sy * (uint32_t)stiles_x;
         const uint32_t gx = sx * ST + (t & 3), gy = sy * ST + (t >> 2);
         if (gx < (uint32_t)tiles_x && gy < (uint32_t)tiles_y)
@@ -464,25 +460,45 @@ tile_scan_kernel(uint32_t VT, uint32_t capacity, uint32_t* __restrict__ tile_sta
     uint32_t carry = 0;
     constexpr int IT = 8;
     uint32_t nxt[IT];                                    // the next step's counts are in flight while this one is scanned
+    auto load8 = [&](uint32_t i, uint32_t* out) {        // tile_start is 256-byte aligned and i a multiple of 8
+        if (i + IT <= VT) {
+            const uint4 a = *reinterpret_cast<const uint4*>(tile_start + i), b = *reinterpret_cast<const uint4*>(tile_start + i + 4);
+            out[0] = a.x; out[1] = a.y; out[2] = a.z; out[3] = a.w; out[4] = b.x; out[5] = b.y; out[6] = b.z; out[7] = b.w;
+        } else {
 #pragma unroll
-    for (int k = 0; k < IT; ++k) nxt[k] = threadIdx.x * IT + k < VT ? tile_start[threadIdx.x * IT + k] : 0u;
+            for (int k = 0; k < IT; ++k) out[k] = i + k < VT ? tile_start[i + k] : 0u;
+        }
+    };
+    load8(threadIdx.x * IT, nxt);
     for (uint32_t start = 0; start < VT; start += TSCAN_THREADS * IT) {
         const uint32_t i0 = start + threadIdx.x * IT;
         uint32_t v[IT], sum = 0;
 #pragma unroll
         for (int k = 0; k < IT; ++k) { v[k] = nxt[k]; sum += v[k]; }
-        const uint32_t i1 = i0 + TSCAN_THREADS * IT;
-#pragma unroll
-        for (int k = 0; k < IT; ++k) nxt[k] = i1 + k < VT ? tile_start[i1 + k] : 0u;
+        load8(i0 + TSCAN_THREADS * IT, nxt);
         uint32_t total;
         uint32_t ex = carry + block_exclusive_scan_1024(sum, s_warp, total);
+        if (i0 + IT <= VT) {                              // whole group: 2 + 4 vector stores instead of 16 scalar ones
+            uint32_t e[IT + 1];
+            e[0] = ex;
 #pragma unroll
-        for (int k = 0; k < IT; ++k) {
-            if (i0 + k < VT) {
-                tile_start[i0 + k] = ex;
-                ranges[i0 + k] = make_uint2(min(ex, capacity), min(ex + v[k], capacity));
+            for (int k = 0; k < IT; ++k) e[k + 1] = e[k] + v[k];
+            *reinterpret_cast<uint4*>(tile_start + i0) = make_uint4(e[0], e[1], e[2], e[3]);
+            *reinterpret_cast<uint4*>(tile_start + i0 + 4) = make_uint4(e[4], e[5], e[6], e[7]);
+            uint4* rp = reinterpret_cast<uint4*>(ranges + i0);
+#pragma unroll
+            for (int k = 0; k < IT; k += 2)
+                rp[k / 2] = make_uint4(min(e[k], capacity), min(e[k + 1], capacity), min(e[k + 1], capacity),
+                                       min(e[k + 2], capacity));
+        } else {
+#pragma unroll
+            for (int k = 0; k < IT; ++k) {
+                if (i0 + k < VT) {
+                    tile_start[i0 + k] = ex;
+                    ranges[i0 + k] = make_uint2(min(ex, capacity), min(ex + v[k], capacity));
+                }
+                ex += v[k];
             }
-            ex += v[k];
         }
         carry += total;
     }
@@ -562,7 +578,7 @@ tile_order_kernel(uint32_t VT, const uint2* __restrict__ ranges, uint32_t* __res
 template <bool EXTRA>
 __global__ void __launch_bounds__(CHUNK)
 scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __restrict__ chunk_key,
-                       const uint32_t* __restrict__ chunk_base, const uint2* __restrict__ st_ranges, uint32_t S,
+                       const uint32_t* __restrict__ chunk_base, const uint2* __restrict__ st_ranges, int view_bits,
                        int stiles_x, int tiles_x, int tiles_y, int P, uint32_t capacity,
                        const uint32_t* __restrict__ vals, const uint32_t* __restrict__ skeys,
                        const uint32_t* __restrict__ chunk_offs, const uint32_t* __restrict__ tile_start,
@@ -584,8 +600,8 @@ scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __
         const uint2 r = st_ranges[o.key];
         o.first = r.x + (cid - chunk_base[o.key]) * CHUNK;
         o.count = min((uint32_t)CHUNK, r.y - o.first);
-        o.view = o.key / S;
-        const uint32_t sidx = o.key - o.view * S;
+        o.view = o.key & ((1u << view_bits) - 1u);
+        const uint32_t sidx = o.key >> view_bits;
         const uint32_t sy = sidx / (uint32_t)stiles_x;
         o.ox = (sidx - sy * (uint32_t)stiles_x) * ST;
         o.oy = sy * ST;
@@ -714,11 +730,12 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
         return GSR_OK;
     }
     if (L.tile_bits > ST_KEY_BITS) return GSR_ERR_UNSUPPORTED;      // check_dims refuses such batches before
+    (void)VS;
     const uint32_t cap = (uint32_t)capacity;
     const uint32_t nblocks = (VP + EMIT_TILE - 1) / EMIT_TILE;
     const uint32_t* sorted_g = at<uint32_t>(gws, L.sorted_vals_in ? L.dvals1 : L.dvals0);
     const ushort4* rects = at<ushort4>(gws, L.rects);
-    const bool fused_hist = L.tile_passes <= EMIT_HIST_PASSES;
+    const uint32_t NK = L.num_keys;                      // key slots: supertiles per view << view_bits
     uint32_t* key_hist = at<uint32_t>(bws, L.key_hist);
     uint2* st_ranges = at<uint2>(bws, L.st_ranges);
     uint32_t* chunk_base = at<uint32_t>(bws, L.chunk_base);
@@ -733,10 +750,10 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     GSR_CUDA_TRY(cudaMemsetAsync(bws, 0, L.binning_zero_bytes, s));
     {
         // key counts in shared memory: the keys of the (at most EMIT_TILE / P + 2) views a block's slots belong to
-        const uint32_t nv = (uint32_t)V < (uint32_t)(EMIT_TILE / P + 2) ? (uint32_t)V : (uint32_t)(EMIT_TILE / P + 2);
+        uint32_t nv = (uint32_t)V < (uint32_t)(EMIT_TILE / P + 2) ? (uint32_t)V : (uint32_t)(EMIT_TILE / P + 2);
         uint32_t bins = nv * S;
         constexpr uint32_t MAX_BINS = 24 * 1024;                     // 96 KB next to the kernel's 40 KB of static smem
-        if (bins > MAX_BINS) bins = 0;                               // (tiny P with thousands of supertiles: global atomics)
+        if (bins > MAX_BINS) bins = nv = 0;                          // (tiny P with thousands of supertiles: global atomics)
         static bool attr_set = false;
         if (!attr_set) {
             GSR_CUDA_TRY(cudaFuncSetAttribute(emit_st_instances_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -753,24 +770,26 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
         GSR_LAUNCH_CHECK();
 #endif
         emit_st_instances_kernel<<<nblocks, SCAN_BLOCK, bins * 4, s>>>(
-            VP, P, L.stiles_x, S, sorted_g, rects, at<uint32_t>(gws, L.vis_count), cap, nblocks,
-            at<uint32_t>(bws, L.ikeys0), at<uint32_t>(bws, L.ivals0),
-            counters, fused_hist ? L.tile_passes : 0, L.tile_bits, at<uint32_t>(bws, L.ihist),
-            offs, at<uint32_t>(bws, L.emit_ticket), key_hist, bins);
+            VP, P, L.stiles_x, S, L.view_bits, sorted_g, rects, at<uint32_t>(gws, L.vis_count), cap, nblocks,
+            at<uint32_t>(bws, L.ikeys0), at<uint32_t>(bws, L.ivals0), counters, offs, at<uint32_t>(bws, L.emit_ticket),
+            key_hist, nv);
+        GSR_LAUNCH_CHECK();
+        sort_hist_from_keys_kernel<<<1, 1024, 0, s>>>(NK, L.view_bits, L.tile_passes, key_hist, at<uint32_t>(bws, L.ihist));
         GSR_LAUNCH_CHECK();
     }
     stage_end(ST_EMIT, s);
     // the chunk table only needs the key counts: it runs on the side stream while the instances are sorted
     int rc = side_fork(s, &side);
     if (rc != GSR_OK) return rc;
-    chunk_table_kernel<<<1, CT_THREADS, 0, side>>>(VS, key_hist, st_ranges, chunk_base, chunk_key, max_chunks, counters);
+    chunk_table_kernel<<<1, CT_THREADS, 0, side>>>(NK, S, L.view_bits, key_hist, st_ranges, chunk_base, chunk_key, max_chunks,
+                                                   counters);
     GSR_LAUNCH_CHECK();
     stage_begin(ST_TILE_SORT, s);
     rc = radix_sort_pairs<uint32_t>(at<uint32_t>(bws, L.ikeys0), at<uint32_t>(bws, L.ikeys1),
                                     at<uint32_t>(bws, L.ivals0), at<uint32_t>(bws, L.ivals1), capacity,
-                                    counters + CNT_ST_RENDERED, 0, L.tile_bits, at<uint32_t>(bws, L.ihist),
+                                    counters + CNT_ST_RENDERED, L.view_bits, L.tile_bits, at<uint32_t>(bws, L.ihist),
                                     at<uint32_t>(bws, L.ilookback), at<uint32_t>(bws, L.ihist) + MAX_PASSES * RADIX, s, 1,
-                                    fused_hist, true);
+                                    true, true);
     stage_end(ST_TILE_SORT, s);
     if (rc != GSR_OK) return rc;
     rc = side_join(s);
@@ -781,8 +800,8 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     stage_begin(ST_RANGES, s);
     chunk_count_kernel<<<chunk_grid, 256, 0, s>>>(counters, chunk_key, chunk_base, st_ranges, skeys, chunk_counts);
     GSR_LAUNCH_CHECK();
-    tile_offsets_kernel<<<VS, ST_TILES * 32, 0, s>>>(VS, S, L.stiles_x, L.tiles_x, L.tiles_y, chunk_base, max_chunks,
-                                                    chunk_counts, tile_start);
+    tile_offsets_kernel<<<NK, ST_TILES * 32, 0, s>>>(V, L.view_bits, L.stiles_x, L.tiles_x, L.tiles_y, chunk_base, st_ranges,
+                                                    max_chunks, chunk_counts, tile_start);
     GSR_LAUNCH_CHECK();
     tile_scan_kernel<<<1, TSCAN_THREADS, 0, s>>>(VT, cap, tile_start, at<uint2>(iws, L.ranges), counters);
     GSR_LAUNCH_CHECK();
@@ -813,12 +832,12 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
         const float4* rgb4 = sh_coeffs > 0 ? at<float4>(gws, L.rgb) : nullptr;
         if (channels > 3) {
             scatter_records_kernel<true><<<scatter_grid, CHUNK, 0, s>>>(
-                counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals, skeys,
+                counters, chunk_key, chunk_base, st_ranges, L.view_bits, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals, skeys,
                 chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, at<float4>(gws, L.ext4),
                 at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC), at<float4>(bws, L.recD));
         } else {
             scatter_records_kernel<false><<<scatter_grid, CHUNK, 0, s>>>(
-                counters, chunk_key, chunk_base, st_ranges, S, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals, skeys,
+                counters, chunk_key, chunk_base, st_ranges, L.view_bits, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals, skeys,
                 chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, nullptr, at<float4>(bws, L.recA),
                 at<float4>(bws, L.recB), at<float4>(bws, L.recC), nullptr);
         }

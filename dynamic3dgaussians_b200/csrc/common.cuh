@@ -88,6 +88,8 @@ struct Layout : GsrLayout {
     size_t key_hist, emit_lookback, emit_ticket;
     // geometry workspace, internal: per view, the number of Gaussians the depth sort kept (those that touch a tile)
     size_t vis_count;
+    int view_bits, st_bits;       // instance key = supertile << view_bits | view
+    uint32_t num_keys;            // supertiles per view << view_bits
 };
 
 inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
@@ -105,10 +107,16 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     L.tiles_y = ty;
     L.stiles_x = (tx + ST - 1) / ST;
     L.stiles_y = (ty + ST - 1) / ST;
-    const size_t VS = (size_t)V * L.stiles_x * L.stiles_y;
-    L.tile_bits = ceil_log2((uint32_t)VS);    // key bits of the instance sort: view * S + supertile
+    // instance key = supertile << view_bits | view.  The instances are emitted view by view in depth order, so a STABLE
+    // sort on the supertile bits alone leaves them grouped by key with every group in depth order: one radix pass for up
+    // to 256 supertiles per view (a 1024x1024 image), two beyond -- the view bits are never sorted on.
+    L.view_bits = ceil_log2((uint32_t)(V > 0 ? V : 1));
+    L.st_bits = ceil_log2((uint32_t)(L.stiles_x * L.stiles_y));
+    L.tile_bits = L.view_bits + L.st_bits;    // live key bits (the upper half of the 32-bit key carries the tile hit mask)
+    const size_t VS = (size_t)(L.stiles_x * L.stiles_y) << L.view_bits;      // key slots (those of views >= V stay empty)
+    L.num_keys = (uint32_t)VS;
     L.depth_passes = 32 / RADIX_BITS;         // per-view segmented sort of the 32 depth bits
-    L.tile_passes = (L.tile_bits + RADIX_BITS - 1) / RADIX_BITS;
+    L.tile_passes = (L.st_bits + RADIX_BITS - 1) / RADIX_BITS;
     L.sorted_keys_in = (L.tile_passes & 1);   // which ping-pong buffer holds the result of the instance sort
     L.sorted_vals_in = (L.depth_passes & 1);  // ... and of the depth sort
     size_t o = 0;

@@ -74,21 +74,34 @@ radix_histogram_kernel(const KeyT* __restrict__ keys, uint32_t n_max, const uint
     };
 
     const uint32_t rows = (n + 31u) / 32u;
-    constexpr int UNROLL = 4;
+    // 8 rows of keys per step, and the NEXT step's keys are already in flight while this step's byte counters are
+    // updated (ncu on the round-1 loop: 3 CTAs / SM by shared memory, long-scoreboard stalls 4.6 per issue -- the loads'
+    // latency was exposed)
+    constexpr int UNROLL = 8;
     for (uint32_t r0 = blockIdx.x * HIST_ROWS_PER_BLOCK; r0 < rows; r0 += gridDim.x * HIST_ROWS_PER_BLOCK) {
         const uint32_t r1 = min(r0 + HIST_ROWS_PER_BLOCK, rows);
         int since_flush = 0;
+        KeyT nxt[UNROLL];
+        auto load = [&](uint32_t r) {
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) {
+                const uint32_t row = r + 8 * u;
+                const uint32_t e = row * 32u + lane;
+                // a key outside the range reads as the sentinel and is skipped below (rows past r1 belong to other CTAs)
+                nxt[u] = (row < r1 && e < n) ? keys[e] : ~(KeyT)0;
+            }
+        };
+        load(r0 + warp);
         for (uint32_t r = r0 + warp; r < r1; r += 8 * UNROLL) {
             KeyT key[UNROLL];
             bool ok[UNROLL];
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u) {
                 const uint32_t row = r + 8 * u;
-                const uint32_t e = row * 32u + lane;
-                ok[u] = row < r1 && e < n;
-                key[u] = ok[u] ? keys[e] : (KeyT)0;
-                if (drop_sentinel) ok[u] = ok[u] && key[u] != ~(KeyT)0;
+                key[u] = nxt[u];
+                ok[u] = row < r1 && row * 32u + lane < n && !(drop_sentinel && key[u] == ~(KeyT)0);
             }
+            if (r + 8 * UNROLL < r1) load(r + 8 * UNROLL);
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u) {
                 if (ok[u]) {

@@ -42,7 +42,8 @@ def test_workspace_protocol_host_side():
     L = RZ.workspace_layout(300_000, 27, 640, 360, 3, 0, 1000)
     assert (L.tiles_x, L.tiles_y) == (40, 23)
     assert (L.stiles_x, L.stiles_y) == (10, 6)                 # supertiles of 4x4 tiles
-    assert L.tile_bits == 11 and L.tile_passes == 2 and L.depth_passes == 4      # 27*60 supertile keys; 32 depth bits per view
+    assert L.tile_bits == 11 and L.tile_passes == 1 and L.depth_passes == 4      # key = 6 supertile bits << 5 | view:
+    # one sort pass on the supertile bits; 32 depth bits per view
     assert L.counters == 0
     offs = [getattr(L, n) for n in _lib._LAYOUT_SIZE_T[:18]]
     assert all(o % 256 == 0 for o in offs)

@@ -220,7 +220,9 @@ def test_gradients_vs_patched_reference_backward(P, n_views):
     """Second gradient witness: the reference's own backward kernels with the minimal repairs of
     oracle/build_ref.py PATCHES, at C1 and at HEADLINE size (300k Gaussians, 640x360), where autograd through the oracle
     cannot run.  Colour, depth and alpha cotangents.  Two routes for T_final:
-      * handed over directly (alphas = -final_T): <= 1e-4 in the max-norm and per element;
+      * handed over directly (alphas = -final_T): <= 1e-4 in the max-norm (measured 1e-6 .. 3e-6) and per element -- both
+        sides sum with float atomics in arbitrary order, so at most 2 in 100 000 elements may sit just outside the
+        per-element bound (seen: 0 or 1 of 900 000);
       * as the reference recovers it, 1 - alpha_out (backward.cu:484): float32 cancellation makes every T of a nearly
         saturated pixel ~1e-3 relatively wrong -- the reference's own precision, bounded here at 5e-3.
     Remaining documented difference of the reference formulas: 1 / (det^2 + 1e-7) in computeCov2DCUDA (backward.cu:215;
@@ -253,13 +255,13 @@ def test_gradients_vs_patched_reference_backward(P, n_views):
         for direct in (True, False):
             rg = rr.backward(gc[v], gd[v], ga[v], alphas=(-fT[v]).contiguous() if direct else None)
             if direct:
-                _check_grad(f"means2D[{v}]", g["means2D"][v], rg["means2D"])
+                _check_grad(f"means2D[{v}]", g["means2D"][v], rg["means2D"], elem_frac=2e-5)
             else:
                 assert rel_err(g["means2D"][v], rg["means2D"]) <= 5e-3
             part = {k: rg[k] for k in names}
             acc[direct] = part if acc[direct] is None else {k: acc[direct][k] + part[k] for k in names}
     for k in names:
-        _check_grad(k, g[k], acc[True][k].reshape(g[k].shape))
+        _check_grad(k, g[k], acc[True][k].reshape(g[k].shape), elem_frac=2e-5)
         assert rel_err(g[k], acc[False][k].reshape(g[k].shape)) <= 5e-3, k
 
 
