@@ -16,7 +16,8 @@ EXPORTED_SYMBOLS = [
     "gsr_abi_version", "gsr_strerror", "gsr_last_cuda_error", "gsr_set_option", "gsr_get_option",
     "gsr_workspace_sizes", "gsr_workspace_layout",
     "gsr_forward_geometry", "gsr_forward_render", "gsr_read_counters", "gsr_backward", "gsr_mark_visible",
-    "gsr_export_view_binning", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_knn_temp_bytes", "gsr_knn",
+    "gsr_export_view_binning", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_sort_pairs_static_max",
+    "gsr_sort_pairs_static", "gsr_knn_temp_bytes", "gsr_knn",
     "gsr_dyn_losses_temp_bytes", "gsr_dyn_losses",
     "gsr_image_loss_state_bytes", "gsr_image_loss_forward", "gsr_image_loss_backward", "gsr_adam_step",
     "gsr_fp32_peak_probe", "gsr_probe_geometry", "gsr_stage_timing_enable", "gsr_stage_timing_count", "gsr_stage_name",
@@ -97,6 +98,9 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.gsr_sort_temp_bytes.restype = sz
     lib.gsr_sort_temp_bytes.argtypes = [i64, i32]
     lib.gsr_sort_pairs.argtypes = [i32, vp, vp, vp, vp, i64, i32, i32, vp, sz, vp]
+    lib.gsr_sort_pairs_static_max.restype = i64
+    lib.gsr_sort_pairs_static_max.argtypes = []
+    lib.gsr_sort_pairs_static.argtypes = [i32, vp, vp, vp, vp, i64, i32, i32, vp]
     lib.gsr_knn_temp_bytes.restype = sz
     lib.gsr_knn_temp_bytes.argtypes = [i64]
     lib.gsr_knn.argtypes = [i64, i32, vp, vp, vp, vp, vp, sz, vp]

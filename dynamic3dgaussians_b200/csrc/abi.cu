@@ -3,6 +3,7 @@
 #include <math.h>
 #include <stdio.h>
 #include <string.h>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -570,6 +571,55 @@ int gsr_sort_pairs(int key_bytes, const void* keys_in, void* keys_out, const uin
     GSR_CUDA_TRY(cudaMemcpyAsync(keys_out, t + off[res ? 1 : 0], (size_t)n * key_bytes, cudaMemcpyDeviceToDevice, s));
     GSR_CUDA_TRY(cudaMemcpyAsync(vals_out, t + off[res ? 3 : 2], (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
     return GSR_OK;
+}
+
+// ---- the same sort with its scratch in a library-owned device array: no allocation anywhere on the call ----
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, serving loops).  GSR_SORT_STATIC_MAX_PAIRS pairs of 8-byte keys need
+// sort_layout(GSR_SORT_STATIC_MAX_PAIRS, 8) = 6.7 MiB; every GPU that loads the library holds the array until exit.
+constexpr size_t SORT_STATIC_BYTES = 7u << 20;
+static __device__ __align__(256) unsigned char g_sort_static_scratch[SORT_STATIC_BYTES];
+
+// In host code `g_sort_static_scratch` is only a handle for the runtime: the device address comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+static int sort_static_scratch(char** out) {
+    constexpr int MAX_DEVICES = 64;
+    static std::mutex mu;
+    static char* addr[MAX_DEVICES] = {};
+    int dev = -1;
+    GSR_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEVICES) return GSR_ERR_INVALID_ARGUMENT;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void* p = nullptr;
+        GSR_CUDA_TRY(cudaGetSymbolAddress(&p, g_sort_static_scratch));
+        addr[dev] = (char*)p;
+    }
+    *out = addr[dev];
+    return GSR_OK;
+}
+
+int64_t gsr_sort_pairs_static_max(void) { return GSR_SORT_STATIC_MAX_PAIRS; }
+
+int gsr_sort_pairs_static(int key_bytes, const void* keys_in, void* keys_out, const uint32_t* vals_in,
+                          uint32_t* vals_out, int64_t n, int begin_bit, int end_bit, gsr_stream_t stream) {
+    if (key_bytes != 4 && key_bytes != 8) return GSR_ERR_INVALID_ARGUMENT;
+    if (n < 0 || begin_bit < 0 || end_bit > key_bytes * 8 || end_bit < begin_bit) return GSR_ERR_INVALID_ARGUMENT;
+    if (n > GSR_SORT_STATIC_MAX_PAIRS) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "gsr_sort_pairs_static: n = %lld exceeds GSR_SORT_STATIC_MAX_PAIRS = %d; "
+                 "use gsr_sort_pairs with caller-owned scratch", (long long)n, GSR_SORT_STATIC_MAX_PAIRS);
+        return GSR_ERR_WORKSPACE_TOO_SMALL;
+    }
+    size_t off[7];
+    if (sort_layout(n, key_bytes, off) > SORT_STATIC_BYTES) return GSR_ERR_WORKSPACE_TOO_SMALL;
+    if (n == 0) return GSR_OK;
+    char* scratch = nullptr;
+    int rc = sort_static_scratch(&scratch);
+    if (rc != GSR_OK) return rc;
+    // radix_sort_pairs clears the histogram, look-back and ticket words it uses at the start of every call (the
+    // array keeps the previous call's contents); the key/value ping-pong buffers are fully overwritten.
+    return gsr_sort_pairs(key_bytes, keys_in, keys_out, vals_in, vals_out, n, begin_bit, end_bit, scratch,
+                          SORT_STATIC_BYTES, stream);
 }
 
 int gsr_stage_timing_enable(int on) {

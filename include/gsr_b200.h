@@ -204,6 +204,20 @@ size_t gsr_sort_temp_bytes(int64_t n, int key_bytes);
 int gsr_sort_pairs(int key_bytes, const void* keys_in, void* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
                    int64_t n, int begin_bit, int end_bit, void* tmp, size_t tmp_bytes, gsr_stream_t stream);
 
+/* The same sort with NO allocation anywhere on the call: the scratch gsr_sort_pairs takes from the caller lives in a
+ * file-scope `static __device__` array inside the library (7 MiB, held by every GPU that loads the library until the
+ * process exits), so the call can be made where cudaMalloc cannot (under CUDA graph capture, in a serving loop).
+ * This entry point has NO counterpart in the reference.
+ * Limit: n <= GSR_SORT_STATIC_MAX_PAIRS; a larger n returns GSR_ERR_WORKSPACE_TOO_SMALL with the reason in
+ * gsr_last_cuda_error().  Results are those of gsr_sort_pairs, bit for bit.  Every call on a device shares the one
+ * array: calls that overlap on the GPU (different streams, different threads) race -- serialise them.  The sort
+ * clears the histogram / look-back / ticket words it needs at the start of each call; nothing else is read before
+ * it is written. */
+#define GSR_SORT_STATIC_MAX_PAIRS 262144
+int64_t gsr_sort_pairs_static_max(void);   /* GSR_SORT_STATIC_MAX_PAIRS */
+int gsr_sort_pairs_static(int key_bytes, const void* keys_in, void* keys_out, const uint32_t* vals_in,
+                          uint32_t* vals_out, int64_t n, int begin_bit, int end_bit, gsr_stream_t stream);
+
 /*
  * k-nearest-neighbour search (replaces SimpleKNN::knn, K/simple_knn.cu:192-228; K = 3 is distCUDA2).
  *   mean_dist2 [P]  mean of the squared distances to the K nearest other points
