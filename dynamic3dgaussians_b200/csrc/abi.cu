@@ -310,8 +310,8 @@ int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels,
         rc = radix_sort_pairs<uint32_t>(at<uint32_t>(geom_ws, L.dkeys0), at<uint32_t>(geom_ws, L.dkeys1),
                                         at<uint32_t>(geom_ws, L.dvals0), at<uint32_t>(geom_ws, L.dvals1), P, nullptr,
                                         0, 32, at<uint32_t>(geom_ws, L.dhist), at<uint32_t>(geom_ws, L.dlookback),
-                                        at<uint32_t>(geom_ws, L.dcounters), s, V, false, true,
-                                        at<uint32_t>(geom_ws, L.vis_count));
+                                        at<uint32_t>(geom_ws, L.dcounters), s, V, /*hist_ready=*/true, true,
+                                        at<uint32_t>(geom_ws, L.vis_count));   // (histograms: the preprocess kernel)
     }
     if (rc) return rc;
     // (the instance count -- the reference's num_rendered -- is summed by the preprocess kernel itself)

@@ -2,7 +2,7 @@
 // Replaces FORWARD::preprocess / preprocessCUDA (R/cuda_rasterizer/forward.cu:166-269) and checkFrustum
 // (R/cuda_rasterizer/rasterizer_impl.cu:54-66).
 //
-// One thread per (view, Gaussian).  Besides the reference's per-Gaussian state it emits the depth-sort pair
+// One thread per (view, Gaussian) of a persistent grid.  Besides the reference's per-Gaussian state it emits the depth-sort pair
 // (view << 32 | depth bits, Gaussian index): the (tile, depth) instance sort of the reference is split into a depth
 // sort over Gaussians (here, P entries per view) followed by a stable tile sort over instances, which yields the
 // identical order with ~4x less sort traffic.
@@ -80,8 +80,22 @@ __device__ __forceinline__ float3 eval_sh_pinned(int deg, int M, const float* __
     return out;
 }
 
-__global__ void __launch_bounds__(256)
-preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
+// Persistent: the (view, chunk of PP_CHUNK Gaussians) work items are dealt out as ONE contiguous run per CTA, so a CTA
+// sees at most a few views.  That lets the kernel also take the depth sort's four digit histograms (what
+// radix_histogram_kernel would re-read all V x P keys for): counted in shared memory, flushed to dhist[view][pass][bin]
+// when the run leaves a view.  Keys of culled Gaussians (the sentinel ~0, dropped by the sort's first pass) are not counted.
+#ifndef GSR_PP_CTAS
+#define GSR_PP_CTAS 5
+#endif
+#ifndef GSR_PP_CHUNK
+#define GSR_PP_CHUNK 1024
+#endif
+constexpr int PP_CHUNK = GSR_PP_CHUNK;
+constexpr int PP_CTAS_PER_SM = GSR_PP_CTAS;
+constexpr int DEPTH_PASSES = 4;            // 32-bit depth keys, 8-bit digits
+
+__global__ void __launch_bounds__(256, PP_CTAS_PER_SM)
+preprocess_kernel(const CamDev* __restrict__ cams, int V, int P, int sh_coeffs,
                   const float* __restrict__ means3D, const float* __restrict__ opacities,
                   const float* __restrict__ scales, const float* __restrict__ rotations,
                   const float* __restrict__ cov3D_precomp, const float* __restrict__ sh,
@@ -89,99 +103,149 @@ preprocess_kernel(const CamDev* __restrict__ cams, int P, int sh_coeffs,
                   int32_t* __restrict__ radii, ushort4* __restrict__ rects, float4* __restrict__ geomrec,
                   float* __restrict__ rgb, uint8_t* __restrict__ clamped,
                   uint32_t* __restrict__ dkeys, uint32_t* __restrict__ dvals, int32_t* __restrict__ radii_out,
-                  uint32_t* __restrict__ counters) {
+                  uint32_t* __restrict__ counters, uint32_t* __restrict__ dhist) {
     __shared__ CamDev cam;
     __shared__ uint32_t s_tiles[8];
-    const int v = blockIdx.y;
-    {
-        const uint32_t* src = reinterpret_cast<const uint32_t*>(cams + v);
-        uint32_t* dst = reinterpret_cast<uint32_t*>(&cam);
-        for (int i = threadIdx.x; i < (int)(sizeof(CamDev) / 4); i += blockDim.x) dst[i] = src[i];
+    __shared__ uint32_t s_dh[DEPTH_PASSES * RADIX];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int chunks = (P + PP_CHUNK - 1) / PP_CHUNK;
+    const long long items = (long long)V * chunks;
+    const int c_begin = (int)(items * blockIdx.x / gridDim.x), c_end = (int)(items * (blockIdx.x + 1) / gridDim.x);
+    for (int i = tid; i < DEPTH_PASSES * RADIX; i += 256) s_dh[i] = 0;
+    uint32_t tiles_acc = 0;
+    int cur_view = -1;
+
+    for (int it = c_begin; it < c_end; ++it) {
+        const int v = it / chunks, chunk = it - v * chunks;
+        if (v != cur_view) {
+            __syncthreads();                                   // everyone is done with the old camera and its counts
+            if (cur_view >= 0) {
+                uint32_t* dst = dhist + (size_t)cur_view * DEPTH_PASSES * RADIX;
+                for (int i = tid; i < DEPTH_PASSES * RADIX; i += 256) {
+                    const uint32_t c = s_dh[i];
+                    if (c) { atomicAdd(&dst[i], c); s_dh[i] = 0; }
+                }
+            }
+            const uint32_t* src = reinterpret_cast<const uint32_t*>(cams + v);
+            uint32_t* dstc = reinterpret_cast<uint32_t*>(&cam);
+            for (int i = tid; i < (int)(sizeof(CamDev) / 4); i += 256) dstc[i] = src[i];
+            cur_view = v;
+            __syncthreads();
+        }
+#pragma unroll 1
+        for (int sub = 0; sub < PP_CHUNK / 256; ++sub) {
+            const int g = chunk * PP_CHUNK + sub * 256 + tid;
+            const bool live = g < P;
+            const size_t idx = (size_t)v * P + (live ? g : 0);
+
+            int radius = 0;
+            ushort4 rect = make_ushort4(0, 0, 0, 0);
+            uint32_t depth_key = 0xffffffffu;      // culled Gaussians sort behind every visible one of their view
+
+            const float x = live ? means3D[3 * g] : 0.0f, y = live ? means3D[3 * g + 1] : 0.0f,
+                        z = live ? means3D[3 * g + 2] : 0.0f;
+            const float depth = live ? xform_row(cam.view, 2, x, y, z) : 0.0f;          // p_view.z, auxiliary.h:156
+            if (depth > 0.0f) {                                           // near cull: z <= 0 (auxiliary.h:158)
+                const float hx = xform_row(cam.proj, 0, x, y, z);
+                const float hy = xform_row(cam.proj, 1, x, y, z);
+                const float hw = xform_row(cam.proj, 3, x, y, z);
+                const float pw = __frcp_rn(__fadd_rn(hw, 0.0000001f));
+                const float ndc_x = __fmul_rn(hx, pw), ndc_y = __fmul_rn(hy, pw);
+
+                float cv[6];
+                if (cov3D_precomp != nullptr) {
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) cv[i] = cov3D_precomp[6 * (size_t)g + i];
+                } else {
+                    const float3 sc = make_float3(scales[3 * g], scales[3 * g + 1], scales[3 * g + 2]);
+                    const float4 q = reinterpret_cast<const float4*>(rotations)[g];
+                    cov3d_from_scale_rot(sc, cam.scale_modifier, q, cv);
+                }
+                Cov2DInter ci;
+                cov2d(cam, x, y, z, cv, ci);
+                const float det = __fmaf_rn(ci.a, ci.c, -__fmul_rn(ci.b, ci.b));   // a*c - b*b as the reference SASS has it
+                if (det != 0.0f) {
+                    const float det_inv = __frcp_rn(det);
+                    const float conic_x = __fmul_rn(ci.c, det_inv);
+                    const float conic_y = __fmul_rn(det_inv, -ci.b);
+                    const float conic_z = __fmul_rn(ci.a, det_inv);
+                    const float mid = __fmul_rn(__fadd_rn(ci.a, ci.c), 0.5f);
+                    const float sq = __fsqrt_rn(fmaxf(__fmaf_rn(mid, mid, -det), 0.1f));
+                    const float lam = fmaxf(__fadd_rn(mid, sq), __fsub_rn(mid, sq));
+                    const float my_radius = ceilf(__fmul_rn(__fsqrt_rn(lam), 3.0f));
+                    const float2 pix = make_float2(ndc2pix(ndc_x, cam.width), ndc2pix(ndc_y, cam.height));
+                    const int r_i = (int)my_radius;
+                    uint2 mn, mx;
+                    tile_rect(pix, r_i, tiles_x, tiles_y, mn, mx);
+                    mn.y = max(mn.y, (uint32_t)cam.row_begin);           // band of tile rows rendered by this call
+                    mx.y = max(min(mx.y, (uint32_t)cam.row_end), mn.y);
+                    const uint32_t area = (mx.x - mn.x) * (mx.y - mn.y);
+                    if (area != 0) {
+                        if (sh != nullptr) {
+                            bool cl[3];
+                            const float3 c = eval_sh_pinned(cam.sh_degree, sh_coeffs, sh + (size_t)g * sh_coeffs * 3,
+                                                            make_float3(x, y, z), cam.campos, cl);
+                            reinterpret_cast<float4*>(rgb)[idx] = make_float4(c.x, c.y, c.z, 0.0f);
+                            clamped[3 * idx] = cl[0];
+                            clamped[3 * idx + 1] = cl[1];
+                            clamped[3 * idx + 2] = cl[2];
+                        }
+                        const float op = opacities[g];
+                        geomrec[2 * idx] = make_float4(pix.x, pix.y, conic_x, conic_y);          // the blend kernels' recA
+                        geomrec[2 * idx + 1] = make_float4(conic_z, op, depth, blend_skip_threshold(op));   // ... and recB
+                        radius = r_i;
+                        rect = make_ushort4((unsigned short)mn.x, (unsigned short)mn.y, (unsigned short)mx.x,
+                                            (unsigned short)mx.y);
+                        depth_key = __float_as_uint(depth);
+                        tiles_acc += area;
+                    }
+                }
+            }
+            else if (live && cam.prefiltered) {
+                // in_frustum with prefiltered = true (auxiliary.h:160-167): the reference prints and traps; here the flag
+                // comes back through gsr_read_counters and the host raises
+                counters[CNT_PREFILTER] = 1u;
+            }
+            if (live) {
+                radii[idx] = radius;
+                if (radii_out) radii_out[idx] = radius;
+                rects[idx] = rect;
+                dkeys[idx] = depth_key;            // sorted per view (segmented sort), so the key is the depth alone; the
+                dvals[idx] = (uint32_t)g;          // sort's first pass drops the culled ones (key 0xffffffff)
+            }
+            // digit counts of the kept keys.  The three low digits are spread (mantissa bits): plain shared atomics.  The
+            // top digit (sign + 7 exponent bits) takes a handful of values per view: one atomic per distinct value per warp.
+            const bool kept = depth_key != 0xffffffffu;
+            if (kept) {
+                atomicAdd(&s_dh[0 * RADIX + (depth_key & 0xffu)], 1u);
+                atomicAdd(&s_dh[1 * RADIX + ((depth_key >> 8) & 0xffu)], 1u);
+                atomicAdd(&s_dh[2 * RADIX + ((depth_key >> 16) & 0xffu)], 1u);
+            }
+            uint32_t todo = __ballot_sync(0xffffffffu, kept);
+            const uint32_t top = depth_key >> 24;
+            for (int round = 0; todo != 0u && round < 4; ++round) {
+                const uint32_t lead = __shfl_sync(0xffffffffu, top, __ffs(todo) - 1);
+                const uint32_t same = __ballot_sync(0xffffffffu, kept && top == lead) & todo;
+                if (lane == __ffs(todo) - 1) atomicAdd(&s_dh[3 * RADIX + lead], (uint32_t)__popc(same));
+                todo &= ~same;
+            }
+            if ((todo >> lane) & 1u) atomicAdd(&s_dh[3 * RADIX + top], 1u);
+        }
     }
     __syncthreads();
-    const int g = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool live = g < P;
-    const size_t idx = (size_t)v * P + (live ? g : 0);
-
-    int radius = 0;
-    ushort4 rect = make_ushort4(0, 0, 0, 0);
-    uint32_t depth_key = 0xffffffffu;      // culled Gaussians sort behind every visible one of their view
-
-    const float x = live ? means3D[3 * g] : 0.0f, y = live ? means3D[3 * g + 1] : 0.0f, z = live ? means3D[3 * g + 2] : 0.0f;
-    const float depth = live ? xform_row(cam.view, 2, x, y, z) : 0.0f;          // p_view.z, auxiliary.h:156
-    if (depth > 0.0f) {                                           // near cull: z <= 0 (auxiliary.h:158)
-        const float hx = xform_row(cam.proj, 0, x, y, z);
-        const float hy = xform_row(cam.proj, 1, x, y, z);
-        const float hw = xform_row(cam.proj, 3, x, y, z);
-        const float pw = __frcp_rn(__fadd_rn(hw, 0.0000001f));
-        const float ndc_x = __fmul_rn(hx, pw), ndc_y = __fmul_rn(hy, pw);
-
-        float cv[6];
-        if (cov3D_precomp != nullptr) {
-#pragma unroll
-            for (int i = 0; i < 6; ++i) cv[i] = cov3D_precomp[6 * (size_t)g + i];
-        } else {
-            const float3 s = make_float3(scales[3 * g], scales[3 * g + 1], scales[3 * g + 2]);
-            const float4 q = reinterpret_cast<const float4*>(rotations)[g];
-            cov3d_from_scale_rot(s, cam.scale_modifier, q, cv);
+    if (cur_view >= 0) {
+        uint32_t* dst = dhist + (size_t)cur_view * DEPTH_PASSES * RADIX;
+        for (int i = tid; i < DEPTH_PASSES * RADIX; i += 256) {
+            const uint32_t c = s_dh[i];
+            if (c) atomicAdd(&dst[i], c);
         }
-        Cov2DInter ci;
-        cov2d(cam, x, y, z, cv, ci);
-        const float det = __fmaf_rn(ci.a, ci.c, -__fmul_rn(ci.b, ci.b));   // a*c - b*b as the reference SASS has it
-        if (det != 0.0f) {
-            const float det_inv = __frcp_rn(det);
-            const float conic_x = __fmul_rn(ci.c, det_inv);
-            const float conic_y = __fmul_rn(det_inv, -ci.b);
-            const float conic_z = __fmul_rn(ci.a, det_inv);
-            const float mid = __fmul_rn(__fadd_rn(ci.a, ci.c), 0.5f);
-            const float sq = __fsqrt_rn(fmaxf(__fmaf_rn(mid, mid, -det), 0.1f));
-            const float lam = fmaxf(__fadd_rn(mid, sq), __fsub_rn(mid, sq));
-            const float my_radius = ceilf(__fmul_rn(__fsqrt_rn(lam), 3.0f));
-            const float2 pix = make_float2(ndc2pix(ndc_x, cam.width), ndc2pix(ndc_y, cam.height));
-            const int r_i = (int)my_radius;
-            uint2 mn, mx;
-            tile_rect(pix, r_i, tiles_x, tiles_y, mn, mx);
-            mn.y = max(mn.y, (uint32_t)cam.row_begin);           // band of tile rows rendered by this call
-            mx.y = max(min(mx.y, (uint32_t)cam.row_end), mn.y);
-            const uint32_t area = (mx.x - mn.x) * (mx.y - mn.y);
-            if (area != 0) {
-                if (sh != nullptr) {
-                    bool cl[3];
-                    const float3 c = eval_sh_pinned(cam.sh_degree, sh_coeffs, sh + (size_t)g * sh_coeffs * 3,
-                                                    make_float3(x, y, z), cam.campos, cl);
-                    reinterpret_cast<float4*>(rgb)[idx] = make_float4(c.x, c.y, c.z, 0.0f);
-                    clamped[3 * idx] = cl[0];
-                    clamped[3 * idx + 1] = cl[1];
-                    clamped[3 * idx + 2] = cl[2];
-                }
-                const float op = opacities[g];
-                geomrec[2 * idx] = make_float4(pix.x, pix.y, conic_x, conic_y);          // the blend kernels' recA
-                geomrec[2 * idx + 1] = make_float4(conic_z, op, depth, blend_skip_threshold(op));   // ... and recB
-                radius = r_i;
-                rect = make_ushort4((unsigned short)mn.x, (unsigned short)mn.y, (unsigned short)mx.x, (unsigned short)mx.y);
-                depth_key = __float_as_uint(depth);
-            }
-        }
-    }
-    else if (live && cam.prefiltered) {
-        // in_frustum with prefiltered = true (auxiliary.h:160-167): the reference prints and traps; here the flag comes
-        // back through gsr_read_counters and the host raises
-        counters[CNT_PREFILTER] = 1u;
-    }
-    if (live) {
-        radii[idx] = radius;
-        if (radii_out) radii_out[idx] = radius;
-        rects[idx] = rect;
-        dkeys[idx] = depth_key;            // sorted per view (segmented sort), so the key is the depth alone; the sort's
-        dvals[idx] = (uint32_t)g;          // first pass drops the culled ones (key 0xffffffff)
     }
     // the batch's (Gaussian, tile) instance count -- what the reference returns as num_rendered (rasterizer_impl.cu:285-287):
     // one atomic per CTA
-    uint32_t tiles = (uint32_t)(rect.z - rect.x) * (uint32_t)(rect.w - rect.y);
-    tiles = __reduce_add_sync(0xffffffffu, tiles);
-    if ((threadIdx.x & 31) == 0) s_tiles[threadIdx.x >> 5] = tiles;
+    const uint32_t tiles = __reduce_add_sync(0xffffffffu, tiles_acc);
+    if (lane == 0) s_tiles[tid >> 5] = tiles;
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (tid == 0) {
         uint32_t t = 0;
 #pragma unroll
         for (int w = 0; w < 8; ++w) t += s_tiles[w];
@@ -217,12 +281,20 @@ int launch_preprocess(const CamDev* cams, int V, int P, int sh_coeffs, const flo
                       const float* scales, const float* rotations, const float* cov3D_precomp, const float* sh,
                       void* ws, const Layout& L, int32_t* radii_out, cudaStream_t s) {
     if (P == 0 || V == 0) return GSR_OK;
-    dim3 grid((P + 255) / 256, V);
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        GSR_CUDA_TRY(cudaGetDevice(&dev));
+        GSR_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    }
+    const long long items = (long long)V * ((P + PP_CHUNK - 1) / PP_CHUNK);
+    const long long full = (long long)sms * PP_CTAS_PER_SM;
+    const int grid = (int)(items < full ? items : full);
     preprocess_kernel<<<grid, 256, 0, s>>>(
-        cams, P, sh_coeffs, means3D, opacities, scales, rotations, cov3D_precomp, sh, L.tiles_x, L.tiles_y,
+        cams, V, P, sh_coeffs, means3D, opacities, scales, rotations, cov3D_precomp, sh, L.tiles_x, L.tiles_y,
         at<int32_t>(ws, L.radii), at<ushort4>(ws, L.rects), at<float4>(ws, L.geomrec), at<float>(ws, L.rgb),
         at<uint8_t>(ws, L.clamped), at<uint32_t>(ws, L.dkeys0), at<uint32_t>(ws, L.dvals0), radii_out,
-        at<uint32_t>(ws, L.counters));
+        at<uint32_t>(ws, L.counters), at<uint32_t>(ws, L.dhist));
     GSR_LAUNCH_CHECK();
     return GSR_OK;
 }

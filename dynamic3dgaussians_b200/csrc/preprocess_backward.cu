@@ -374,7 +374,10 @@ int launch_preprocess_backward(int V, int P, int W, int H, int channels, int sh_
     const uint8_t* cl = at<uint8_t>(gws, L.clamped);
     const float* rec = at<float>(gws, L.grad_rec);
     const bool split = sh == nullptr;                    // see the kernel: TPG threads per Gaussian unless SH
-    constexpr int TPG = 4;
+#ifndef GSR_PB_TPG
+#define GSR_PB_TPG 1      // measured at C2 on B200: 1 thread per Gaussian 0.195 ms, 4 threads 0.215 ms
+#endif
+    constexpr int TPG = GSR_PB_TPG;
     const int blocks = split ? (int)(((size_t)P * TPG + 255) / 256) : (P + 255) / 256;
 #define GSR_PB(NCH_, TPG_)                                                                                            \
     preprocess_backward_kernel<NCH_, TPG_><<<blocks, 256, 0, s>>>(cams, V, P, sh_coeffs, means3D, scales, rotations,  \

@@ -318,7 +318,8 @@ int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1,
                      uint32_t* tile_counters, cudaStream_t s, int segments, bool hist_ready, bool scratch_zeroed,
                      uint32_t* n_kept_dev) {
     if (n_max <= 0 || end_bit <= begin_bit || segments <= 0) return GSR_OK;
-    if (n_kept_dev && (hist_ready || n_dev)) return GSR_ERR_INVALID_ARGUMENT;
+    if (n_kept_dev && n_dev) return GSR_ERR_INVALID_ARGUMENT;      // (hist_ready + n_kept_dev: the given histograms must
+                                                                    //  count the non-sentinel keys only)
     if (n_max >= (int64_t)VALUE_MASK) return GSR_ERR_UNSUPPORTED;
     if (segments > 65535) return GSR_ERR_UNSUPPORTED;
     const int passes = (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS;
