@@ -42,6 +42,9 @@ def parse():
     ap.add_argument("--rebalance", type=int, default=0, help="N>1: feedback rounds of the cost-aware partition (dist.rescale_row_costs); at C2 the tile-list model is already within the run-to-run noise of the ranks")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of one CUDA graph per step")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--exchange", default=os.environ.get("GSR_EXCHANGE", "peer"), choices=["peer", "peer-p2p", "peer-mc", "nccl"],
+                    help="N>1: sum of the gradient slab over the ranks -- the library's kernel over peer memory (P2P, or "
+                         "multimem reduce in the switch) or ncclAllReduce")
     ap.add_argument("--no-extras", action="store_true", help="skip the apples-to-apples / c4 / kNN / dyn-loss sub-lines")
     ap.add_argument("--workload", default="c2", choices=["c2", "c4", "c5"],
                     help="c2 (default, the metric's configuration: 300k Gaussians, 27 views 640x360, strong scaling); "
@@ -198,15 +201,21 @@ def build_workload(args, device):
     return sc, sets
 
 
-def kernels_per_step(L, with_allreduce: bool, views: int = 0) -> int:
-    """Launches of OUR kernels in one forward+backward (memsets/memcpys not counted)."""
-    # preprocess | depth sort (hist, scan, passes) | count + scan | emit | supertile sort (scan, passes) |
-    # st ranges, chunk table, chunk count, tile offsets, tile scan | pack colours, scatter records | blend
-    fwd = 1 + (2 + L.depth_passes) + 2 + 1 + (1 + L.tile_passes) + 5 + 2 + 1
-    bwd = 1 + 1
+def kernels_per_step(L, with_exchange: bool, views: int = 0) -> int:
+    """Launches of OUR kernels in one forward+backward (memsets / memcpys and NCCL's own kernels not counted); the names
+    are those of the committed ncu launch list (profiles/r02_launches_c2.txt)."""
+    fwd = (-(-max(views, 1) // 16)      # store_cams_kernel: 16 cameras per launch, as kernel arguments
+           + 1                          # preprocess_kernel (also takes the depth sort's digit histograms)
+           + 1 + L.depth_passes         # radix_scan_hist_kernel + onesweep_pass_kernel per depth digit
+           + 3                          # st_count_reduce_kernel, block_sums_scan_kernel, emit_st_instances_kernel
+           + 2 + L.tile_passes          # sort_hist_from_keys_kernel, radix_scan_hist_kernel + onesweep passes (supertile bits)
+           + 5                          # chunk_table, chunk_count, tile_offsets, tile_scan, tile_order
+           + 2                          # pack_colors_kernel, scatter_records_kernel
+           + 1)                         # blend_forward_kernel
+    bwd = 1 + 1                         # blend_backward_kernel, preprocess_backward_kernel
     # launches of a few views (<= 148 * 8 * 4 CTAs) order the backward's CTAs by walked depth: one more kernel
     small = 0 < views * L.tiles_x * L.tiles_y <= 148 * 8 * 4
-    return fwd + bwd + (1 if small else 0)
+    return fwd + bwd + (1 if small else 0) + (1 if with_exchange else 0)      # peer_allreduce_kernel
 
 
 def fp32_peak_tflops(lib, device) -> dict:
@@ -265,7 +274,7 @@ def run_ours(args, world, rank, local):
 
     cap = [None]
     rebalance_ms = []
-    slab = D.GradSlab(P, dev)
+    slab = D.make_slab(P, dev, None, args.exchange) if world > 1 else D.GradSlab(P, dev)     # (collective when peer memory)
     local = [D.select_views(cot, mine)]       # the loss side hands each rank the cotangents of its own views
 
     def step():
@@ -326,7 +335,8 @@ def run_ours(args, world, rank, local):
     graphed = None
     if not args.no_graph:
         # the whole step (forward, backward, all-reduce) as ONE CUDA graph launch: same kernels, no host work per step
-        graphed = D.GraphedStep(sets, mine, rv, local[0], capacity=cap[0] if cap[0] is not None else 0, label=label)
+        graphed = D.GraphedStep(sets, mine, rv, local[0], capacity=cap[0] if cap[0] is not None else 0, label=label,
+                                exchange=args.exchange)
         eager_step = step
 
         def step():                                            # noqa: F811
@@ -348,6 +358,35 @@ def run_ours(args, world, rank, local):
     ms = max_over_ranks(e0.elapsed_time(e1), world)
     clocks = sampler.stop() if rank == 0 else None
 
+    exchange = None
+    if world > 1:
+        # what the exchange costs: the step's graph without it (each rank alone, max over ranks), and the exchange alone
+        # on the slab (all ranks start together, so this is its floor -- in the step it also absorbs the ranks' skew)
+        ex_slab = graphed.slab if graphed is not None else slab
+        assert not (hasattr(ex_slab, "gave_up") and ex_slab.gave_up()), "a peer never arrived inside the timed region"
+        g0 = D.GraphedStep(sets, mine, rv, local[0], capacity=cap[0] if cap[0] is not None else 0, reduce=False, label=label)
+        x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.replay()
+        barrier(world)
+        x0.record()
+        for _ in range(10):
+            g0.replay()
+        x1.record()
+        torch.cuda.synchronize()
+        no_ex = max_over_ranks(x0.elapsed_time(x1) / 10, world)
+        del g0
+        for _ in range(3):
+            ex_slab.allreduce()
+        barrier(world)
+        x0.record()
+        for _ in range(20):
+            ex_slab.allreduce()
+        x1.record()
+        torch.cuda.synchronize()
+        alone = max_over_ranks(x0.elapsed_time(x1) / 20, world)
+        exchange = {"how": ex_slab.exchange, "bytes": int(ex_slab.flat.numel() * 4),
+                    "alone_ms": round(alone, 4), "step_without_it_ms_max_over_ranks": round(no_ex, 4),
+                    "exposed_in_step_ms": round(ms / max(args.steps, 1) - no_ex, 4)}
     if graphed is not None:
         assert not graphed.overflowed(), "instance capacity exceeded inside the timed region"
         step = eager_step
@@ -374,7 +413,7 @@ def run_ours(args, world, rank, local):
         pairs = int(ncon.sum(dtype=torch.int64).item())
         R = st.num_rendered
         vis = float((st.radii > 0).float().mean().item())
-    res = dict(ms=ms, host_ms=t_host, visible=vis if st is not None else 0.0, stages=stages, pairs=pairs, R=R, R1=R1 if st is not None else 0, clocks=clocks, views_per_rank=[round(sum(1.0 if isinstance(u, int) else (u[2] - u[1]) / float((IMG_H + 15) // 16) for u in p), 2) for p in parts], parts=parts, rebalance_ms=rebalance_ms,
+    res = dict(ms=ms, host_ms=t_host, visible=vis if st is not None else 0.0, stages=stages, pairs=pairs, R=R, R1=R1 if st is not None else 0, clocks=clocks, views_per_rank=[round(sum(1.0 if isinstance(u, int) else (u[2] - u[1]) / float((IMG_H + 15) // 16) for u in p), 2) for p in parts], parts=parts, rebalance_ms=rebalance_ms, exchange=exchange,
                launches=kernels_per_step(L, world > 1, st.V) * args.steps if st is not None else 0, state=st, dev=dev,
                rv=rv, sets=sets, sc=sc, lib=lib, cot=cot)
     # correctness signal that survives sharding: the all-reduced gradient slab of the LAST (eager, stage-timed) step is the
@@ -423,7 +462,7 @@ def run_e2e(args, res, world, rank):
     nw = world if (world > 1 and tdist.is_initialized()) else 1
     drank = tdist.get_rank() if nw > 1 else 0
     n_par = sum(sizes)
-    chunk = -(-n_par // nw)
+    chunk = -(-n_par // (4 * nw)) * 4                              # whole float4s: the peer kernel's slice of a rank
     lo, hi = drank * chunk, (drank + 1) * chunk
     par_full = torch.zeros(chunk * nw)
     par_full[:n_par] = torch.cat([rv_host[k].reshape(-1).float() for k in names])
@@ -442,9 +481,20 @@ def run_e2e(args, res, world, rank):
     # host (D2H stream).  Every step still copies ITS inputs in and ITS results out inside the timed region.
     cur = torch.cuda.current_stream(dev)
     h2d_s, d2h_s = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
-    bufs = [dict(par=torch.zeros(chunk * nw, dtype=torch.float32, device=dev),
-                 tgt=torch.empty(tgt_host.shape, dtype=torch.uint8, device=dev),
-                 ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
+    # N > 1: the parameter slab is gathered and the gradient slab reduce-scattered by the library's kernel over peer
+    # memory (dist.PeerBuffer), NCCL when symmetric memory is not available or --exchange nccl
+    peer = nw > 1 and args.exchange != "nccl"
+    bufs = []
+    for _ in range(2):
+        ppar = pgrad = None
+        if peer:
+            try:
+                ppar, pgrad = D.PeerBuffer(chunk * nw, dev), D.PeerBuffer(chunk * nw, dev)
+            except Exception:                                        # noqa: BLE001 -- same outcome on every rank
+                peer, ppar, pgrad = False, None, None
+        bufs.append(dict(par=ppar.t if ppar else torch.zeros(chunk * nw, dtype=torch.float32, device=dev), ppar=ppar,
+                         pgrad=pgrad, tgt=torch.empty(tgt_host.shape, dtype=torch.uint8, device=dev),
+                         ready=torch.cuda.Event(), free=torch.cuda.Event()))
     for b in bufs:
         b["free"].record(cur)
 
@@ -457,8 +507,10 @@ def run_e2e(args, res, world, rank):
             b["ready"].record(h2d_s)
 
     def compute(b):
-        if nw > 1:
-            tdist.all_gather_into_tensor(b["par"], b["par"][lo:hi])         # in place: every rank now holds the slab
+        if b["ppar"] is not None:
+            b["ppar"].allgather()                                           # in place: every rank now holds the slab
+        elif nw > 1:
+            tdist.all_gather_into_tensor(b["par"], b["par"][lo:hi])
         m, c, o, s, r = b["leaves"]
         color, _, depth, alpha, radii = RZ.rasterize_views(my_sets, m, o, colors_precomp=c, scales=s, rotations=r,
                                                            capacity=cap_e2e, state_out=states, bands=my_bands)
@@ -468,13 +520,16 @@ def run_e2e(args, res, world, rank):
         loss = TO.l1_loss_u8(color, b["tgt"], row_weight)
         loss.backward()
         torch.cat([t.grad.reshape(-1) for t in b["leaves"]], out=b["grad"][:n_par])
-        D.allreduce_grads(b["grad"])
+        if b["pgrad"] is not None:
+            b["pgrad"].reduce_scatter()                                     # this rank reads back its own slice only
+        else:
+            D.allreduce_grads(b["grad"])
         return loss.detach().reshape(1), b["grad"][lo:hi]
 
     for b in bufs:
         # leaves share storage with the upload target
         b["leaves"] = [t.view(sh).detach().requires_grad_(True) for t, sh in zip(b["par"][:n_par].split(sizes), shapes)]
-        b["grad"] = torch.zeros_like(b["par"])
+        b["grad"] = b["pgrad"].t if b["pgrad"] is not None else torch.zeros_like(b["par"])
         b["drained"] = torch.cuda.Event()
         b["drained"].record(cur)
     if not args.no_graph:
@@ -582,7 +637,8 @@ def run_e2e(args, res, world, rank):
     return {"value": round(mpix, 2), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
             "steps": n, "ms_per_step": round(ms / n, 3), "loss_rank0": loss_value, "legs_alone_rank0": legs,
             "host_io": "bytes are job totals; parameter slab uploaded / gradient slab read back once per step "
-                       + (f"(1/{nw} per rank, all-gathered / all-reduced over NVLink)" if nw > 1 else "(one rank)")}
+                       + (f"(1/{nw} per rank; all-gather of the parameters and reduce-scatter of the gradients over NVLink by "
+                          + ("the library's peer-memory kernel)" if peer else "NCCL)") if nw > 1 else "(one rank)")}
 
 
 def run_train_loop(args, res):
@@ -906,11 +962,12 @@ def main():
         work = {
             "blend_backward": ("fp32", 80.0 * pairs), "blend_forward": ("fp32", 27.0 * pairs),
             "supertile_sort": ("hbm", 16.0 * L.tile_passes * R1),
-            "depth_sort": ("hbm", (4.0 + 16.0 * L.depth_passes) * Vl * P),
+            # first pass reads every (key, index) pair and writes the kept ones (Gaussians that touch a tile); the other
+            # passes move the kept pairs; the digit histograms come from the preprocess kernel (no extra read)
+            "depth_sort": ("hbm", (8.0 + 8.0 * res.get("visible", 1.0) + 16.0 * (L.depth_passes - 1) * res.get("visible", 1.0)) * Vl * P),
             "preprocess": ("hbm", (44.0 + 56.0 * Vl) * P), "scatter_records": ("hbm", (4.0 + 8.0 + 48.0) * R1 + 48.0 * R),
             "emit_supertile_instances": ("hbm", 12.0 * Vl * P + 8.0 * R1), "tile_offsets": ("hbm", (4.0 + 4.0 + 8.0) * R1),
             "grad_zero": ("hbm", 48.0 * Vl * P), "preprocess_backward": ("hbm", (44.0 + 56.0) * P + 68.0 * Vl * P),
-            "instance_count": ("hbm", 12.0 * Vl * P),
         }
         # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed ncu --set full
         # capture of this same command (profiles/; refreshed whenever the kernel changes) -- never measured under ncu here
@@ -964,7 +1021,8 @@ def main():
                                       else "colour+depth cotangents"),
                        "views_per_rank": res["views_per_rank"],
                        **({"rank_ms_before_each_rebalance": res["rebalance_ms"]} if res["rebalance_ms"] else {}), "parallelism": f"view-sharded dp{world}" + ("" if world == 1 or args.whole_views else " (cuts inside a view fall on tile-row bands)"),
-                       "launch": "eager" if args.no_graph else "one CUDA graph per step (forward + backward + all-reduce)",
+                       "launch": "eager" if args.no_graph else "one CUDA graph per step (forward + backward + exchange)",
+                       **({"exchange": res["exchange"]["how"]} if res.get("exchange") else {}),
                        "l2": "per-step working set (>1 GB of per-view state and instance records) exceeds the 126 MB L2",
                        "num_rendered_rank0": R, "visible_fraction_rank0": round(res.get("visible", 0.0), 4), "supertile_instances_rank0": res.get("R1", 0), "pairs_rank0": pairs},
             "clocks": res["clocks"], "e2e": e2e, "gpu_launches": res["launches"],
@@ -977,6 +1035,7 @@ def main():
                                       "what": "sum over stages of (this build's algorithmic work / measured peak) "
                                               "divided by the measured step"},
             "grad_check": res.get("grad_check"),
+            **({"exchange": res["exchange"]} if res.get("exchange") else {}),
             "host_enqueue_ms_per_step_rank0": round(res["host_ms"], 3),
             "train_it_per_s_equiv": round(V * steps / (ms * 1e-3), 1),
         }

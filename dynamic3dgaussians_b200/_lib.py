@@ -12,12 +12,18 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 # GSR_LIB_PATH: load another build of the same library (A/B runs of kernel variants; tests/gpu_ab.sh)
 LIB_PATH = os.environ.get("GSR_LIB_PATH") or os.path.join(HERE, "libgsr_b200.so")
 
+PEER_ALLREDUCE, PEER_REDUCE_SCATTER, PEER_ALLGATHER = 0, 1, 2
+PEER_MAX_WORLD = 8
+PEER_MAX_CTAS = 256
+PEER_FLAG_WORDS = 4608            # include/gsr_b200.h GSR_PEER_*
+PEER_ERROR_WORD = 2 * PEER_MAX_CTAS * PEER_MAX_WORLD + PEER_MAX_CTAS
+
 EXPORTED_SYMBOLS = [
     "gsr_abi_version", "gsr_strerror", "gsr_last_cuda_error", "gsr_set_option", "gsr_get_option",
     "gsr_workspace_sizes", "gsr_workspace_layout",
     "gsr_forward_geometry", "gsr_forward_render", "gsr_read_counters", "gsr_backward", "gsr_mark_visible",
     "gsr_export_view_binning", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_sort_pairs_static_max",
-    "gsr_sort_pairs_static", "gsr_knn_temp_bytes", "gsr_knn",
+    "gsr_sort_pairs_static", "gsr_peer_allreduce", "gsr_knn_temp_bytes", "gsr_knn",
     "gsr_dyn_losses_temp_bytes", "gsr_dyn_losses",
     "gsr_image_loss_state_bytes", "gsr_image_loss_forward", "gsr_image_loss_backward", "gsr_adam_step",
     "gsr_fp32_peak_probe", "gsr_probe_geometry", "gsr_stage_timing_enable", "gsr_stage_timing_count", "gsr_stage_name",
@@ -101,6 +107,7 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.gsr_sort_pairs_static_max.restype = i64
     lib.gsr_sort_pairs_static_max.argtypes = []
     lib.gsr_sort_pairs_static.argtypes = [i32, vp, vp, vp, vp, i64, i32, i32, vp]
+    lib.gsr_peer_allreduce.argtypes = [i32, i32, i32, vp, vp, vp, i64, i32, vp]
     lib.gsr_knn_temp_bytes.restype = sz
     lib.gsr_knn_temp_bytes.argtypes = [i64]
     lib.gsr_knn.argtypes = [i64, i32, vp, vp, vp, vp, vp, sz, vp]

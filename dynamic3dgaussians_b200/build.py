@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libgsr_b200.so")
 SOURCES = ["abi.cu", "preprocess.cu", "radix_sort.cu", "binning.cu", "blend_forward.cu", "blend_backward.cu", "blend_features.cu",
-           "preprocess_backward.cu", "knn.cu", "dyn_losses.cu", "image_loss.cu", "adam.cu", "train_glue.cu"]
+           "preprocess_backward.cu", "peer_allreduce.cu", "knn.cu", "dyn_losses.cu", "image_loss.cu", "adam.cu", "train_glue.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

@@ -622,6 +622,13 @@ int gsr_sort_pairs_static(int key_bytes, const void* keys_in, void* keys_out, co
                           SORT_STATIC_BYTES, stream);
 }
 
+int gsr_peer_allreduce(int mode, int world, int rank, const void* const* bufs, const void* const* flags,
+                       void* multicast_buf, int64_t n_floats, int blocks, gsr_stream_t stream) {
+    if (!bufs || !flags) return GSR_ERR_INVALID_ARGUMENT;
+    if (n_floats == 0) return GSR_OK;
+    return launch_peer_allreduce(mode, world, rank, bufs, flags, multicast_buf, n_floats, blocks, (cudaStream_t)stream);
+}
+
 int gsr_stage_timing_enable(int on) {
     if (on && !g_ev_made) {
         for (int i = 0; i < ST_COUNT; ++i)

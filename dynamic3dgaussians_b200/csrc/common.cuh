@@ -58,7 +58,10 @@ constexpr int SORT_THREADS = 256;
 constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
 template <typename KeyT> struct SortCfg;
-template <> struct SortCfg<uint32_t> { static constexpr int ITEMS = 16; };
+#ifndef GSR_SORT_ITEMS32
+#define GSR_SORT_ITEMS32 16
+#endif
+template <> struct SortCfg<uint32_t> { static constexpr int ITEMS = GSR_SORT_ITEMS32; };
 template <> struct SortCfg<uint64_t> { static constexpr int ITEMS = 12; };
 template <typename KeyT> constexpr int sort_tile() { return SORT_THREADS * SortCfg<KeyT>::ITEMS; }
 constexpr int MAX_PASSES = 8;
@@ -231,6 +234,8 @@ int launch_preprocess(const CamDev* cams, int V, int P, int sh_coeffs,
                       const float* means3D, const float* opacities, const float* scales, const float* rotations,
                       const float* cov3D_precomp, const float* sh, void* geom_ws, const Layout& L,
                       int32_t* radii_out, cudaStream_t s);   // sets counters[CNT_PREFILTER] (see preprocess.cu)
+int launch_peer_allreduce(int mode, int world, int rank, const void* const* bufs_host, const void* const* flags_host,
+                          void* multicast_buf, int64_t n_floats, int blocks, cudaStream_t s);
 int launch_mark_visible(const float* view, int P, const float* means3D, uint8_t* present, cudaStream_t s);
 
 template <typename KeyT>

@@ -131,9 +131,11 @@ class GradSlab:
 
     WIDTHS = dict(means3D=3, colors=3, opacity=1, scales=3, rotations=4)
 
-    def __init__(self, P: int, device):
+    exchange = "nccl all_reduce"
+
+    def __init__(self, P: int, device, flat: Optional[torch.Tensor] = None):
         self.P = P
-        self.flat = torch.zeros(P * GRAD_WIDTH, dtype=torch.float32, device=device)
+        self.flat = torch.zeros(P * GRAD_WIDTH, dtype=torch.float32, device=device) if flat is None else flat
         self.views = {}
         o = 0
         for k in GRAD_KEYS:
@@ -144,6 +146,119 @@ class GradSlab:
     def as_rows(self) -> torch.Tensor:
         """[P,14] copy in the pack_grads() column order (for callers that want one row per Gaussian)."""
         return torch.cat([self.views[k] for k in GRAD_KEYS], dim=1)
+
+
+    def allreduce(self, group=None):
+        """Sum over the ranks, in place (NCCL on GPUs, gloo in the CPU tests; PeerSlab: one kernel over peer memory)."""
+        return allreduce_grads(self.flat, group)
+
+
+class PeerBuffer:
+    """A float32 buffer in SYMMETRIC memory (torch.distributed._symmetric_memory: the same allocation on every rank of
+    one NVSwitch node, each mapped into every process) plus the flag block of the library's peer kernel
+    (gsr_peer_allreduce, csrc/peer_allreduce.cu), which sums / scatters / gathers it by loading from and storing to the
+    peers' copies over NVLink: one kernel, no staging copies, capturable in a CUDA graph.  torch only allocates the memory
+    and exchanges the mappings.  Construction is collective (every rank of `group`, same size, same order); so is every
+    call.  `multicast`: all-reduce in the switch (multimem.ld_reduce / multimem.st on the NVLS mapping) when it exists;
+    None = GSR_PEER_MULTICAST if set, else on from 8 ranks up (where it measured faster)."""
+
+    def __init__(self, n_floats: int, device, group=None, multicast: Optional[bool] = None, blocks: int = 0):
+        import ctypes as C
+        import os
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        from . import _lib
+        group = group if group is not None else dist.group.WORLD
+        self.n = int(n_floats)
+        self.n_pad = (self.n + 3) // 4 * 4
+        self._buf = symm.empty(self.n_pad, dtype=torch.float32, device=device)
+        self._flags = symm.empty(_lib.PEER_FLAG_WORDS, dtype=torch.int32, device=device)
+        self._buf.zero_()
+        self._flags.zero_()
+        hb = symm.rendezvous(self._buf, group)
+        hf = symm.rendezvous(self._flags, group)
+        self.world, self.rank = int(hb.world_size), int(hb.rank)
+        if self.world > _lib.PEER_MAX_WORLD:
+            raise RuntimeError(f"PeerBuffer: {self.world} ranks, the kernel handles {_lib.PEER_MAX_WORLD}")
+        self._bufs = (C.c_void_p * self.world)(*[int(x) for x in hb.buffer_ptrs])
+        self._flagps = (C.c_void_p * self.world)(*[int(x) for x in hf.buffer_ptrs])
+        if multicast is None:
+            # measured (tests/gpu_peer_check.py, 16.8 MB): 8 GPUs multimem 57 us / P2P 67 us / NCCL 97 us;
+            # 2 GPUs P2P 37 us / multimem 60 us / NCCL 55 us
+            env = os.environ.get("GSR_PEER_MULTICAST")
+            multicast = (env == "1") if env in ("0", "1") else self.world >= 8
+        mc = int(getattr(hb, "multicast_ptr", 0) or 0)
+        self._mc = mc if (multicast and mc) else 0
+        self._handles = (hb, hf)                     # keep the mappings alive
+        self.blocks = int(blocks)
+        self.device = self._buf.device
+        self.t = self._buf[:self.n]
+        self.slice_floats = -(-(self.n_pad // 4) // self.world) * 4      # rank r owns [r * slice_floats, (r+1) * ...)
+        self.how = ("one kernel over peer memory (gsr_peer_allreduce" +
+                    (", multimem reduce in the switch)" if self._mc else ", P2P loads / stores over NVLink)"))
+        torch.cuda.synchronize(device)
+        dist.barrier(group)                          # every rank's flag block is zero before anyone's first call
+
+    def _run(self, mode: int, mc: int = 0):
+        from . import _lib
+        lib = _lib.load()
+        _lib.check(lib.gsr_peer_allreduce(mode, self.world, self.rank, self._bufs, self._flagps, mc or None, self.n_pad,
+                                          self.blocks, torch.cuda.current_stream(self.device).cuda_stream),
+                   "gsr_peer_allreduce")
+
+    def allreduce(self):
+        from . import _lib
+        self._run(_lib.PEER_ALLREDUCE, self._mc)
+
+    def reduce_scatter(self):
+        """Rank r's slice [r * slice_floats, (r + 1) * slice_floats) becomes the sum over the ranks; the rest is untouched."""
+        from . import _lib
+        self._run(_lib.PEER_REDUCE_SCATTER)
+
+    def allgather(self):
+        """Rank r's slice goes to every peer's buffer."""
+        from . import _lib
+        self._run(_lib.PEER_ALLGATHER)
+
+    def gave_up(self) -> bool:
+        """True if a wait inside the kernel timed out (a peer never made its call); synchronises."""
+        from . import _lib
+        return bool(int(self._flags[_lib.PEER_ERROR_WORD].item()))
+
+
+class PeerSlab(GradSlab):
+    """GradSlab in a PeerBuffer: the backward kernels write the gradients straight into symmetric memory and the sum over
+    the ranks is the library's peer kernel instead of an ncclAllReduce."""
+
+    def __init__(self, P: int, device, group=None, multicast: Optional[bool] = None, blocks: int = 0):
+        self.peer = PeerBuffer(P * GRAD_WIDTH, device, group, multicast, blocks)
+        self.exchange = self.peer.how
+        super().__init__(P, device, flat=self.peer.t)
+
+    def allreduce(self, group=None):
+        self.peer.allreduce()
+
+    def gave_up(self) -> bool:
+        return self.peer.gave_up()
+
+
+def make_slab(P: int, device, group=None, exchange: Optional[str] = None) -> GradSlab:
+    """The gradient slab for a sharded step: PeerSlab on the GPUs of one node (world > 1, NCCL backend), GradSlab
+    otherwise.  exchange: "peer" (P2P or multimem by world size) | "peer-p2p" | "peer-mc" | "nccl"; None reads GSR_EXCHANGE (default "peer").  If symmetric memory
+    cannot be set up, the reason is kept in the returned GradSlab's `exchange` string and NCCL does the sum."""
+    import os
+    import torch.distributed as dist
+    exchange = exchange or os.environ.get("GSR_EXCHANGE", "peer")
+    dev = torch.device(device)
+    if (exchange == "nccl" or dev.type != "cuda" or not dist.is_initialized() or dist.get_world_size(group) == 1
+            or dist.get_backend(group) != "nccl"):
+        return GradSlab(P, device)
+    try:
+        return PeerSlab(P, device, group, multicast={"peer-mc": True, "peer-p2p": False}.get(exchange))
+    except Exception as e:                          # noqa: BLE001 -- any failure to map peer memory: NCCL still works
+        slab = GradSlab(P, device)
+        slab.exchange = f"nccl all_reduce (symmetric memory unavailable: {type(e).__name__}: {str(e)[:200]})"
+        return slab
 
 
 def allreduce_grads(slab: torch.Tensor, group=None, async_op: bool = False):
@@ -205,7 +320,7 @@ def sharded_step(settings, my_views: Sequence, params: dict, cotangents: dict, g
         out = None
         slab.flat.zero_()
     if reduce:
-        allreduce_grads(slab.flat, group)
+        slab.allreduce(group)
     return out, slab
 
 
@@ -219,12 +334,16 @@ class GraphedStep:
       * `capacity` must be given (a graph cannot size its workspaces from a device-side count); `overflowed()` tells
         after a replay whether the instance count exceeded it;
       * outputs (`self.out`, the tuple of forward_views) and the gradient slab (`self.slab`) are overwritten by every
-        replay.  The all-reduce over `group` is part of the graph (NCCL collectives are capturable)."""
+        replay.  The sum over `group` is part of the graph: one kernel over peer memory (PeerSlab), or the NCCL
+        all-reduce where symmetric memory is not available (NCCL collectives are capturable too)."""
 
     def __init__(self, settings, my_views: Sequence, params: dict, cotangents: dict, capacity: int, group=None,
-                 warmup: int = 2, reduce: bool = True, label: Optional[torch.Tensor] = None):
+                 warmup: int = 2, reduce: bool = True, label: Optional[torch.Tensor] = None,
+                 exchange: Optional[str] = None):
         dev = params["means3D"].device
-        self.slab = GradSlab(params["means3D"].shape[0], dev)
+        # (a collective when the slab is peer memory: every rank builds its GraphedStep at the same point)
+        self.slab = make_slab(params["means3D"].shape[0], dev, group, exchange) if reduce else \
+            GradSlab(params["means3D"].shape[0], dev)
         self.out = None
         args = (settings, list(my_views), params, cotangents)
         kw = dict(group=group, capacity=int(capacity), slab=self.slab, local_cotangents=True, reduce=reduce, label=label)

@@ -219,6 +219,30 @@ int gsr_sort_pairs_static(int key_bytes, const void* keys_in, void* keys_out, co
                           uint32_t* vals_out, int64_t n, int begin_bit, int end_bit, gsr_stream_t stream);
 
 /*
+ * Sum of a float32 buffer over the ranks of one NVSwitch node, as ONE kernel over peer memory: the exchange step of the
+ * view-sharded path (per-Gaussian gradient slab).  The reference is single-GPU (REF/train.py trains
+ * on one device), so there is no reference interface behind this one; it takes the place of the ncclAllReduce call of
+ * round 1.  bufs[p] / flags[p] (HOST arrays of `world` DEVICE pointers) are rank p's buffer and flag block as mapped into
+ * THIS process (symmetric memory: every rank allocates the same sizes and the mappings are exchanged by the host side,
+ * dynamic3dgaussians_b200/dist.py PeerSlab).  A flag block is GSR_PEER_FLAG_WORDS uint32, zeroed once before the first
+ * call on any rank.  multicast_buf (nullable): the multicast (NVLS) mapping of the same buffers; when given, the
+ * reduction happens in the switch (multimem.ld_reduce / multimem.st).  n_floats: a multiple of 4; buffers 16-byte aligned.
+ * Every rank must make the call, with the same n_floats and blocks (<= GSR_PEER_MAX_CTAS; 0 = default), once per step and
+ * in the same order; the sum lands in every rank's buffer, bit-identical on all ranks.  Stream-ordered, capturable
+ * into a CUDA graph (the flag words are epoch counters kept on the device).  A peer that never arrives is given up on
+ * after ~4 s: word GSR_PEER_ERROR_WORD of the local flag block is then 1.
+ */
+#define GSR_PEER_MAX_WORLD 8
+#define GSR_PEER_MAX_CTAS 256
+#define GSR_PEER_FLAG_WORDS 4608
+#define GSR_PEER_ERROR_WORD (2 * GSR_PEER_MAX_CTAS * GSR_PEER_MAX_WORLD + GSR_PEER_MAX_CTAS)
+#define GSR_PEER_ALLREDUCE 0       /* the sum lands in every rank's buffer */
+#define GSR_PEER_REDUCE_SCATTER 1  /* rank r's buffer gets the sum of slice r only (slices: ceil(n_floats/4/world) float4s) */
+#define GSR_PEER_ALLGATHER 2       /* slice r of rank r's buffer is copied into slice r of every peer's buffer */
+int gsr_peer_allreduce(int mode, int world, int rank, const void* const* bufs, const void* const* flags,
+                       void* multicast_buf, int64_t n_floats, int blocks, gsr_stream_t stream);
+
+/*
  * k-nearest-neighbour search (replaces SimpleKNN::knn, K/simple_knn.cu:192-228; K = 3 is distCUDA2).
  *   mean_dist2 [P]  mean of the squared distances to the K nearest other points
  *   idx        [P][K] int32 their indices (ascending distance);  dist2 [P][K] (nullable) the squared distances

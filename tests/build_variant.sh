@@ -5,7 +5,7 @@ set -e
 cd "$(dirname "$0")/../dynamic3dgaussians_b200"
 name=$1; shift
 mkdir -p variants build_$name
-for f in abi preprocess radix_sort binning blend_forward blend_backward blend_features preprocess_backward knn dyn_losses image_loss adam train_glue; do
+for f in abi preprocess radix_sort binning blend_forward blend_backward blend_features preprocess_backward peer_allreduce knn dyn_losses image_loss adam train_glue; do
   nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC --expt-relaxed-constexpr "$@" -c csrc/$f.cu -o build_$name/$f.o &
 done
 wait
