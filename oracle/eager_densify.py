@@ -3,7 +3,9 @@
 Follows REF/external.py:244-292 literally -- clone (cat), split (cat, shrink), remove the split parents, prune by
 opacity / size -- each as its own torch.cat / boolean-mask round like `cat_params_to_optimizer` (:159-183) and
 `remove_points` (:186-208) do, with the Adam moments carried along (zeros for new rows).  The Gaussian noise of the split
-(:264-266) is injected by the caller so that results are comparable.  Only tests/ may import this file."""
+(:264-266) is injected by the caller so that results are comparable.  Pinned against the reference's own densify() run
+on a seeded scene with its Adam optimizer (tests/golden/ref_python_fixtures.npz, tests/test_ref_fixtures.py: same rows,
+order, values and moments).  Only tests/ may import this file."""
 import torch
 
 KEYS = ('means3D', 'rgb_colors', 'seg_colors', 'unnorm_rotations', 'logit_opacities', 'log_scales')

@@ -1,7 +1,9 @@
 """TEST INFRASTRUCTURE ONLY.  PyTorch-eager CPU restatement of the rigidity / rotation / isometry losses, line by line
 from REF/train.py:253-273 with the helpers of REF/helpers.py:118-133 (weighted_l2_loss_v1/_v2, quat_mult) and
-REF/external.py:61-78 (build_rotation); gradients by autograd.  The reference ships no test or fixture for this code
-("parity unpinned" by the reference); tests pin it with float64 finite differences."""
+REF/external.py:61-78 (build_rotation); gradients by autograd.  The reference ships no test or fixture for this code, so
+it is pinned against the reference's OWN Python run on seeded inputs: tests/golden/ref_python_fixtures.npz (written by
+tests/golden/make_ref_fixtures.py, which imports REF/helpers.py and REF/external.py unmodified and exec's the functions of
+REF/train.py) -- values and gradients <= 1e-6 / 1e-5 (tests/test_ref_fixtures.py) -- and with float64 finite differences."""
 import torch
 
 

@@ -3,7 +3,9 @@
 Follows REF/helpers.py l1_loss_v1 (`torch.abs(x - y).mean()`), REF/external.py:90-97 (gaussian / create_window: the
 1-D window is built with math.exp in double precision, stored as float32, normalised, and the 2-D window is its outer
 product) and REF/external.py:112-133 (_ssim: five grouped conv2d with zero padding window//2, c1 = 0.01^2, c2 = 0.03^2,
-mean over everything), and REF/train.py:183 for the 0.8 / 0.2 mix.  Only tests/ and bench.py may import this file."""
+mean over everything), and REF/train.py:183 for the 0.8 / 0.2 mix.  Pinned against the reference's own calc_ssim /
+l1_loss_v1 run on seeded images (tests/golden/ref_python_fixtures.npz, tests/test_ref_fixtures.py, <= 1e-6 incl. the
+gradient).  Only tests/ and bench.py may import this file."""
 from math import exp
 
 import torch
