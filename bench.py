@@ -205,7 +205,7 @@ def kernels_per_step(L, with_exchange: bool, views: int = 0) -> int:
     """Launches of OUR kernels in one forward+backward (memsets / memcpys and NCCL's own kernels not counted); the names
     are those of the committed ncu launch list (profiles/r02_launches_c2.txt)."""
     fwd = (-(-max(views, 1) // 16)      # store_cams_kernel: 16 cameras per launch, as kernel arguments
-           + 1                          # preprocess_kernel (also takes the depth sort's digit histograms)
+           + 2                          # gaussian_static_kernel, preprocess_kernel (also takes the depth sort's digit histograms)
            + 1 + L.depth_passes         # radix_scan_hist_kernel + onesweep_pass_kernel per depth digit
            + 3                          # st_count_reduce_kernel, block_sums_scan_kernel, emit_st_instances_kernel
            + 2 + L.tile_passes          # sort_hist_from_keys_kernel, radix_scan_hist_kernel + onesweep passes (supertile bits)

@@ -204,6 +204,7 @@ static int* option_slot(const char* key) {
     if (!strcmp(key, "blend_ilp")) return &g_options.blend_ilp;
     if (!strcmp(key, "bwd_cost_order")) return &g_options.bwd_cost_order;
     if (!strcmp(key, "nvtx")) return &g_options.nvtx;
+    if (!strcmp(key, "pdl")) return &g_options.pdl;
     return nullptr;
 }
 
@@ -300,7 +301,7 @@ int gsr_forward_geometry(const GsrCamera* cams_host, int V, int P, int channels,
     {
         StageScope sc(ST_PREPROCESS, s);
         rc = launch_preprocess(at<CamDev>(geom_ws, L.cams), V, P, sh_coeffs, means3D, opacities, scales, rotations,
-                               cov3D_precomp, sh, geom_ws, L, radii, s);
+                               cov3D_precomp, sh, cams_host[0].scale_modifier, geom_ws, L, radii, s);
     }
     if (rc) return rc;
     {

@@ -110,6 +110,8 @@ constexpr int EMIT_WINDOW = 2048;        // staged outputs per round (a CTA of 1
 __global__ void __launch_bounds__(SCAN_BLOCK)
 st_count_reduce_kernel(uint32_t VP, int P, const uint32_t* __restrict__ sorted_g, const ushort4* __restrict__ rects,
                        const uint32_t* __restrict__ vis_count, uint32_t* __restrict__ block_sums) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
     const uint32_t base = blockIdx.x * EMIT_TILE + threadIdx.x * EMIT_ITEMS;
     uint32_t sum = 0, gidx;
@@ -150,6 +152,8 @@ __device__ __forceinline__ uint32_t block_exclusive_scan_1024(uint32_t v, uint32
 // total -> counters[CNT_ST_RENDERED]
 __global__ void __launch_bounds__(1024)
 block_sums_scan_kernel(uint32_t nblocks, uint32_t* __restrict__ block_sums, uint32_t* __restrict__ counters) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     __shared__ uint32_t s_warp[32];
     uint32_t carry = 0;
     for (uint32_t start = 0; start < nblocks; start += 4096) {
@@ -177,6 +181,8 @@ emit_st_instances_kernel(uint32_t VP, int P, int stiles_x, uint32_t S, int view_
                          uint32_t* __restrict__ ikeys, uint32_t* __restrict__ ivals, uint32_t* __restrict__ counters,
                          uint32_t* __restrict__ lookback, uint32_t* __restrict__ ticket,
                          uint32_t* __restrict__ key_hist, uint32_t khist_views /* 0: global atomics */) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     extern __shared__ uint32_t s_khist[];                 // [S][khist_views]: instances per key of the block's views
     __shared__ uint32_t s_warp[SCAN_BLOCK / 32];
     __shared__ uint32_t s_key[EMIT_WINDOW];              // key | supertile x << 16 | supertile y << 24
@@ -310,6 +316,8 @@ emit_st_instances_kernel(uint32_t VP, int P, int stiles_x, uint32_t S, int view_
 __global__ void __launch_bounds__(1024)
 sort_hist_from_keys_kernel(uint32_t num_keys, int view_bits, int passes, const uint32_t* __restrict__ key_hist,
                            uint32_t* __restrict__ sort_hist) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     __shared__ uint32_t s_h[MAX_PASSES][RADIX];
     for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) (&s_h[0][0])[i] = 0;
     __syncthreads();
@@ -381,6 +389,8 @@ __global__ void __launch_bounds__(256)
 chunk_count_kernel(const uint32_t* __restrict__ counters, const uint32_t* __restrict__ chunk_key,
                    const uint32_t* __restrict__ chunk_base, const uint2* __restrict__ st_ranges,
                    const uint32_t* __restrict__ skeys, uint32_t* __restrict__ chunk_counts) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     const int lane = threadIdx.x & 31;
     const uint32_t wpb = blockDim.x >> 5;
     const uint32_t nch = counters[CNT_NCHUNKS];
@@ -421,6 +431,8 @@ __global__ void __launch_bounds__(ST_TILES * 32)
 tile_offsets_kernel(int V, int view_bits, int stiles_x, int tiles_x, int tiles_y,
                     const uint32_t* __restrict__ chunk_base, const uint2* __restrict__ st_ranges, uint32_t max_chunks,
                     uint32_t* __restrict__ chunk_counts, uint32_t* __restrict__ tile_start) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     const uint32_t k = blockIdx.x;
     const uint32_t view = k & ((1u << view_bits) - 1u), s = k >> view_bits;
     if (view >= (uint32_t)V) return;                     // key slots of views the batch does not have
@@ -456,6 +468,8 @@ constexpr int TSCAN_THREADS = 1024;          // one CTA on the critical path: as
 __global__ void __launch_bounds__(TSCAN_THREADS)
 tile_scan_kernel(uint32_t VT, uint32_t capacity, uint32_t* __restrict__ tile_start, uint2* __restrict__ ranges,
                  uint32_t* __restrict__ counters) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     __shared__ uint32_t s_warp[32];
     uint32_t carry = 0;
     constexpr int IT = 8;
@@ -586,6 +600,8 @@ scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __
                        const float4* __restrict__ rgb_sh4, const float4* __restrict__ ext4,
                        float4* __restrict__ recA, float4* __restrict__ recB, float4* __restrict__ recC,
                        float4* __restrict__ recD) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     __shared__ uint32_t s_wcnt[ST_TILES][CHUNK / 32];
     __shared__ uint32_t s_tbase[ST_TILES];            // list position of this chunk's first hit, per tile
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -683,6 +699,8 @@ scatter_records_kernel(const uint32_t* __restrict__ counters, const uint32_t* __
 __global__ void __launch_bounds__(256)
 pack_colors_kernel(int P, const float* __restrict__ colors, const float* __restrict__ extra,
                    float4* __restrict__ col4, float4* __restrict__ ext4) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= P) return;
     if (colors) col4[g] = make_float4(colors[3 * g], colors[3 * g + 1], colors[3 * g + 2], 0.0f);
@@ -722,7 +740,7 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     if (VP == 0 || capacity <= 0) {     // every tile list empty: zero counts through the same scan (ranges, launch order)
         if (VT == 0) return GSR_OK;
         GSR_CUDA_TRY(cudaMemsetAsync(at<uint32_t>(iws, L.tile_start), 0, ((size_t)VT + 1) * sizeof(uint32_t), s));
-        tile_scan_kernel<<<1, TSCAN_THREADS, 0, s>>>(VT, 0u, at<uint32_t>(iws, L.tile_start), at<uint2>(iws, L.ranges),
+        launch_kernel(tile_scan_kernel, 1, TSCAN_THREADS, 0, s, VT, 0u, at<uint32_t>(iws, L.tile_start), at<uint2>(iws, L.ranges),
                                                   counters);
         GSR_LAUNCH_CHECK();
         tile_order_kernel<<<1, TSCAN_THREADS, 0, s>>>(VT, at<uint2>(iws, L.ranges), at<uint32_t>(iws, L.tile_order));
@@ -764,17 +782,17 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
         uint32_t* offs = at<uint32_t>(bws, L.emit_lookback);
 #else
         uint32_t* offs = at<uint32_t>(gws, L.block_sums);
-        st_count_reduce_kernel<<<nblocks, SCAN_BLOCK, 0, s>>>(VP, P, sorted_g, rects, at<uint32_t>(gws, L.vis_count), offs);
+        launch_kernel(st_count_reduce_kernel, nblocks, SCAN_BLOCK, 0, s, VP, P, sorted_g, rects, at<uint32_t>(gws, L.vis_count), offs);
         GSR_LAUNCH_CHECK();
-        block_sums_scan_kernel<<<1, 1024, 0, s>>>(nblocks, offs, counters);
+        launch_kernel(block_sums_scan_kernel, 1, 1024, 0, s, nblocks, offs, counters);
         GSR_LAUNCH_CHECK();
 #endif
-        emit_st_instances_kernel<<<nblocks, SCAN_BLOCK, bins * 4, s>>>(
+        launch_kernel(emit_st_instances_kernel, nblocks, SCAN_BLOCK, bins * 4, s, 
             VP, P, L.stiles_x, S, L.view_bits, sorted_g, rects, at<uint32_t>(gws, L.vis_count), cap, nblocks,
             at<uint32_t>(bws, L.ikeys0), at<uint32_t>(bws, L.ivals0), counters, offs, at<uint32_t>(bws, L.emit_ticket),
             key_hist, nv);
         GSR_LAUNCH_CHECK();
-        sort_hist_from_keys_kernel<<<1, 1024, 0, s>>>(NK, L.view_bits, L.tile_passes, key_hist, at<uint32_t>(bws, L.ihist));
+        launch_kernel(sort_hist_from_keys_kernel, 1, 1024, 0, s, NK, L.view_bits, L.tile_passes, key_hist, at<uint32_t>(bws, L.ihist));
         GSR_LAUNCH_CHECK();
     }
     stage_end(ST_EMIT, s);
@@ -798,12 +816,12 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     const uint32_t* svals = at<uint32_t>(bws, L.sorted_keys_in ? L.ivals1 : L.ivals0);
     const uint32_t chunk_grid = max_chunks < 148u * 8u ? max_chunks : 148u * 8u;   // persistent CTAs, 8 per SM
     stage_begin(ST_RANGES, s);
-    chunk_count_kernel<<<chunk_grid, 256, 0, s>>>(counters, chunk_key, chunk_base, st_ranges, skeys, chunk_counts);
+    launch_kernel(chunk_count_kernel, chunk_grid, 256, 0, s, counters, chunk_key, chunk_base, st_ranges, skeys, chunk_counts);
     GSR_LAUNCH_CHECK();
-    tile_offsets_kernel<<<NK, ST_TILES * 32, 0, s>>>(V, L.view_bits, L.stiles_x, L.tiles_x, L.tiles_y, chunk_base, st_ranges,
+    launch_kernel(tile_offsets_kernel, NK, ST_TILES * 32, 0, s, V, L.view_bits, L.stiles_x, L.tiles_x, L.tiles_y, chunk_base, st_ranges,
                                                     max_chunks, chunk_counts, tile_start);
     GSR_LAUNCH_CHECK();
-    tile_scan_kernel<<<1, TSCAN_THREADS, 0, s>>>(VT, cap, tile_start, at<uint2>(iws, L.ranges), counters);
+    launch_kernel(tile_scan_kernel, 1, TSCAN_THREADS, 0, s, VT, cap, tile_start, at<uint2>(iws, L.ranges), counters);
     GSR_LAUNCH_CHECK();
     stage_end(ST_RANGES, s);
     // the launch order of the blend kernels is not needed before the records are in place: side stream again
@@ -814,7 +832,7 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
     {
         StageScope sc(ST_GATHER, s);
         if (colors_precomp || extra_colors) {
-            pack_colors_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, colors_precomp, extra_colors, at<float4>(gws, L.col4),
+            launch_kernel(pack_colors_kernel, (P + 255) / 256, 256, 0, s, P, colors_precomp, extra_colors, at<float4>(gws, L.col4),
                                                                at<float4>(gws, L.ext4));
             GSR_LAUNCH_CHECK();
         }
@@ -831,12 +849,12 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
         const float4* col4 = colors_precomp ? at<float4>(gws, L.col4) : nullptr;
         const float4* rgb4 = sh_coeffs > 0 ? at<float4>(gws, L.rgb) : nullptr;
         if (channels > 3) {
-            scatter_records_kernel<true><<<scatter_grid, CHUNK, 0, s>>>(
+            launch_kernel(scatter_records_kernel<true>, scatter_grid, CHUNK, 0, s, 
                 counters, chunk_key, chunk_base, st_ranges, L.view_bits, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals, skeys,
                 chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, at<float4>(gws, L.ext4),
                 at<float4>(bws, L.recA), at<float4>(bws, L.recB), at<float4>(bws, L.recC), at<float4>(bws, L.recD));
         } else {
-            scatter_records_kernel<false><<<scatter_grid, CHUNK, 0, s>>>(
+            launch_kernel(scatter_records_kernel<false>, scatter_grid, CHUNK, 0, s, 
                 counters, chunk_key, chunk_base, st_ranges, L.view_bits, L.stiles_x, L.tiles_x, L.tiles_y, P, cap, svals, skeys,
                 chunk_counts, tile_start, at<float4>(gws, L.geomrec), col4, rgb4, nullptr, at<float4>(bws, L.recA),
                 at<float4>(bws, L.recB), at<float4>(bws, L.recC), nullptr);

@@ -70,6 +70,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                        const float* __restrict__ dL_dcolor, const float* __restrict__ dL_dextra,
                        const float* __restrict__ dL_ddepth, const float* __restrict__ dL_dalpha,
                        float* __restrict__ grad_rec) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     constexpr bool EXTRA = NCH > 3;
     static_assert(!M2C || EXTRA, "the colour-only moments only differ from the totals when extra colours are blended");
     constexpr int K = GR_COL + NCH + (M2C ? 2 : 0);
@@ -323,6 +325,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 constexpr int ORD_THREADS = 1024;
 __global__ void __launch_bounds__(ORD_THREADS)
 tile_order_by_cost_kernel(uint32_t VT, const uint32_t* __restrict__ cost, uint32_t* __restrict__ order) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     __shared__ uint32_t s_bucket[ORD_THREADS];
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_maxc;
@@ -396,20 +400,20 @@ int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, c
     const uint32_t* order = at<uint32_t>(iws, L.tile_order);
     if (options().bwd_cost_order && blend_ilp(blocks) > 1) {          // small launch: deepest tiles first (see tile_order_by_cost_kernel)
         uint32_t* ord = at<uint32_t>(iws, L.tile_order_bwd);
-        tile_order_by_cost_kernel<<<1, ORD_THREADS, 0, s>>>((uint32_t)blocks, at<uint32_t>(iws, L.tile_cost), ord);
+        launch_kernel(tile_order_by_cost_kernel, 1, ORD_THREADS, 0, s, (uint32_t)blocks, at<uint32_t>(iws, L.tile_cost), ord);
         GSR_LAUNCH_CHECK();
         order = ord;
     }
     if (channels == 3)
-        blend_backward_kernel<3, false><<<blocks, NT2, 0, s>>>(ranges, order, A, B, C, D, cams, W, H,
+        launch_kernel(blend_backward_kernel<3, false>, blocks, NT2, 0, s, ranges, order, A, B, C, D, cams, W, H,
                                                                L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
                                                                dL_dalpha, rec);
     else if (channels == 6 && color_only_means2D)
-        blend_backward_kernel<6, true><<<blocks, NT2, 0, s>>>(ranges, order, A, B, C, D, cams, W, H,
+        launch_kernel(blend_backward_kernel<6, true>, blocks, NT2, 0, s, ranges, order, A, B, C, D, cams, W, H,
                                                               L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
                                                               dL_dalpha, rec);
     else if (channels == 6)
-        blend_backward_kernel<6, false><<<blocks, NT2, 0, s>>>(ranges, order, A, B, C, D, cams, W, H,
+        launch_kernel(blend_backward_kernel<6, false>, blocks, NT2, 0, s, ranges, order, A, B, C, D, cams, W, H,
                                                                L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
                                                                dL_dalpha, rec);
     else

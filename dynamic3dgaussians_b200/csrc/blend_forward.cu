@@ -78,6 +78,8 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                       float* __restrict__ out_color, float* __restrict__ out_extra, float* __restrict__ out_depth,
                       float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib, float* __restrict__ final_T,
                       uint32_t* __restrict__ tile_cost) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     constexpr bool EXTRA = NCH > 3;
     // one block per ring slot, so that the loop addresses all of an entry's records off ONE register (base + 16 j)
     struct __align__(128) Stage {
@@ -374,7 +376,7 @@ int launch_blend_forward(int V, int W, int H, int channels, const void* gws, con
     float* fT = at<float>(iws, L.final_T);
     const int ilp = blend_ilp(blocks);           // see common.cuh: small launches end with lone heavy tiles
 #define GSR_FWD(NCH_, ILP_)                                                                                           \
-    blend_forward_kernel<NCH_, ILP_><<<blocks, NT2, 0, s>>>(ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, \
+    launch_kernel(blend_forward_kernel<NCH_, ILP_>, blocks, NT2, 0, s, ranges, at<uint32_t>(iws, L.tile_order), A, B, C, D, cams, \
                                                             W, H, L.tiles_x, T, out_color, out_extra, out_depth,      \
                                                             out_alpha, nc, fT, at<uint32_t>(iws, L.tile_cost))
     if (channels == 3) {

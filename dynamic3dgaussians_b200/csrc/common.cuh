@@ -135,7 +135,7 @@ inline void compute_layout(int P, int V, int W, int H, int channels, int sh_coef
     L.radii = take(VP * 4);
     L.rects = take(VP * 8);               // ushort4 tile rectangle (min.x, min.y, max.x, max.y), all zero when culled
     L.geomrec = take(VP * 32);            // (mean.x, mean.y, conic.a, conic.b | conic.c, opacity, depth, skip threshold)
-    L.cov3D = take((size_t)P * 24);
+    L.cov3D = take((size_t)P * 32);       // per Gaussian, view-independent: (cov3D[0..3] | cov3D[4..5], opacity, skip threshold)
     L.rgb = take(sh_coeffs > 0 ? VP * 16 : 0);     // float4 per (view, Gaussian): SH colours
     L.col4 = take((size_t)P * 16);                 // float4-packed colors_precomp / extra colours (per Gaussian)
     L.ext4 = take(channels > 3 ? (size_t)P * 16 : 0);
@@ -196,8 +196,43 @@ struct Options {
     int blend_ilp = 0;        // forward blend loop: 0 = by launch size (blend_ilp()), 1 / 2 = force that variant
     int bwd_cost_order = 1;   // small backward launches ordered by the depth the forward walked (tile_order_by_cost_kernel)
     int nvtx = 0;             // an NVTX range around every stage (profilers)
+    int pdl = 0;              // programmatic dependent launch between the step's kernels (launch_kernel below); measured: off
 };
 Options& options();
+
+// Programmatic dependent launch (sm_90+): a kernel launched through launch_kernel() may be scheduled while its
+// predecessor in the stream is still running -- its CTAs take SM slots as the predecessor's free them and park in
+// pdl_wait() (griddepcontrol.wait: until the predecessor grid has completed and its writes are visible), so the launch
+// latency and the ramp-up of the grid no longer sit between two kernels.  A step is ~25 short dependent kernels; at a
+// 1/8 share of a timestep or one training view those gaps are a tenth of the step.  Rules: a kernel launched this way
+// touches NO global memory before pdl_wait() (reads: not yet written; writes: the predecessor may still read the old
+// values), and every such kernel calls pdl_trigger() (griddepcontrol.launch_dependents) at its top so that ITS successor
+// may be scheduled as soon as all of its CTAs have started.  Launched without the attribute (option "pdl" = 0, or after
+// a memset / event wait) both instructions are no-ops.
+// Measured at C2 on a B200 (profiles/gpu_check.sh, A/B of the same library): launched one by one from the host the stages
+// shorten by 2-8 % (depth sort 0.2185 -> 0.2133 ms, emit 0.184 -> 0.175, tile offsets 0.096 -> 0.091), but the step
+// replayed as ONE CUDA graph -- the path the bench and the training loop use -- gets slower (4.27 -> 4.40 ms; a 1/8 share
+// 0.709 -> 0.730): graph kernel nodes already follow each other within ~1 us, and the parked CTAs of the successor take
+// slots from the predecessor's last wave.  Hence off by default; gsr_set_option("pdl", 1) turns it on for eager callers.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline void launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = options().pdl ? 1 : 0;
+    (void)cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);     // errors: GSR_LAUNCH_CHECK() after the call
+}
+#endif
 
 // optional per-stage device timing (bench.py's roofline numbers): events are recorded on the launching stream
 enum Stage : int { ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_TILE_SCAN, ST_EMIT, ST_TILE_SORT, ST_RANGES, ST_GATHER,
@@ -232,7 +267,7 @@ void set_cuda_error(cudaError_t e, const char* where);
 // ------------------------------------------------------------------------------------------------------------
 int launch_preprocess(const CamDev* cams, int V, int P, int sh_coeffs,
                       const float* means3D, const float* opacities, const float* scales, const float* rotations,
-                      const float* cov3D_precomp, const float* sh, void* geom_ws, const Layout& L,
+                      const float* cov3D_precomp, const float* sh, float scale_modifier, void* geom_ws, const Layout& L,
                       int32_t* radii_out, cudaStream_t s);   // sets counters[CNT_PREFILTER] (see preprocess.cu)
 int launch_peer_allreduce(int mode, int world, int rank, const void* const* bufs_host, const void* const* flags_host,
                           void* multicast_buf, int64_t n_floats, int blocks, cudaStream_t s);

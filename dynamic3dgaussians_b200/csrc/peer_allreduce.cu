@@ -101,6 +101,8 @@ constexpr int MODE_MULTIMEM = 3;
 template <int WORLD, int MODE>
 __global__ void __launch_bounds__(512)
 peer_allreduce_kernel(const __grid_constant__ PeerPtrs pp, float* __restrict__ mc_buf, int world_rt, int rank, size_t n4) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     constexpr int WMAX = WORLD > 0 ? WORLD : PEER_MAX_WORLD;
     const int world = WORLD > 0 ? WORLD : world_rt;
     const int cta = blockIdx.x, tid = threadIdx.x;
@@ -196,7 +198,7 @@ int launch_peer_allreduce(int mode, int world, int rank, const void* const* bufs
     }
     const size_t n4 = (size_t)n_floats / 4;
     float* mc = (float*)multicast_buf;
-#define GSR_PEER(W_, M_) peer_allreduce_kernel<W_, M_><<<blocks, 512, 0, s>>>(pp, mc, world, rank, n4)
+#define GSR_PEER(W_, M_) launch_kernel(peer_allreduce_kernel<W_, M_>, blocks, 512, 0, s, pp, mc, world, rank, n4)
 #define GSR_PEER_W(M_)                                                                                                 \
     switch (world) {                                                                                                   \
         case 2: GSR_PEER(2, M_); break;                                                                                \

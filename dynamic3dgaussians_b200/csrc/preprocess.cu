@@ -80,6 +80,31 @@ __device__ __forceinline__ float3 eval_sh_pinned(int deg, int M, const float* __
     return out;
 }
 
+// What does not depend on the view, once per Gaussian instead of once per (view, Gaussian): the 3D covariance
+// (computeCov3D, forward.cu:118-150, or the caller's cov3D_precomp), the opacity and the blend kernels' conservative skip
+// threshold (a logf).  Two float4 per Gaussian, read by preprocess_kernel next to the mean.
+__global__ void __launch_bounds__(256)
+gaussian_static_kernel(int P, const float* __restrict__ opacities, const float* __restrict__ scales,
+                       const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp, float scale_modifier,
+                       float4* __restrict__ gstatic) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= P) return;
+    float cv[6];
+    if (cov3D_precomp != nullptr) {
+#pragma unroll
+        for (int i = 0; i < 6; ++i) cv[i] = cov3D_precomp[6 * (size_t)g + i];
+    } else {
+        const float3 sc = make_float3(scales[3 * g], scales[3 * g + 1], scales[3 * g + 2]);
+        const float4 q = reinterpret_cast<const float4*>(rotations)[g];
+        cov3d_from_scale_rot(sc, scale_modifier, q, cv);
+    }
+    const float op = opacities[g];
+    gstatic[2 * (size_t)g] = make_float4(cv[0], cv[1], cv[2], cv[3]);
+    gstatic[2 * (size_t)g + 1] = make_float4(cv[4], cv[5], op, blend_skip_threshold(op));
+}
+
 // Persistent: the (view, chunk of PP_CHUNK Gaussians) work items are dealt out as ONE contiguous run per CTA, so a CTA
 // sees at most a few views.  That lets the kernel also take the depth sort's four digit histograms (what
 // radix_histogram_kernel would re-read all V x P keys for): counted in shared memory, flushed to dhist[view][pass][bin]
@@ -96,14 +121,15 @@ constexpr int DEPTH_PASSES = 4;            // 32-bit depth keys, 8-bit digits
 
 __global__ void __launch_bounds__(256, PP_CTAS_PER_SM)
 preprocess_kernel(const CamDev* __restrict__ cams, int V, int P, int sh_coeffs,
-                  const float* __restrict__ means3D, const float* __restrict__ opacities,
-                  const float* __restrict__ scales, const float* __restrict__ rotations,
-                  const float* __restrict__ cov3D_precomp, const float* __restrict__ sh,
+                  const float* __restrict__ means3D, const float4* __restrict__ gstatic,
+                  const float* __restrict__ sh,
                   int tiles_x, int tiles_y,
                   int32_t* __restrict__ radii, ushort4* __restrict__ rects, float4* __restrict__ geomrec,
                   float* __restrict__ rgb, uint8_t* __restrict__ clamped,
                   uint32_t* __restrict__ dkeys, uint32_t* __restrict__ dvals, int32_t* __restrict__ radii_out,
                   uint32_t* __restrict__ counters, uint32_t* __restrict__ dhist) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     __shared__ CamDev cam;
     __shared__ uint32_t s_tiles[8];
     __shared__ uint32_t s_dh[DEPTH_PASSES * RADIX];
@@ -152,15 +178,10 @@ preprocess_kernel(const CamDev* __restrict__ cams, int V, int P, int sh_coeffs,
                 const float pw = __frcp_rn(__fadd_rn(hw, 0.0000001f));
                 const float ndc_x = __fmul_rn(hx, pw), ndc_y = __fmul_rn(hy, pw);
 
-                float cv[6];
-                if (cov3D_precomp != nullptr) {
-#pragma unroll
-                    for (int i = 0; i < 6; ++i) cv[i] = cov3D_precomp[6 * (size_t)g + i];
-                } else {
-                    const float3 sc = make_float3(scales[3 * g], scales[3 * g + 1], scales[3 * g + 2]);
-                    const float4 q = reinterpret_cast<const float4*>(rotations)[g];
-                    cov3d_from_scale_rot(sc, cam.scale_modifier, q, cv);
-                }
+                // view-independent part, computed once per Gaussian by gaussian_static_kernel: 3D covariance, opacity and
+                // the blend's skip threshold
+                const float4 gs0 = gstatic[2 * (size_t)g], gs1 = gstatic[2 * (size_t)g + 1];
+                const float cv[6] = {gs0.x, gs0.y, gs0.z, gs0.w, gs1.x, gs1.y};
                 Cov2DInter ci;
                 cov2d(cam, x, y, z, cv, ci);
                 const float det = __fmaf_rn(ci.a, ci.c, -__fmul_rn(ci.b, ci.b));   // a*c - b*b as the reference SASS has it
@@ -190,9 +211,8 @@ preprocess_kernel(const CamDev* __restrict__ cams, int V, int P, int sh_coeffs,
                             clamped[3 * idx + 1] = cl[1];
                             clamped[3 * idx + 2] = cl[2];
                         }
-                        const float op = opacities[g];
                         geomrec[2 * idx] = make_float4(pix.x, pix.y, conic_x, conic_y);          // the blend kernels' recA
-                        geomrec[2 * idx + 1] = make_float4(conic_z, op, depth, blend_skip_threshold(op));   // ... and recB
+                        geomrec[2 * idx + 1] = make_float4(conic_z, gs1.z, depth, gs1.w);        // ... and recB
                         radius = r_i;
                         rect = make_ushort4((unsigned short)mn.x, (unsigned short)mn.y, (unsigned short)mx.x,
                                             (unsigned short)mx.y);
@@ -279,8 +299,11 @@ int launch_store_cams(const CamPack& pack, CamDev* dst, cudaStream_t s) {
 
 int launch_preprocess(const CamDev* cams, int V, int P, int sh_coeffs, const float* means3D, const float* opacities,
                       const float* scales, const float* rotations, const float* cov3D_precomp, const float* sh,
-                      void* ws, const Layout& L, int32_t* radii_out, cudaStream_t s) {
+                      float scale_modifier, void* ws, const Layout& L, int32_t* radii_out, cudaStream_t s) {
     if (P == 0 || V == 0) return GSR_OK;
+    launch_kernel(gaussian_static_kernel, (P + 255) / 256, 256, 0, s, P, opacities, scales, rotations, cov3D_precomp, scale_modifier,
+                                                           at<float4>(ws, L.cov3D));
+    GSR_LAUNCH_CHECK();
     static int sms = 0;
     if (!sms) {
         int dev = 0;
@@ -290,8 +313,8 @@ int launch_preprocess(const CamDev* cams, int V, int P, int sh_coeffs, const flo
     const long long items = (long long)V * ((P + PP_CHUNK - 1) / PP_CHUNK);
     const long long full = (long long)sms * PP_CTAS_PER_SM;
     const int grid = (int)(items < full ? items : full);
-    preprocess_kernel<<<grid, 256, 0, s>>>(
-        cams, V, P, sh_coeffs, means3D, opacities, scales, rotations, cov3D_precomp, sh, L.tiles_x, L.tiles_y,
+    launch_kernel(preprocess_kernel, grid, 256, 0, s, 
+        cams, V, P, sh_coeffs, means3D, at<float4>(ws, L.cov3D), sh, L.tiles_x, L.tiles_y,
         at<int32_t>(ws, L.radii), at<ushort4>(ws, L.rects), at<float4>(ws, L.geomrec), at<float>(ws, L.rgb),
         at<uint8_t>(ws, L.clamped), at<uint32_t>(ws, L.dkeys0), at<uint32_t>(ws, L.dvals0), radii_out,
         at<uint32_t>(ws, L.counters), at<uint32_t>(ws, L.dhist));

@@ -122,6 +122,8 @@ preprocess_backward_kernel(const CamDev* __restrict__ cams, int V, int P, int sh
                            float* __restrict__ dL_dextra, float* __restrict__ dL_dopacity,
                            float* __restrict__ dL_dscales, float* __restrict__ dL_drotations,
                            float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int sub = t % TPG;
     const bool live = t / TPG < P;                        // (no early return: the whole warp takes part in the shuffles)
@@ -402,7 +404,7 @@ int launch_preprocess_backward(int V, int P, int W, int H, int channels, int sh_
     constexpr int TPG = GSR_PB_TPG;
     const int blocks = split ? (int)(((size_t)P * TPG + 255) / 256) : (P + 255) / 256;
 #define GSR_PB(NCH_, TPG_)                                                                                            \
-    preprocess_backward_kernel<NCH_, TPG_><<<blocks, 256, 0, s>>>(cams, V, P, sh_coeffs, means3D, scales, rotations,  \
+    launch_kernel(preprocess_backward_kernel<NCH_, TPG_>, blocks, 256, 0, s, cams, V, P, sh_coeffs, means3D, scales, rotations,  \
                                                                  cov3D_precomp, sh, rad, cl, rec, label, dL_dmeans3D, \
                                                                  dL_dmeans2D, dL_dmeans2D_color_only, dL_dcolors,     \
                                                                  dL_dextra_colors, dL_dopacity, dL_dscales,           \

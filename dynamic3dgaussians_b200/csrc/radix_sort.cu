@@ -126,6 +126,8 @@ radix_histogram_kernel(const KeyT* __restrict__ keys, uint32_t n_max, const uint
 // n_kept (nullable): n_kept[segment] <- number of keys counted in the segment's first-pass histogram (see radix_sort_pairs)
 __global__ void __launch_bounds__(RADIX) radix_scan_hist_kernel(uint32_t* __restrict__ hist, uint32_t* __restrict__ n_kept,
                                                                 int passes) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     __shared__ uint32_t warp_tot[RADIX / 32];
     uint32_t* h = hist + blockIdx.x * RADIX;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -151,6 +153,8 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
                      uint32_t n_max, const uint32_t* __restrict__ n_dev, int shift, uint32_t digit_mask,
                      const uint32_t* __restrict__ hist_excl, size_t hist_seg_stride, uint32_t* __restrict__ lookback,
                      size_t lookback_seg_stride, uint32_t* __restrict__ tile_counter, bool drop_sentinel) {
+    pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
+    pdl_trigger();
     constexpr int ITEMS = SortCfg<KeyT>::ITEMS;
     constexpr int TILE = SORT_THREADS * ITEMS;
     constexpr int WARPS = SORT_THREADS / 32;
@@ -348,7 +352,7 @@ int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1,
             keys0, (uint32_t)n_max, n_dev, begin_bit, end_bit, passes, hist, n_kept_dev != nullptr);
         GSR_LAUNCH_CHECK();
     }
-    radix_scan_hist_kernel<<<passes * segments, RADIX, 0, s>>>(hist, n_kept_dev, passes);
+    launch_kernel(radix_scan_hist_kernel, passes * segments, RADIX, 0, s, hist, n_kept_dev, passes);
     GSR_LAUNCH_CHECK();
     const size_t dyn = (size_t)TILE * (sizeof(KeyT) + 4);
     for (int p = 0; p < passes; ++p) {
@@ -360,7 +364,7 @@ int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1,
         uint32_t* vout = (p & 1) ? vals0 : vals1;
         // with sentinel dropping the first pass reads all n_max keys and writes the kept ones; the others move those only
         const uint32_t* n_pass = (n_kept_dev && p > 0) ? n_kept_dev : n_dev;
-        onesweep_pass_kernel<KeyT><<<dim3(tiles, segments), SORT_THREADS, dyn, s>>>(
+        launch_kernel(onesweep_pass_kernel<KeyT>, dim3(tiles, segments), SORT_THREADS, dyn, s, 
             kin, kout, vin, vout, (uint32_t)n_max, n_pass, shift, (1u << bits) - 1u, hist + p * RADIX, hist_seg,
             lookback + (size_t)p * segments * lb_seg, lb_seg, tile_counters + (size_t)p * segments,
             n_kept_dev != nullptr && p == 0);

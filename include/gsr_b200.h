@@ -108,6 +108,9 @@ const char* gsr_last_cuda_error(void);
  *                     per trip (identical bits; tuning and tests)
  *   "bwd_cost_order"  1 (default): small backward launches order their CTAs by the depth the forward walked each tile
  *   "nvtx"            1: an NVTX range around every stage (preprocess, depth_sort, ..., blend_backward), for profilers
+ *   "pdl"             1: the step's kernels are chained by programmatic dependent launch (a kernel is scheduled while its
+ *                     predecessor drains and waits in griddepcontrol.wait); helps host-launched steps by 1-2 %, measured
+ *                     slower under CUDA-graph replay, hence 0 (plain stream order) by default
  * Unknown key or value out of range: GSR_ERR_INVALID_ARGUMENT.  Apart from these switches, the stage-timing events and the
  * blend trace pointers below, the library keeps no state: everything lives in the caller's workspaces.
  */

@@ -20,6 +20,18 @@ for n in ("gpurun_out/bench_$tag.json", "gpurun_out/bench_${tag}_emu8.json"):
     except Exception as e:
         print(n, "failed", e)
 PY
+# A/B of the programmatic dependent launch chain (same library, option "pdl")
+GSR_PDL=1 python bench.py --steps 20 --warmup 5 --no-train --no-extras --no-cpu-baseline --no-e2e > gpurun_out/bench_${tag}_pdl.json 2> gpurun_out/bench_${tag}_pdl.err
+GSR_PDL=1 python bench.py --steps 20 --warmup 5 --no-train --no-extras --no-cpu-baseline --no-e2e --emulate-world 8 --emulate-rank 3 > gpurun_out/bench_${tag}_pdl_emu8.json 2> gpurun_out/bench_${tag}_pdl_emu8.err
+python - <<PY
+import json
+for n in ("gpurun_out/bench_${tag}_pdl.json", "gpurun_out/bench_${tag}_pdl_emu8.json"):
+    try:
+        d = json.loads(open(n).read().strip().splitlines()[-1])
+        print(n, d["value"], d["ms_per_step"], json.dumps(d["stage_ms_rank0"]))
+    except Exception as e:
+        print(n, "failed", e)
+PY
 EMU=""; [ -n "$NCU_EMU" ] && EMU="--emulate-world 8 --emulate-rank 3"
 ncu --metrics gpu__time_duration.sum --clock-control none -c 500 --csv --log-file gpurun_out/launches_$tag.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-train --no-e2e --no-graph --no-extras $EMU > gpurun_out/ncu_$tag.log 2>&1
