@@ -129,6 +129,13 @@ def _worker(rank, world, port, out):
         h = D.allreduce_grads(z, async_op=True)
         h.wait()
         ok = ok and torch.allclose(z, per_view[0], atol=1e-6)
+        # make_slab: without GPUs / NCCL there is no peer memory -- a plain GradSlab whose allreduce() goes through the
+        # process group (the peer kernel itself: tests/test_gpu_peer.py on one GPU, tests/test_gpu_peer_multi.py on several)
+        ms = D.make_slab(P, "cpu")
+        ok = ok and type(ms) is D.GradSlab and ms.exchange == "nccl all_reduce"
+        ms.views["means3D"].copy_(per_view[mine].sum(dim=0)[:, 0:3] if mine else torch.zeros(P, 3))
+        ms.allreduce()
+        ok = ok and torch.allclose(ms.views["means3D"], per_view.sum(dim=0)[:, 0:3], atol=1e-5)
         out[rank] = bool(ok)
     finally:
         dist.destroy_process_group()
@@ -149,3 +156,5 @@ def test_two_rank_gloo_allreduce_equals_single_process_sum():
 def test_allreduce_is_a_noop_without_a_process_group():
     t = torch.ones(3, D.GRAD_WIDTH)
     assert D.allreduce_grads(t) is None and torch.equal(t, torch.ones(3, D.GRAD_WIDTH))
+    slab = D.make_slab(5, "cpu")                      # no process group: the plain slab, and its allreduce is a no-op too
+    assert type(slab) is D.GradSlab and slab.allreduce() is None
