@@ -20,6 +20,10 @@
 #include "geom_math.cuh"
 #include "packed_reduce.cuh"
 
+#ifndef GSR_PATCH_TEST
+#define GSR_PATCH_TEST blend_patch_hit_exact
+#endif
+
 namespace gsr {
 
 namespace {
@@ -201,7 +205,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             if (g < nb && (uint32_t)(c * BATCH + sb * SUB) < warp_last) {
                 const float4 a = stage[buf].a[g];
                 const float4 b = stage[buf].b[g];
-                hit = blend_patch_hit(a.x, a.y, a.z, a.w, b.x, b.w, patch_x0, patch_y0);
+                hit = GSR_PATCH_TEST(a.x, a.y, a.z, a.w, b.x, b.w, patch_x0, patch_y0);
             }
             wm[sb] = __ballot_sync(FULL, hit);
         }

@@ -18,6 +18,10 @@
 //   with the reference bit for bit.
 #include "geom_math.cuh"
 
+#ifndef GSR_PATCH_TEST
+#define GSR_PATCH_TEST blend_patch_hit_exact
+#endif
+
 namespace gsr {
 
 namespace {
@@ -70,7 +74,10 @@ __device__ __forceinline__ PairAlpha pair_alpha(const float4 a, const float4 b, 
 }
 
 template <int NCH, int ILP>
-__global__ void __launch_bounds__(NT2, (NCH > 3 || ILP > 1) ? 6 : 8)
+#ifndef GSR_FWD_MINB
+#define GSR_FWD_MINB 8
+#endif
+__global__ void __launch_bounds__(NT2, (NCH > 3 || ILP > 1) ? 6 : GSR_FWD_MINB)
 blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                       const float4* __restrict__ recA, const float4* __restrict__ recB,
                       const float4* __restrict__ recC, const float4* __restrict__ recD,
@@ -183,7 +190,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
             if (g < nb) {
                 const float4 a = stage[buf].a[g];
                 const float4 b = stage[buf].b[g];
-                hit = blend_patch_hit(a.x, a.y, a.z, a.w, b.x, b.w, patch_x0, patch_y0);
+                hit = GSR_PATCH_TEST(a.x, a.y, a.z, a.w, b.x, b.w, patch_x0, patch_y0);
             }
             wm[sb] = __ballot_sync(0xffffffffu, hit);
         }
