@@ -402,7 +402,7 @@ int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, c
     const float* fT = at<float>(iws, L.final_T);
     float* rec = at<float>(gws, L.grad_rec);
     const uint32_t* order = at<uint32_t>(iws, L.tile_order);
-    if (options().bwd_cost_order && blend_ilp(blocks) > 1) {          // small launch: deepest tiles first (see tile_order_by_cost_kernel)
+    if (options().bwd_cost_order && blocks <= BWD_COST_ORDER_MAX_BLOCKS) {          // small launch: deepest tiles first (see tile_order_by_cost_kernel)
         uint32_t* ord = at<uint32_t>(iws, L.tile_order_bwd);
         launch_kernel(tile_order_by_cost_kernel, 1, ORD_THREADS, 0, s, (uint32_t)blocks, at<uint32_t>(iws, L.tile_cost), ord);
         GSR_LAUNCH_CHECK();

@@ -77,7 +77,10 @@ template <int NCH, int ILP>
 #ifndef GSR_FWD_MINB
 #define GSR_FWD_MINB 8
 #endif
-__global__ void __launch_bounds__(NT2, (NCH > 3 || ILP > 1) ? 6 : GSR_FWD_MINB)
+#ifndef GSR_FWD_MINB_ILP
+#define GSR_FWD_MINB_ILP 6
+#endif
+__global__ void __launch_bounds__(NT2, NCH > 3 ? 6 : (ILP > 1 ? GSR_FWD_MINB_ILP : GSR_FWD_MINB))
 blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                       const float4* __restrict__ recA, const float4* __restrict__ recB,
                       const float4* __restrict__ recC, const float4* __restrict__ recD,

@@ -292,16 +292,17 @@ int side_join(cudaStream_t main);
 int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int64_t capacity,
                    const float* colors_precomp, const float* extra_colors,
                    void* geom_ws, void* binning_ws, void* image_ws, const Layout& L, cudaStream_t s);
-// Forward blend: BLEND_ILP_SMALL list entries per loop trip for launches of at most BLEND_ILP_MAX_BLOCKS CTAs (a few
-// views).  Such launches end with a handful of deep tiles running alone (tests/gpu_tile_trace.py: at one C2 view the
-// deepest tile lasts the whole kernel while the average SM is done at half of it).  A lone tile has one warp per
-// scheduler, so its time is that warp's instruction stream on one scheduler's pipes: two entries per trip with the
-// alphas computed side by side and a branch-free blend shorten the stream's stalls (-15 % on a one-view launch), more
-// entries per trip or fewer resident CTAs change nothing (measured), and the same change makes the backward slower
-// (more instructions on the same scheduler), so the backward has one variant.  The issue-bound 27-view launch is 3 %
-// faster with the one-entry loop, hence the switch.  GSR_BLEND_ILP=1|2 forces a variant (tuning and tests; the
-// variants produce identical bits).
-constexpr int BLEND_ILP_MAX_BLOCKS = 148 * 8 * 4;
+// Forward blend: BLEND_ILP list entries per loop trip -- the alphas (and the colour loads) of the trip's entries depend on
+// nothing the loop carries and are computed side by side, only the short T chain is walked entry by entry, with a
+// branch-free blend.  Round 1 used it for launches of a few views only (the issue-bound 27-view launch was 3 % faster
+// with the one-entry loop and its early `continue`s); with the exact ellipse / patch test of round 2 the work lists hold
+// almost only entries that blend, the early exits have little left to skip, and two entries per trip win at every size
+// (C2 on a B200: 1/8 share 0.182 -> 0.162 ms, 1/2 share 0.569 -> 0.544, all 27 views 1.117 -> 1.067; C5 2.33 -> 2.20).
+// More entries per trip or fewer resident CTAs change nothing (measured), and the same change makes the backward slower
+// (more instructions on the same scheduler), so the backward has one variant.  gsr_set_option("blend_ilp", 1 | 2) forces
+// a variant (tuning and tests; the variants produce identical bits).
+constexpr int BLEND_ILP_MAX_BLOCKS = 1 << 30;
+constexpr int BWD_COST_ORDER_MAX_BLOCKS = 148 * 8 * 4;   // backward launches up to this size order their CTAs by walked depth
 constexpr int BLEND_ILP_SMALL = 2;
 int blend_ilp(int blocks);
 int set_blend_forward_trace(unsigned long long* p);     // diagnostics (gsr_debug_blend_trace)
