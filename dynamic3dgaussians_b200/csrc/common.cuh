@@ -303,7 +303,10 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
 // a variant (tuning and tests; the variants produce identical bits).
 constexpr int BLEND_ILP_MAX_BLOCKS = 1 << 30;
 constexpr int BWD_COST_ORDER_MAX_BLOCKS = 148 * 8 * 4;   // backward launches up to this size order their CTAs by walked depth
-constexpr int BLEND_ILP_SMALL = 2;
+#ifndef GSR_BLEND_ILP_N
+#define GSR_BLEND_ILP_N 2
+#endif
+constexpr int BLEND_ILP_SMALL = GSR_BLEND_ILP_N;
 int blend_ilp(int blocks);
 int set_blend_forward_trace(unsigned long long* p);     // diagnostics (gsr_debug_blend_trace)
 int set_blend_backward_trace(unsigned long long* p);
