@@ -143,7 +143,7 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     _lib = lib
     # The library itself never reads the environment (gsr_set_option); the tuning variables the tools of round 1 used are
     # forwarded once, here, by the host binding.
-    for env, key in (("GSR_BLEND_ILP", "blend_ilp"), ("GSR_BWD_COST_ORDER", "bwd_cost_order"), ("GSR_NVTX", "nvtx"), ("GSR_PDL", "pdl")):
+    for env, key in (("GSR_BLEND_ILP", "blend_ilp"), ("GSR_BWD_COST_ORDER", "bwd_cost_order"), ("GSR_NVTX", "nvtx"), ("GSR_PDL", "pdl"), ("GSR_BWD_ILP", "bwd_ilp")):
         v = os.environ.get(env)
         if v not in (None, ""):
             check(lib.gsr_set_option(key.encode(), int(v)), f"set_option({key})")

@@ -205,13 +205,14 @@ static int* option_slot(const char* key) {
     if (!strcmp(key, "bwd_cost_order")) return &g_options.bwd_cost_order;
     if (!strcmp(key, "nvtx")) return &g_options.nvtx;
     if (!strcmp(key, "pdl")) return &g_options.pdl;
+    if (!strcmp(key, "bwd_ilp")) return &g_options.bwd_ilp;
     return nullptr;
 }
 
 int gsr_set_option(const char* key, int value) {
     int* slot = option_slot(key);
     if (!slot) return GSR_ERR_INVALID_ARGUMENT;
-    if (slot == &g_options.blend_ilp && (value < 0 || value > 2)) return GSR_ERR_INVALID_ARGUMENT;
+    if ((slot == &g_options.blend_ilp || slot == &g_options.bwd_ilp) && (value < 0 || value > 2)) return GSR_ERR_INVALID_ARGUMENT;
     *slot = value;
     return GSR_OK;
 }

@@ -61,11 +61,11 @@ constexpr int NW2 = NT2 / 32;
 // render alone -- colour, depth and alpha cotangents, without the extra (segmentation) channels -- into record slots
 // GR_COL + NCH and + 1.  The reference takes its densification statistic from the colour render's dL/dmeans2D only
 // (REF/train.py:245, REF/external.py:136-140; REF/README.md:89 on why fusing the two renders changes t = 0 otherwise).
-template <int NCH, bool M2C>
 #ifndef GSR_BWD_MINB
 #define GSR_BWD_MINB 8
 #endif
-__global__ void __launch_bounds__(NT2, GSR_BWD_MINB)
+template <int NCH, bool M2C, int BILP>
+__global__ void __launch_bounds__(NT2, BILP > 1 ? 4 : GSR_BWD_MINB)
 blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                        const float4* __restrict__ recA, const float4* __restrict__ recB,
                        const float4* __restrict__ recC, const float4* __restrict__ recD,
@@ -221,6 +221,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 #ifdef GSR_TRACE_COUNTS
             n_list += __popc(m);
 #endif
+            if constexpr (BILP == 1) {
             while (m != 0u) {                                       // warp-uniform, back to front
                 const int jl = 31 - __clz(m);
                 m &= ~(1u << jl);
@@ -298,6 +299,114 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 // one reduction (RED) per (warp patch, Gaussian, value): the K sums sit in K different lanes and land in
                 // one 64-byte gradient record
                 red_add_if(writer, grad_rec + (size_t)__float_as_uint(col.w) * grad_rec_stride(NCH) + my_slot, v[0]);
+            }
+            } else {
+            // BILP list entries per trip, for launches of at most one wave of CTAs (a training view): every tile is
+            // resident from the first microsecond, the kernel lasts as long as its deepest tile -- one warp per
+            // scheduler for most of the time -- and that warp's time is the latency of its
+            // instruction stream -- an exp, two reciprocals and five dependent shuffle stages per entry -- not issue
+            // slots.  The alphas, the cotangent dot products and the two butterflies of the trip's entries depend on
+            // nothing the loop carries and run side by side; only T and the colour-behind recurrence are walked entry by
+            // entry, in list order and with the one-entry loop's operations, so every value has the same bits.  (On the
+            // issue-bound full-size launch the extra instructions of the padding entry cost more than they hide.)
+            while (m != 0u) {
+                int jj[BILP];
+                bool has[BILP];
+#pragma unroll
+                for (int e = 0; e < BILP; ++e) {
+                    has[e] = m != 0u;
+                    const int jl = 31 - __clz(m | 1u);
+                    m &= ~(1u << jl);                              // (no-op once m is 0)
+                    jj[e] = has[e] ? lo + jl : jj[0];
+                }
+                float dxe[BILP], opa[BILP];
+                float2 dye[BILP], Ge[BILP], alpha[BILP], rom[BILP], se[BILP], sce[BILP];
+                float4 cole[BILP];
+                bool v0e[BILP], v1e[BILP];
+                bool any_pre = false;
+#pragma unroll
+                for (int e = 0; e < BILP; ++e) {
+                    const int j = jj[e];
+                    const float4 a = stage[buf].a[j];
+                    const float4 b = stage[buf].b[j];
+                    cole[e] = stage[buf].c[j];
+                    const float dx = __fadd_rn(a.x, npx);
+                    const float2 dy = __fadd2_rn(splat(a.y), npy);
+                    const float dxca = __fmul_rn(dx, a.z), ndxcb = __fmul_rn(dx, -a.w);
+                    const float2 t3 = __fmul2_rn(dy, __fmul2_rn(dy, splat(b.x)));
+                    const float2 q = __ffma2_rn(splat(dx), splat(dxca), t3);
+                    const float2 power = __ffma2_rn(q, splat(-0.5f), __fmul2_rn(dy, splat(ndxcb)));
+                    const bool pre0 = has[e] && (j < rel0) && !(power.x > 0.0f) && !(power.x < b.w);
+                    const bool pre1 = has[e] && (j < rel1) && !(power.y > 0.0f) && !(power.y < b.w);
+                    any_pre = any_pre || pre0 || pre1;
+                    const float2 G = expf2_pinned(power);
+                    const float2 og = __fmul2_rn(splat(b.y), G);
+                    float2 al = f2(fminf(0.99f, og.x), fminf(0.99f, og.y));
+                    v0e[e] = pre0 && !(al.x < 1.0f / 255.0f);
+                    v1e[e] = pre1 && !(al.y < 1.0f / 255.0f);
+                    al.x = v0e[e] ? al.x : 0.0f;
+                    al.y = v1e[e] ? al.y : 0.0f;
+                    const float2 om = __fadd2_rn(splat(1.0f), f2(-al.x, -al.y));
+                    rom[e] = f2(rcp_approx(om.x), rcp_approx(om.y));
+                    float2 s = __ffma2_rn(splat(cole[e].x), gC[0],
+                               __ffma2_rn(splat(cole[e].y), gC[1],
+                               __ffma2_rn(splat(cole[e].z), gC[2], __ffma2_rn(splat(b.z), gD, gA))));
+                    sce[e] = s;
+                    if (EXTRA) {
+                        const float4 x = stage[buf].d[j];
+                        s = __ffma2_rn(splat(x.x), gC[NCH - 3],
+                            __ffma2_rn(splat(x.y), gC[NCH - 2], __ffma2_rn(splat(x.z), gC[NCH - 1], s)));
+                    }
+                    se[e] = s;
+                    dxe[e] = dx; dye[e] = dy; Ge[e] = G; alpha[e] = al; opa[e] = b.y;
+                }
+                if (!__any_sync(FULL, any_pre)) continue;          // warp-uniform: none of the trip's entries blends here
+                float ve[BILP][K];
+#pragma unroll
+                for (int e = 0; e < BILP; ++e) {
+#ifdef GSR_TRACE_COUNTS
+                    n_done += has[e] ? 1 : 0;
+#endif
+                    // the carried part, entry by entry: alpha = 0 (entry absent or blending nothing here) leaves T and acc
+                    // exactly as they are (MUFU.RCP(1) = 1)
+                    T = __fmul2_rn(T, rom[e]);
+                    const float2 w = __fmul2_rn(alpha[e], T);
+                    const float2 sd = __fadd2_rn(se[e], f2(-acc.x, -acc.y));
+                    float2 gq = __fmul2_rn(Ge[e], __fmul2_rn(sd, T));
+                    acc = __ffma2_rn(alpha[e], sd, acc);
+                    gq.x = v0e[e] ? gq.x : 0.0f;
+                    gq.y = v1e[e] ? gq.y : 0.0f;
+                    float* v = ve[e];
+#pragma unroll
+                    for (int k = 0; k < NCH; ++k) v[GR_COL + k] = fmaf(w.y, gC[k].y, w.x * gC[k].x);
+                    v[GR_DEPTH] = fmaf(w.y, gD.y, w.x * gD.x);
+                    const float2 am = __fmul2_rn(splat(opa[e]), gq);
+                    const float2 uy = __fmul2_rn(am, dye[e]);
+                    const float sam = am.x + am.y;
+                    v[GR_MX] = sam * dxe[e];
+                    v[GR_MY] = uy.x + uy.y;
+                    v[GR_CA] = v[GR_MX] * dxe[e];
+                    v[GR_CB] = v[GR_MY] * dxe[e];
+                    v[GR_CC] = fmaf(uy.y, dye[e].y, uy.x * dye[e].x);
+                    v[GR_OP] = gq.x + gq.y;
+                    if (M2C) {
+                        const float2 sd_c = __fadd2_rn(sce[e], f2(-acc_c.x, -acc_c.y));
+                        float2 gq_c = __fmul2_rn(Ge[e], __fmul2_rn(sd_c, T));
+                        acc_c = __ffma2_rn(alpha[e], sd_c, acc_c);
+                        gq_c.x = v0e[e] ? gq_c.x : 0.0f;
+                        gq_c.y = v1e[e] ? gq_c.y : 0.0f;
+                        const float2 am_c = __fmul2_rn(splat(opa[e]), gq_c);
+                        v[GR_COL + NCH] = (am_c.x + am_c.y) * dxe[e];
+                        v[GR_COL + NCH + 1] = fmaf(am_c.y, dye[e].y, am_c.x * dye[e].x);
+                    }
+                }
+#pragma unroll
+                for (int e = 0; e < BILP; ++e) PackedReduce<K>::run(ve[e], lane);
+#pragma unroll
+                for (int e = 0; e < BILP; ++e)
+                    red_add_if(writer && has[e], grad_rec + (size_t)__float_as_uint(cole[e].w) * grad_rec_stride(NCH) + my_slot,
+                               ve[e][0]);
+            }
             }
         }
         // done with this ring slot; the last of the four warps to say so refills it
@@ -408,20 +517,27 @@ int launch_blend_backward(int V, int P, int W, int H, int channels, void* gws, c
         GSR_LAUNCH_CHECK();
         order = ord;
     }
+    // two entries per trip for small launches (see the kernel); option "bwd_ilp": 0 = by launch size, 1 / 2 = forced
+    const int forced = options().bwd_ilp;
+    const bool two = forced == 2 || (forced != 1 && blocks <= BWD_ILP_MAX_BLOCKS);
+#define GSR_BWD(NCH_, M2C_)                                                                                             \
+    do {                                                                                                                \
+        if (two)                                                                                                        \
+            launch_kernel(blend_backward_kernel<NCH_, M2C_, 2>, blocks, NT2, 0, s, ranges, order, A, B, C, D, cams, W, H, \
+                          L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, rec);                       \
+        else                                                                                                            \
+            launch_kernel(blend_backward_kernel<NCH_, M2C_, 1>, blocks, NT2, 0, s, ranges, order, A, B, C, D, cams, W, H, \
+                          L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth, dL_dalpha, rec);                       \
+    } while (0)
     if (channels == 3)
-        launch_kernel(blend_backward_kernel<3, false>, blocks, NT2, 0, s, ranges, order, A, B, C, D, cams, W, H,
-                                                               L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
-                                                               dL_dalpha, rec);
+        GSR_BWD(3, false);
     else if (channels == 6 && color_only_means2D)
-        launch_kernel(blend_backward_kernel<6, true>, blocks, NT2, 0, s, ranges, order, A, B, C, D, cams, W, H,
-                                                              L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
-                                                              dL_dalpha, rec);
+        GSR_BWD(6, true);
     else if (channels == 6)
-        launch_kernel(blend_backward_kernel<6, false>, blocks, NT2, 0, s, ranges, order, A, B, C, D, cams, W, H,
-                                                               L.tiles_x, T, nc, fT, dL_dcolor, dL_dextra, dL_ddepth,
-                                                               dL_dalpha, rec);
+        GSR_BWD(6, false);
     else
         return GSR_ERR_UNSUPPORTED;
+#undef GSR_BWD
     GSR_LAUNCH_CHECK();
     return GSR_OK;
 }

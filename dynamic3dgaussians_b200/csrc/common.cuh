@@ -196,6 +196,7 @@ struct Options {
     int blend_ilp = 0;        // forward blend loop: 0 = by launch size (blend_ilp()), 1 / 2 = force that variant
     int bwd_cost_order = 1;   // small backward launches ordered by the depth the forward walked (tile_order_by_cost_kernel)
     int nvtx = 0;             // an NVTX range around every stage (profilers)
+    int bwd_ilp = 0;          // backward blend loop: 0 = by launch size (two entries per trip for small launches), 1 / 2 = forced
     int pdl = 0;              // programmatic dependent launch between the step's kernels (launch_kernel below); measured: off
 };
 Options& options();
@@ -302,7 +303,14 @@ int launch_binning(int V, int P, int W, int H, int channels, int sh_coeffs, int6
 // (more instructions on the same scheduler), so the backward has one variant.  gsr_set_option("blend_ilp", 1 | 2) forces
 // a variant (tuning and tests; the variants produce identical bits).
 constexpr int BLEND_ILP_MAX_BLOCKS = 1 << 30;
-constexpr int BWD_COST_ORDER_MAX_BLOCKS = 148 * 8 * 4;   // backward launches up to this size order their CTAs by walked depth
+constexpr int BWD_COST_ORDER_MAX_BLOCKS = 148 * 8 * 4;
+#ifndef GSR_BWD_ILP_MAX_BLOCKS
+#define GSR_BWD_ILP_MAX_BLOCKS (148 * 8)
+#endif
+// Backward launches up to this size -- at most one wave of CTAs, i.e. a training view -- take two list entries per trip
+// (blend_backward_kernel<.., .., 2>).  Measured on a B200 at C2: one 640x360 view per optimizer step 1146 -> 1241 it/s;
+// larger launches are issue-bound and lose (1/8 share of a timestep 0.2385 -> 0.250 ms, all 27 views 1.63 -> 1.77 ms).
+constexpr int BWD_ILP_MAX_BLOCKS = GSR_BWD_ILP_MAX_BLOCKS;   // backward launches up to this size order their CTAs by walked depth
 #ifndef GSR_BLEND_ILP_N
 #define GSR_BLEND_ILP_N 2
 #endif

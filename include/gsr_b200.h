@@ -106,6 +106,8 @@ const char* gsr_last_cuda_error(void);
  * Process-wide switches.  The library never reads the environment; whoever embeds it sets these explicitly.
  *   "blend_ilp"       0 (default): forward blend loop variant picked by launch size; 1 / 2: force one / two list entries
  *                     per trip (identical bits; tuning and tests)
+ *   "bwd_ilp"         0 (default): backward blend loop variant picked by launch size (two list entries per trip for small
+ *                     launches); 1 / 2: force one / two entries per trip (identical bits; tuning and tests)
  *   "bwd_cost_order"  1 (default): small backward launches order their CTAs by the depth the forward walked each tile
  *   "nvtx"            1: an NVTX range around every stage (preprocess, depth_sort, ..., blend_backward), for profilers
  *   "pdl"             1: the step's kernels are chained by programmatic dependent launch (a kernel is scheduled while its
