@@ -82,7 +82,8 @@ typedef struct GsrWorkspaceSizes {
 
 /* Offsets (bytes) of the arrays inside the workspaces, for tests / tools that want to look at intermediate state. */
 typedef struct GsrLayout {
-    /* geom workspace */
+    /* geom workspace (cov3D: 8 floats per Gaussian -- the 3D covariance, the opacity and the blend kernels' skip threshold,
+     * i.e. everything per Gaussian that does not depend on the view) */
     size_t cams, counters, radii, rects, geomrec, cov3D, rgb, col4, ext4, clamped;
     size_t dkeys0, dkeys1, dvals0, dvals1, dhist, dlookback, dcounters, block_sums, grad_rec;
     /* binning workspace: supertile-instance sort arrays, chunk tables, per-instance records */
