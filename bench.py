@@ -591,7 +591,9 @@ def run_e2e(args, res, world, rank):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n = max(3, args.steps // 2)
     e0.record()
+    t_host = time.perf_counter()
     run(n)
+    t_host = (time.perf_counter() - t_host) * 1e3 / n        # host time to ENQUEUE a step (diagnostic: must stay below ms/step)
     e1.record()
     barrier(world)
     ms = max_over_ranks(e0.elapsed_time(e1), world)
@@ -635,7 +637,8 @@ def run_e2e(args, res, world, rank):
 
     legs = {"h2d_ms": leg(leg_h2d), "compute_ms": leg(leg_compute), "d2h_ms": leg(leg_d2h)}
     return {"value": round(mpix, 2), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-            "steps": n, "ms_per_step": round(ms / n, 3), "loss_rank0": loss_value, "legs_alone_rank0": legs,
+            "steps": n, "ms_per_step": round(ms / n, 3), "host_enqueue_ms_per_step_rank0": round(t_host, 3),
+            "loss_rank0": loss_value, "legs_alone_rank0": legs,
             "host_io": "bytes are job totals; parameter slab uploaded / gradient slab read back once per step "
                        + (f"(1/{nw} per rank; all-gather of the parameters and reduce-scatter of the gradients over NVLink by "
                           + ("the library's peer-memory kernel)" if peer else "NCCL)") if nw > 1 else "(one rank)")}
