@@ -581,7 +581,8 @@ def run_e2e(args, res, world, rank):
     def run(k):
         prefetch(0)
         for i in range(k):
-            prefetch(i + 1)
+            if i + 1 < k:
+                prefetch(i + 1)
             step(i)
         cur.wait_stream(d2h_s)
         cur.wait_stream(h2d_s)
