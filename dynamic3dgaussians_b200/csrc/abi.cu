@@ -578,8 +578,8 @@ int gsr_sort_pairs(int key_bytes, const void* keys_in, void* keys_out, const uin
 // ---- the same sort with its scratch in a library-owned device array: no allocation anywhere on the call ----
 // No counterpart in the reference; added for callers that cannot call cudaMalloc
 // (CUDA graph capture, serving loops).  GSR_SORT_STATIC_MAX_PAIRS pairs of 8-byte keys need
-// sort_layout(GSR_SORT_STATIC_MAX_PAIRS, 8) = 6.7 MiB; every GPU that loads the library holds the array until exit.
-constexpr size_t SORT_STATIC_BYTES = 7u << 20;
+// sort_layout(GSR_SORT_STATIC_MAX_PAIRS, 8) = 7.4 MiB; every GPU that loads the library holds the array until exit.
+constexpr size_t SORT_STATIC_BYTES = 8u << 20;
 static __device__ __align__(256) unsigned char g_sort_static_scratch[SORT_STATIC_BYTES];
 
 // In host code `g_sort_static_scratch` is only a handle for the runtime: the device address comes from

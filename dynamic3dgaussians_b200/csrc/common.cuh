@@ -61,9 +61,12 @@ template <typename KeyT> struct SortCfg;
 #ifndef GSR_SORT_ITEMS32
 #define GSR_SORT_ITEMS32 16
 #endif
-template <> struct SortCfg<uint32_t> { static constexpr int ITEMS = GSR_SORT_ITEMS32; };
-template <> struct SortCfg<uint64_t> { static constexpr int ITEMS = 12; };
-template <typename KeyT> constexpr int sort_tile() { return SORT_THREADS * SortCfg<KeyT>::ITEMS; }
+// keys per thread: ITEMS for sorts that fill the machine, ITEMS_SMALL (half the tile, twice the CTAs) for sorts whose
+// big-tile grid would leave SMs idle -- one training view is 300k keys = 74 tiles of 4096 on 148 SMs
+template <> struct SortCfg<uint32_t> { static constexpr int ITEMS = GSR_SORT_ITEMS32, ITEMS_SMALL = GSR_SORT_ITEMS32 / 2; };
+template <> struct SortCfg<uint64_t> { static constexpr int ITEMS = 12, ITEMS_SMALL = 6; };
+constexpr int SORT_SMALL_GRID = 148;     // use the small tile when the big-tile grid has at most this many CTAs
+template <typename KeyT> constexpr int sort_tile() { return SORT_THREADS * SortCfg<KeyT>::ITEMS_SMALL; }   // sizing: the smaller
 constexpr int MAX_PASSES = 8;
 
 inline int sort_num_tiles(int64_t n, int key_bytes) {

@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(RADIX) radix_scan_hist_kernel(uint32_t* __rest
     if (n_kept && tid == RADIX - 1 && (int)(blockIdx.x % passes) == 0) n_kept[blockIdx.x / passes] = base + inc;
 }
 
-template <typename KeyT>
+template <typename KeyT, int ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS, 4)
 onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                      const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
@@ -155,7 +155,6 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
                      size_t lookback_seg_stride, uint32_t* __restrict__ tile_counter, bool drop_sentinel) {
     pdl_wait();          // (common.cuh) nothing global is touched before the predecessor kernel has completed
     pdl_trigger();
-    constexpr int ITEMS = SortCfg<KeyT>::ITEMS;
     constexpr int TILE = SORT_THREADS * ITEMS;
     constexpr int WARPS = SORT_THREADS / 32;
     __shared__ uint32_t s_warp_hist[WARPS][RADIX];
@@ -328,7 +327,9 @@ int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1,
     if (segments > 65535) return GSR_ERR_UNSUPPORTED;
     const int passes = (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS;
     if (passes > MAX_PASSES) return GSR_ERR_INVALID_ARGUMENT;
-    constexpr int TILE = SORT_THREADS * SortCfg<KeyT>::ITEMS;
+    constexpr int TILE_BIG = SORT_THREADS * SortCfg<KeyT>::ITEMS, TILE_SMALL = SORT_THREADS * SortCfg<KeyT>::ITEMS_SMALL;
+    const bool small = ((n_max + TILE_BIG - 1) / TILE_BIG) * segments <= SORT_SMALL_GRID;     // see SortCfg
+    const int TILE = small ? TILE_SMALL : TILE_BIG;
     const int tiles = (int)((n_max + TILE - 1) / TILE);
     const size_t hist_seg = (size_t)passes * RADIX;
     const size_t lb_seg = (size_t)tiles * RADIX;
@@ -364,10 +365,16 @@ int radix_sort_pairs(KeyT* keys0, KeyT* keys1, uint32_t* vals0, uint32_t* vals1,
         uint32_t* vout = (p & 1) ? vals0 : vals1;
         // with sentinel dropping the first pass reads all n_max keys and writes the kept ones; the others move those only
         const uint32_t* n_pass = (n_kept_dev && p > 0) ? n_kept_dev : n_dev;
-        launch_kernel(onesweep_pass_kernel<KeyT>, dim3(tiles, segments), SORT_THREADS, dyn, s, 
-            kin, kout, vin, vout, (uint32_t)n_max, n_pass, shift, (1u << bits) - 1u, hist + p * RADIX, hist_seg,
-            lookback + (size_t)p * segments * lb_seg, lb_seg, tile_counters + (size_t)p * segments,
-            n_kept_dev != nullptr && p == 0);
+        if (small)
+            launch_kernel(onesweep_pass_kernel<KeyT, SortCfg<KeyT>::ITEMS_SMALL>, dim3(tiles, segments), SORT_THREADS, dyn, s,
+                kin, kout, vin, vout, (uint32_t)n_max, n_pass, shift, (1u << bits) - 1u, hist + p * RADIX, hist_seg,
+                lookback + (size_t)p * segments * lb_seg, lb_seg, tile_counters + (size_t)p * segments,
+                n_kept_dev != nullptr && p == 0);
+        else
+            launch_kernel(onesweep_pass_kernel<KeyT, SortCfg<KeyT>::ITEMS>, dim3(tiles, segments), SORT_THREADS, dyn, s,
+                kin, kout, vin, vout, (uint32_t)n_max, n_pass, shift, (1u << bits) - 1u, hist + p * RADIX, hist_seg,
+                lookback + (size_t)p * segments * lb_seg, lb_seg, tile_counters + (size_t)p * segments,
+                n_kept_dev != nullptr && p == 0);
         GSR_LAUNCH_CHECK();
     }
     return GSR_OK;

@@ -211,7 +211,7 @@ int gsr_sort_pairs(int key_bytes, const void* keys_in, void* keys_out, const uin
                    int64_t n, int begin_bit, int end_bit, void* tmp, size_t tmp_bytes, gsr_stream_t stream);
 
 /* The same sort with NO allocation anywhere on the call: the scratch gsr_sort_pairs takes from the caller lives in a
- * file-scope `static __device__` array inside the library (7 MiB, held by every GPU that loads the library until the
+ * file-scope `static __device__` array inside the library (8 MiB, held by every GPU that loads the library until the
  * process exits), so the call can be made where cudaMalloc cannot (under CUDA graph capture, in a serving loop).
  * This entry point has NO counterpart in the reference.
  * Limit: n <= GSR_SORT_STATIC_MAX_PAIRS; a larger n returns GSR_ERR_WORKSPACE_TOO_SMALL with the reason in
