@@ -498,19 +498,27 @@ def run_e2e(args, res, world, rank):
     for b in bufs:
         b["free"].record(cur)
 
-    def prefetch(i):
+    def prefetch(i, gate=None):
         b = bufs[i % 2]
         with torch.cuda.stream(h2d_s):
             h2d_s.wait_event(b["free"])
+            if gate is not None:
+                h2d_s.wait_event(gate)
             b["par"][lo:hi].copy_(par_host, non_blocking=True)
             b["tgt"].copy_(tgt_host, non_blocking=True)
             b["ready"].record(h2d_s)
 
-    def compute(b):
+    def gather(b):
         if b["ppar"] is not None:
             b["ppar"].allgather()                                           # in place: every rank now holds the slab
         elif nw > 1:
             tdist.all_gather_into_tensor(b["par"], b["par"][lo:hi])
+
+    def compute(b):
+        gather(b)
+        return compute_rest(b)
+
+    def compute_rest(b):
         m, c, o, s, r = b["leaves"]
         color, _, depth, alpha, radii = RZ.rasterize_views(my_sets, m, o, colors_precomp=c, scales=s, rotations=r,
                                                            capacity=cap_e2e, state_out=states, bands=my_bands)
@@ -551,27 +559,21 @@ def run_e2e(args, res, world, rank):
         for b in bufs:
             for t in b["leaves"]:
                 t.grad = None
+            if nw > 1:
+                b["g_gather"] = torch.cuda.CUDAGraph()                 # the all-gather is a graph of its own: see run()
+                with torch.cuda.graph(b["g_gather"], pool=pool):
+                    gather(b)
+                pool = b["g_gather"].pool() if pool is None else pool
             b["graph"] = torch.cuda.CUDAGraph()
             with torch.cuda.graph(b["graph"], pool=pool):
-                b["out"] = compute(b)
+                b["out"] = compute_rest(b)
             pool = b["graph"].pool() if pool is None else pool
 
-    def step(i):
-        b = bufs[i % 2]
-        cur.wait_event(b["ready"])
-        cur.wait_event(b["drained"])               # this buffer's previous results have left for the host
-        if "graph" in b:
-            b["graph"].replay()
-            lossd, grads = b["out"]
-        else:
-            for t in b["leaves"]:
-                t.grad = None
-            lossd, grads = compute(b)
-        b["free"].record(cur)
-        done = torch.cuda.Event()
-        done.record(cur)
+    def download(b, done, lossd, grads, gate=None):
         with torch.cuda.stream(d2h_s):
             d2h_s.wait_event(done)
+            if gate is not None:
+                d2h_s.wait_event(gate)
             grad_host.copy_(grads, non_blocking=True)
             loss_host.copy_(lossd, non_blocking=True)
             b["drained"].record(d2h_s)
@@ -579,11 +581,46 @@ def run_e2e(args, res, world, rank):
             lossd.record_stream(d2h_s)
 
     def run(k):
+        # N = 1: upload of step i+1 and download of step i-1 simply run next to step i.  N > 1: the exchange kernels'
+        # barriers use system-scope fences, and a system-scope fence does not return while a DMA copy is in flight
+        # (tests/gpu_fence_dma_probe.py: the exchange takes 30 us alone, 65 us next to a D2H and 143 us next to an H2D
+        # copy; NCCL's kernels behave the same) -- copies that start when a step ends land exactly on the next step's
+        # all-gather.  So the copies are released by an event recorded AFTER the all-gather of the running step: they
+        # overlap the render, which issues no system-scope fence until its last kernel, a whole render later.
         prefetch(0)
+        pending = None                               # the previous step's results, not yet on their way to the host
         for i in range(k):
+            b = bufs[i % 2]
+            cur.wait_event(b["ready"])
+            cur.wait_event(b["drained"])             # this buffer's previous results have left for the host
+            gate = None
+            if nw > 1:
+                if "g_gather" in b:
+                    b["g_gather"].replay()
+                else:
+                    gather(b)
+                gate = torch.cuda.Event()
+                gate.record(cur)
+            if pending is not None:
+                download(*pending, gate=gate)
             if i + 1 < k:
-                prefetch(i + 1)
-            step(i)
+                prefetch(i + 1, gate=gate)
+            if "graph" in b:
+                b["graph"].replay()
+                lossd, grads = b["out"]
+            else:
+                for t in b["leaves"]:
+                    t.grad = None
+                lossd, grads = compute_rest(b)
+            b["free"].record(cur)
+            done = torch.cuda.Event()
+            done.record(cur)
+            pending = (b, done, lossd, grads)
+            if nw == 1:                              # nothing to stay clear of: the download starts as soon as the step ends
+                download(*pending)
+                pending = None
+        if pending is not None:
+            download(*pending)
         cur.wait_stream(d2h_s)
         cur.wait_stream(h2d_s)
 
@@ -624,6 +661,8 @@ def run_e2e(args, res, world, rank):
     def leg_compute():
         b = bufs[0]
         if "graph" in b:
+            if "g_gather" in b:
+                b["g_gather"].replay()
             b["graph"].replay()
         else:
             for t in b["leaves"]:
@@ -640,6 +679,9 @@ def run_e2e(args, res, world, rank):
     return {"value": round(mpix, 2), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
             "steps": n, "ms_per_step": round(ms / n, 3), "host_enqueue_ms_per_step_rank0": round(t_host, 3),
             "loss_rank0": loss_value, "legs_alone_rank0": legs,
+            "pipeline": ("copies of step i+1 / i-1 run next to step i"
+                         + ("; they are released after step i's all-gather, because a system-scope fence (every collective "
+                            "kernel has them) does not return while a DMA copy is in flight" if nw > 1 else "")),
             "host_io": "bytes are job totals; parameter slab uploaded / gradient slab read back once per step "
                        + (f"(1/{nw} per rank; all-gather of the parameters and reduce-scatter of the gradients over NVLink by "
                           + ("the library's peer-memory kernel)" if peer else "NCCL)") if nw > 1 else "(one rank)")}
